@@ -1,0 +1,34 @@
+"""``vote_train_set`` (reference: commands/message/vote_train_set_command.py:28-74)."""
+
+import contextlib
+
+from myfyp_b200.communication.commands.command import Command
+from myfyp_b200.management.logger import logger
+
+
+class VoteTrainSetCommand(Command):
+    def __init__(self, state) -> None:
+        self.state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "vote_train_set"
+
+    def execute(self, source: str, round: int, *args, **kwargs) -> None:
+        st = self.state
+        if st.round is None:
+            logger.debug(st.addr, f"Vote received from {source} while not learning. Ignored.")
+            return
+        # votes may arrive one round early (the sender finished its round first)
+        if round in (st.round, st.round + 1):
+            votes = list(args)
+            tmp = {}
+            for i in range(0, len(votes) - 1, 2):
+                tmp[votes[i]] = int(votes[i + 1])
+            with st.train_set_votes_lock:
+                st.train_set_votes[source] = tmp
+            with contextlib.suppress(Exception):
+                st.wait_votes_ready_lock.release()
+            st.notify()
+        else:
+            logger.debug(st.addr, f"Vote from {source} in a late round. Ignored. {round} != {st.round} / {st.round + 1}")

@@ -1,0 +1,42 @@
+"""``add_model`` = full aggregated model diffusion (reference: commands/weights/full_model_command.py:31-89)."""
+
+from typing import Callable
+
+from myfyp_b200.communication.commands.command import Command
+from myfyp_b200.communication.commands.weights._common import handle_bad_model
+from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
+from myfyp_b200.management.logger import logger
+
+
+class FullModelCommand(Command):
+    def __init__(self, state, stop: Callable[[], None], aggregator, learner, protocol=None) -> None:
+        self.state, self.stop, self.aggregator, self.learner, self.protocol = state, stop, aggregator, learner, protocol
+
+    @staticmethod
+    def get_name() -> str:
+        return "add_model"
+
+    def execute(self, source: str, round: int, weights=None, **kwargs) -> None:
+        if weights is None:
+            raise ValueError("Weights are required")
+        st = self.state
+        if st.round is None:
+            logger.debug(st.addr, "❌ Tried to add a model while learning is not running")
+            return
+        if round != st.round:
+            logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
+            return
+        if st.aggregated_model_event.is_set():
+            logger.debug(st.addr, "😲 Aggregated model not expected.")
+            return
+        try:
+            logger.info(st.addr, "📦 Aggregated model received.")
+            self.learner.set_model(weights)
+            st.aggregated_model_event.set()
+            st.notify()
+        except DecodingParamsError:
+            handle_bad_model(st, self.stop, source, "❌ Error decoding parameters", self.protocol)
+        except ModelNotMatchingError:
+            handle_bad_model(st, self.stop, source, "❌ Models not matching", self.protocol)
+        except Exception as e:  # noqa: BLE001
+            handle_bad_model(st, self.stop, source, f"❌ Unknown error adding model: {e}", self.protocol)

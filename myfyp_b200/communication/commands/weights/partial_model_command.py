@@ -1,0 +1,52 @@
+"""``partial_model`` (reference: commands/weights/partial_model_command.py:33-112).
+
+``weights`` is either the reference's pickled byte blob or a device descriptor
+(:class:`myfyp_b200.parallel.fabric.SlabRef`).  With a descriptor nothing is copied
+here: the aggregator keeps the descriptor and the aggregation kernel pulls the
+sender's slab out of (peer) HBM when it reduces.
+"""
+
+from typing import Callable, List, Optional
+
+from myfyp_b200.communication.commands.command import Command
+from myfyp_b200.communication.commands.message.models_aggregated_command import ModelsAggregatedCommand
+from myfyp_b200.communication.commands.weights._common import handle_bad_model
+from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
+from myfyp_b200.management.logger import logger
+
+
+class PartialModelCommand(Command):
+    def __init__(self, state, stop: Callable[[], None], aggregator, comm_proto, learner) -> None:
+        self.state, self.stop, self.aggregator = state, stop, aggregator
+        self.communication_protocol, self.learner = comm_proto, learner
+
+    @staticmethod
+    def get_name() -> str:
+        return "partial_model"
+
+    def execute(self, source: str, round: int, weights=None, contributors: Optional[List[str]] = None, num_samples: Optional[int] = None, **kwargs) -> None:
+        if weights is None or contributors is None or num_samples is None:
+            raise ValueError("Weights, contributors and weight are required")
+        st = self.state
+        if st.round is None:
+            logger.debug(st.addr, "Tried to add a model while learning is not running")
+            return
+        if round != st.round:
+            logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
+            return
+        if len(st.train_set) == 0:
+            logger.error(st.addr, "Model Reception when there is no trainset")
+            return
+        try:
+            model = self.learner.get_model().build_copy(params=weights, num_samples=num_samples, contributors=list(contributors))
+            models_added = self.aggregator.add_model(model)
+            if models_added != []:
+                self.communication_protocol.broadcast(
+                    self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round)
+                )
+        except DecodingParamsError:
+            handle_bad_model(st, self.stop, source, "Error decoding parameters", self.communication_protocol)
+        except ModelNotMatchingError:
+            handle_bad_model(st, self.stop, source, "Models not matching", self.communication_protocol)
+        except Exception as e:  # noqa: BLE001
+            handle_bad_model(st, self.stop, source, f"Unknown error adding model: {e}", self.communication_protocol)

@@ -1,0 +1,149 @@
+"""Gossiper: TTL-flood sender thread + the synchronous model-gossip loop.
+
+Reference: communication/protocols/gossiper.py:31-239.  Behavioural contract kept:
+dedupe ring of ``AMOUNT_LAST_MESSAGES_SAVED`` hashes, at most
+``GOSSIP_MESSAGES_PER_PERIOD`` sends per ``GOSSIP_PERIOD``, model gossip to
+``min(GOSSIP_MODELS_PER_ROUND, n)`` random candidates per tick, exit when no candidate
+is left or the status did not change for ``GOSSIP_EXIT_ON_X_EQUAL_ROUNDS`` ticks.
+
+Deliberate differences:
+* the sender thread sleeps on a condition variable, so an idle gossiper costs nothing
+  and ``GOSSIP_PERIOD = 0`` does not busy-spin;
+* periods are *minimum spacings*: a tick that changed the status is followed
+  immediately by the next one, an unchanged one waits (interruptibly) for the period;
+* "X equal rounds" means what the docs say: the last X recorded statuses are all equal.
+"""
+
+from __future__ import annotations
+
+import collections
+import random
+import threading
+import time
+from typing import Any, Callable, Deque, List, Optional, Tuple
+
+from myfyp_b200.communication.protocols.client import Client
+from myfyp_b200.management.logger import logger
+from myfyp_b200.settings import Settings
+
+
+class Gossiper(threading.Thread):
+    def __init__(self, self_addr: str, client: Client, period: Optional[float] = None, messages_per_period: Optional[int] = None) -> None:
+        super().__init__(daemon=True, name=f"gossiper-thread-{self_addr}")
+        self.__self_addr = self_addr
+        self.__client = client
+        self.period = period
+        self.messages_per_period = messages_per_period
+        self.__processed: "collections.OrderedDict[int, None]" = collections.OrderedDict()
+        self.__processed_lock = threading.Lock()
+        self.__pending: Deque[Tuple[Any, List[str]]] = collections.deque()
+        self.__cv = threading.Condition()
+        self.__terminate = threading.Event()
+
+    # ------------------------------------------------------------------ thread control
+    def start(self) -> None:
+        logger.debug(self.__self_addr, "🏁 Starting gossiper...")
+        super().start()
+
+    def stop(self) -> None:
+        logger.debug(self.__self_addr, "🛑 Stopping gossiper...")
+        self.__terminate.set()
+        with self.__cv:
+            self.__cv.notify_all()
+
+    # ------------------------------------------------------------------ flood
+    def add_message(self, msg: Any, pending_neis: List[str]) -> None:
+        if not pending_neis:
+            return
+        with self.__cv:
+            self.__pending.append((msg, list(pending_neis)))
+            self.__cv.notify()
+
+    def check_and_set_processed(self, msg_hash: int) -> bool:
+        """True the first time a hash is seen (and remembers it)."""
+        with self.__processed_lock:
+            if msg_hash in self.__processed:
+                return False
+            while len(self.__processed) > Settings.AMOUNT_LAST_MESSAGES_SAVED:
+                self.__processed.popitem(last=False)
+            self.__processed[msg_hash] = None
+            return True
+
+    def was_processed(self, msg_hash: int) -> bool:
+        """Non-mutating probe used to skip redundant in-process sends."""
+        return msg_hash in self.__processed
+
+    def run(self) -> None:
+        while not self.__terminate.is_set():
+            period = Settings.GOSSIP_PERIOD if self.period is None else self.period
+            budget = Settings.GOSSIP_MESSAGES_PER_PERIOD if self.messages_per_period is None else self.messages_per_period
+            batch: List[Tuple[Any, List[str]]] = []
+            with self.__cv:
+                while not self.__pending and not self.__terminate.is_set():
+                    self.__cv.wait(timeout=1.0)
+                if self.__terminate.is_set():
+                    return
+                while budget > 0 and self.__pending:
+                    msg, neis = self.__pending[0]
+                    if len(neis) <= budget:
+                        batch.append(self.__pending.popleft())
+                        budget -= len(neis)
+                    else:
+                        batch.append((msg, neis[:budget]))
+                        self.__pending[0] = (msg, neis[budget:])
+                        budget = 0
+            t0 = time.monotonic()
+            for msg, neis in batch:
+                for nei in neis:
+                    if self.__terminate.is_set():
+                        return
+                    self.__client.send(nei, msg)
+            # only a *saturated* period needs pacing; otherwise go back to waiting
+            if budget == 0 and period > 0:
+                left = period - (time.monotonic() - t0)
+                if left > 0:
+                    self.__terminate.wait(left)
+
+    # ------------------------------------------------------------------ synchronous model gossip
+    def gossip_weights(
+        self,
+        early_stopping_fn: Callable[[], bool],
+        get_candidates_fn: Callable[[], List[str]],
+        status_fn: Callable[[], Any],
+        model_fn: Callable[[str], Any],
+        period: float,
+        create_connection: bool,
+        wait_fn: Optional[Callable[[float], None]] = None,
+    ) -> None:
+        x = Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS
+        last_status: Deque[str] = collections.deque(maxlen=max(1, x))
+        while True:
+            t0 = time.monotonic()
+            if early_stopping_fn():
+                logger.info(self.__self_addr, "Stopping model gossip process.")
+                return
+            neis = get_candidates_fn()
+            if not neis:
+                logger.info(self.__self_addr, "🤫 Gossip finished.")
+                return
+            logger.debug(self.__self_addr, f"👥 Gossip remaining nodes: {neis}")
+            before = repr(status_fn())
+            last_status.append(before)
+            if len(last_status) == x and all(s == before for s in last_status):
+                logger.info(self.__self_addr, f"⏹️  Gossiping exited for {x} equal rounds.")
+                return
+            for nei in random.sample(neis, min(Settings.GOSSIP_MODELS_PER_ROUND, len(neis))):
+                msg = model_fn(nei)
+                if msg is None:
+                    continue
+                logger.debug(self.__self_addr, f"🗣️ Gossiping model to {nei}.")
+                self.__client.send(nei, msg, create_connection=create_connection)
+            # progress => go again at once; no progress => wait (interruptibly) for the period
+            if repr(status_fn()) != before:
+                continue
+            left = period - (time.monotonic() - t0)
+            if left > 0:
+                if wait_fn is not None:
+                    wait_fn(left)
+                else:
+                    time.sleep(left)

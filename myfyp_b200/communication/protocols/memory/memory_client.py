@@ -1,0 +1,75 @@
+"""In-memory client (reference: communication/protocols/memory/memory_client.py:33-174).
+
+Messages are plain dicts with the reference's keys.  A weights message may carry a
+device descriptor instead of bytes in ``"weights"`` - nothing is serialised in process.
+"""
+
+from __future__ import annotations
+
+import random
+import time
+from typing import Any, Dict, List, Optional
+
+from myfyp_b200.communication.protocols.client import Client
+from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError
+from myfyp_b200.communication.protocols.memory.registry import ServerRegistry
+from myfyp_b200.management.logger import logger
+from myfyp_b200.settings import Settings
+
+
+class InMemoryClient(Client):
+    def __init__(self, self_addr: str, neighbors) -> None:
+        self.__self_addr = self_addr
+        self.__neighbors = neighbors
+
+    def build_message(self, cmd: str, args: Optional[List[str]] = None, round: Optional[int] = None) -> Dict[str, Any]:
+        args = [] if args is None else [str(a) for a in args]
+        return {
+            "source": self.__self_addr,
+            "ttl": Settings.TTL,
+            "hash": hash(str(cmd) + str(args) + str(time.time()) + str(random.randint(0, 100000))),
+            "cmd": cmd,
+            "args": args,
+            "round": -1 if round is None else round,
+        }
+
+    def build_weights(self, cmd: str, round: int, serialized_model: Any, contributors: Optional[List[str]] = None, weight: int = 1) -> Dict[str, Any]:
+        return {
+            "source": self.__self_addr,
+            "round": round,
+            "weights": serialized_model,
+            "contributors": [] if contributors is None else list(contributors),
+            "weight": weight,
+            "cmd": cmd,
+        }
+
+    def send(self, nei: str, msg: Dict[str, Any], create_connection: bool = False, raise_error: bool = False, remove_on_error: bool = True) -> None:
+        try:
+            try:
+                server = self.__neighbors.get(nei)[1]
+            except KeyError as e:
+                raise NeighborNotConnectedError(f"Neighbor {nei} not found.") from e
+            if server is None and create_connection:
+                server = ServerRegistry.lookup(nei)
+            if server is None:
+                raise NeighborNotConnectedError("Neighbor not directly connected (no stub and create_connection is false).")
+            if "weight" in msg:
+                res = server.send_weights(msg)
+            else:
+                # in-process short-circuit of the flood: the receiver has seen this hash already
+                if Settings.DEDUP_BEFORE_SEND and server.gossiper.was_processed(msg["hash"]):
+                    return
+                res = server.send_message(msg)
+            if "error" in res:
+                raise CommunicationError(f"Error while sending a message: {msg['cmd']!r}: {res['error']!r}")
+        except Exception as e:  # noqa: BLE001
+            logger.debug(self.__self_addr, f"Cannot send message {msg['cmd']!r} to {nei}. Error: {e}")
+            if remove_on_error:
+                self.__neighbors.remove(nei, disconnect_msg=True)
+            if raise_error:
+                raise
+
+    def broadcast(self, msg: Dict[str, Any], node_list: Optional[List[str]] = None) -> None:
+        nodes = node_list if node_list is not None else list(self.__neighbors.get_all(only_direct=True))
+        for n in nodes:
+            self.send(n, msg)

@@ -1,0 +1,92 @@
+"""Neighbour table (reference: communication/protocols/neighbors.py:27-167).
+
+``neis[addr] = (channel, stub_or_server, last_beat_time)``; a *direct* neighbour is
+one whose second field is truthy.  Listeners registered with ``on_change`` are called
+after every add/remove so waiting stages wake up without polling.
+"""
+
+from __future__ import annotations
+
+import threading
+from typing import Any, Callable, Dict, List
+
+from myfyp_b200.management.logger import logger
+
+
+class Neighbors:
+    def __init__(self, self_addr: str) -> None:
+        self.self_addr = self_addr
+        self.neis: Dict[str, Any] = {}
+        self.neis_lock = threading.RLock()
+        self._listeners: List[Callable[[], None]] = []
+
+    # -- to be provided by the transport ------------------------------------------
+    def connect(self, addr: str, *args, **kwargs) -> Any:
+        raise NotImplementedError
+
+    def disconnect(self, addr: str, *args, **kwargs) -> None:
+        raise NotImplementedError
+
+    def refresh_or_add(self, addr: str, time: float) -> None:
+        raise NotImplementedError
+
+    # -- generic ---------------------------------------------------------------
+    def on_change(self, fn: Callable[[], None]) -> None:
+        self._listeners.append(fn)
+
+    def _changed(self) -> None:
+        for fn in self._listeners:
+            try:
+                fn()
+            except Exception:
+                pass
+
+    def add(self, addr: str, *args, **kwargs) -> bool:
+        if addr == self.self_addr:
+            logger.info(self.self_addr, "❌ Cannot add itself")
+            return False
+        with self.neis_lock:
+            if addr in self.neis:
+                logger.debug(self.self_addr, f"❌ Cannot add duplicates. {addr} already exists.")
+                return False
+        # connect outside the lock: the handshake calls back into the peer, which may
+        # concurrently be connecting to us (two locks, opposite order => deadlock)
+        try:
+            entry = self.connect(addr, *args, **kwargs)
+        except Exception as e:  # noqa: BLE001
+            logger.info(self.self_addr, f"❌ Cannot add {addr}: {e}")
+            return False
+        with self.neis_lock:
+            cur = self.neis.get(addr)
+            if cur is None or (not cur[1] and entry[1]):
+                self.neis[addr] = entry
+        self._changed()
+        return True
+
+    def remove(self, addr: str, *args, **kwargs) -> None:
+        with self.neis_lock:
+            present = addr in self.neis
+            entry = self.neis.pop(addr, None)
+        if present:
+            try:
+                self.disconnect(addr, *args, entry=entry, **kwargs)
+            except Exception as e:  # noqa: BLE001
+                logger.debug(self.self_addr, f"Error while disconnecting from {addr}: {e}")
+            self._changed()
+
+    def get(self, addr: str) -> Any:
+        return self.neis[addr]
+
+    def get_all(self, only_direct: bool = False) -> Dict[str, Any]:
+        with self.neis_lock:
+            neis = dict(self.neis)
+        if only_direct:
+            return {k: v for k, v in neis.items() if v[1]}
+        return neis
+
+    def exists(self, addr: str) -> bool:
+        return addr in self.neis
+
+    def clear_neighbors(self) -> None:
+        for addr in list(self.neis.keys()):
+            self.remove(addr)

@@ -1,0 +1,108 @@
+"""SCAFFOLD aggregator (Karimireddy et al. 2019).
+
+Reference math, replicated exactly because its tests pin it
+(p2pfl/learning/aggregators/scaffold.py:70-122, test/learning/scaffold_test.py:80-141):
+
+    x <- x + lr_g * sum_k (n_k / sum n) * delta_y_k          (x starts as models[0]'s parameters)
+    c <- c + (1/K) * sum_k delta_c_k                          (c starts at 0)
+
+and the result carries ``additional_info["scaffold"] = {"global_c": c}``.
+``delta_y_i`` / ``delta_c_i`` arrive in each model's ``additional_info["scaffold"]``, either as
+lists of per-layer arrays (wire form) or as flat device slabs (fabric form); device form runs as one
+fused K-way kernel (A8) over both sets of slabs.  ``partial_aggregation=False``.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import numpy as np
+import torch
+
+from myfyp_b200.learning.aggregators.aggregator import Aggregator, NoModelsToAggregateError
+from myfyp_b200.learning.p2pfl_model import P2PFLModel
+
+
+class Scaffold(Aggregator):
+    REQUIRED_INFO_KEYS = ["delta_y_i", "delta_c_i"]
+
+    def __init__(self, node_name: str = "unknown", global_lr: float = 0.1) -> None:
+        super().__init__(node_name)
+        self.global_lr = global_lr
+        self.c: Any = []  # list of arrays (generic path) or flat tensor (slab path)
+        self.global_model_params: Any = []
+        self.partial_aggregation = False
+
+    def get_required_callbacks(self) -> List[str]:
+        return ["scaffold"]
+
+    def _get_and_validate_model_info(self, model: P2PFLModel) -> Dict[str, Any]:
+        info = model.get_info("scaffold")
+        if not all(k in info for k in self.REQUIRED_INFO_KEYS):
+            raise ValueError(f"Model is missing required info keys: {self.REQUIRED_INFO_KEYS}. Model info keys: {list(info.keys())}")
+        return info
+
+    def aggregate(self, models: List[P2PFLModel]) -> P2PFLModel:
+        if not models:
+            raise NoModelsToAggregateError(f"({self.node_name}) Trying to aggregate models when there is no models")
+        from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
+
+        infos = [self._get_and_validate_model_info(m) for m in models]
+        total = sum(m.get_num_samples() for m in models)
+        contributors: List[str] = []
+        for m in models:
+            contributors.extend(m.get_contributors())
+        if all(isinstance(m, TorchP2PFLModel) for m in models):
+            return self._aggregate_slab(models, infos, total, contributors)  # type: ignore[arg-type]
+        return self._aggregate_numpy(models, infos, total, contributors)
+
+    # ------------------------------------------------------------------ generic path (reference math in NumPy)
+    def _aggregate_numpy(self, models, infos, total, contributors) -> P2PFLModel:
+        first = models[0].get_parameters()
+        acc_y = [np.zeros_like(l, dtype=np.float64) for l in first]
+        for m, info in zip(models, infos):
+            for i, layer in enumerate(info["delta_y_i"]):
+                acc_y[i] += np.asarray(layer, dtype=np.float64) * m.get_num_samples()
+        acc_y = [(l / total) * self.global_lr for l in acc_y]
+        if not isinstance(self.global_model_params, list) or not self.global_model_params:
+            self.global_model_params = [np.asarray(p) for p in first]
+        self.global_model_params = [(p + d).astype(p.dtype) for p, d in zip(self.global_model_params, acc_y)]
+        acc_c = [np.zeros_like(np.asarray(l), dtype=np.float64) for l in infos[0]["delta_c_i"]]
+        for info in infos:
+            for i, layer in enumerate(info["delta_c_i"]):
+                acc_c[i] += np.asarray(layer, dtype=np.float64)
+        acc_c = [l / len(models) for l in acc_c]
+        if not isinstance(self.c, list) or not self.c:
+            self.c = [np.zeros_like(l) for l in acc_c]
+        self.c = [c + d for c, d in zip(self.c, acc_c)]
+        out = models[0].build_copy(params=self.global_model_params, num_samples=total, contributors=contributors)
+        out.add_info("scaffold", {"global_c": self.c})
+        return out
+
+    # ------------------------------------------------------------------ slab path (kernel A8)
+    def _aggregate_slab(self, models, infos, total, contributors) -> P2PFLModel:
+        from myfyp_b200 import ops
+
+        first = models[0]
+        dev = first.slab.device
+        dys = [_as_flat(info["delta_y_i"], first) for info in infos]
+        dcs = [_as_flat(info["delta_c_i"], first) for info in infos]
+        if not isinstance(self.global_model_params, torch.Tensor):
+            self.global_model_params = first.slab.to(dev, copy=True)
+        if not isinstance(self.c, torch.Tensor):
+            self.c = torch.zeros_like(self.global_model_params)
+        wy = [self.global_lr * m.get_num_samples() / total for m in models]
+        ops.scaffold_server_update(self.global_model_params, self.c, dys, dcs, wy, 1.0 / len(models))
+        out = first.build_copy(params=self.global_model_params.clone(), num_samples=total, contributors=contributors)
+        out.add_info("scaffold", {"global_c": self.c.clone()})
+        return out
+
+
+def _as_flat(value: Any, like) -> torch.Tensor:
+    """delta in wire form (list of per-layer arrays) or fabric form (flat tensor) -> flat tensor."""
+    if isinstance(value, torch.Tensor):
+        return value
+    host = np.zeros(like.layout.total, dtype=np.float32)
+    for e, layer in zip(like.layout.in_order(), value):
+        host[e.offset : e.offset + e.numel] = np.asarray(layer, dtype=np.float32).reshape(-1)
+    return torch.from_numpy(host).to(like.slab.device)

@@ -1,0 +1,74 @@
+"""SCAFFOLD client side.
+
+Reference: pytorch/callbacks/scaffold_callback.py:54-140 (whose gradient correction is a
+no-op because it edits ``state_dict()`` copies) and the Keras twin
+tensorflow/callbacks/scaffold_callback.py:49-59 (which does apply it).
+
+Per fit:  start: ``c <- additional_info["global_c"]`` (else keep / zeros), ``x <- theta``, ``K <- 0``;
+every step the fused optimizer adds the control-variate term to the gradient (no extra
+kernel, T6); end (kernel T7): ``c_i <- c_i + (x - y)/(K*lr)``, ``delta_y = y - x``, ``delta_c = c_i_new - c_i_old``.
+
+``variant="paper"`` (default): ``g += c - c_i`` (Karimireddy et al., Alg. 1).
+``variant="reference"``: ``g += lr * (c_i - c)`` - what the reference's Keras wrapper computes.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Dict
+
+import numpy as np
+import torch
+
+from myfyp_b200.learning.callbacks.callback import P2PFLCallback
+
+
+class SCAFFOLDCallback(P2PFLCallback):
+    def __init__(self, aggregator=None, variant: str = "paper") -> None:
+        super().__init__()
+        self.variant = variant
+        self.c_i: torch.Tensor | None = None
+        self.c: torch.Tensor | None = None
+        self.x_start: torch.Tensor | None = None
+
+    @staticmethod
+    def get_name() -> str:
+        return "scaffold"
+
+    def on_fit_start(self, learner) -> None:
+        model = learner.get_model()
+        n = model.layout.n_trainable
+        slab = model.slab
+        if self.c_i is None or self.c_i.numel() != n or self.c_i.device != slab.device:
+            self.c_i = torch.zeros(n, dtype=torch.float32, device=slab.device)
+        g = self.additional_info.get("global_c") if isinstance(self.additional_info, dict) else None
+        if g is not None:
+            self.c = _flat_prefix(g, model, n)
+        elif self.c is None or self.c.numel() != n or self.c.device != slab.device:
+            self.c = torch.zeros(n, dtype=torch.float32, device=slab.device)
+        self.x_start = slab[:n].clone()
+
+    def optimizer_terms(self, learner) -> Dict[str, Any]:
+        if self.variant == "reference":
+            return {"cv_global": self.c, "cv_local": self.c_i, "cv_scale": -float(learner.lr)}
+        return {"cv_global": self.c, "cv_local": self.c_i, "cv_scale": 1.0}
+
+    def on_fit_end(self, learner, steps: int, lr: float) -> None:
+        from myfyp_b200 import ops
+
+        model = learner.get_model()
+        n = model.layout.n_trainable
+        total = model.layout.total
+        dy = torch.zeros(total, dtype=torch.float32, device=model.slab.device)
+        dc = torch.zeros(total, dtype=torch.float32, device=model.slab.device)
+        ops.scaffold_finalize(self.c_i, dy[:n], dc[:n], self.x_start, model.slab[:n], max(steps, 1) * lr)
+        # flat device slabs on the fabric; `encode_parameters` turns them into NumPy for the wire
+        self.additional_info = {"delta_y_i": dy, "delta_c_i": dc}
+
+
+def _flat_prefix(value: Any, model, n: int) -> torch.Tensor:
+    if isinstance(value, torch.Tensor):
+        return value.to(model.slab.device)[:n].contiguous()
+    host = np.zeros(model.layout.total, dtype=np.float32)
+    for e, layer in zip(model.layout.in_order(), value):
+        host[e.offset : e.offset + e.numel] = np.asarray(layer, dtype=np.float32).reshape(-1)
+    return torch.from_numpy(host[:n].copy()).to(model.slab.device)

@@ -1,0 +1,34 @@
+"""A small CIFAR-10 CNN (BASELINE.json config 2).  The reference ships no CNN (only the thesis describes a
+FEMNIST one), so the architecture is defined here: 3x[conv3x3-ReLU-maxpool2] + 2 linear layers, ~0.55 M
+parameters (about the "9x the MLP"... order of magnitude the thesis quotes for its CNN)."""
+
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import nn
+
+
+class CNN(nn.Module):
+    def __init__(self, in_channels: int = 3, num_classes: int = 10, width: int = 32, image_size: int = 32) -> None:
+        super().__init__()
+        w = width
+        self.features = nn.Sequential(
+            nn.Conv2d(in_channels, w, 3, padding=1), nn.ReLU(inplace=True), nn.MaxPool2d(2),
+            nn.Conv2d(w, 2 * w, 3, padding=1), nn.ReLU(inplace=True), nn.MaxPool2d(2),
+            nn.Conv2d(2 * w, 4 * w, 3, padding=1), nn.ReLU(inplace=True), nn.MaxPool2d(2),
+        )
+        s = image_size // 8
+        self.classifier = nn.Sequential(nn.Flatten(), nn.Linear(4 * w * s * s, 256), nn.ReLU(inplace=True), nn.Linear(256, num_classes))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.classifier(self.features(x.float()))
+
+
+def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, channels_last: bool = True, **kwargs):
+    from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
+
+    if seed is not None:
+        torch.manual_seed(seed)
+    return TorchP2PFLModel(CNN(**kwargs), device=device)

@@ -1,0 +1,314 @@
+"""Hot ops.  CUDA tensors -> hand-written sm_100a kernels (libmyfyp_b200.so); CPU tensors -> PyTorch.
+
+The CPU branch exists so the control plane and the oracles run on a box without a GPU; it is the
+"plain PyTorch fp32 reference of the same op" the kernel tests compare against.  Kernel numbering
+(A1..A8, T1..T8) follows SURVEY §8.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from typing import Any, List, Optional, Sequence, Tuple
+
+import torch
+
+from myfyp_b200.ops import native
+
+MAX_K = 64  # models per K-way kernel launch (kernel-argument pointer table)
+
+
+def _cuda(t: torch.Tensor) -> bool:
+    return t.is_cuda
+
+
+def pick_device(slabs: Sequence[torch.Tensor], prefer: Optional[torch.device] = None) -> torch.device:
+    """Where a K-way reduction runs: the preferred (receiver's) device if it is CUDA, else the first CUDA one."""
+    if prefer is not None and prefer.type == "cuda":
+        return prefer
+    for s in slabs:
+        if s.is_cuda:
+            return s.device
+    return slabs[0].device
+
+
+def _same_place(slabs: Sequence[torch.Tensor], device: torch.device) -> List[torch.Tensor]:
+    """CPU inputs of a CUDA reduction are staged; CUDA inputs (any GPU) are read in place over NVLink."""
+    if device.type == "cuda":
+        return [s if s.is_cuda else s.to(device, non_blocking=True) for s in slabs]
+    return [s.cpu() if s.is_cuda else s for s in slabs]
+
+
+# ====================================================================== A4: pull copy
+def pull_copy(dst: torch.Tensor, src: torch.Tensor) -> None:
+    """``dst <- src`` (flat fp32).  On CUDA: one vectorised pull kernel; ``src`` may be a peer GPU's slab."""
+    if dst.data_ptr() == src.data_ptr() and dst.device == src.device:
+        return
+    n = dst.numel()
+    if dst.is_cuda and src.is_cuda and src.dtype == torch.float32 and src.is_contiguous():
+        lib = native.load()
+        with native.device_guard(dst.device):
+            native.check(lib.b2_pull_copy(native.ptr(dst), native.ptr(src), ctypes.c_int64(n), native.stream_ptr(dst.device)), "b2_pull_copy")
+        native.count_launch()
+    else:
+        dst.copy_(src.reshape(-1)[:n].to(torch.float32), non_blocking=True)
+
+
+# ====================================================================== A1: K-way weighted sum
+def fedavg(slabs: Sequence[torch.Tensor], weights: Sequence[float], device: Optional[torch.device] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out = sum_k w_k * slab_k`` in ONE pass (K pulls fused with the weighted sum)."""
+    device = device or pick_device(slabs)
+    slabs = _same_place(slabs, device)
+    n = slabs[0].numel()
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=device)
+    if device.type == "cuda":
+        lib = native.load()
+        with native.device_guard(device):
+            for c0 in range(0, len(slabs), MAX_K):
+                chunk, w = slabs[c0 : c0 + MAX_K], weights[c0 : c0 + MAX_K]
+                native.check(
+                    lib.b2_fedavg(native.ptr(out), native.ptr_array(chunk), native.float_array(w), len(chunk), ctypes.c_int64(n), ctypes.c_int(1 if c0 else 0), native.stream_ptr(device)),
+                    "b2_fedavg",
+                )
+                native.count_launch()
+    else:
+        acc = torch.zeros(n, dtype=torch.float32)
+        for s, w in zip(slabs, weights):
+            acc.add_(s.to(torch.float32), alpha=float(w))
+        out.copy_(acc)
+    return out
+
+
+# ====================================================================== A3: streaming accumulate
+def accumulate(acc: torch.Tensor, src: torch.Tensor, w: float, beta: float = 1.0) -> None:
+    """``acc = beta*acc + w*src`` - the partial-model transfer itself when ``src`` is a peer slab."""
+    if acc.is_cuda:
+        lib = native.load()
+        with native.device_guard(acc.device):
+            native.check(
+                lib.b2_accumulate(native.ptr(acc), native.ptr(src), ctypes.c_float(w), ctypes.c_float(beta), ctypes.c_int64(acc.numel()), native.stream_ptr(acc.device)),
+                "b2_accumulate",
+            )
+        native.count_launch()
+    else:
+        acc.mul_(beta).add_(src.to(acc.device), alpha=float(w))
+
+
+# ====================================================================== A5: median / trimmed mean
+def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Optional[torch.device] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Coordinate-wise median (``trim=None``; even K -> mean of the two middle values, like NumPy) or trimmed mean."""
+    device = device or pick_device(slabs)
+    slabs = _same_place(slabs, device)
+    k, n = len(slabs), slabs[0].numel()
+    if k > MAX_K:
+        raise ValueError(f"median over {k} models: at most {MAX_K} per launch")
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=device)
+    if device.type == "cuda":
+        lib = native.load()
+        with native.device_guard(device):
+            native.check(
+                lib.b2_median(native.ptr(out), native.ptr_array(slabs), k, ctypes.c_int(-1 if trim is None else trim), ctypes.c_int64(n), native.stream_ptr(device)),
+                "b2_median",
+            )
+        native.count_launch()
+    else:
+        st = torch.sort(torch.stack([s.to(torch.float32) for s in slabs]), dim=0).values
+        if trim is None:
+            out.copy_((st[(k - 1) // 2] + st[k // 2]) * 0.5)
+        else:
+            out.copy_(st[trim : k - trim].mean(dim=0))
+    return out
+
+
+# ====================================================================== A6/A7: Krum
+def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None) -> torch.Tensor:
+    """K x K matrix of squared L2 distances.  CUDA: centred Gram matrix on tcgen05 (A6) + d = Gii+Gjj-2Gij."""
+    device = device or pick_device(slabs)
+    slabs = _same_place(slabs, device)
+    k, n = len(slabs), slabs[0].numel()
+    if device.type == "cuda":
+        if k > MAX_K:
+            raise ValueError(f"krum over {k} models: at most {MAX_K}")
+        lib = native.load()
+        gram = torch.zeros(MAX_K * MAX_K, dtype=torch.float32, device=device)
+        with native.device_guard(device):
+            native.check(lib.b2_krum_gram(native.ptr(gram), native.ptr_array(slabs), k, ctypes.c_int64(n), native.stream_ptr(device)), "b2_krum_gram")
+        native.count_launch()
+        g = gram.view(MAX_K, MAX_K)[:k, :k].double()
+        d = torch.diagonal(g)
+        return (d[:, None] + d[None, :] - 2 * g).clamp_min(0).float()
+    m = torch.stack([s.double() for s in slabs])
+    m = m - m[0:1]
+    g = m @ m.T
+    d = torch.diagonal(g)
+    return (d[:, None] + d[None, :] - 2 * g).clamp_min(0).float()
+
+
+def krum_select(dist: torch.Tensor, f: int, m: int) -> Tuple[List[float], List[int]]:
+    """Krum scores (sum of the K-f-2 smallest distances to others) and the indices of the ``m`` best."""
+    k = dist.shape[0]
+    if dist.is_cuda:
+        lib = native.load()
+        scores = torch.empty(k, dtype=torch.float32, device=dist.device)
+        sel = torch.empty(k, dtype=torch.int32, device=dist.device)
+        d = dist.contiguous()
+        with native.device_guard(dist.device):
+            native.check(lib.b2_krum_select(native.ptr(d), k, f, native.ptr(scores), native.ptr(sel), native.stream_ptr(dist.device)), "b2_krum_select")
+        native.count_launch()
+        return scores.tolist(), sel[:m].tolist()
+    from myfyp_b200.learning.aggregators.krum import krum_select_reference
+
+    return krum_select_reference(dist.numpy(), f, m)
+
+
+# ====================================================================== A8 / T7: Scaffold
+def scaffold_server_update(x: torch.Tensor, c: torch.Tensor, dys: Sequence[torch.Tensor], dcs: Sequence[torch.Tensor], wy: Sequence[float], wc: float) -> None:
+    """``x += sum_k wy_k * dy_k``; ``c += wc * sum_k dc_k`` - one pass over 2K (peer) slabs."""
+    if x.is_cuda:
+        dys, dcs = _same_place(dys, x.device), _same_place(dcs, x.device)
+        lib = native.load()
+        with native.device_guard(x.device):
+            native.check(
+                lib.b2_scaffold_server(native.ptr(x), native.ptr(c), native.ptr_array(dys), native.ptr_array(dcs), native.float_array(wy), ctypes.c_float(wc), len(dys), ctypes.c_int64(x.numel()), native.stream_ptr(x.device)),
+                "b2_scaffold_server",
+            )
+        native.count_launch()
+    else:
+        for dy, w in zip(dys, wy):
+            x.add_(dy.to(x.device), alpha=float(w))
+        for dc in dcs:
+            c.add_(dc.to(c.device), alpha=float(wc))
+
+
+def scaffold_finalize(c_i: torch.Tensor, dy: torch.Tensor, dc: torch.Tensor, x: torch.Tensor, y: torch.Tensor, k_lr: float) -> None:
+    """``adj = (x-y)/(K*lr)``; ``dc = adj``; ``c_i += adj``; ``dy = y - x`` (reference scaffold_callback.py:124-140)."""
+    if c_i.is_cuda:
+        lib = native.load()
+        with native.device_guard(c_i.device):
+            native.check(
+                lib.b2_scaffold_finalize(native.ptr(c_i), native.ptr(dy), native.ptr(dc), native.ptr(x), native.ptr(y), ctypes.c_float(1.0 / k_lr), ctypes.c_int64(c_i.numel()), native.stream_ptr(c_i.device)),
+                "b2_scaffold_finalize",
+            )
+        native.count_launch()
+    else:
+        adj = (x - y) / k_lr
+        dc.copy_(adj)
+        c_i.add_(adj)
+        dy.copy_(y - x)
+
+
+# ====================================================================== T6: fused optimizers
+def adam_step(
+    p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,
+    weight_decay: float = 0.0, prox_mu: float = 0.0, prox_ref: Optional[torch.Tensor] = None, cv_global: Optional[torch.Tensor] = None,
+    cv_local: Optional[torch.Tensor] = None, cv_scale: float = 1.0, zero_grad: bool = True,
+) -> None:
+    """Adam over the flat slab.  ``g' = g + wd*p + mu*(p - ref) + cv_scale*(c - c_i)``; clears ``g`` afterwards."""
+    if p.is_cuda:
+        lib = native.load()
+        bc1, bc2 = 1.0 - beta1**step, 1.0 - beta2**step
+        with native.device_guard(p.device):
+            native.check(
+                lib.b2_adam_step(
+                    native.ptr(p), native.ptr(g), native.ptr(m), native.ptr(v), ctypes.c_int64(p.numel()), ctypes.c_float(lr), ctypes.c_float(beta1), ctypes.c_float(beta2),
+                    ctypes.c_float(eps), ctypes.c_float(weight_decay), ctypes.c_float(bc1), ctypes.c_float(bc2), ctypes.c_float(prox_mu if prox_ref is not None else 0.0),
+                    native.ptr(prox_ref), native.ptr(cv_global), native.ptr(cv_local), ctypes.c_float(cv_scale), ctypes.c_int(1 if zero_grad else 0), native.stream_ptr(p.device),
+                ),
+                "b2_adam_step",
+            )
+        native.count_launch()
+        return
+    gg = _effective_grad(p, g, weight_decay, prox_mu, prox_ref, cv_global, cv_local, cv_scale)
+    m.mul_(beta1).add_(gg, alpha=1 - beta1)
+    v.mul_(beta2).addcmul_(gg, gg, value=1 - beta2)
+    denom = (v / (1 - beta2**step)).sqrt_().add_(eps)
+    p.data.addcdiv_(m / (1 - beta1**step), denom, value=-lr)
+    if zero_grad:
+        g.zero_()
+
+
+def sgd_step(
+    p: torch.Tensor, g: torch.Tensor, buf: torch.Tensor, lr: float = 1e-2, momentum: float = 0.0, weight_decay: float = 0.0, prox_mu: float = 0.0,
+    prox_ref: Optional[torch.Tensor] = None, cv_global: Optional[torch.Tensor] = None, cv_local: Optional[torch.Tensor] = None, cv_scale: float = 1.0, zero_grad: bool = True,
+) -> None:
+    """SGD(+momentum) over the flat slab with the same fused FedProx / Scaffold terms."""
+    if p.is_cuda:
+        lib = native.load()
+        with native.device_guard(p.device):
+            native.check(
+                lib.b2_sgd_step(
+                    native.ptr(p), native.ptr(g), native.ptr(buf), ctypes.c_int64(p.numel()), ctypes.c_float(lr), ctypes.c_float(momentum), ctypes.c_float(weight_decay),
+                    ctypes.c_float(prox_mu if prox_ref is not None else 0.0), native.ptr(prox_ref), native.ptr(cv_global), native.ptr(cv_local), ctypes.c_float(cv_scale),
+                    ctypes.c_int(1 if zero_grad else 0), native.stream_ptr(p.device),
+                ),
+                "b2_sgd_step",
+            )
+        native.count_launch()
+        return
+    gg = _effective_grad(p, g, weight_decay, prox_mu, prox_ref, cv_global, cv_local, cv_scale)
+    if momentum != 0.0:
+        buf.mul_(momentum).add_(gg)
+        gg = buf
+    p.data.add_(gg, alpha=-lr)
+    if zero_grad:
+        g.zero_()
+
+
+def _effective_grad(p, g, wd, mu, ref, c, c_i, cv_scale) -> torch.Tensor:
+    gg = g.clone()
+    if wd:
+        gg.add_(p.data, alpha=wd)
+    if ref is not None and mu:
+        gg.add_(p.data - ref, alpha=mu)
+    if c is not None and c_i is not None:
+        gg.add_(c - c_i, alpha=cv_scale)
+    return gg
+
+
+# ====================================================================== T3/T8: fused softmax cross-entropy
+class _XentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        b, c = logits.shape
+        lg = logits.contiguous().float()
+        loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(lg)
+        lib = native.load()
+        with native.device_guard(logits.device):
+            native.check(
+                lib.b2_xent_fwd_bwd(native.ptr(lg), native.ptr(labels), native.ptr(loss), native.ptr(dlogits), native.ptr(None), b, c, ctypes.c_float(1.0 / b), native.stream_ptr(logits.device)),
+                "b2_xent_fwd_bwd",
+            )
+        native.count_launch()
+        ctx.save_for_backward(dlogits)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * grad_out, None
+
+
+def cross_entropy(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """Mean NLL of log-softmax(logits); forward computes ``dlogits`` too (one kernel, no softmax round trip)."""
+    if logits.is_cuda:
+        return _XentFn.apply(logits, labels)
+    return torch.nn.functional.cross_entropy(logits.float(), labels)
+
+
+def cross_entropy_eval(logits: torch.Tensor, labels: torch.Tensor, acc: torch.Tensor) -> None:
+    """``acc[0] += sum of per-sample NLL``; ``acc[1] += number of correct argmax`` (fused T3+T8)."""
+    b, c = logits.shape
+    if logits.is_cuda:
+        lg = logits.contiguous().float()
+        lib = native.load()
+        with native.device_guard(logits.device):
+            native.check(
+                lib.b2_xent_fwd_bwd(native.ptr(lg), native.ptr(labels), native.ptr(acc[0:1]), native.ptr(None), native.ptr(acc[1:2]), b, c, ctypes.c_float(1.0), native.stream_ptr(logits.device)),
+                "b2_xent_fwd_bwd",
+            )
+        native.count_launch()
+    else:
+        acc[0] += torch.nn.functional.cross_entropy(logits.float(), labels, reduction="sum")
+        acc[1] += (logits.argmax(dim=1) == labels).sum()

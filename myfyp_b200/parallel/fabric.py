@@ -1,0 +1,104 @@
+"""The NVLink fabric: device placement, published-slab snapshots, peer access, IPC arenas.
+
+No counterpart in the reference (its "data plane" is pickled bytes through gRPC or a function call,
+SURVEY §5.9).  Two deployment shapes:
+
+* **one process, many GPUs** - peer access is enabled between every GPU pair; a :class:`SlabRef`
+  carries the tensor itself and kernels dereference it directly (local HBM or over NVLink);
+* **one process per GPU** (``torchrun``) - every rank owns an *arena* allocated with ``cudaMalloc``
+  through the native library, exports its CUDA-IPC handle once, and maps every peer's arena;
+  a :class:`SlabRef` is then ``(rank, offset, generation)`` and resolves to a tensor view of the
+  mapped arena.  Published snapshots rotate through ``GENERATIONS`` slots per node so a peer can
+  still pull round r while the owner publishes round r+1.
+
+Nodes are *placed* on GPUs round-robin (many per GPU), SURVEY §5.8.
+"""
+
+from __future__ import annotations
+
+import dataclasses
+import threading
+from typing import Dict, List, Optional
+
+import torch
+
+from myfyp_b200.parallel.slab import SlabRef
+
+
+@dataclasses.dataclass
+class Snapshot:
+    tensor: Optional[torch.Tensor]
+    rank: int = -1
+    offset: int = 0
+    generation: int = 0
+
+
+class Fabric:
+    _instance: Optional["Fabric"] = None
+    _lock = threading.Lock()
+
+    def __init__(self) -> None:
+        self.rank = -1  # single-process mode
+        self.world = 1
+        self._peer_enabled = False
+        self._arena = None  # multi-process mode: ArenaPool (see ipc.py)
+        self._placement_counter = 0
+
+    @classmethod
+    def get(cls) -> "Fabric":
+        if cls._instance is None:
+            with cls._lock:
+                if cls._instance is None:
+                    cls._instance = Fabric()
+        return cls._instance
+
+    # ------------------------------------------------------------------ placement
+    def device_count(self) -> int:
+        return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+    def place(self, index: Optional[int] = None) -> torch.device:
+        """Device for the ``index``-th node of this process (round-robin over visible GPUs; CPU without GPUs)."""
+        n = self.device_count()
+        if n == 0:
+            return torch.device("cpu")
+        if self.rank >= 0:  # one process per GPU: everything on the local GPU
+            return torch.device("cuda", torch.cuda.current_device())
+        if index is None:
+            index = self._placement_counter
+            self._placement_counter += 1
+        return torch.device("cuda", index % n)
+
+    # ------------------------------------------------------------------ peer access (single process)
+    def enable_peer_access(self) -> int:
+        """``cudaDeviceEnablePeerAccess`` for every ordered GPU pair; returns how many pairs can reach each other."""
+        if self._peer_enabled:
+            return 0
+        n = self.device_count()
+        ok = 0
+        if n > 1:
+            from myfyp_b200.ops import native
+
+            lib = native.load()
+            ok = lib.b2_enable_peer_access_all()
+        self._peer_enabled = True
+        return ok
+
+    # ------------------------------------------------------------------ snapshots
+    def snapshot(self, slab: torch.Tensor) -> Snapshot:
+        """Immutable copy of ``slab`` that peers may read until they drop their descriptor."""
+        if self._arena is not None and slab.is_cuda:
+            return self._arena.publish(slab)
+        if slab.is_cuda:
+            self.enable_peer_access()
+        return Snapshot(slab.clone())
+
+    def attach_arena(self, arena) -> None:
+        self._arena = arena
+        self.rank, self.world = arena.rank, arena.world
+
+    def resolve(self, ref: SlabRef) -> torch.Tensor:
+        if ref.tensor is not None:
+            return ref.tensor
+        if self._arena is None:
+            raise RuntimeError("descriptor from another process but no IPC arena is attached (Fabric.attach_arena)")
+        return self._arena.view(ref.rank, ref.offset, ref.numel)

@@ -1,0 +1,98 @@
+"""TrainStage (reference: stages/base_node/train_stage.py:44-187).
+
+evaluate -> fit -> add own model -> announce -> gossip partial aggregates inside the train set until every
+member covers the train set -> aggregate -> adopt -> announce ``models_ready``.
+
+Data plane: what is gossiped is ``aggregator.get_model(except_nodes=what the peer announced)``
+(SURVEY App. C.1).  To a peer on the NVLink fabric the message carries a slab descriptor; the peer's
+aggregation kernel pulls it out of our HBM when it reduces.  Off-fabric peers get the reference pickle.
+"""
+
+from __future__ import annotations
+
+from typing import Any, List, Set, Type, Union
+
+from myfyp_b200.communication.commands.message.metrics_command import MetricsCommand
+from myfyp_b200.communication.commands.message.models_aggregated_command import ModelsAggregatedCommand
+from myfyp_b200.communication.commands.message.models_ready_command import ModelsReadyCommand
+from myfyp_b200.communication.commands.weights.partial_model_command import PartialModelCommand
+from myfyp_b200.learning.aggregators.aggregator import NoModelsToAggregateError
+from myfyp_b200.management.logger import logger
+from myfyp_b200.stages.base_node.start_learning_stage import _transport
+from myfyp_b200.stages.stage import EarlyStopException, Stage, check_early_stop
+from myfyp_b200.stages.stage_factory import StageFactory
+
+
+class TrainStage(Stage):
+    @staticmethod
+    def name() -> str:
+        return "TrainStage"
+
+    @staticmethod
+    def execute(state=None, communication_protocol=None, learner=None, aggregator=None, **kwargs) -> Union[Type[Stage], None]:
+        if state is None or communication_protocol is None or aggregator is None or learner is None:
+            raise Exception("Invalid parameters on TrainStage.")
+        try:
+            check_early_stop(state)
+            aggregator.set_nodes_to_aggregate(state.train_set)
+            check_early_stop(state)
+            evaluate_and_broadcast(state, learner, communication_protocol)
+            check_early_stop(state)
+
+            logger.info(state.addr, "🏋️‍♀️ Training...")
+            learner.fit()
+            check_early_stop(state)
+
+            models_added = aggregator.add_model(learner.get_model().snapshot_model())
+            communication_protocol.broadcast(communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=state.round))
+            TrainStage.__gossip_model_aggregation(state, communication_protocol, aggregator)
+            check_early_stop(state)
+
+            agg_model = aggregator.wait_and_get_aggregation()
+            learner.set_model(agg_model)
+            communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
+            return StageFactory.get_stage("GossipModelStage")
+        except EarlyStopException:
+            return None
+
+    @staticmethod
+    def __gossip_model_aggregation(state, communication_protocol, aggregator) -> None:
+        def early_stopping_fn() -> bool:
+            return state.round is None
+
+        def aggregated_by(node: str) -> List[str]:
+            return state.models_aggregated.get(node, [])
+
+        def remaining(node: str) -> Set[str]:
+            return set(state.train_set) - set(aggregated_by(node))
+
+        def get_candidates_fn() -> List[str]:
+            return [n for n in set(state.train_set) - {state.addr} if len(remaining(n)) != 0]
+
+        def status_fn() -> Any:
+            return [(n, aggregated_by(n)) for n in communication_protocol.get_neighbors(only_direct=False) if n in state.train_set]
+
+        def model_fn(node: str) -> Any:
+            try:
+                model = aggregator.get_model(aggregated_by(node))
+            except NoModelsToAggregateError:
+                logger.debug(state.addr, f"❔ No models to aggregate from {node}.")
+                return None
+            if state.round is None:
+                raise Exception("Round not initialized.")
+            return communication_protocol.build_weights(
+                PartialModelCommand.get_name(), state.round, _transport(model, communication_protocol, node), model.get_contributors(), model.get_num_samples()
+            )
+
+        communication_protocol.gossip_weights(
+            early_stopping_fn, get_candidates_fn, status_fn, model_fn, create_connection=True, wait_fn=state.wait_change
+        )
+
+
+def evaluate_and_broadcast(state, learner, communication_protocol) -> None:
+    logger.info(state.addr, "🔬 Evaluating...")
+    results = learner.evaluate()
+    logger.info(state.addr, f"📈 Evaluated. Results: {results}")
+    if len(results) > 0:
+        flat = [str(item) for pair in results.items() for item in pair]
+        communication_protocol.broadcast(communication_protocol.build_msg(MetricsCommand.get_name(), flat, round=state.round))
