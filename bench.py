@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""Headline benchmark: FL rounds/sec of an 8-node federation on N B200s (BASELINE.json, config 2).
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
+
+One *step* = one full federated round of the whole federation (vote -> evaluate -> local epoch -> partial-model
+gossip -> FedAvg -> diffusion) through the public API: ``Node(...)``, ``connect``, ``set_start_learning(rounds, 1)``.
+The federation is fixed (8 nodes, CNN on CIFAR-10-shaped synthetic data, fully connected, FedAvg, every node in the
+train set) and is spread over the N GPUs ("strong" scaling; N = 8 is exactly "one node per B200").
+N = 1 uses the in-memory protocol in one process; N > 1 uses the gRPC protocol between ranks for the control plane
+and CUDA-IPC slab descriptors + peer loads over NVLink for the data plane.
+
+`value` is device-timed (CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks)
+with device-resident data; `e2e` repeats the same K rounds with every node's partition coming from pinned host
+memory each round (H2D) and each round's losses/metrics read back (D2H), timed by the host clock.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+TOTAL_NODES = 8
+SAMPLES_PER_NODE = 512
+TEST_PER_NODE = 128
+BATCH = 64
+METRIC = "fl_rounds_per_sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="cnn", choices=["cnn", "mlp", "resnet18"])
+    ap.add_argument("--nodes", type=int, default=TOTAL_NODES)
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self) -> None:
+        self.proc = None
+        self.lines = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self, gpus: int) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                if int(f[0]) >= gpus:
+                    continue
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def make_model(name: str, device, seed: int):
+    from myfyp_b200.models import cnn_model, mlp_model, resnet18_model
+
+    return {"cnn": cnn_model, "mlp": mlp_model, "resnet18": resnet18_model}[name](device=device, seed=seed)
+
+
+def make_data(name: str, n_nodes: int):
+    from myfyp_b200.learning.dataset import P2PFLDataset, RandomIIDPartitionStrategy
+
+    shape = (28, 28) if name == "mlp" else (3, 32, 32)
+    data = P2PFLDataset.synthetic(shape, 10, SAMPLES_PER_NODE * n_nodes, TEST_PER_NODE * n_nodes, seed=0)
+    return data.generate_partitions(n_nodes, RandomIIDPartitionStrategy)
+
+
+def run_ours(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    multi = world > 1
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if multi:
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+
+    from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
+    from myfyp_b200.communication.protocols.memory.memory_communication_protocol import InMemoryCommunicationProtocol
+    from myfyp_b200.learning.aggregators import FedAvg
+    from myfyp_b200.node import Node
+    from myfyp_b200.ops import native
+    from myfyp_b200.parallel.fabric import Fabric
+    from myfyp_b200.settings import Settings
+    from myfyp_b200.utils.utils import set_fast_settings
+
+    native.load()
+    n_nodes = args.nodes
+    set_fast_settings(train_set_size=n_nodes)
+    Settings.USE_SSL = False
+    torch.manual_seed(1234 + rank)
+
+    owner = [i * world // n_nodes for i in range(n_nodes)]  # node i lives on rank owner[i]
+    mine = [i for i in range(n_nodes) if owner[i] == rank]
+    parts = make_data(args.model, n_nodes)
+    if multi:
+        job = os.environ.get("MASTER_PORT", "29500")
+        addrs = [f"unix:///tmp/b2bench-{job}-{i}.sock" for i in range(n_nodes)]
+        for i in mine:
+            try:
+                os.unlink(addrs[i][len("unix://"):])
+            except OSError:
+                pass
+        proto = GrpcCommunicationProtocol
+    else:
+        addrs = [f"node-{i}" for i in range(n_nodes)]
+        proto = InMemoryCommunicationProtocol
+
+    models = {i: make_model(args.model, dev, seed=i) for i in mine}
+    if multi:
+        from myfyp_b200.parallel.ipc import ArenaPool, register_addresses
+
+        slot = max(m.layout.total for m in models.values()) if models else 64
+        arena = ArenaPool(rank, world, dev, slot_elems=slot, slots=max(4 * len(mine) * 3, 8))
+        arena.exchange()
+        Fabric.get().attach_arena(arena)
+        register_addresses({addrs[i]: owner[i] for i in range(n_nodes)})
+
+    nodes = {i: Node(models[i], parts[i], address=addrs[i], aggregator=FedAvg(), protocol=proto, batch_size=BATCH, lr=1e-3) for i in mine}
+    for n in nodes.values():
+        n.start()
+    if multi:
+        dist.barrier()
+    for i in mine:  # fully connected: i -> j for i < j (the handshake makes it symmetric)
+        for j in range(i + 1, n_nodes):
+            nodes[i].connect(addrs[j])
+    deadline = time.time() + 60
+    while any(len(n.get_neighbors(only_direct=True)) < n_nodes - 1 for n in nodes.values()):
+        if time.time() > deadline:
+            raise RuntimeError("topology did not converge")
+        time.sleep(0.02)
+    if multi:
+        dist.barrier()
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def flush_l2() -> None:
+        flush_buf.zero_()
+
+    first = nodes[mine[0]] if mine else None
+    if first is not None:
+        first.learner.pre_fit_hook = flush_l2  # one L2 flush per round per GPU
+
+    def barrier() -> None:
+        torch.cuda.synchronize(dev)
+        if multi:
+            dist.barrier()
+
+    def run_rounds(rounds: int) -> None:
+        hist = {i: len(n.learning_workflow.history) for i, n in nodes.items()}
+        if rank == 0:
+            nodes[0].set_start_learning(rounds=rounds, epochs=1)
+        t_end = time.time() + 600
+        for i, n in nodes.items():
+            while not (len(n.learning_workflow.history) > hist[i] and n.learning_workflow.finished):
+                if time.time() > t_end:
+                    raise RuntimeError(f"node {i} did not finish: {n.learning_workflow.history[-3:]}")
+                time.sleep(0.001)
+
+    def set_host_mode(flag: bool) -> None:
+        for n in nodes.values():
+            n.learner.data_on_host = flag
+            n.learner.h2d_bytes = n.learner.d2h_bytes = 0
+
+    def allmax(x: float) -> float:
+        if not multi:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x: float) -> float:
+        if not multi:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- warm-up (W rounds, untimed), then EXACTLY K timed rounds, device-timed
+    barrier()
+    run_rounds(args.warmup)
+    barrier()
+    sampler = ClockSampler()
+    if rank == 0:
+        sampler.start()
+    native.reset_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(torch.cuda.current_stream(dev))
+    run_rounds(args.steps)
+    e1.record(torch.cuda.current_stream(dev))
+    barrier()
+    ms = allmax(e0.elapsed_time(e1))
+    launches = int(allsum(native.launches()))
+    clocks = sampler.stop(world) if rank == 0 else {}
+
+    # ---- end-to-end: inputs from pinned host memory every round, results read back every round
+    e2e = None
+    if not args.no_e2e:
+        set_host_mode(True)
+        barrier()
+        run_rounds(max(1, min(args.warmup, 2)))
+        set_host_mode(True)  # reset byte counters
+        barrier()
+        t0 = time.perf_counter()
+        run_rounds(args.steps)
+        barrier()
+        wall = allmax(time.perf_counter() - t0)
+        h2d = allsum(sum(n.learner.h2d_bytes for n in nodes.values())) / args.steps
+        d2h = allsum(sum(n.learner.d2h_bytes for n in nodes.values())) / args.steps
+        e2e = {"value": args.steps / wall, "unit": "rounds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * wall / args.steps}
+        set_host_mode(False)
+
+    for n in nodes.values():
+        n.stop()
+    if multi:
+        dist.barrier()
+    if rank == 0:
+        value = args.steps / (ms / 1e3)
+        base = None
+        try:
+            with open(os.path.join(ROOT, "BASELINE.json")) as f:
+                base = json.load(f).get("published", {}).get(METRIC)
+        except Exception:
+            pass
+        out = {
+            "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": (value / base) if base else None, "dtype": "bf16" if args.model == "mlp" else "fp32+tf32",
+            "data": "synthetic", "impl": "ours",
+            "config": {
+                "model": {"cnn": "CNN (3 conv + 2 fc, 0.55M params) on CIFAR-10-shaped data", "mlp": "MLP 784-256-128-10 on MNIST-shaped data", "resnet18": "ResNet-18 CIFAR"}[args.model],
+                "nodes": n_nodes, "nodes_per_gpu": n_nodes / world, "train_set_size": n_nodes, "topology": "full", "aggregator": "FedAvg",
+                "samples_per_node": SAMPLES_PER_NODE, "global_batch": BATCH * n_nodes, "batch_per_node": BATCH, "local_epochs": 1, "seq_len": None,
+                "protocol": "grpc+cuda-ipc" if multi else "in-memory", "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
+                "step": "one federated round of all nodes",
+            },
+            "clocks": clocks, "gpu_launches": launches,
+        }
+        if e2e is not None:
+            out["e2e"] = e2e
+        print(json.dumps(out), flush=True)
+    if multi:
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    args = parse()
+    if args.impl == "reference":
+        from bench.reference_arm import run_reference
+
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

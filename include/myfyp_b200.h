@@ -1,0 +1,99 @@
+/* myfyp_b200 - C ABI of libmyfyp_b200.so (hand-written sm_100a kernels + the native side of the fabric).
+ *
+ * Conventions: every entry point returns 0 on success and non-zero on failure (b2_last_error() has the text);
+ * kernels launch on the CURRENT device into `stream` (a cudaStream_t passed as void*); pointers are device
+ * pointers unless the name says host; "slab" = flat fp32 buffer, 16-byte aligned.  Source pointers of the
+ * aggregation kernels may be peer-GPU memory (peer access or CUDA-IPC mappings): the loads are the transfer.
+ * Each declaration cites the reference (PrivEimantas/myFYP = p2pfl 0.4.0) code whose math it implements.
+ */
+#ifndef MYFYP_B200_H
+#define MYFYP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------------ runtime */
+const char* b2_last_error(void);
+int b2_version(void);
+int b2_device_count(void);
+/* cudaDeviceEnablePeerAccess for every ordered GPU pair of this process; returns the number of enabled pairs. */
+int b2_enable_peer_access_all(void);
+/* Publish arena of one rank (cudaMalloc + zero fill) and its CUDA-IPC export / import. */
+void* b2_arena_alloc(int64_t bytes);
+int b2_arena_free(void* p);
+int b2_ipc_export(void* base, char* out_handle64);
+void* b2_ipc_open(const char* handle64);
+int b2_ipc_close(void* p);
+
+/* ------------------------------------------------------------------------------------------------ aggregation */
+/* A1 FedAvg K-way pull-reduce: out = (accumulate ? out : 0) + sum_k weights[k] * srcs[k].  `srcs`/`weights` are HOST
+ * arrays of K <= 64 entries.  Reference math: p2pfl/learning/aggregators/fedavg.py:61-69 (NumPy, per layer). */
+int b2_fedavg(float* out, const void* const* srcs, const float* weights, int K, int64_t n, int accumulate, void* stream);
+/* A3 streaming accumulate: acc = beta*acc + w*src (the partial-model transfer fused with the accumulation).
+ * Reference: aggregator.add_model + fedavg.py:61-69. */
+int b2_accumulate(float* acc, const float* src, float w, float beta, int64_t n, void* stream);
+/* A4 model pull copy: dst = src (InitModel / FullModel diffusion).  Reference: full_model_command.py:72 + the
+ * pickle / deepcopy / load_state_dict chain (lightning_model.py:69-98, p2pfl_model.py:81-101,185). */
+int b2_pull_copy(float* dst, const float* src, int64_t n, void* stream);
+/* A5 coordinate-wise median (trim < 0; even K -> mean of the two middle values) or trimmed mean (drop the `trim`
+ * smallest and largest).  Reference: intended math of the FedMedian stub, fedmedian.py:55-65. */
+int b2_median(float* out, const void* const* srcs, int K, int trim, int64_t n, void* stream);
+/* A8 Scaffold server update: x += sum_k wy[k]*dy[k];  c += wc * sum_k dc[k].  Reference: scaffold.py:70-111. */
+int b2_scaffold_server(float* x, float* c, const void* const* dys, const void* const* dcs, const float* wy, float wc, int K, int64_t n, void* stream);
+/* T7 Scaffold client finalize: adj=(x-y)*inv_klr; dc=adj; c_i+=adj; dy=y-x.  Reference: scaffold_callback.py:124-140. */
+int b2_scaffold_finalize(float* c_i, float* dy, float* dc, const float* x, const float* y, float inv_klr, int64_t n, void* stream);
+
+/* A6 Krum Gram matrix on tcgen05: gram[i*ld+j] = <src_i - src_0, src_j - src_0>, i,j < K <= 64, ld = 64, fp32 via
+ * 3xTF32 split.  Split-K over coordinate chunks: every CTA keeps its partial Gram in TMEM, spills it to
+ * `workspace` and the last CTA to finish reduces the partials in a fixed order (deterministic).
+ * `workspace` must hold b2_krum_gram_workspace_bytes() bytes and its first 4 bytes must be zero before the first
+ * call (the kernel re-zeroes them).  No reference counterpart (Krum is absent from p2pfl). */
+int64_t b2_krum_gram_workspace_bytes(void);
+int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* workspace, int passes, void* stream);
+/* A7 Krum scores + ranking from a K x K squared-distance matrix: scores[i] = sum of the K-f-2 smallest d(i,j), j != i;
+ * order[] = indices sorted by (score, index). */
+int b2_krum_select(const float* dist, int K, int f, float* scores, int* order, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ local training */
+/* T6 fused Adam over a flat slab; g' = g + wd*p + prox_mu*(p - prox_ref) + cv_scale*(cv_global - cv_local); clears g.
+ * Reference: torch.optim.Adam (lightning_model.py:181-183), Scaffold term scaffold_callback.py:90-110. */
+int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
+                 float bias_corr2, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad,
+                 void* stream);
+int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momentum, float weight_decay, float prox_mu, const float* prox_ref,
+                const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream);
+/* T3+T8 fused log-softmax + NLL (+ gradient, + argmax accuracy).  loss_out/correct are accumulated atomically.
+ * Reference: F.cross_entropy(log_softmax(x)) lightning_model.py:178,189 and torchmetrics Accuracy :204. */
+int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out, float* dlogits, float* correct, int B, int C, float scale, void* stream);
+
+/* T1/T2 bf16 GEMM on tcgen05 + TMA: D[M,N] = epilogue(A[M,K] * B[N,K]^T).  See csrc/gemm.cu for the epilogue flags.
+ * Reference: the three nn.Linear GEMMs of the MLP and their autograd backward (lightning_model.py:169-179). */
+typedef struct {
+  const void* A;      /* bf16 [M, lda]  K-major */
+  const void* B;      /* bf16 [N, ldb]  K-major */
+  int M, N, K;        /* K multiple of 64; lda/ldb in elements, multiples of 8 */
+  int lda, ldb;
+  float* out_f32;     /* optional fp32 [M, ldo] */
+  void* out_bf16;     /* optional bf16 [M, ldo16] */
+  void* out_bf16_t;   /* optional bf16 transposed [N, ldt] (activation kept K-major for the next wgrad) */
+  int ldo, ldo16, ldt;
+  const float* bias;  /* optional per-N bias (added before the activation) */
+  const void* mask;   /* optional bf16 [M, ldm]: out *= (mask > 0)  (ReLU backward) */
+  int ldm;
+  float* colsum;      /* optional fp32 [N]: += column sums of the output (bias gradient), atomic */
+  int relu;           /* apply ReLU */
+  int accumulate;     /* out_f32 += result instead of = */
+} b2_gemm_args;
+int b2_gemm_bf16(const b2_gemm_args* args, void* stream);
+/* fp32 [R,C] (pitch lds) -> bf16 row-major copy (pitch ldd, optional), bf16 transposed copy [C,R] (pitch ldt, optional),
+ * column sums += (optional, atomic).  Staging step of the GEMMs above; the reference has no counterpart (it trains in fp32
+ * through torch autograd). */
+int b2_cast_transpose(const float* src, int R, int C, int lds, void* dst_bf16, int ldd, void* dst_bf16_t, int ldt, float* colsum, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MYFYP_B200_H */

@@ -1,0 +1,271 @@
+// A6 + A7: Krum.  Not in the reference; oracle = fp64 direct pairwise distances.
+//
+// A6  Gram matrix of the centred models on the 5th-gen tensor cores.
+//       G[i][j] = sum_c (theta_i[c]-theta_0[c]) * (theta_j[c]-theta_0[c]),   d_ij = G_ii + G_jj - 2 G_ij
+//     The K models are K separately allocated slabs (local HBM or peer GPUs), so the operand tile is assembled by
+//     the producer warps: 128-bit loads (the loads are the NVLink transfer), subtract the reference model, split
+//     into tf32 hi / lo parts, store into the canonical SWIZZLE_128B K-major layout.  One tile serves as BOTH MMA
+//     operands (A = B).  One elected thread issues tcgen05.mma kind::tf32 (M=128, N=Kpad, K=8); 3 MMAs per k-step
+//     (hi*hi + hi*lo + lo*hi) give fp32-class accuracy.  The accumulator lives in TMEM across ALL coordinate
+//     chunks of the CTA (split-K over coordinates across CTAs), is read once with tcgen05.ld, spilled to the
+//     workspace, and the last CTA to finish reduces the partial Grams in a fixed order.
+//     smem tile per stage: 64 rows x 128 coords fp32 (4 swizzle atoms) for hi and for lo = 64 KB; 3 stages.
+//     The MMA reads 128 A-rows: rows 64..127 alias the following atom - they only produce accumulator rows
+//     64..127, which nobody reads.
+// A7  scores + ranking in one tiny CTA.
+#include "../../include/myfyp_b200.h"
+#include "common.cuh"
+#include "tcgen05.cuh"
+
+namespace b2 {
+
+constexpr int GR_ROWS = 64;                         // max models
+constexpr int GR_CC = 128;                          // coordinates per stage
+constexpr int GR_ATOMS = GR_CC / 32;                // 32 fp32 = 128 B per swizzle row
+constexpr int GR_ATOM_BYTES = GR_ROWS * 128;        // 8 KB
+constexpr int GR_TILE_BYTES = GR_ATOMS * GR_ATOM_BYTES;  // 32 KB (hi) ; lo follows
+constexpr int GR_STAGE_BYTES = 2 * GR_TILE_BYTES;   // 64 KB
+constexpr int GR_STAGES = 3;
+constexpr int GR_PRODUCERS = 256;
+constexpr int GR_THREADS = GR_PRODUCERS + 32;       // + the MMA / TMEM warp
+constexpr int GR_SMEM = GR_STAGES * GR_STAGE_BYTES + GR_ATOM_BYTES /*over-read pad*/ + 1024 /*align*/;
+constexpr int GR_MAX_CTAS = 296;
+constexpr int GR_HEADER = 256;
+
+__global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restrict__ gram, const __grid_constant__ PtrTable srcs, int K, int64_t n, int passes,
+                                                                   unsigned int* __restrict__ counter, float* __restrict__ partials) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[GR_STAGES], empty_bar[GR_STAGES], done_bar;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ int is_last_s;
+
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kpad = (K + 15) & ~15;  // MMA N (multiple of 16 for M=128)
+
+  if (tid == 0) {
+    for (int s = 0; s < GR_STAGES; ++s) {
+      tc::mbar_init(&full_bar[s], GR_PRODUCERS);
+      tc::mbar_init(&empty_bar[s], 1);
+    }
+    tc::mbar_init(&done_bar, 1);
+    tc::mbar_fence_init();
+  }
+  if (warp == 8) tc::tmem_alloc<64>(&tmem_base_s);
+  // rows K..63 are never written by the producers: zero the whole tile area once
+  for (int i = tid; i < (GR_STAGES * GR_STAGE_BYTES + GR_ATOM_BYTES) / 16; i += GR_THREADS) reinterpret_cast<float4*>(tiles)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  tc::fence_proxy_async();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int64_t n_chunks = (n + GR_CC - 1) / GR_CC;
+  const int64_t my_chunks = (n_chunks > blockIdx.x) ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  if (warp < 8) {
+    // ================================ producers: pull, centre, split, swizzle-store
+    const int items = K * (GR_CC / 4);  // float4 items per stage
+    const float* ref = srcs.p[0];
+    for (int64_t it = 0; it < my_chunks; ++it) {
+      const int s = (int)(it % GR_STAGES);
+      const uint32_t ph = (uint32_t)((it / GR_STAGES) & 1);
+      tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+      const int64_t c0 = (blockIdx.x + it * gridDim.x) * (int64_t)GR_CC;
+      uint8_t* hi_tile = tiles + s * GR_STAGE_BYTES;
+      uint8_t* lo_tile = hi_tile + GR_TILE_BYTES;
+      for (int q0 = 0; q0 < items; q0 += 4 * GR_PRODUCERS) {
+        float4 v[4], r[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int q = q0 + u * GR_PRODUCERS + tid;
+          const int row = q >> 5, j = q & 31;
+          const int64_t c = c0 + 4 * j;
+          v[u] = r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (q < items && c < n) {  // n % 4 == 0 is enforced by the host wrapper
+            v[u] = ld_stream(reinterpret_cast<const float4*>(srcs.p[row] + c));
+            r[u] = __ldg(reinterpret_cast<const float4*>(ref + c));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int q = q0 + u * GR_PRODUCERS + tid;
+          if (q < items) {
+            const int row = q >> 5, j = q & 31;
+            const float d[4] = {v[u].x - r[u].x, v[u].y - r[u].y, v[u].z - r[u].z, v[u].w - r[u].w};
+            float4 h, l;
+            float* hp = &h.x;
+            float* lp = &l.x;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              hp[e] = __uint_as_float(__float_as_uint(d[e]) & 0xffffe000u);  // tf32 keeps 10 mantissa bits
+              lp[e] = d[e] - hp[e];
+            }
+            const uint32_t off = (uint32_t)(j >> 3) * GR_ATOM_BYTES + tc::sw128_offset((uint32_t)row, (uint32_t)(j & 7));
+            *reinterpret_cast<float4*>(hi_tile + off) = h;
+            *reinterpret_cast<float4*>(lo_tile + off) = l;
+          }
+        }
+      }
+      tc::fence_proxy_async();
+      tc::mbar_arrive(&full_bar[s]);
+    }
+  } else if (tc::elect_one()) {
+    // ================================ MMA issuer (one thread)
+    const uint32_t idesc = tc::make_idesc(tc::FMT_TF32, 128, (uint32_t)kpad);
+    uint32_t accumulate = 0;
+    for (int64_t it = 0; it < my_chunks; ++it) {
+      const int s = (int)(it % GR_STAGES);
+      const uint32_t ph = (uint32_t)((it / GR_STAGES) & 1);
+      tc::mbar_wait(&full_bar[s], ph);
+      tc::fence_after_sync();
+      const uint32_t hi_addr = tc::smem_u32(tiles + s * GR_STAGE_BYTES);
+      const uint32_t lo_addr = hi_addr + GR_TILE_BYTES;
+#pragma unroll
+      for (int a = 0; a < GR_ATOMS; ++a) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {  // 8 tf32 = 32 bytes per k-step inside the 128-byte swizzle row
+          const uint32_t o = (uint32_t)a * GR_ATOM_BYTES + (uint32_t)ks * 32u;
+          const uint64_t dh = tc::smem_desc_sw128(hi_addr + o), dl = tc::smem_desc_sw128(lo_addr + o);
+          tc::mma_tf32(tmem_base, dh, dh, idesc, accumulate);
+          accumulate = 1;
+          if (passes >= 3) {
+            tc::mma_tf32(tmem_base, dh, dl, idesc, 1);
+            tc::mma_tf32(tmem_base, dl, dh, idesc, 1);
+          }
+        }
+      }
+      tc::mma_commit(&empty_bar[s]);  // stage reusable once these MMAs have read it
+    }
+    tc::mma_commit(&done_bar);
+  }
+
+  // ================================ epilogue: TMEM -> workspace partial (rows < 64 live in warps 0,1)
+  __syncwarp();
+  float* mine = partials + (size_t)blockIdx.x * (GR_ROWS * GR_ROWS);
+  if (warp < 2) {
+    tc::mbar_wait(&done_bar, 0);
+    tc::fence_after_sync();
+    const int row = warp * 32 + (tid & 31);
+#pragma unroll
+    for (int cb = 0; cb < 2; ++cb) {
+      float v[32];
+      if (my_chunks > 0 && cb * 32 < kpad) {
+        tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = 0.f;
+      }
+#pragma unroll
+      for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(mine + row * GR_ROWS + cb * 32 + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+    }
+    tc::fence_before_sync();
+  }
+  __threadfence();
+  __syncthreads();
+  if (warp == 8) tc::tmem_dealloc<64>(tmem_base);
+  if (tid == 0) {
+    const unsigned int prev = atomicAdd(counter, 1u);
+    is_last_s = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last_s) {
+    __threadfence();
+    for (int o = tid; o < GR_ROWS * GR_ROWS; o += GR_THREADS) {
+      float acc = 0.f;
+      for (unsigned int b = 0; b < gridDim.x; ++b) acc += __ldcg(partials + (size_t)b * (GR_ROWS * GR_ROWS) + o);
+      const int i = o / GR_ROWS, j = o % GR_ROWS;
+      gram[o] = (i < K && j < K) ? acc : 0.f;
+    }
+    if (tid == 0) *counter = 0u;  // ready for the next call
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ A7
+__global__ void __launch_bounds__(64) krum_select_kernel(const float* __restrict__ dist, int K, int f, float* __restrict__ scores, int* __restrict__ order) {
+  __shared__ float s_score[B2_MAX_K];
+  const int i = threadIdx.x;
+  if (i < K) {
+    float d[B2_MAX_K];
+    int m = 0;
+    for (int j = 0; j < K; ++j) {
+      if (j == i) continue;
+      float x = dist[i * K + j];
+      int p = m++;
+      while (p > 0 && d[p - 1] > x) { d[p] = d[p - 1]; --p; }  // insertion sort (K <= 64)
+      d[p] = x;
+    }
+    int closest = K - f - 2;
+    if (closest < 1) closest = 1;
+    if (closest > m) closest = m;
+    float sc = 0.f;
+    for (int j = 0; j < closest; ++j) sc += d[j];
+    s_score[i] = sc;
+    scores[i] = sc;
+  }
+  __syncthreads();
+  if (i < K) {
+    const float me = s_score[i];
+    int rank = 0;
+    for (int j = 0; j < K; ++j) rank += (s_score[j] < me || (s_score[j] == me && j < i)) ? 1 : 0;
+    order[rank] = i;
+  }
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" {
+
+int64_t b2_krum_gram_workspace_bytes(void) { return GR_HEADER + (int64_t)GR_MAX_CTAS * GR_ROWS * GR_ROWS * (int64_t)sizeof(float); }
+
+int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* workspace, int passes, void* stream) {
+  if (K < 1 || K > GR_ROWS) {
+    set_error("krum_gram: K=%d outside [1,%d]", K, GR_ROWS);
+    return 1;
+  }
+  if (n <= 0 || (n & 3)) {
+    set_error("krum_gram: n=%lld must be a positive multiple of 4", (long long)n);
+    return 1;
+  }
+  if (workspace == nullptr) {
+    set_error("krum_gram: workspace is NULL");
+    return 1;
+  }
+  PtrTable pt;
+  for (int k = 0; k < B2_MAX_K; ++k) pt.p[k] = static_cast<const float*>(srcs[k < K ? k : 0]);
+  for (int k = 0; k < K; ++k)
+    if (!aligned16(srcs[k])) {
+      set_error("krum_gram: slab %d is not 16-byte aligned", k);
+      return 1;
+    }
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+    attr_set[dev] = true;
+  }
+  const int64_t chunks = (n + GR_CC - 1) / GR_CC;
+  int grid = sm_count();
+  if (grid > GR_MAX_CTAS) grid = GR_MAX_CTAS;
+  if (chunks < grid) grid = (int)chunks;
+  unsigned int* counter = static_cast<unsigned int*>(workspace);
+  float* partials = reinterpret_cast<float*>(static_cast<char*>(workspace) + GR_HEADER);
+  krum_gram_kernel<<<grid, GR_THREADS, GR_SMEM, static_cast<cudaStream_t>(stream)>>>(gram, pt, K, n, passes, counter, partials);
+  B2_LAUNCH_CHECK("krum_gram_kernel");
+  return 0;
+}
+
+int b2_krum_select(const float* dist, int K, int f, float* scores, int* order, void* stream) {
+  if (K < 1 || K > B2_MAX_K) {
+    set_error("krum_select: K=%d outside [1,%d]", K, B2_MAX_K);
+    return 1;
+  }
+  krum_select_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(dist, K, f, scores, order);
+  B2_LAUNCH_CHECK("krum_select_kernel");
+  return 0;
+}
+
+}  // extern "C"

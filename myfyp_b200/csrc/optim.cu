@@ -1,0 +1,106 @@
+// T6: fused multi-tensor optimizers over the flat slab (Adam, SGD+momentum) with the FedProx proximal term and
+// the Scaffold control-variate term folded into the gradient, and the gradient slab cleared on the way out.
+//   g' = g + wd*p + mu*(p - p_ref) + cv_scale*(c - c_i)
+// Reference path: torch.optim.Adam(lr=1e-3) per Lightning fit (lightning_model.py:181-183) plus a Python
+// callback for Scaffold (scaffold_callback.py:90-110); FedProx does not exist there.
+#include "../../include/myfyp_b200.h"
+#include "common.cuh"
+
+namespace b2 {
+
+struct FusedTerms {
+  const float4* prox_ref;
+  const float4* cv_global;
+  const float4* cv_local;
+  float prox_mu, cv_scale, wd;
+};
+
+__device__ __forceinline__ float4 effective_grad(const float4 g, const float4 p, const FusedTerms& t, int64_t i) {
+  float4 r = g;
+  if (t.wd != 0.f) { r.x = fmaf(t.wd, p.x, r.x); r.y = fmaf(t.wd, p.y, r.y); r.z = fmaf(t.wd, p.z, r.z); r.w = fmaf(t.wd, p.w, r.w); }
+  if (t.prox_ref != nullptr) {
+    const float4 q = t.prox_ref[i];
+    r.x = fmaf(t.prox_mu, p.x - q.x, r.x); r.y = fmaf(t.prox_mu, p.y - q.y, r.y); r.z = fmaf(t.prox_mu, p.z - q.z, r.z); r.w = fmaf(t.prox_mu, p.w - q.w, r.w);
+  }
+  if (t.cv_global != nullptr) {
+    const float4 c = t.cv_global[i], ci = t.cv_local[i];
+    r.x = fmaf(t.cv_scale, c.x - ci.x, r.x); r.y = fmaf(t.cv_scale, c.y - ci.y, r.y); r.z = fmaf(t.cv_scale, c.z - ci.z, r.z); r.w = fmaf(t.cv_scale, c.w - ci.w, r.w);
+  }
+  return r;
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4, float lr,
+                                                   float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, FusedTerms t, int zero_grad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 pv = p[i], mv = m[i], vv = v[i];
+    const float4 gv = effective_grad(g[i], pv, t, i);
+#define B2_ADAM1(c)                                                       \
+  mv.c = fmaf(b1, mv.c, (1.f - b1) * gv.c);                               \
+  vv.c = fmaf(b2, vv.c, (1.f - b2) * gv.c * gv.c);                        \
+  pv.c -= lr * (mv.c * inv_bc1) / (sqrtf(vv.c) * inv_sqrt_bc2 + eps);
+    B2_ADAM1(x) B2_ADAM1(y) B2_ADAM1(z) B2_ADAM1(w)
+#undef B2_ADAM1
+    p[i] = pv; m[i] = mv; v[i] = vv;
+    if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ buf, int64_t n4, float lr, float momentum,
+                                                  FusedTerms t, int zero_grad) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 pv = p[i];
+    float4 gv = effective_grad(g[i], pv, t, i);
+    if (momentum != 0.f) {
+      float4 b = buf[i];
+      b.x = fmaf(momentum, b.x, gv.x); b.y = fmaf(momentum, b.y, gv.y); b.z = fmaf(momentum, b.z, gv.z); b.w = fmaf(momentum, b.w, gv.w);
+      buf[i] = b;
+      gv = b;
+    }
+    pv.x -= lr * gv.x; pv.y -= lr * gv.y; pv.z -= lr * gv.z; pv.w -= lr * gv.w;
+    p[i] = pv;
+    if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+static int check_slab(const void* a, const void* b, const void* c, const void* d, int64_t n) {
+  if ((n & 3) || !aligned16(a) || !aligned16(b) || (c && !aligned16(c)) || (d && !aligned16(d))) {
+    set_error("optimizer slabs must be 16-byte aligned with n %% 4 == 0 (the slab layout pads to 64 elements)");
+    return 1;
+  }
+  return 0;
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" {
+
+int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
+                 float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream) {
+  if (n <= 0) return 0;
+  if (check_slab(p, g, m, v, n) || check_slab(p, p, prox_ref, cv_global, n) || check_slab(p, p, cv_local, nullptr, n)) return 1;
+  FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
+               reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
+  adam_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
+                                                                                      reinterpret_cast<float4*>(v), n / 4, lr, beta1, beta2, eps, 1.f / bias_corr1,
+                                                                                      rsqrtf(bias_corr2), t, zero_grad);
+  B2_LAUNCH_CHECK("adam_kernel");
+  return 0;
+}
+
+int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momentum, float weight_decay, float prox_mu, const float* prox_ref, const float* cv_global,
+                const float* cv_local, float cv_scale, int zero_grad, void* stream) {
+  if (n <= 0) return 0;
+  if (check_slab(p, g, buf, prox_ref, n) || check_slab(p, p, cv_global, cv_local, n)) return 1;
+  FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
+               reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
+  sgd_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(buf),
+                                                                                     n / 4, lr, momentum, t, zero_grad);
+  B2_LAUNCH_CHECK("sgd_kernel");
+  return 0;
+}
+
+}  // extern "C"

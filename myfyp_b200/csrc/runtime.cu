@@ -1,0 +1,114 @@
+// Library runtime: error string, device queries, peer access, IPC arenas (the native side of the fabric).
+#include <cstdarg>
+#include <mutex>
+
+#include "../../include/myfyp_b200.h"
+#include "common.cuh"
+
+namespace b2 {
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+  return (int)e ? (int)e : -1;
+}
+
+int sm_count() {
+  static int cache[64];
+  static bool have[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return B2_SMS_FALLBACK;
+  if (!have[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = B2_SMS_FALLBACK;
+    cache[dev] = n;
+    have[dev] = true;
+  }
+  return cache[dev];
+}
+}  // namespace b2
+
+extern "C" {
+
+const char* b2_last_error(void) { return b2::g_err; }
+
+int b2_version(void) { return 100; }
+
+int b2_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int b2_enable_peer_access_all(void) {
+  int n = b2_device_count(), ok = 0, cur = 0;
+  if (n < 2) return 0;
+  cudaGetDevice(&cur);
+  for (int i = 0; i < n; ++i) {
+    cudaSetDevice(i);
+    for (int j = 0; j < n; ++j) {
+      if (i == j) continue;
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, i, j);
+      if (!can) continue;
+      cudaError_t e = cudaDeviceEnablePeerAccess(j, 0);
+      if (e == cudaSuccess || e == cudaErrorPeerAccessAlreadyEnabled) ++ok;
+      cudaGetLastError();
+    }
+  }
+  cudaSetDevice(cur);
+  return ok;
+}
+
+void* b2_arena_alloc(int64_t bytes) {
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, (size_t)bytes);
+  if (e != cudaSuccess) {
+    b2::cuda_fail(e, "cudaMalloc(arena)");
+    return nullptr;
+  }
+  cudaMemset(p, 0, (size_t)bytes);
+  return p;
+}
+
+int b2_arena_free(void* p) {
+  B2_CUDA(cudaFree(p));
+  return 0;
+}
+
+int b2_ipc_export(void* base, char* out_handle64) {
+  cudaIpcMemHandle_t h;
+  B2_CUDA(cudaIpcGetMemHandle(&h, base));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(out_handle64, &h, sizeof(h));
+  return 0;
+}
+
+void* b2_ipc_open(const char* handle64) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) {
+    b2::cuda_fail(e, "cudaIpcOpenMemHandle");
+    return nullptr;
+  }
+  return p;
+}
+
+int b2_ipc_close(void* p) {
+  B2_CUDA(cudaIpcCloseMemHandle(p));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,68 @@
+// T3 + T8: fused log-softmax + NLL loss, its gradient, and the argmax-accuracy count - one kernel, one warp per
+// row (C is small: 10 for MNIST/CIFAR).  Reference path: F.cross_entropy on log_softmax output
+// (lightning_model.py:178,189) + torchmetrics Accuracy (:204) = several kernels and a softmax round trip.
+//   loss_out   += scale * sum_rows ( logsumexp(row) - row[label] )        (atomic, one add per CTA)
+//   dlogits[r] = scale * (softmax(row) - onehot(label))                   (optional)
+//   correct    += #rows with argmax == label                              (optional; first max wins, like torch)
+#include "../../include/myfyp_b200.h"
+#include "common.cuh"
+
+namespace b2 {
+
+__global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_out,
+                                                   float* __restrict__ dlogits, float* __restrict__ correct, int B, int C, float scale) {
+  __shared__ float s_loss[8], s_corr[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float wl = 0.f, wc = 0.f;
+  for (int row = blockIdx.x * 8 + warp; row < B; row += gridDim.x * 8) {
+    const float* x = logits + (int64_t)row * C;
+    const int lab = (int)labels[row];
+    float mx = -INFINITY;
+    int amax = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) {
+      const float v = x[c];
+      if (v > mx) { mx = v; amax = c; }
+    }
+    // warp arg-max (lowest index among equal maxima)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, amax, o);
+      if (om > mx || (om == mx && oa < amax)) { mx = om; amax = oa; }
+    }
+    float se = 0.f;
+    for (int c = lane; c < C; c += 32) se += __expf(x[c] - mx);
+    se = warp_sum(se);
+    const float lse = mx + __logf(se);
+    if (dlogits != nullptr) {
+      const float inv = scale / se;
+      float* d = dlogits + (int64_t)row * C;
+      for (int c = lane; c < C; c += 32) d[c] = __expf(x[c] - mx) * inv - (c == lab ? scale : 0.f);
+    }
+    if (lane == 0) {
+      wl += lse - x[lab];
+      wc += (amax == lab) ? 1.f : 0.f;
+    }
+  }
+  if (lane == 0) { s_loss[warp] = wl; s_corr[warp] = wc; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tl = 0.f, tc = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { tl += s_loss[w]; tc += s_corr[w]; }
+    if (tl != 0.f) atomicAdd(loss_out, tl * scale);
+    if (correct != nullptr && tc != 0.f) atomicAdd(correct, tc);
+  }
+}
+
+}  // namespace b2
+
+extern "C" int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out, float* dlogits, float* correct, int B, int C, float scale, void* stream) {
+  if (B <= 0 || C <= 0) return 0;
+  int grid = (B + 7) / 8;
+  const int cap = b2::sm_count() * 8;
+  if (grid > cap) grid = cap;
+  b2::xent_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, labels, loss_out, dlogits, correct, B, C, scale);
+  B2_LAUNCH_CHECK("xent_kernel");
+  return 0;
+}

@@ -208,6 +208,10 @@ class TorchP2PFLModel(P2PFLModel):
             self.model.to(device)
             self._int_entries = []
             self._adopt_module(self.model)
+            if getattr(self.model, "native", None) is not None or (device.type == "cuda" and getattr(self.model, "wants_native", False)):
+                from myfyp_b200.models.native_mlp import attach_native_mlp
+
+                attach_native_mlp(self)
         else:
             self.slab = self.slab.to(device)
         return self

@@ -43,12 +43,19 @@ class TorchLearner(Learner):
         persist_optimizer: bool = False,
         shuffle: bool = True,
         max_steps_per_epoch: Optional[int] = None,
+        data_on_host: bool = False,
     ) -> None:
         super().__init__(model, data, self_addr, aggregator)
         self.batch_size, self.lr, self.optimizer = batch_size, lr, optimizer
         self.momentum, self.weight_decay = momentum, weight_decay
         self.persist_optimizer, self.shuffle = persist_optimizer, shuffle
         self.max_steps_per_epoch = max_steps_per_epoch
+        # data_on_host: the partition stays in pinned host memory and is copied to the GPU at every fit /
+        # evaluate (the end-to-end mode of bench.py); default is device-resident data
+        self.data_on_host = data_on_host
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.pre_fit_hook = None
         self._interrupt = False
         self._opt_state: Dict[str, Any] = {}
         self._data_cache: Dict[Any, Any] = {}
@@ -59,10 +66,17 @@ class TorchLearner(Learner):
 
     # ------------------------------------------------------------------ data
     def _tensors(self, train: bool):
-        key = (id(self.data), train, str(self.model.device))
+        dev = self.model.device
+        host = self.data_on_host and dev.type == "cuda"
+        key = (id(self.data), train, "host" if host else str(dev))
         if key not in self._data_cache:
-            self._data_cache[key] = self.data.export(TensorExportStrategy, train=train, device=self.model.device)
-        return self._data_cache[key]
+            x, y = self.data.export(TensorExportStrategy, train=train, device="cpu" if host else dev)
+            self._data_cache[key] = (x.pin_memory(), y.pin_memory()) if host else (x, y)
+        x, y = self._data_cache[key]
+        if host:  # this call's inputs travel host -> device now
+            self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+            x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+        return x, y
 
     def set_data(self, data) -> None:
         super().set_data(data)
@@ -90,6 +104,8 @@ class TorchLearner(Learner):
         model: TorchP2PFLModel = self.model  # type: ignore[assignment]
         module = model.get_model()
         self._interrupt = False
+        if self.pre_fit_hook is not None:
+            self.pre_fit_hook()
         x, y = self._tensors(train=True)
         n = x.shape[0]
         st = self._state(model.layout.n_trainable, model.device)
@@ -127,6 +143,7 @@ class TorchLearner(Learner):
         for cb in self.callbacks:
             cb.on_fit_end(self, steps, self.lr)
         if steps:
+            self.d2h_bytes += 4 * steps
             for i, v in enumerate(losses[:steps].tolist()):  # one D2H copy per fit
                 logger.log_metric(self._self_addr, "train_loss", v, step=self._global_step + i)
             self._global_step += steps
@@ -159,6 +176,7 @@ class TorchLearner(Learner):
                 ops.cross_entropy_eval(module(xb), yb, acc)
         module.train()
         tot = acc.tolist()
+        self.d2h_bytes += 8
         results = {"test_loss": tot[0] / x.shape[0], "test_metric": tot[1] / x.shape[0]}
         for k, v in results.items():
             logger.log_metric(self._self_addr, k, v)

@@ -41,6 +41,7 @@ def mlp_model(device: Optional[str] = None, seed: Optional[int] = None, native: 
     module = MLP(**kwargs)
     model = TorchP2PFLModel(module, device=device)
     if native is None:
+        module.wants_native = True  # attach the tcgen05 path whenever the model lands on a GPU (Node places it)
         native = model.device.type == "cuda"
     if native:
         from myfyp_b200.models.native_mlp import attach_native_mlp

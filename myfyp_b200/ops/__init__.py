@@ -122,7 +122,7 @@ def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Op
 
 
 # ====================================================================== A6/A7: Krum
-def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None) -> torch.Tensor:
+def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None, passes: int = 3) -> torch.Tensor:
     """K x K matrix of squared L2 distances.  CUDA: centred Gram matrix on tcgen05 (A6) + d = Gii+Gjj-2Gij."""
     device = device or pick_device(slabs)
     slabs = _same_place(slabs, device)
@@ -131,9 +131,10 @@ def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device
         if k > MAX_K:
             raise ValueError(f"krum over {k} models: at most {MAX_K}")
         lib = native.load()
-        gram = torch.zeros(MAX_K * MAX_K, dtype=torch.float32, device=device)
+        gram = torch.empty(MAX_K * MAX_K, dtype=torch.float32, device=device)
+        ws = _krum_workspace(device)
         with native.device_guard(device):
-            native.check(lib.b2_krum_gram(native.ptr(gram), native.ptr_array(slabs), k, ctypes.c_int64(n), native.stream_ptr(device)), "b2_krum_gram")
+            native.check(lib.b2_krum_gram(native.ptr(gram), native.ptr_array(slabs), k, ctypes.c_int64(n), native.ptr(ws), ctypes.c_int(passes), native.stream_ptr(device)), "b2_krum_gram")
         native.count_launch()
         g = gram.view(MAX_K, MAX_K)[:k, :k].double()
         d = torch.diagonal(g)
@@ -143,6 +144,19 @@ def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device
     g = m @ m.T
     d = torch.diagonal(g)
     return (d[:, None] + d[None, :] - 2 * g).clamp_min(0).float()
+
+
+_krum_ws = {}
+
+
+def _krum_workspace(device: torch.device) -> torch.Tensor:
+    """Split-K partial Grams + completion counter; zeroed once, the kernel leaves the counter at zero."""
+    key = str(device)
+    if key not in _krum_ws:
+        lib = native.load()
+        lib.b2_krum_gram_workspace_bytes.restype = ctypes.c_int64
+        _krum_ws[key] = torch.zeros(int(lib.b2_krum_gram_workspace_bytes()) // 4, dtype=torch.float32, device=device)
+    return _krum_ws[key]
 
 
 def krum_select(dist: torch.Tensor, f: int, m: int) -> Tuple[List[float], List[int]]:
@@ -312,3 +326,53 @@ def cross_entropy_eval(logits: torch.Tensor, labels: torch.Tensor, acc: torch.Te
     else:
         acc[0] += torch.nn.functional.cross_entropy(logits.float(), labels, reduction="sum")
         acc[1] += (logits.argmax(dim=1) == labels).sum()
+
+
+# ====================================================================== T1/T2: tcgen05 GEMM + staging
+class _GemmArgs(ctypes.Structure):
+    _fields_ = [
+        ("A", ctypes.c_void_p), ("B", ctypes.c_void_p), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int), ("lda", ctypes.c_int), ("ldb", ctypes.c_int),
+        ("out_f32", ctypes.c_void_p), ("out_bf16", ctypes.c_void_p), ("out_bf16_t", ctypes.c_void_p), ("ldo", ctypes.c_int), ("ldo16", ctypes.c_int), ("ldt", ctypes.c_int),
+        ("bias", ctypes.c_void_p), ("mask", ctypes.c_void_p), ("ldm", ctypes.c_int), ("colsum", ctypes.c_void_p), ("relu", ctypes.c_int), ("accumulate", ctypes.c_int),
+    ]
+
+
+def gemm_bf16(
+    a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
+    out_bf16_t: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
+    relu: bool = False, accumulate: bool = False,
+) -> None:
+    """``D[m,n] = epilogue(A[m,k] @ B[n,k]^T)`` on tcgen05 tensor cores (bf16 in, fp32 accumulate); see csrc/gemm.cu.
+
+    ``a``/``b`` are 2-D bf16 tensors whose row pitch (``stride(0)``) is the leading dimension; the logical sizes
+    ``m, n, k`` may be smaller than the allocations (TMA zero-fills the tails).
+    """
+    if not a.is_cuda:
+        raise RuntimeError("gemm_bf16 is the tcgen05 path; on CPU use torch.matmul")
+
+    def ld(t: Optional[torch.Tensor]) -> int:
+        return 0 if t is None else int(t.stride(0))
+
+    args = _GemmArgs(
+        a.data_ptr(), b.data_ptr(), m, n, k, ld(a), ld(b), 0 if out_f32 is None else out_f32.data_ptr(), 0 if out_bf16 is None else out_bf16.data_ptr(),
+        0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld(out_f32), ld(out_bf16), ld(out_bf16_t), 0 if bias is None else bias.data_ptr(),
+        0 if mask is None else mask.data_ptr(), ld(mask), 0 if colsum is None else colsum.data_ptr(), int(relu), int(accumulate),
+    )
+    lib = native.load()
+    with native.device_guard(a.device):
+        native.check(lib.b2_gemm_bf16(ctypes.byref(args), native.stream_ptr(a.device)), "b2_gemm_bf16")
+    native.count_launch()
+
+
+def cast_transpose(src: torch.Tensor, rows: int, cols: int, dst: Optional[torch.Tensor] = None, dst_t: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None) -> None:
+    """fp32 ``src[rows, cols]`` -> bf16 copy ``dst`` and/or transposed bf16 copy ``dst_t`` (+ column sums), one pass."""
+    lib = native.load()
+    with native.device_guard(src.device):
+        native.check(
+            lib.b2_cast_transpose(
+                native.ptr(src), rows, cols, int(src.stride(0)), native.ptr(dst), 0 if dst is None else int(dst.stride(0)), native.ptr(dst_t),
+                0 if dst_t is None else int(dst_t.stride(0)), native.ptr(colsum), native.stream_ptr(src.device),
+            ),
+            "b2_cast_transpose",
+        )
+    native.count_launch()

@@ -1,0 +1,322 @@
+"""Numerics of every hand-written kernel against a plain PyTorch fp32 (or fp64) reference of the same op."""
+
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from myfyp_b200.ops import native
+
+    native.load()  # fail loudly if the library is missing on a GPU box
+    return torch.device("cuda", 0)
+
+
+def _slabs(k, n, dev, seed=0, scale=1.0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return [(torch.randn(n, generator=g) * scale).to(dev) for _ in range(k)]
+
+
+@pytest.mark.parametrize("k,n", [(1, 64), (2, 4096), (5, 235264), (8, 1 << 20), (64, 65536), (70, 8192), (3, 1027)])
+def test_fedavg(dev, k, n):
+    from myfyp_b200 import ops
+
+    slabs = _slabs(k, n, dev)
+    w = torch.rand(k).tolist()
+    out = ops.fedavg(slabs, w)
+    ref = sum(s.double() * wi for s, wi in zip(slabs, w)).float()
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+
+
+def test_fedavg_unaligned_views(dev):
+    from myfyp_b200 import ops
+
+    base = _slabs(3, 5001, dev)
+    slabs = [b[1:] for b in base]  # 4-byte aligned only -> scalar path
+    out = ops.fedavg(slabs, [0.2, 0.3, 0.5])
+    ref = 0.2 * slabs[0] + 0.3 * slabs[1] + 0.5 * slabs[2]
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+
+
+def test_accumulate_and_pull_copy(dev):
+    from myfyp_b200 import ops
+
+    a, b = _slabs(2, 100003, dev)
+    acc = a.clone()
+    ops.accumulate(acc, b, 0.25, beta=0.5)
+    torch.testing.assert_close(acc, 0.5 * a + 0.25 * b, rtol=1e-6, atol=1e-6)
+    dst = torch.empty_like(a)
+    ops.pull_copy(dst, b)
+    assert torch.equal(dst, b)
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 7, 8, 16, 31, 32, 33, 64])
+def test_median(dev, k):
+    from myfyp_b200 import ops
+
+    slabs = _slabs(k, 40000, dev, seed=k)
+    out = ops.median(slabs)
+    st = torch.stack(slabs).sort(dim=0).values
+    ref = (st[(k - 1) // 2] + st[k // 2]) / 2  # NumPy's median (what the reference intends, fedmedian.py:59-62)
+    torch.testing.assert_close(out, ref, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("k,trim", [(5, 1), (8, 2), (16, 3), (40, 10)])
+def test_trimmed_mean(dev, k, trim):
+    from myfyp_b200 import ops
+
+    slabs = _slabs(k, 30000, dev, seed=k)
+    out = ops.median(slabs, trim=trim)
+    st = torch.stack(slabs).sort(dim=0).values
+    torch.testing.assert_close(out, st[trim : k - trim].mean(dim=0), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("k,n,passes", [(2, 4096, 3), (5, 235264, 3), (16, 1 << 20, 3), (64, 131072, 3), (33, 70000, 3), (8, 1 << 20, 1)])
+def test_krum_gram_tcgen05(dev, k, n, passes):
+    """Pairwise distances from the tcgen05 Gram kernel vs fp64 direct distances; models close to each other (late-round regime)."""
+    from myfyp_b200 import ops
+
+    g = torch.Generator().manual_seed(k)
+    base = torch.randn(n, generator=g)
+    slabs = [(base + 0.01 * torch.randn(n, generator=g) * (1 + i % 3)).to(dev) for i in range(k)]
+    d = ops.pairwise_sqdist(slabs, passes=passes).double().cpu()
+    m = torch.stack([s.double().cpu() for s in slabs])
+    ref = torch.cdist(m, m).pow(2)
+    tol = 1e-4 if passes == 3 else 5e-3
+    torch.testing.assert_close(d, ref, rtol=tol, atol=tol * ref.max().item())
+    # what matters for Krum: the ranking
+    from myfyp_b200.learning.aggregators.krum import krum_select_reference
+
+    f = max(0, (k - 3) // 2)
+    s_ref, sel_ref = krum_select_reference(ref.numpy(), f, 1)
+    s_dev, sel_dev = ops.krum_select(ops.pairwise_sqdist(slabs, passes=passes), f, 1)
+    if passes == 3:
+        assert sel_dev == sel_ref
+        torch.testing.assert_close(torch.tensor(s_dev, dtype=torch.float64), torch.tensor(s_ref), rtol=1e-3, atol=1e-6)
+
+
+def test_krum_gram_twice_same_workspace(dev):
+    from myfyp_b200 import ops
+
+    slabs = _slabs(6, 50000, dev)
+    a = ops.pairwise_sqdist(slabs)
+    b = ops.pairwise_sqdist(slabs)
+    assert torch.equal(a, b)  # deterministic reduction + self-resetting counter
+
+
+def test_krum_rejects_byzantine(dev):
+    from myfyp_b200 import ops
+
+    good = _slabs(6, 20000, dev, scale=0.01)
+    bad = [(-5.0 * good[0]).contiguous(), (good[1] + 3.0).contiguous()]
+    scores, order = ops.krum_select(ops.pairwise_sqdist(good + bad), 2, 8)
+    assert set(order[-2:]) == {6, 7}
+
+
+def test_scaffold_kernels(dev):
+    from myfyp_b200 import ops
+
+    n, k = 50048, 5
+    x, c = _slabs(2, n, dev, seed=1)
+    dys, dcs = _slabs(k, n, dev, seed=2), _slabs(k, n, dev, seed=3)
+    wy = torch.rand(k).tolist()
+    xr = x.double() + sum(w * d.double() for w, d in zip(wy, dys))
+    cr = c.double() + sum(d.double() for d in dcs) / k
+    ops.scaffold_server_update(x, c, dys, dcs, wy, 1.0 / k)
+    torch.testing.assert_close(x, xr.float(), rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(c, cr.float(), rtol=1e-5, atol=1e-5)
+    ci, xs, y = _slabs(3, n, dev, seed=4)
+    ci0 = ci.clone()
+    dy, dc = torch.empty(n, device=dev), torch.empty(n, device=dev)
+    ops.scaffold_finalize(ci, dy, dc, xs, y, 19 * 1e-3)
+    adj = (xs - y) / (19 * 1e-3)
+    torch.testing.assert_close(dc, adj, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(ci, ci0 + adj, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(dy, y - xs)
+
+
+@pytest.mark.parametrize("terms", ["plain", "prox", "scaffold", "all"])
+def test_adam_matches_torch(dev, terms):
+    from myfyp_b200 import ops
+
+    n = 70016
+    p0, c, ci, ref_p = _slabs(4, n, dev, seed=5)
+    p = p0.clone()
+    pt = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([pt], lr=1e-3)
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    kw = {}
+    if terms in ("prox", "all"):
+        kw.update(prox_mu=0.1, prox_ref=ref_p)
+    if terms in ("scaffold", "all"):
+        kw.update(cv_global=c, cv_local=ci, cv_scale=1.0)
+    for step in range(1, 4):
+        g = _slabs(1, n, dev, seed=10 + step)[0]
+        eff = g.clone()
+        if "prox_ref" in kw:
+            eff += 0.1 * (pt.detach() - ref_p)
+        if "cv_global" in kw:
+            eff += c - ci
+        pt.grad = eff
+        opt.step()
+        gbuf = g.clone()
+        ops.adam_step(p, gbuf, m, v, step, lr=1e-3, **kw)
+        assert float(gbuf.abs().max()) == 0.0  # gradient slab cleared by the kernel
+    torch.testing.assert_close(p, pt.detach(), rtol=1e-4, atol=1e-5)
+
+
+def test_sgd_momentum_matches_torch(dev):
+    from myfyp_b200 import ops
+
+    n = 30016
+    p0 = _slabs(1, n, dev)[0]
+    p, pt = p0.clone(), p0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([pt], lr=0.05, momentum=0.9, weight_decay=1e-3)
+    buf = torch.zeros(n, device=dev)
+    for step in range(3):
+        g = _slabs(1, n, dev, seed=step + 1)[0]
+        pt.grad = g.clone()
+        opt.step()
+        ops.sgd_step(p, g.clone(), buf, lr=0.05, momentum=0.9, weight_decay=1e-3)
+    torch.testing.assert_close(p, pt.detach(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("b,c", [(1, 10), (32, 10), (257, 10), (64, 100), (16, 1000)])
+def test_xent(dev, b, c):
+    from myfyp_b200 import ops
+
+    logits = (torch.randn(b, c, device=dev) * 3).requires_grad_(True)
+    labels = torch.randint(0, c, (b,), device=dev)
+    loss = ops.cross_entropy(logits, labels)
+    loss.backward()
+    ref_logits = logits.detach().clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(ref_logits, labels)
+    ref.backward()
+    torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(logits.grad, ref_logits.grad, rtol=1e-3, atol=1e-6)
+    acc = torch.zeros(2, device=dev)
+    ops.cross_entropy_eval(logits.detach(), labels, acc)
+    assert abs(acc[0].item() - ref.item() * b) < 1e-3 * max(1.0, ref.item() * b)
+    assert acc[1].item() == (logits.argmax(1) == labels).sum().item()
+
+
+def _bf(t):
+    return t.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (32, 256, 784), (100, 10, 128), (256, 784, 32), (10, 128, 24), (300, 130, 200), (1024, 256, 784)])
+def test_gemm_tcgen05_plain(dev, m, n, k):
+    """D = A B^T on tcgen05/TMEM fed by TMA vs fp32 matmul of the same bf16-rounded operands."""
+    from myfyp_b200 import ops
+
+    pad8 = lambda x: (x + 7) // 8 * 8  # noqa: E731
+    a = torch.zeros(m, pad8(k), dtype=torch.bfloat16, device=dev)
+    b = torch.zeros(n, pad8(k), dtype=torch.bfloat16, device=dev)
+    a[:, :k] = _bf(torch.randn(m, k, device=dev))
+    b[:, :k] = _bf(torch.randn(n, k, device=dev))
+    out = torch.full((m, n), float("nan"), device=dev)
+    ops.gemm_bf16(a, b, m, n, k, out_f32=out)
+    ref = a[:, :k].float() @ b[:, :k].float().T
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=1e-3 * math.sqrt(k))
+
+
+def test_gemm_tcgen05_epilogues(dev):
+    from myfyp_b200 import ops
+
+    m, n, k = 96, 136, 264
+    a, b = _bf(torch.randn(m, k, device=dev)), _bf(torch.randn(n, k, device=dev))
+    bias = torch.randn(n, device=dev)
+    mask = _bf(torch.randn(m, n, device=dev))
+    ref = a.float() @ b.float().T + bias
+    # bias + relu -> bf16 and transposed bf16
+    o16 = torch.zeros(m, n, dtype=torch.bfloat16, device=dev)
+    o16t = torch.zeros(n, 96, dtype=torch.bfloat16, device=dev)
+    ops.gemm_bf16(a, b, m, n, k, out_bf16=o16, out_bf16_t=o16t, bias=bias, relu=True)
+    r = torch.relu(ref)
+    torch.testing.assert_close(o16.float(), r, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(o16t.float(), r.T, rtol=2e-2, atol=2e-2)
+    # mask + column sums + fp32 accumulate
+    of = torch.ones(m, n, device=dev)
+    cs = torch.zeros(n, device=dev)
+    ops.gemm_bf16(a, b, m, n, k, out_f32=of, mask=mask, colsum=cs, accumulate=True)
+    r2 = (a.float() @ b.float().T) * (mask.float() > 0)
+    torch.testing.assert_close(of, r2 + 1.0, rtol=1e-3, atol=2e-2)
+    torch.testing.assert_close(cs, r2.sum(0), rtol=1e-3, atol=5e-2)
+
+
+def test_cast_transpose(dev):
+    from myfyp_b200 import ops
+
+    r, c = 77, 203
+    src = torch.randn(r, c, device=dev)
+    d = torch.zeros(r, 208, dtype=torch.bfloat16, device=dev)
+    dt = torch.zeros(c, 80, dtype=torch.bfloat16, device=dev)
+    cs = torch.zeros(c, device=dev)
+    ops.cast_transpose(src, r, c, dst=d, dst_t=dt, colsum=cs)
+    assert torch.equal(d[:, :c], src.to(torch.bfloat16))
+    assert torch.equal(dt[:, :r], src.to(torch.bfloat16).T)
+    torch.testing.assert_close(cs, src.sum(0), rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("batch", [32, 24, 256])
+def test_native_mlp_step_matches_autograd(dev, batch):
+    """tcgen05 forward/backward of the MLP vs torch autograd in fp32 on the same weights (bf16 operand tolerance)."""
+    from myfyp_b200.models import mlp_model
+
+    model = mlp_model(device="cuda:0", seed=3, native=True)
+    module = model.get_model()
+    x = torch.randn(batch, 28, 28, device=dev)
+    y = torch.randint(0, 10, (batch,), device=dev)
+    loss = torch.zeros(1, device=dev)
+    module.native_train_step(x, y, loss)
+    grads = model.grad_slab.clone()
+    model.grad_slab.zero_()
+    ref_loss = torch.nn.functional.cross_entropy(module(x), y)
+    ref_loss.backward()
+    ref = model.grad_slab.clone()
+    model.grad_slab.zero_()
+    assert abs(loss.item() - ref_loss.item()) < 2e-2 * max(1.0, abs(ref_loss.item()))
+    # relative error on the whole gradient vector (bf16 operands, fp32 accumulation)
+    rel = (grads - ref).norm() / ref.norm()
+    assert rel < 3e-2, rel
+    for e in model.layout.in_order():
+        a, b = grads[e.offset : e.offset + e.numel], ref[e.offset : e.offset + e.numel]
+        assert (a - b).norm() <= 5e-2 * b.norm() + 1e-5, e.name
+
+
+def test_native_mlp_learns(dev):
+    from myfyp_b200.learning.dataset import P2PFLDataset
+    from myfyp_b200.learning.torch_learner import TorchLearner
+    from myfyp_b200.models import mlp_model
+    from myfyp_b200.ops import native
+
+    data = P2PFLDataset.synthetic_mnist(2048, 512, seed=1)
+    model = mlp_model(device="cuda:0", seed=0, native=True)
+    learner = TorchLearner(model, data, "n0", batch_size=64)
+    learner.set_epochs(2)
+    before = learner.evaluate()["test_metric"]
+    n0 = native.launches()
+    learner.fit()
+    assert native.launches() > n0
+    after = learner.evaluate()
+    assert after["test_metric"] > max(0.9, before)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_fedavg_pulls_from_peer_gpus():
+    from myfyp_b200 import ops
+    from myfyp_b200.parallel.fabric import Fabric
+
+    Fabric.get().enable_peer_access()
+    n = 1 << 20
+    slabs = [torch.randn(n, device=f"cuda:{i % torch.cuda.device_count()}") for i in range(4)]
+    out = ops.fedavg(slabs, [0.25] * 4, device=torch.device("cuda", 0))
+    ref = sum(s.to("cuda:0") for s in slabs) * 0.25
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+    med = ops.median(slabs, device=torch.device("cuda", 1))
+    st = torch.stack([s.to("cuda:1") for s in slabs]).sort(dim=0).values
+    torch.testing.assert_close(med, (st[1] + st[2]) / 2, rtol=1e-6, atol=1e-6)
