@@ -288,7 +288,7 @@ def run_ours(args) -> None:
 def main() -> None:
     args = parse()
     if args.impl == "reference":
-        from bench.reference_arm import run_reference
+        from benchmarks.reference_arm import run_reference
 
         run_reference(args)
     else:
