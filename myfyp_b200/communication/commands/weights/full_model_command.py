@@ -1,5 +1,6 @@
 """``add_model`` = full aggregated model diffusion (reference: commands/weights/full_model_command.py:31-89)."""
 
+import threading
 from typing import Callable
 
 from myfyp_b200.communication.commands.command import Command
@@ -11,6 +12,7 @@ from myfyp_b200.management.logger import logger
 class FullModelCommand(Command):
     def __init__(self, state, stop: Callable[[], None], aggregator, learner, protocol=None) -> None:
         self.state, self.stop, self.aggregator, self.learner, self.protocol = state, stop, aggregator, learner, protocol
+        self._mutex = threading.Lock()  # several neighbours may push the aggregate at the same instant
 
     @staticmethod
     def get_name() -> str:
@@ -26,13 +28,14 @@ class FullModelCommand(Command):
         if round != st.round:
             logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
             return
-        if st.aggregated_model_event.is_set():
-            logger.debug(st.addr, "😲 Aggregated model not expected.")
-            return
         try:
-            logger.info(st.addr, "📦 Aggregated model received.")
-            self.learner.set_model(weights)
-            st.aggregated_model_event.set()
+            with self._mutex:
+                if st.aggregated_model_event.is_set():
+                    logger.debug(st.addr, "😲 Aggregated model not expected.")
+                    return
+                logger.info(st.addr, "📦 Aggregated model received.")
+                self.learner.set_model(weights)
+                st.aggregated_model_event.set()
             st.notify()
         except DecodingParamsError:
             handle_bad_model(st, self.stop, source, "❌ Error decoding parameters", self.protocol)

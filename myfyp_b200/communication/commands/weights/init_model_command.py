@@ -1,5 +1,6 @@
 """``init_model`` (reference: commands/weights/init_model_command.py:31-97)."""
 
+import threading
 from typing import Callable, Optional
 
 from myfyp_b200.communication.commands.command import Command
@@ -11,6 +12,7 @@ from myfyp_b200.management.logger import logger
 class InitModelCommand(Command):
     def __init__(self, state, stop: Callable[[], None], aggregator, learner, protocol=None) -> None:
         self.state, self.stop, self.aggregator, self.learner, self.protocol = state, stop, aggregator, learner, protocol
+        self._mutex = threading.Lock()  # several initialised neighbours may push init_model at the same instant
 
     @staticmethod
     def get_name() -> str:
@@ -27,12 +29,13 @@ class InitModelCommand(Command):
         if round != st.round:
             logger.debug(st.addr, f"Model initialisation in a late round ({round} != {st.round}).")
             return
-        if not st.model_initialized_lock.locked():
-            logger.debug(st.addr, "Model initialisation message when the model is already initialised. Ignored.")
-            return
         try:
-            self.learner.set_model(weights)
-            st.model_initialized_lock.release()
+            with self._mutex:
+                if not st.model_initialized_lock.locked():
+                    logger.debug(st.addr, "Model initialisation message when the model is already initialised. Ignored.")
+                    return
+                self.learner.set_model(weights)
+                st.model_initialized_lock.release()
             st.notify()
             logger.info(st.addr, "🤖 Model Weights Initialized")
         except DecodingParamsError:

@@ -96,7 +96,7 @@ def test_krum_gram_tcgen05(dev, k, n, passes):
     s_dev, sel_dev = ops.krum_select(ops.pairwise_sqdist(slabs, passes=passes), f, 1)
     if passes == 3:
         assert sel_dev == sel_ref
-        torch.testing.assert_close(torch.tensor(s_dev, dtype=torch.float64), torch.tensor(s_ref), rtol=1e-3, atol=1e-6)
+        torch.testing.assert_close(torch.tensor(s_dev, dtype=torch.float64), torch.tensor(s_ref, dtype=torch.float64), rtol=1e-3, atol=1e-6)
 
 
 def test_krum_gram_twice_same_workspace(dev):
@@ -262,9 +262,38 @@ def test_cast_transpose(dev):
     torch.testing.assert_close(cs, src.sum(0), rtol=1e-5, atol=1e-4)
 
 
+def _mlp_bf16_emulation(module, x, y):
+    """The same forward/backward in plain PyTorch fp32 math, with bf16 rounding exactly where the kernels round."""
+    bf = lambda t: t.to(torch.bfloat16).float()  # noqa: E731
+    batch = x.shape[0]
+    W = [bf(l.weight.detach()) for l in module.layers]
+    b = [l.bias.detach() for l in module.layers]
+    L = len(W)
+    h = [bf(x.reshape(batch, -1).float())]
+    for i in range(L):
+        z = h[i] @ W[i].T + b[i]
+        if i < L - 1:
+            h.append(bf(torch.relu(z)))
+    logits = z
+    loss = torch.nn.functional.cross_entropy(logits, y)
+    dl = torch.softmax(logits, 1)
+    dl[torch.arange(batch), y] -= 1
+    dl /= batch
+    gw, gb = [None] * L, [None] * L
+    dz, gb[L - 1] = bf(dl), dl.sum(0)
+    for i in range(L - 1, -1, -1):
+        gw[i] = dz.T @ h[i]
+        if i > 0:
+            dzf = (dz @ W[i]) * (h[i] > 0)
+            gb[i - 1] = dzf.sum(0)
+            dz = bf(dzf)
+    return loss, gw, gb
+
+
 @pytest.mark.parametrize("batch", [32, 24, 256])
-def test_native_mlp_step_matches_autograd(dev, batch):
-    """tcgen05 forward/backward of the MLP vs torch autograd in fp32 on the same weights (bf16 operand tolerance)."""
+def test_native_mlp_step_matches_reference(dev, batch):
+    """tcgen05 forward/backward of the MLP: tight vs the fp32 PyTorch restatement with bf16-rounded operands,
+    loose vs true-fp32 autograd (bf16 operand noise under the cancellation of a random-init gradient is 3-6 %)."""
     from myfyp_b200.models import mlp_model
 
     model = mlp_model(device="cuda:0", seed=3, native=True)
@@ -279,13 +308,15 @@ def test_native_mlp_step_matches_autograd(dev, batch):
     ref_loss.backward()
     ref = model.grad_slab.clone()
     model.grad_slab.zero_()
+    emu_loss, gw, gb = _mlp_bf16_emulation(module, x, y)
+    assert abs(loss.item() - emu_loss.item()) < 1e-4 * max(1.0, abs(emu_loss.item()))
     assert abs(loss.item() - ref_loss.item()) < 2e-2 * max(1.0, abs(ref_loss.item()))
-    # relative error on the whole gradient vector (bf16 operands, fp32 accumulation)
-    rel = (grads - ref).norm() / ref.norm()
-    assert rel < 3e-2, rel
-    for e in model.layout.in_order():
-        a, b = grads[e.offset : e.offset + e.numel], ref[e.offset : e.offset + e.numel]
-        assert (a - b).norm() <= 5e-2 * b.norm() + 1e-5, e.name
+    for i in range(len(gw)):
+        for name, g in ((f"layers.{i}.weight", gw[i]), (f"layers.{i}.bias", gb[i])):
+            e = model.layout.entries[name]
+            a = grads[e.offset : e.offset + e.numel]
+            assert (a - g.reshape(-1)).norm() <= 1e-3 * g.norm() + 1e-7, name
+    assert (grads - ref).norm() / ref.norm() < 1e-1
 
 
 def test_native_mlp_learns(dev):
