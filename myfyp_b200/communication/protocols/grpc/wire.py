@@ -153,16 +153,17 @@ def encode_response(error: Optional[str] = None) -> bytes:
     return b"" if error is None else _ld(1, error.encode())
 
 
-def decode_response(data: bytes) -> Optional[str]:
+def decode_response(data: bytes) -> str:
+    """Error text, or "" when the optional field is absent (grpc treats a ``None`` from a deserializer as a failure)."""
     for f, _, v in _fields(data):
         if f == 1:
             return v.decode()
-    return None
+    return ""
 
 
 def encode_empty(_: Any = None) -> bytes:
     return b""
 
 
-def decode_empty(_: bytes) -> None:
-    return None
+def decode_empty(_: bytes) -> bytes:
+    return b""

@@ -1,0 +1,73 @@
+"""Two OS processes, one node each, real gRPC over unix sockets (no in-process shortcut), pickled weights on the wire."""
+
+import multiprocessing as mp
+import os
+import tempfile
+import time
+
+import numpy as np
+
+
+def _worker(rank, addrs, q, rounds):
+    import torch
+
+    torch.set_num_threads(1)
+    from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
+    from myfyp_b200.learning.dataset import P2PFLDataset, RandomIIDPartitionStrategy
+    from myfyp_b200.models import mlp_model
+    from myfyp_b200.node import Node
+    from myfyp_b200.utils.utils import set_test_settings, wait_convergence
+
+    set_test_settings()
+    from myfyp_b200.management.logger import logger
+
+    logger.set_level("ERROR")
+    data = P2PFLDataset.synthetic_mnist(400, 100, seed=0).generate_partitions(2, RandomIIDPartitionStrategy)[rank]
+    node = Node(mlp_model(seed=rank), data, address=addrs[rank], protocol=GrpcCommunicationProtocol, batch_size=32)
+    node.start()
+    q.put(("up", rank))
+    if rank == 0:
+        t_conn = time.time() + 60  # the peer process may still be importing torch
+        while not node.connect(addrs[1]):
+            assert time.time() < t_conn, "could not reach the peer process"
+            time.sleep(0.5)
+    wait_convergence([node], 1, wait=10, only_direct=True)
+    if rank == 0:
+        node.set_start_learning(rounds=rounds, epochs=1)
+    t_end = time.time() + 90
+    while not (len(node.learning_workflow.history) > 1 and node.learning_workflow.finished):
+        assert time.time() < t_end, node.learning_workflow.history
+        time.sleep(0.02)
+    params = node.get_model().get_parameters()
+    q.put(("done", rank, [float(np.sum(p)) for p in params], node.learning_workflow.history))
+    time.sleep(1.0)
+    node.stop()
+
+
+def test_two_processes_grpc_unix_sockets():
+    ctx = mp.get_context("spawn")
+    d = tempfile.mkdtemp()
+    addrs = [f"unix://{d}/n{i}.sock" for i in range(2)]
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, addrs, q, 2)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = {}
+    deadline = time.time() + 150
+    while len(results) < 2 and time.time() < deadline:
+        try:
+            msg = q.get(timeout=1)
+        except Exception:
+            if any(p.exitcode not in (None, 0) for p in procs):
+                break
+            continue
+        if msg[0] == "done":
+            results[msg[1]] = msg[2:]
+    for p in procs:
+        p.join(20)
+        if p.is_alive():
+            p.terminate()
+    assert len(results) == 2, "a worker died"
+    (s0, h0), (s1, h1) = results[0], results[1]
+    np.testing.assert_allclose(s0, s1, rtol=1e-4, atol=1e-3)  # same aggregated model on both sides
+    assert h0.count("RoundFinishedStage") == 2 and h1.count("RoundFinishedStage") == 2
