@@ -112,10 +112,22 @@ def run_ours(args) -> None:
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     multi = world > 1
+    local_rank = local_rank % torch.cuda.device_count()  # several ranks may share a GPU when debugging on a small box
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    if os.environ.get("B2_BENCH_DEBUG"):
+        import faulthandler
+
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        fh = open(os.path.join(ROOT, "gpurun_out", f"bench_hang_rank{rank}.txt"), "w")
+        faulthandler.dump_traceback_later(int(os.environ["B2_BENCH_DEBUG"]), file=fh, exit=True)
+    shared_gpu = world > torch.cuda.device_count()  # debugging only: NCCL refuses two ranks on one GPU
     if multi:
-        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+        if shared_gpu:
+            dist.init_process_group("gloo")
+        else:
+            dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+    red_dev = torch.device("cpu") if shared_gpu else dev
 
     from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
     from myfyp_b200.communication.protocols.memory.memory_communication_protocol import InMemoryCommunicationProtocol
@@ -130,6 +142,12 @@ def run_ours(args) -> None:
     n_nodes = args.nodes
     set_fast_settings(train_set_size=n_nodes)
     Settings.USE_SSL = False
+    if os.environ.get("B2_BENCH_DEBUG"):
+        from myfyp_b200.management.logger import logger
+
+        Settings.LOG_DIR = os.path.join(ROOT, "gpurun_out", f"logs_rank{rank}")
+        logger.enable_file_logging()
+        logger.set_level("DEBUG")
     torch.manual_seed(1234 + rank)
 
     owner = [i * world // n_nodes for i in range(n_nodes)]  # node i lives on rank owner[i]
@@ -207,14 +225,14 @@ def run_ours(args) -> None:
     def allmax(x: float) -> float:
         if not multi:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        t = torch.tensor([x], dtype=torch.float64, device=red_dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
     def allsum(x: float) -> float:
         if not multi:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        t = torch.tensor([x], dtype=torch.float64, device=red_dev)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 

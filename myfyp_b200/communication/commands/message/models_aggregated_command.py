@@ -14,7 +14,12 @@ class ModelsAggregatedCommand(Command):
 
     def execute(self, source: str, round: int, *args, **kwargs) -> None:
         if round == self.state.round:
-            self.state.models_aggregated[source] = list(args)
+            # Within a round a node's held set only grows, so announcements are merged, not overwritten: two
+            # announcements of one node can overtake each other (concurrent handlers, async fan-out), and a stale
+            # "last writer" would make every later FedAvg offer overlap what the node already holds -> rejected
+            # forever -> the round ends by timeout.  (The reference overwrites, models_agregated_command.py:49-51.)
+            cur = self.state.models_aggregated.get(source, [])
+            self.state.models_aggregated[source] = cur + [a for a in args if a not in cur]
             self.state.notify()
         else:
             logger.debug(self.state.addr, f"models_aggregated from {source} in a late round ({round} != {self.state.round}). Ignored.")

@@ -41,7 +41,9 @@ class PartialModelCommand(Command):
             model = self.learner.get_model().build_copy(params=weights, num_samples=num_samples, contributors=list(contributors))
             models_added = self.aggregator.add_model(model)
             if models_added != []:
-                self.communication_protocol.broadcast(
+                # we are inside the sender's RPC / call stack: announce from the gossiper thread, never block here
+                # (a synchronous fan-out from inside a handler can exhaust the peers' RPC workers)
+                self.communication_protocol.broadcast_async(
                     self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round)
                 )
         except DecodingParamsError:

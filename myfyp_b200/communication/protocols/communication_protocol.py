@@ -76,6 +76,10 @@ class CommunicationProtocol(abc.ABC):
         wait_fn: Optional[Callable[[float], None]] = None,
     ) -> None: ...
 
+    def broadcast_async(self, msg: Any) -> None:
+        """Like :meth:`broadcast` but never blocks the caller on the peers (default: plain broadcast)."""
+        self.broadcast(msg)
+
     # --- B200 data-plane hook (no counterpart in the reference) -------------------
     def fabric_reachable(self, nei: str) -> bool:
         """True when a device descriptor sent to ``nei`` can be dereferenced there."""

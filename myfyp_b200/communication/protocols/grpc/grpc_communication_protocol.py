@@ -72,6 +72,16 @@ class GrpcCommunicationProtocol(CommunicationProtocol):
         self._client.broadcast(msg, node_list)
 
     @running
+    def broadcast_async(self, msg: Any) -> None:
+        """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers)."""
+        if isinstance(msg, dict) and "hash" in msg:
+            self._gossiper.check_and_set_processed(msg["hash"])
+        nodes = list(self._neighbors.get_all(only_direct=True))
+        if isinstance(msg, dict) and "hash" in msg:
+            msg["seen"] = [self.addr, *nodes]
+        self._gossiper.add_message(msg, nodes)
+
+    @running
     def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]:
         return self._neighbors.get_all(only_direct)
 

@@ -50,7 +50,7 @@ class GrpcServer:
     # ------------------------------------------------------------------ lifecycle
     def start(self, wait: bool = False) -> None:
         opts = [("grpc.max_send_message_length", MAX_MSG), ("grpc.max_receive_message_length", MAX_MSG), ("grpc.so_reuseport", 0)]
-        self.__server = grpc.server(futures.ThreadPoolExecutor(max_workers=8, thread_name_prefix=f"grpc-{self.addr}"), options=opts)
+        self.__server = grpc.server(futures.ThreadPoolExecutor(max_workers=32, thread_name_prefix=f"grpc-{self.addr}"), options=opts)
         handlers = {
             "handshake": grpc.unary_unary_rpc_method_handler(self._rpc_handshake, request_deserializer=wire.decode_handshake, response_serializer=wire.encode_response),
             "disconnect": grpc.unary_unary_rpc_method_handler(self._rpc_disconnect, request_deserializer=wire.decode_handshake, response_serializer=wire.encode_empty),
@@ -134,7 +134,10 @@ class GrpcServer:
         if not is_weights and msg["ttl"] > 0:
             fwd = dict(msg)
             fwd["ttl"] = msg["ttl"] - 1
-            self.__gossiper.add_message(fwd, [n for n in self.__neighbors.get_all(only_direct=True) if n != msg["source"]])
+            seen = msg.get("seen") or []
+            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n != msg["source"] and n not in seen]
+            fwd["seen"] = [*seen, *pending]
+            self.__gossiper.add_message(fwd, pending)
         return None
 
     # ------------------------------------------------------------------ RPC adapters

@@ -5,7 +5,12 @@ encoder/decoder is written out by hand.  Field numbers and types are the referen
 (communication/protocols/grpc/proto/node.proto:26-54), which keeps mixed deployments interoperable:
 
     RootMessage { string source=1; optional int32 round=2; string cmd=3; oneof { Message message=4; Weights weights=5; } }
-    Message     { int32 ttl=1; int64 hash=2; repeated string args=3; }
+    Message     { int32 ttl=1; int64 hash=2; repeated string args=3; [repeated string seen=4;] }
+
+``seen`` is an extension of this framework: the addresses already known to have (or to be about to get) a flooded
+message; a receiver forwards only to direct neighbours not listed.  In a full mesh that removes every redundant
+forward (the reference sends (n-1)(n-2) of them per message); a reference peer ignores the
+unknown field and simply floods as before, so mixed deployments still work.
     Weights     { bytes weights=1; repeated string contributors=2; int32 num_samples=3; }
     HandShakeRequest { string addr=1; }      ResponseMessage { optional string error=1; }
 """
@@ -104,6 +109,8 @@ def encode_root(msg: Dict[str, Any]) -> bytes:
         m += _key(2, 0) + _varint(int(msg["hash"]))
         for a in msg.get("args", []):
             m += _ld(3, str(a).encode())
+        for a in msg.get("seen") or []:  # extension field 4 (unknown to the reference's parser, which skips it)
+            m += _ld(4, str(a).encode())
         out += _ld(4, bytes(m))
     return bytes(out)
 
@@ -118,7 +125,7 @@ def decode_root(data: bytes) -> Dict[str, Any]:
         elif f == 3:
             msg["cmd"] = v.decode()
         elif f == 4:
-            msg.update(ttl=0, hash=0, args=[])
+            msg.update(ttl=0, hash=0, args=[], seen=[])
             for f2, _, v2 in _fields(v):
                 if f2 == 1:
                     msg["ttl"] = _signed(v2, 32)
@@ -126,6 +133,8 @@ def decode_root(data: bytes) -> Dict[str, Any]:
                     msg["hash"] = _signed(v2, 64)
                 elif f2 == 3:
                     msg["args"].append(v2.decode())
+                elif f2 == 4:
+                    msg["seen"].append(v2.decode())
         elif f == 5:
             msg.update(weights=b"", contributors=[], weight=0)
             for f2, _, v2 in _fields(v):

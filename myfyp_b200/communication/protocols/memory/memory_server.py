@@ -68,8 +68,9 @@ class InMemoryServer:
         if request["ttl"] > 0:
             fwd = dict(request)
             fwd["ttl"] = request["ttl"] - 1
-            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n != request["source"] and n != request.get("via")]
-            fwd["via"] = self.addr
+            seen = request.get("seen") or []
+            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n != request["source"] and n not in seen]
+            fwd["seen"] = [*seen, *pending]
             self.__gossiper.add_message(fwd, pending)
         handler = self.__commands.get(cmd)
         if handler is None:

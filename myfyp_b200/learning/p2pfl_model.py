@@ -136,6 +136,7 @@ class TorchP2PFLModel(P2PFLModel):
         self.slab: torch.Tensor
         self.grad_slab: Optional[torch.Tensor] = None
         self._int_entries: List[str] = []
+        self._ref: Optional[SlabRef] = None  # held models: the descriptor (arena coordinates) the slab came with
         if model is not None:
             if device is not None:
                 model.to(device)
@@ -230,7 +231,22 @@ class TorchP2PFLModel(P2PFLModel):
         return SlabRef(snap.tensor, self.layout.total, self.layout.hash, str(self.slab.device), dict(self.additional_info), snap.rank, snap.offset, snap.generation)
 
     def as_ref(self) -> SlabRef:
-        """Descriptor of the slab itself (no copy) - only for held models nobody mutates."""
+        """Descriptor of the slab itself - only for held models nobody mutates.
+
+        A slab that arrived as a descriptor keeps that descriptor (it may name an IPC arena slot that peers in
+        other processes can map).  With an arena attached, a process-local slab (an aggregation result) is copied
+        into an arena slot once, because a peer process can only dereference arena coordinates.
+        """
+        import dataclasses
+
+        if self._ref is not None:
+            return dataclasses.replace(self._ref, additional_info=dict(self.additional_info))
+        from myfyp_b200.parallel.fabric import Fabric
+
+        if Fabric.get().has_arena() and self.slab.is_cuda:
+            snap = Fabric.get().snapshot(self.slab)
+            self._ref = SlabRef(snap.tensor, self.layout.total, self.layout.hash, str(self.slab.device), {}, snap.rank, snap.offset, snap.generation)
+            return dataclasses.replace(self._ref, additional_info=dict(self.additional_info))
         return SlabRef(self.slab, self.layout.total, self.layout.hash, str(self.slab.device), dict(self.additional_info))
 
     def encode_for_transport(self, device_ok: bool) -> Union[bytes, SlabRef]:
@@ -300,6 +316,7 @@ class TorchP2PFLModel(P2PFLModel):
             held.set_parameters(params)
         elif isinstance(params, SlabRef):
             held.additional_info.update(params.additional_info)
+            held._ref = params
         return held
 
     def snapshot_model(self) -> "TorchP2PFLModel":

@@ -92,6 +92,9 @@ class Fabric:
             self.enable_peer_access()
         return Snapshot(slab.clone())
 
+    def has_arena(self) -> bool:
+        return self._arena is not None
+
     def attach_arena(self, arena) -> None:
         self._arena = arena
         self.rank, self.world = arena.rank, arena.world

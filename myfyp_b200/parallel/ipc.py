@@ -60,7 +60,7 @@ def register_addresses(mapping: Dict[str, int]) -> None:
 def address_on_fabric(addr: str) -> bool:
     from myfyp_b200.parallel.fabric import Fabric
 
-    return Fabric.get()._arena is not None and addr in _addr_to_rank
+    return Fabric.get().has_arena() and addr in _addr_to_rank
 
 
 class ArenaPool:
