@@ -30,8 +30,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 TOTAL_NODES = 8
-SAMPLES_PER_NODE = 512
-TEST_PER_NODE = 128
+SAMPLES_PER_NODE = 6250  # CIFAR-10's 50 000 training images split IID over the 8 nodes
+TEST_PER_NODE = 1250  # its 10 000 test images, likewise
 BATCH = 64
 METRIC = "fl_rounds_per_sec"
 
@@ -271,6 +271,16 @@ def run_ours(args) -> None:
         e2e = {"value": args.steps / wall, "unit": "rounds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * wall / args.steps}
         set_host_mode(False)
 
+    stage_ms = {}
+    if nodes:
+        from collections import defaultdict
+
+        acc = defaultdict(float)
+        for n in nodes.values():
+            for name, dt in n.learning_workflow.timings:
+                acc[name] += dt
+        rounds_run = args.warmup + args.steps + (0 if args.no_e2e else args.steps + max(1, min(args.warmup, 2)))
+        stage_ms = {k: round(1e3 * v / len(nodes) / rounds_run, 2) for k, v in acc.items()}
     for n in nodes.values():
         n.stop()
     if multi:
@@ -294,7 +304,7 @@ def run_ours(args) -> None:
                 "protocol": "grpc+cuda-ipc" if multi else "in-memory", "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
                 "step": "one federated round of all nodes",
             },
-            "clocks": clocks, "gpu_launches": launches,
+            "clocks": clocks, "gpu_launches": launches, "stage_ms_per_round_rank0": stage_ms,
         }
         if e2e is not None:
             out["e2e"] = e2e

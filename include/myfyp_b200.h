@@ -61,8 +61,11 @@ int b2_krum_select(const float* dist, int K, int f, float* scores, int* order, v
 /* T6 fused Adam over a flat slab; g' = g + wd*p + prox_mu*(p - prox_ref) + cv_scale*(cv_global - cv_local); clears g.
  * Reference: torch.optim.Adam (lightning_model.py:181-183), Scaffold term scaffold_callback.py:90-110. */
 int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
-                 float bias_corr2, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad,
-                 void* stream);
+                 float bias_corr2, const float* dev_state, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale,
+                 int zero_grad, void* stream);
+/* Device-resident Adam step state {step, 1-beta1^step, 1-beta2^step}: advance it by one step.  When `dev_state` is passed to
+ * b2_adam_step the bias corrections are read from it (so a captured CUDA graph of an epoch replays correctly). */
+int b2_adam_prepare(float* state, float beta1, float beta2, void* stream);
 int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momentum, float weight_decay, float prox_mu, const float* prox_ref,
                 const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream);
 /* T3+T8 fused log-softmax + NLL (+ gradient, + argmax accuracy).  loss_out/correct are accumulated atomically.

@@ -29,8 +29,22 @@ __device__ __forceinline__ float4 effective_grad(const float4 g, const float4 p,
   return r;
 }
 
+// state = {step, 1-beta1^step, 1-beta2^step}: the step counter lives on the device so that a captured CUDA graph of a
+// whole local epoch replays with the right bias corrections (a host-side step would be frozen into the graph).
+__global__ void adam_prepare_kernel(float* __restrict__ state, float b1, float b2) {
+  const float step = state[0] + 1.f;
+  state[0] = step;
+  state[1] = 1.f - powf(b1, step);
+  state[2] = 1.f - powf(b2, step);
+}
+
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4, float lr,
-                                                   float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, FusedTerms t, int zero_grad) {
+                                                   float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, const float* __restrict__ state, FusedTerms t,
+                                                   int zero_grad) {
+  if (state != nullptr) {
+    inv_bc1 = 1.f / state[1];
+    inv_sqrt_bc2 = rsqrtf(state[2]);
+  }
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pv = p[i], mv = m[i], vv = v[i];
@@ -78,15 +92,21 @@ using namespace b2;
 
 extern "C" {
 
+int b2_adam_prepare(float* state, float beta1, float beta2, void* stream) {
+  adam_prepare_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, beta1, beta2);
+  B2_LAUNCH_CHECK("adam_prepare_kernel");
+  return 0;
+}
+
 int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
-                 float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream) {
+                 const float* dev_state, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream) {
   if (n <= 0) return 0;
   if (check_slab(p, g, m, v, n) || check_slab(p, p, prox_ref, cv_global, n) || check_slab(p, p, cv_local, nullptr, n)) return 1;
   FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
                reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
   adam_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
                                                                                       reinterpret_cast<float4*>(v), n / 4, lr, beta1, beta2, eps, 1.f / bias_corr1,
-                                                                                      rsqrtf(bias_corr2), t, zero_grad);
+                                                                                      rsqrtf(bias_corr2), dev_state, t, zero_grad);
   B2_LAUNCH_CHECK("adam_kernel");
   return 0;
 }

@@ -24,7 +24,11 @@ class FedProxCallback(P2PFLCallback):
 
     def on_fit_start(self, learner) -> None:
         model = learner.get_model()
-        self.ref = model.slab[: model.layout.n_trainable].clone()
+        cur = model.slab[: model.layout.n_trainable]
+        if self.ref is None or self.ref.shape != cur.shape or self.ref.device != cur.device:
+            self.ref = cur.clone()  # allocated once: captured CUDA graphs keep pointing at it
+        else:
+            self.ref.copy_(cur)
 
     def optimizer_terms(self, learner) -> Dict[str, Any]:
         return {"prox_mu": self.mu, "prox_ref": self.ref}

@@ -40,12 +40,16 @@ class SCAFFOLDCallback(P2PFLCallback):
         slab = model.slab
         if self.c_i is None or self.c_i.numel() != n or self.c_i.device != slab.device:
             self.c_i = torch.zeros(n, dtype=torch.float32, device=slab.device)
+        # c and x_start are allocated once and refreshed in place: captured CUDA graphs keep pointing at them
+        if self.c is None or self.c.numel() != n or self.c.device != slab.device:
+            self.c = torch.zeros(n, dtype=torch.float32, device=slab.device)
         g = self.additional_info.get("global_c") if isinstance(self.additional_info, dict) else None
         if g is not None:
-            self.c = _flat_prefix(g, model, n)
-        elif self.c is None or self.c.numel() != n or self.c.device != slab.device:
-            self.c = torch.zeros(n, dtype=torch.float32, device=slab.device)
-        self.x_start = slab[:n].clone()
+            self.c.copy_(_flat_prefix(g, model, n))
+        if self.x_start is None or self.x_start.numel() != n or self.x_start.device != slab.device:
+            self.x_start = slab[:n].clone()
+        else:
+            self.x_start.copy_(slab[:n])
 
     def optimizer_terms(self, learner) -> Dict[str, Any]:
         if self.variant == "reference":

@@ -1,22 +1,27 @@
-"""The PyTorch learner: a hand-rolled, device-resident training loop.
+"""The PyTorch learner: a hand-rolled, device-resident, CUDA-graph-captured training loop.
 
-Replaces the reference's ``LightningLearner`` (pytorch/lightning_learner.py:49-152), which builds a
-new ``lightning.Trainer`` per ``fit`` and streams batch-size-1 batches through a DataLoader.  Here:
+Replaces the reference's ``LightningLearner`` (pytorch/lightning_learner.py:49-152), which builds a new
+``lightning.Trainer`` per ``fit`` and streams batch-size-1 batches through a DataLoader.  Here:
 
-* the node's whole partition sits in HBM (``TensorExportStrategy``); a batch is an index slice;
-* loss = fused log-softmax + NLL kernel (T3/T8); optimizer = ONE fused multi-tensor kernel over the
-  flat slab (T6) that also applies FedProx / Scaffold terms and clears the gradients;
+* the node's whole partition sits in HBM (``TensorExportStrategy``); a batch is an index gather;
+* loss = fused log-softmax + NLL kernel (T3/T8); optimizer = ONE fused multi-tensor kernel over the flat slab (T6)
+  that also applies FedProx / Scaffold terms and clears the gradients;
 * a module exposing ``native_train_step`` (our tcgen05 models) bypasses autograd entirely;
-* per-step ``train_loss`` values stay on the device and reach the metric store with one D2H copy
-  per fit; evaluation returns ``test_loss`` / ``test_metric`` (accuracy) like the reference
+* on CUDA one whole local epoch (gathers, forward, loss, backward, optimizer for every batch) is captured ONCE
+  into a CUDA graph and replayed per epoch on the learner's own stream: with 4-8 nodes per GPU and 0.5-45 MB models
+  the step is launch-bound, so a fit costs one graph launch instead of thousands of kernel launches, and the nodes
+  of a GPU overlap on the device.  The Adam step counter lives on the device so replays keep exact bias corrections;
+* per-step ``train_loss`` values stay on the device and reach the metric store with one D2H copy per fit;
+  evaluation returns ``test_loss`` / ``test_metric`` (accuracy) like the reference
   (lightning_model.py:197-207).
 
-Like the reference (a fresh Trainer => fresh optimizer per fit) the optimizer state is reset every
-``fit`` unless ``persist_optimizer=True``.
+Like the reference (a fresh Trainer => fresh optimizer per fit) the optimizer state is reset every ``fit`` unless
+``persist_optimizer=True``.
 """
 
 from __future__ import annotations
 
+import threading
 from typing import Any, Dict, Optional
 
 import torch
@@ -26,6 +31,8 @@ from myfyp_b200.learning.dataset.p2pfl_dataset import TensorExportStrategy
 from myfyp_b200.learning.learner import Learner
 from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
 from myfyp_b200.management.logger import logger
+
+_capture_lock = threading.Lock()  # one stream capture at a time per process
 
 
 class TorchLearner(Learner):
@@ -44,12 +51,14 @@ class TorchLearner(Learner):
         shuffle: bool = True,
         max_steps_per_epoch: Optional[int] = None,
         data_on_host: bool = False,
+        use_cuda_graph: bool = True,
     ) -> None:
         super().__init__(model, data, self_addr, aggregator)
         self.batch_size, self.lr, self.optimizer = batch_size, lr, optimizer
         self.momentum, self.weight_decay = momentum, weight_decay
         self.persist_optimizer, self.shuffle = persist_optimizer, shuffle
         self.max_steps_per_epoch = max_steps_per_epoch
+        self.use_cuda_graph = use_cuda_graph
         # data_on_host: the partition stays in pinned host memory and is copied to the GPU at every fit /
         # evaluate (the end-to-end mode of bench.py); default is device-resident data
         self.data_on_host = data_on_host
@@ -59,6 +68,9 @@ class TorchLearner(Learner):
         self._interrupt = False
         self._opt_state: Dict[str, Any] = {}
         self._data_cache: Dict[Any, Any] = {}
+        self._static: Dict[Any, Any] = {}  # static device buffers the graphs read (x, y, perm, losses...)
+        self._graphs: Dict[Any, Any] = {}
+        self._stream: Optional[torch.cuda.Stream] = None
         self._global_step = 0
 
     def get_framework(self) -> str:
@@ -73,21 +85,30 @@ class TorchLearner(Learner):
             x, y = self.data.export(TensorExportStrategy, train=train, device="cpu" if host else dev)
             self._data_cache[key] = (x.pin_memory(), y.pin_memory()) if host else (x, y)
         x, y = self._data_cache[key]
-        if host:  # this call's inputs travel host -> device now
+        if host:  # this call's inputs travel host -> device now, into the static buffers the graphs read
             self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
-            x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+            skey = ("xy", train)
+            if skey not in self._static:
+                self._static[skey] = (torch.empty_like(x, device=dev), torch.empty_like(y, device=dev))
+            sx, sy = self._static[skey]
+            sx.copy_(x, non_blocking=True)
+            sy.copy_(y, non_blocking=True)
+            return sx, sy
         return x, y
 
     def set_data(self, data) -> None:
         super().set_data(data)
         self._data_cache.clear()
+        self._static.clear()
+        self._graphs.clear()
 
     # ------------------------------------------------------------------ optimizer state
     def _state(self, n: int, device) -> Dict[str, Any]:
         st = self._opt_state
         if st.get("n") != n or st.get("device") != device:
             st.clear()
-            st.update(n=n, device=device, m=torch.zeros(n, device=device), v=torch.zeros(n, device=device), step=0)
+            st.update(n=n, device=device, m=torch.zeros(n, device=device), v=torch.zeros(n, device=device), step=0, dev_state=torch.zeros(4, device=device))
+            self._graphs.clear()
         return st
 
     def _optimizer_step(self, st: Dict[str, Any], terms: Dict[str, Any]) -> None:
@@ -95,56 +116,122 @@ class TorchLearner(Learner):
         n = model.layout.n_trainable
         st["step"] += 1
         if self.optimizer == "adam":
-            ops.adam_step(model.slab[:n], model.grad_slab[:n], st["m"], st["v"], st["step"], lr=self.lr, weight_decay=self.weight_decay, **terms)
+            ops.adam_step(model.slab[:n], model.grad_slab[:n], st["m"], st["v"], st["step"], lr=self.lr, weight_decay=self.weight_decay, dev_state=st["dev_state"], **terms)
         else:
             ops.sgd_step(model.slab[:n], model.grad_slab[:n], st["m"], lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay, **terms)
+
+    # ------------------------------------------------------------------ one epoch (eager, or the body that gets captured)
+    def _epoch_body(self, x, y, perm, losses, steps: int, st, terms) -> int:
+        module = self.model.get_model()
+        native = getattr(module, "native_train_step", None)
+        done = 0
+        for s in range(steps):
+            if self._interrupt:
+                break
+            idx = perm[s * self.batch_size : (s + 1) * self.batch_size]
+            xb, yb = x.index_select(0, idx), y.index_select(0, idx)
+            if native is not None:
+                native(xb, yb, losses[s : s + 1])
+            else:
+                loss = ops.cross_entropy(module(xb), yb)
+                loss.backward()
+                losses[s : s + 1].copy_(loss.detach().reshape(1))
+            self._optimizer_step(st, terms)
+            done += 1
+        return done
+
+    def _graph_for(self, key, build):
+        """Capture ``build()`` once into a CUDA graph (after an eager warm-up run of it on the learner's stream)."""
+        if key in self._graphs:
+            return self._graphs[key]
+        model: TorchP2PFLModel = self.model  # type: ignore[assignment]
+        stream = self._stream
+        with _capture_lock:
+            # warm-up: lazy inits (cuDNN plans, smem attributes, workspaces) must happen outside the capture;
+            # it is a real step, so parameters / optimizer state are restored afterwards
+            keep = (model.slab.clone(), model.grad_slab.clone(), self._opt_state["m"].clone(), self._opt_state["v"].clone(), self._opt_state["dev_state"].clone())
+            build()
+            stream.synchronize()
+            model.slab.copy_(keep[0])
+            model.grad_slab.copy_(keep[1])
+            self._opt_state["m"].copy_(keep[2])
+            self._opt_state["v"].copy_(keep[3])
+            self._opt_state["dev_state"].copy_(keep[4])
+            stream.synchronize()
+            g = torch.cuda.CUDAGraph()
+            before = ops.native.launches()
+            with torch.cuda.graph(g, stream=stream, capture_error_mode="thread_local"):
+                build()
+            g.native_kernels = ops.native.launches() - before  # our kernels per replay (for launch accounting)
+            ops.native.count_launch(-g.native_kernels)  # captured, not executed
+        self._graphs[key] = g
+        return g
 
     # ------------------------------------------------------------------ fit / evaluate
     def fit(self) -> TorchP2PFLModel:
         model: TorchP2PFLModel = self.model  # type: ignore[assignment]
         module = model.get_model()
+        dev = model.device
         self._interrupt = False
         if self.pre_fit_hook is not None:
             self.pre_fit_hook()
-        x, y = self._tensors(train=True)
-        n = x.shape[0]
-        st = self._state(model.layout.n_trainable, model.device)
-        if not self.persist_optimizer:
-            st["m"].zero_()
-            st["v"].zero_()
-            st["step"] = 0
-        for cb in self.callbacks:
-            cb.on_fit_start(self)
-        terms: Dict[str, Any] = {}
-        for cb in self.callbacks:
-            terms.update(cb.optimizer_terms(self))
-        steps_per_epoch = (n + self.batch_size - 1) // self.batch_size
-        if self.max_steps_per_epoch is not None:
-            steps_per_epoch = min(steps_per_epoch, self.max_steps_per_epoch)
-        losses = torch.zeros(max(self.epochs * steps_per_epoch, 1), device=model.device)
-        native = getattr(module, "native_train_step", None)
-        module.train()
-        steps = 0
-        for _ in range(self.epochs):
-            perm = torch.randperm(n, device=model.device) if self.shuffle else torch.arange(n, device=model.device)
-            for s in range(steps_per_epoch):
-                if self._interrupt:
-                    break
-                idx = perm[s * self.batch_size : (s + 1) * self.batch_size]
-                xb, yb = x[idx], y[idx]
-                if native is not None:
-                    native(xb, yb, losses[steps : steps + 1])
-                else:
-                    loss = ops.cross_entropy(module(xb), yb)
-                    loss.backward()
-                    losses[steps] = loss.detach()
-                self._optimizer_step(st, terms)
-                steps += 1
-        for cb in self.callbacks:
-            cb.on_fit_end(self, steps, self.lr)
+        cuda = dev.type == "cuda"
+        if cuda and self._stream is None:
+            self._stream = torch.cuda.Stream(dev)
+        ctx = torch.cuda.stream(self._stream) if cuda else _NullCtx()
+        if cuda:
+            self._stream.wait_stream(torch.cuda.current_stream(dev))  # parameters were written on the caller's stream
+        with ctx:
+            x, y = self._tensors(train=True)
+            n = x.shape[0]
+            st = self._state(model.layout.n_trainable, dev)
+            if not self.persist_optimizer:
+                st["m"].zero_()
+                st["v"].zero_()
+                st["dev_state"].zero_()
+                st["step"] = 0
+            for cb in self.callbacks:
+                cb.on_fit_start(self)
+            terms: Dict[str, Any] = {}
+            for cb in self.callbacks:
+                terms.update(cb.optimizer_terms(self))
+            steps_per_epoch = (n + self.batch_size - 1) // self.batch_size
+            if self.max_steps_per_epoch is not None:
+                steps_per_epoch = min(steps_per_epoch, self.max_steps_per_epoch)
+            total = max(self.epochs * steps_per_epoch, 1)
+            all_losses = torch.zeros(total, device=dev)
+            module.train()
+            steps = 0
+            graph_ok = cuda and self.use_cuda_graph
+            if graph_ok:
+                pkey = ("perm", n)
+                if pkey not in self._static:
+                    self._static[pkey] = (torch.arange(n, device=dev), torch.zeros(steps_per_epoch, device=dev))
+                perm, losses = self._static[pkey]
+                gkey = ("fit", n, steps_per_epoch, self.batch_size, self.optimizer, x.data_ptr(), tuple(sorted((k, v.data_ptr() if isinstance(v, torch.Tensor) else v) for k, v in terms.items())))
+                for e in range(self.epochs):
+                    if self._interrupt:
+                        break
+                    if self.shuffle:
+                        perm.copy_(torch.randperm(n, device=dev))
+                    g = self._graph_for(gkey, lambda: self._epoch_body(x, y, perm, losses, steps_per_epoch, st, terms))
+                    g.replay()
+                    all_losses[e * steps_per_epoch : (e + 1) * steps_per_epoch].copy_(losses)
+                    st["step"] += steps_per_epoch
+                    steps += steps_per_epoch
+                    ops.native.count_launch(g.native_kernels)
+            else:
+                for e in range(self.epochs):
+                    perm = torch.randperm(n, device=dev) if self.shuffle else torch.arange(n, device=dev)
+                    steps += self._epoch_body(x, y, perm, all_losses[e * steps_per_epoch :], steps_per_epoch, st, terms)
+            for cb in self.callbacks:
+                cb.on_fit_end(self, steps, self.lr)
+            vals = all_losses[:steps].tolist() if steps else []  # one D2H copy per fit (synchronises the learner's stream)
+        if cuda:
+            self._stream.synchronize()
         if steps:
             self.d2h_bytes += 4 * steps
-            for i, v in enumerate(losses[:steps].tolist()):  # one D2H copy per fit
+            for i, v in enumerate(vals):
                 logger.log_metric(self._self_addr, "train_loss", v, step=self._global_step + i)
             self._global_step += steps
         model.set_contribution([self._self_addr], self.data.get_num_samples(train=True))
@@ -154,19 +241,10 @@ class TorchLearner(Learner):
     def interrupt_fit(self) -> None:
         self._interrupt = True
 
-    @torch.no_grad()
-    def evaluate(self) -> Dict[str, float]:
-        model: TorchP2PFLModel = self.model  # type: ignore[assignment]
-        module = model.get_model()
-        try:
-            x, y = self._tensors(train=False)
-        except Exception:  # noqa: BLE001
-            return {}
-        if x.shape[0] == 0:
-            return {}
-        module.eval()
+    def _eval_body(self, x, y, acc) -> None:
+        module = self.model.get_model()
         native = getattr(module, "native_eval", None)
-        acc = torch.zeros(2, device=model.device)  # [sum loss, correct]
+        acc.zero_()
         bs = max(self.batch_size, 256)
         for s in range(0, x.shape[0], bs):
             xb, yb = x[s : s + bs], y[s : s + bs]
@@ -174,13 +252,51 @@ class TorchLearner(Learner):
                 native(xb, yb, acc)
             else:
                 ops.cross_entropy_eval(module(xb), yb, acc)
-        module.train()
-        tot = acc.tolist()
+
+    @torch.no_grad()
+    def evaluate(self) -> Dict[str, float]:
+        model: TorchP2PFLModel = self.model  # type: ignore[assignment]
+        module = model.get_model()
+        dev = model.device
+        cuda = dev.type == "cuda"
+        if cuda and self._stream is None:
+            self._stream = torch.cuda.Stream(dev)
+        ctx = torch.cuda.stream(self._stream) if cuda else _NullCtx()
+        if cuda:
+            self._stream.wait_stream(torch.cuda.current_stream(dev))
+        with ctx:
+            try:
+                x, y = self._tensors(train=False)
+            except Exception:  # noqa: BLE001
+                return {}
+            if x.shape[0] == 0:
+                return {}
+            module.eval()
+            if "acc" not in self._static:
+                self._static["acc"] = torch.zeros(2, device=dev)  # [sum loss, correct]
+            acc = self._static["acc"]
+            if cuda and self.use_cuda_graph:
+                self._state(model.layout.n_trainable, dev)
+                g = self._graph_for(("eval", x.shape[0], x.data_ptr()), lambda: self._eval_body(x, y, acc))
+                g.replay()
+                ops.native.count_launch(g.native_kernels)
+            else:
+                self._eval_body(x, y, acc)
+            module.train()
+            tot = acc.tolist()
         self.d2h_bytes += 8
         results = {"test_loss": tot[0] / x.shape[0], "test_metric": tot[1] / x.shape[0]}
         for k, v in results.items():
             logger.log_metric(self._self_addr, k, v)
         return results
+
+
+class _NullCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
 
 
 # name used by scripts written against the reference

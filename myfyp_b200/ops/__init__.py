@@ -216,23 +216,33 @@ def scaffold_finalize(c_i: torch.Tensor, dy: torch.Tensor, dc: torch.Tensor, x: 
 def adam_step(
     p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,
     weight_decay: float = 0.0, prox_mu: float = 0.0, prox_ref: Optional[torch.Tensor] = None, cv_global: Optional[torch.Tensor] = None,
-    cv_local: Optional[torch.Tensor] = None, cv_scale: float = 1.0, zero_grad: bool = True,
+    cv_local: Optional[torch.Tensor] = None, cv_scale: float = 1.0, zero_grad: bool = True, dev_state: Optional[torch.Tensor] = None,
 ) -> None:
-    """Adam over the flat slab.  ``g' = g + wd*p + mu*(p - ref) + cv_scale*(c - c_i)``; clears ``g`` afterwards."""
+    """Adam over the flat slab.  ``g' = g + wd*p + mu*(p - ref) + cv_scale*(c - c_i)``; clears ``g`` afterwards.
+
+    ``dev_state`` (3 floats on the device: step, 1-b1^step, 1-b2^step) replaces the host-side ``step``: it is advanced
+    by a 1-thread kernel and read by the update kernel, which is what makes a whole epoch CUDA-graph-capturable.
+    """
     if p.is_cuda:
         lib = native.load()
-        bc1, bc2 = 1.0 - beta1**step, 1.0 - beta2**step
+        bc1, bc2 = (1.0 - beta1**step, 1.0 - beta2**step) if dev_state is None else (1.0, 1.0)
         with native.device_guard(p.device):
+            if dev_state is not None:
+                native.check(lib.b2_adam_prepare(native.ptr(dev_state), ctypes.c_float(beta1), ctypes.c_float(beta2), native.stream_ptr(p.device)), "b2_adam_prepare")
+                native.count_launch()
             native.check(
                 lib.b2_adam_step(
                     native.ptr(p), native.ptr(g), native.ptr(m), native.ptr(v), ctypes.c_int64(p.numel()), ctypes.c_float(lr), ctypes.c_float(beta1), ctypes.c_float(beta2),
-                    ctypes.c_float(eps), ctypes.c_float(weight_decay), ctypes.c_float(bc1), ctypes.c_float(bc2), ctypes.c_float(prox_mu if prox_ref is not None else 0.0),
+                    ctypes.c_float(eps), ctypes.c_float(weight_decay), ctypes.c_float(bc1), ctypes.c_float(bc2), native.ptr(dev_state), ctypes.c_float(prox_mu if prox_ref is not None else 0.0),
                     native.ptr(prox_ref), native.ptr(cv_global), native.ptr(cv_local), ctypes.c_float(cv_scale), ctypes.c_int(1 if zero_grad else 0), native.stream_ptr(p.device),
                 ),
                 "b2_adam_step",
             )
         native.count_launch()
         return
+    if dev_state is not None:
+        dev_state[0] += 1
+        step = int(dev_state[0].item())
     gg = _effective_grad(p, g, weight_decay, prox_mu, prox_ref, cv_global, cv_local, cv_scale)
     m.mul_(beta1).add_(gg, alpha=1 - beta1)
     v.mul_(beta2).addcmul_(gg, gg, value=1 - beta2)

@@ -337,6 +337,48 @@ def test_native_mlp_learns(dev):
     assert after["test_metric"] > max(0.9, before)
 
 
+def test_cnn_learner_trains_and_gradients_live_in_the_slab(dev):
+    from myfyp_b200.learning.dataset import P2PFLDataset
+    from myfyp_b200.learning.torch_learner import TorchLearner
+    from myfyp_b200.models import cnn_model
+
+    data = P2PFLDataset.synthetic_cifar10(1024, 256, seed=2)
+    model = cnn_model(device="cuda:0", seed=0)
+    learner = TorchLearner(model, data, "n0", batch_size=64)
+    learner.set_epochs(2)
+    before = learner.evaluate()["test_metric"]
+    learner.fit()
+    after = learner.evaluate()
+    assert after["test_metric"] > max(0.8, before)
+    lo, hi = model.grad_slab.data_ptr(), model.grad_slab.data_ptr() + 4 * model.grad_slab.numel()
+    for p in model.get_model().parameters():
+        assert p.grad is not None and lo <= p.grad.data_ptr() < hi  # autograd accumulated in place, into the gradient slab
+    assert float(model.grad_slab.abs().max()) == 0.0  # and the fused optimizer cleared it
+
+
+@pytest.mark.parametrize("kind", ["mlp", "cnn"])
+def test_cuda_graph_epoch_equals_eager_epoch(dev, kind):
+    """A fit replayed from the captured epoch graph ends at the same parameters as the same fit run kernel by kernel."""
+    from myfyp_b200.learning.dataset import P2PFLDataset
+    from myfyp_b200.learning.torch_learner import TorchLearner
+    from myfyp_b200.models import cnn_model, mlp_model
+
+    mk = (lambda: mlp_model(device="cuda:0", seed=5, native=True)) if kind == "mlp" else (lambda: cnn_model(device="cuda:0", seed=5))
+    data = P2PFLDataset.synthetic_mnist(300, 64, seed=3) if kind == "mlp" else P2PFLDataset.synthetic_cifar10(300, 64, seed=3)
+    outs = []
+    for graph in (False, True):
+        model = mk()
+        learner = TorchLearner(model, data, "n", batch_size=64, shuffle=False, use_cuda_graph=graph)
+        for _ in range(2):  # second fit = a pure replay
+            learner.fit()
+        outs.append((model.slab.clone(), learner.evaluate()))
+    if kind == "mlp":  # our kernels are deterministic: replay == eager
+        torch.testing.assert_close(outs[0][0], outs[1][0], rtol=2e-3, atol=2e-4)
+    else:  # the autograd conv path may pick different (atomic, tf32) cuDNN algorithms under capture
+        assert (outs[0][0] - outs[1][0]).norm() < 5e-2 * outs[0][0].norm()
+    assert abs(outs[0][1]["test_loss"] - outs[1][1]["test_loss"]) < 5e-2
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_fedavg_pulls_from_peer_gpus():
     from myfyp_b200 import ops
