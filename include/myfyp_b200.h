@@ -53,6 +53,14 @@ int b2_scaffold_finalize(float* c_i, float* dy, float* dc, const float* x, const
  * call (the kernel re-zeroes them).  No reference counterpart (Krum is absent from p2pfl). */
 int64_t b2_krum_gram_workspace_bytes(void);
 int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* workspace, int passes, void* stream);
+/* Allocation-free variant of b2_krum_gram (no counterpart in the reference): same kernel, same output, but the split-K
+ * scratch is a 1 048 832-byte array built into the library image instead of a caller workspace.  For hosts that cannot
+ * allocate device memory where they call this (another runtime owns the HBM, or a device-wide synchronising cudaMalloc is
+ * not acceptable next to running training streams).  Limits: K <= 64, n <= b2_krum_gram_static_max_n() (2^26); larger
+ * requests fail with an error.  The first call on a device resolves the scratch address - issue it before any stream
+ * capture.  All calls share the scratch: do not let two of them overlap on the GPU. */
+int64_t b2_krum_gram_static_max_n(void);
+int b2_krum_gram_static(float* gram, const void* const* srcs, int K, int64_t n, int passes, void* stream);
 /* A7 Krum scores + ranking from a K x K squared-distance matrix: scores[i] = sum of the K-f-2 smallest d(i,j), j != i;
  * order[] = indices sorted by (score, index). */
 int b2_krum_select(const float* dist, int K, int f, float* scores, int* order, void* stream);

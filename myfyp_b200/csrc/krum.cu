@@ -13,6 +13,8 @@
 //     The MMA reads 128 A-rows: rows 64..127 alias the following atom - they only produce accumulator rows
 //     64..127, which nobody reads.
 // A7  scores + ranking in one tiny CTA.
+#include <mutex>
+
 #include "../../include/myfyp_b200.h"
 #include "common.cuh"
 #include "tcgen05.cuh"
@@ -255,6 +257,89 @@ int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* w
   float* partials = reinterpret_cast<float*>(static_cast<char*>(workspace) + GR_HEADER);
   krum_gram_kernel<<<grid, GR_THREADS, GR_SMEM, static_cast<cudaStream_t>(stream)>>>(gram, pt, K, n, passes, counter, partials);
   B2_LAUNCH_CHECK("krum_gram_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+//
+// b2_krum_gram_static: the same Gram kernel, for callers that must not allocate device memory.
+//
+// Who that is: a C/C++ host that runs the Krum scoring inside somebody else's process - an aggregation service thread
+// next to a trainer whose caching allocator has already claimed the HBM, a plugin inside a runtime that owns every byte
+// of device memory, a latency-critical control loop.  Such a caller has no torch allocator to borrow a workspace from,
+// cudaMalloc may simply fail there, and cudaMalloc / cudaFree synchronise the whole device, which would stall the other
+// nodes' training streams that share the GPU.  So the split-K scratch (completion counter + one partial Gram per CTA)
+// lives in a file-scope __device__ array that is part of the library image:
+//   * size: 256 B header + B2_STATIC_GRAM_CTAS (64) partials of 64 x 64 fp32 = 1 048 832 bytes, held by every GPU that
+//     loads the library until the process exits;
+//   * limits: K <= 64 models, n <= B2_STATIC_GRAM_MAX_N (2^26 coordinates = 256 MiB per model).  With at most 64 CTAs
+//     the kernel cannot stream a larger model at a sensible fraction of the bandwidth; bigger problems belong to
+//     b2_krum_gram with a caller-sized workspace.  Anything beyond the limits is rejected with an error, never clamped;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress with that device current -
+//     in host code the array's name is only a host-side handle, not a device pointer) and sets the kernel's
+//     shared-memory attribute; make that first call before any stream capture begins;
+//   * all calls share the one array and it keeps whatever the previous call left: the counter block is cleared on the
+//     stream before every launch, the partials are fully overwritten by the CTAs that run.  Two calls that overlap on
+//     the GPU (different streams, no dependency between them) race on the array - serialise them.
+// Inputs and the 64 x 64 output are still the caller's.  No cudaMalloc / cudaFree / allocating library call is made.
+#define B2_STATIC_GRAM_CTAS 64
+#define B2_STATIC_GRAM_MAX_N (int64_t(1) << 26)
+static __device__ __align__(256) unsigned char g_static_gram_scratch[GR_HEADER + B2_STATIC_GRAM_CTAS * GR_ROWS * GR_ROWS * sizeof(float)];
+
+int64_t b2_krum_gram_static_max_n(void) { return B2_STATIC_GRAM_MAX_N; }
+
+int b2_krum_gram_static(float* gram, const void* const* srcs, int K, int64_t n, int passes, void* stream) {
+  if (K < 1 || K > GR_ROWS) {
+    set_error("krum_gram_static: K=%d outside [1,%d]", K, GR_ROWS);
+    return 1;
+  }
+  if (n <= 0 || (n & 3)) {
+    set_error("krum_gram_static: n=%lld must be a positive multiple of 4", (long long)n);
+    return 1;
+  }
+  if (n > B2_STATIC_GRAM_MAX_N) {
+    set_error("krum_gram_static: n=%lld exceeds the built-in scratch limit of %lld coordinates; use b2_krum_gram with a workspace", (long long)n,
+              (long long)B2_STATIC_GRAM_MAX_N);
+    return 1;
+  }
+  if (gram == nullptr || srcs == nullptr) {
+    set_error("krum_gram_static: NULL argument");
+    return 1;
+  }
+  PtrTable pt;
+  for (int k = 0; k < B2_MAX_K; ++k) pt.p[k] = static_cast<const float*>(srcs[k < K ? k : 0]);
+  for (int k = 0; k < K; ++k)
+    if (!aligned16(srcs[k])) {
+      set_error("krum_gram_static: slab %d is not 16-byte aligned", k);
+      return 1;
+    }
+  // once per device, with that device current: resolve the device address of the scratch symbol
+  static void* scratch_ptr[64] = {nullptr};
+  static std::mutex setup_mutex;
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("krum_gram_static: device ordinal %d not supported", dev);
+    return 1;
+  }
+  {
+    std::lock_guard<std::mutex> lock(setup_mutex);
+    if (scratch_ptr[dev] == nullptr) {
+      void* p = nullptr;
+      B2_CUDA(cudaGetSymbolAddress(&p, g_static_gram_scratch));
+      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+      scratch_ptr[dev] = p;
+    }
+  }
+  unsigned char* base = static_cast<unsigned char*>(scratch_ptr[dev]);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t chunks = (n + GR_CC - 1) / GR_CC;
+  int grid = sm_count();
+  if (grid > B2_STATIC_GRAM_CTAS) grid = B2_STATIC_GRAM_CTAS;
+  if (chunks < grid) grid = (int)chunks;
+  B2_CUDA(cudaMemsetAsync(base, 0, GR_HEADER, s));  // the completion counter must start at zero
+  krum_gram_kernel<<<grid, GR_THREADS, GR_SMEM, s>>>(gram, pt, K, n, passes, reinterpret_cast<unsigned int*>(base), reinterpret_cast<float*>(base + GR_HEADER));
+  B2_LAUNCH_CHECK("krum_gram_kernel(static scratch)");
   return 0;
 }
 
