@@ -9,6 +9,10 @@
 //     (hi*hi + hi*lo + lo*hi) give fp32-class accuracy.  The accumulator lives in TMEM across ALL coordinate
 //     chunks of the CTA (split-K over coordinates across CTAs), is read once with tcgen05.ld, spilled to the
 //     workspace, and the last CTA to finish reduces the partial Grams in a fixed order.
+//     The MMA pipeline accumulates in fp32 with a small systematic drift per accumulation step, so one chain over
+//     thousands of k-steps loses a few 1e-4 relative on the (all-positive) diagonal.  The stages therefore rotate over
+//     8 independent TMEM accumulators (8 x 64 columns = the SM's whole tensor memory); the epilogue adds them in
+//     registers.  Chains are 8x shorter, the drift 8x smaller.
 //     smem tile per stage: 64 rows x 128 coords fp32 (4 swizzle atoms) for hi and for lo = 64 KB; 3 stages.
 //     The MMA reads 128 A-rows: rows 64..127 alias the following atom - they only produce accumulator rows
 //     64..127, which nobody reads.
@@ -31,6 +35,7 @@ constexpr int GR_STAGES = 3;
 constexpr int GR_PRODUCERS = 256;
 constexpr int GR_THREADS = GR_PRODUCERS + 32;       // + the MMA / TMEM warp
 constexpr int GR_SMEM = GR_STAGES * GR_STAGE_BYTES + GR_ATOM_BYTES /*over-read pad*/ + 1024 /*align*/;
+constexpr int GR_ACCS = 8;                          // TMEM accumulators used round-robin (8 x 64 columns = all 512)
 constexpr int GR_MAX_CTAS = 296;
 constexpr int GR_HEADER = 256;
 
@@ -53,7 +58,7 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
     tc::mbar_init(&done_bar, 1);
     tc::mbar_fence_init();
   }
-  if (warp == 8) tc::tmem_alloc<64>(&tmem_base_s);
+  if (warp == 8) tc::tmem_alloc<64 * GR_ACCS>(&tmem_base_s);
   // rows K..63 are never written by the producers: zero the whole tile area once
   for (int i = tid; i < (GR_STAGES * GR_STAGE_BYTES + GR_ATOM_BYTES) / 16; i += GR_THREADS) reinterpret_cast<float4*>(tiles)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   tc::fence_proxy_async();
@@ -115,7 +120,6 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
   } else if (tc::elect_one()) {
     // ================================ MMA issuer (one thread)
     const uint32_t idesc = tc::make_idesc(tc::FMT_TF32, 128, (uint32_t)kpad);
-    uint32_t accumulate = 0;
     for (int64_t it = 0; it < my_chunks; ++it) {
       const int s = (int)(it % GR_STAGES);
       const uint32_t ph = (uint32_t)((it / GR_STAGES) & 1);
@@ -123,17 +127,19 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
       tc::fence_after_sync();
       const uint32_t hi_addr = tc::smem_u32(tiles + s * GR_STAGE_BYTES);
       const uint32_t lo_addr = hi_addr + GR_TILE_BYTES;
+      const uint32_t d_tmem = tmem_base + (uint32_t)(it % GR_ACCS) * 64u;  // this stage's accumulator
+      uint32_t accumulate = it >= GR_ACCS ? 1u : 0u;                       // first visit overwrites
 #pragma unroll
       for (int a = 0; a < GR_ATOMS; ++a) {
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {  // 8 tf32 = 32 bytes per k-step inside the 128-byte swizzle row
           const uint32_t o = (uint32_t)a * GR_ATOM_BYTES + (uint32_t)ks * 32u;
           const uint64_t dh = tc::smem_desc_sw128(hi_addr + o), dl = tc::smem_desc_sw128(lo_addr + o);
-          tc::mma_tf32(tmem_base, dh, dh, idesc, accumulate);
+          tc::mma_tf32(d_tmem, dh, dh, idesc, accumulate);
           accumulate = 1;
           if (passes >= 3) {
-            tc::mma_tf32(tmem_base, dh, dl, idesc, 1);
-            tc::mma_tf32(tmem_base, dl, dh, idesc, 1);
+            tc::mma_tf32(d_tmem, dh, dl, idesc, 1);
+            tc::mma_tf32(d_tmem, dl, dh, idesc, 1);
           }
         }
       }
@@ -152,11 +158,16 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
 #pragma unroll
     for (int cb = 0; cb < 2; ++cb) {
       float v[32];
-      if (my_chunks > 0 && cb * 32 < kpad) {
-        tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
-      } else {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = 0.f;
+      for (int e = 0; e < 32; ++e) v[e] = 0.f;
+      if (cb * 32 < kpad) {
+        const int used = (int)(my_chunks < GR_ACCS ? my_chunks : GR_ACCS);  // accumulators that were written at all
+        for (int a = 0; a < used; ++a) {
+          float t[32];
+          tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * 64 + cb * 32), t);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] += t[e];
+        }
       }
 #pragma unroll
       for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(mine + row * GR_ROWS + cb * 32 + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
@@ -165,7 +176,7 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
   }
   __threadfence();
   __syncthreads();
-  if (warp == 8) tc::tmem_dealloc<64>(tmem_base);
+  if (warp == 8) tc::tmem_dealloc<64 * GR_ACCS>(tmem_base);
   if (tid == 0) {
     const unsigned int prev = atomicAdd(counter, 1u);
     is_last_s = (prev == gridDim.x - 1);
