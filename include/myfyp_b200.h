@@ -46,6 +46,25 @@ int b2_scaffold_server(float* x, float* c, const void* const* dys, const void* c
 /* T7 Scaffold client finalize: adj=(x-y)*inv_klr; dc=adj; c_i+=adj; dy=y-x.  Reference: scaffold_callback.py:124-140. */
 int b2_scaffold_finalize(float* c_i, float* dy, float* dc, const float* x, const float* y, float inv_klr, int64_t n, void* stream);
 
+/* A2 two-shot FedAvg across G GPUs as one kernel per GPU: reduce-scatter by coordinate shard + all-gather, both as peer
+ * loads, synchronised by flags in peer-mapped memory.  Every rank fills one b2_twoshot_args (in DEVICE memory) with the
+ * addresses of all ranks' inputs / outputs / flag blocks as mapped on ITS device - once - and launches with the same `epoch`
+ * (1, 2, 3... per call).  Flag blocks hold b2_twoshot_flag_bytes() bytes and start zeroed.  `ranks_in_launch` > 1 runs
+ * several ranks in one launch on one GPU (dev_args is then an array) - used for single-GPU testing.
+ * No reference counterpart (the reference averages pickled NumPy arrays on the host, fedavg.py:61-69). */
+#define B2_TWOSHOT_MAX_RANKS 16
+typedef struct {
+  const void* srcs[B2_TWOSHOT_MAX_RANKS];  /* input slab of every rank */
+  void* outs[B2_TWOSHOT_MAX_RANKS];        /* output slab of every rank (outs[rank] is written by this rank) */
+  void* flags[B2_TWOSHOT_MAX_RANKS];       /* flag block of every rank */
+  int64_t n;                               /* elements, multiple of 4 */
+  int world, rank;
+} b2_twoshot_args;
+int64_t b2_twoshot_flag_bytes(void);
+/* `weights` is a HOST array of `world` floats (n_g / sum n); `epoch` must be 1, 2, 3... on successive calls (same on every rank). */
+int b2_fedavg_twoshot(const b2_twoshot_args* dev_args, int ranks_in_launch, int64_t n, const float* weights, int world, unsigned int epoch, int max_ctas,
+                      void* stream);
+
 /* A6 Krum Gram matrix on tcgen05: gram[i*ld+j] = <src_i - src_0, src_j - src_0>, i,j < K <= 64, ld = 64, fp32 via
  * 3xTF32 split.  Split-K over coordinate chunks: every CTA keeps its partial Gram in TMEM, spills it to
  * `workspace` and the last CTA to finish reduces the partials in a fixed order (deterministic).

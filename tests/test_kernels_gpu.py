@@ -393,3 +393,24 @@ def test_fedavg_pulls_from_peer_gpus():
     med = ops.median(slabs, device=torch.device("cuda", 1))
     st = torch.stack([s.to("cuda:1") for s in slabs]).sort(dim=0).values
     torch.testing.assert_close(med, (st[1] + st[2]) / 2, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("world,n", [(2, 4096), (4, 235264), (8, 1 << 20), (3, 1000 * 4)])
+def test_twoshot_fedavg_emulated_ranks(dev, world, n):
+    """The fused reduce-scatter + all-gather kernel with all ranks in one launch (the single-GPU way to run ranks that wait on each other)."""
+    from myfyp_b200.parallel.collective import TwoShotFedAvg
+
+    coll = TwoShotFedAvg.emulated(n, world, dev)
+    g = torch.Generator().manual_seed(world)
+    for call in range(3):  # epochs advance, flags and counters are reused
+        xs = [torch.randn(n, generator=g).to(dev) for _ in range(world)]
+        w = torch.rand(world, generator=g)
+        w = (w / w.sum()).tolist()
+        for r in range(world):
+            coll.srcs[r].copy_(xs[r])
+            coll.outs[r].fill_(float("nan"))
+        coll(w)
+        torch.cuda.synchronize(dev)
+        ref = sum(x.double() * wi for x, wi in zip(xs, w)).float()
+        for r in range(world):
+            torch.testing.assert_close(coll.outs[r], ref, rtol=1e-5, atol=1e-5, msg=f"rank {r} call {call}")
