@@ -295,7 +295,7 @@ def run_ours(args) -> None:
             pass
         out = {
             "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": (value / base) if base else None, "dtype": "bf16" if args.model == "mlp" else "fp32+tf32",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": (value / base) if base else None, "dtype": "bf16" if args.model in ("mlp", "cnn") else "fp32+tf32",
             "data": "synthetic", "impl": "ours",
             "config": {
                 "model": {"cnn": "CNN (3 conv + 2 fc, 0.55M params) on CIFAR-10-shaped data", "mlp": "MLP 784-256-128-10 on MNIST-shaped data", "resnet18": "ResNet-18 CIFAR"}[args.model],

@@ -102,9 +102,9 @@ int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out,
 /* T1/T2 bf16 GEMM on tcgen05 + TMA: D[M,N] = epilogue(A[M,K] * B[N,K]^T).  See csrc/gemm.cu for the epilogue flags.
  * Reference: the three nn.Linear GEMMs of the MLP and their autograd backward (lightning_model.py:169-179). */
 typedef struct {
-  const void* A;      /* bf16 [M, lda]  K-major */
-  const void* B;      /* bf16 [N, ldb]  K-major */
-  int M, N, K;        /* K multiple of 64; lda/ldb in elements, multiples of 8 */
+  const void* A;      /* bf16 [M, lda] (K-major) or, with a_mn, [K, lda] */
+  const void* B;      /* bf16 [N, ldb] (K-major) or, with b_mn, [K, ldb] */
+  int M, N, K;        /* any sizes (TMA zero-fills the tails); lda/ldb in elements, multiples of 8 */
   int lda, ldb;
   float* out_f32;     /* optional fp32 [M, ldo] */
   void* out_bf16;     /* optional bf16 [M, ldo16] */
@@ -116,12 +116,24 @@ typedef struct {
   float* colsum;      /* optional fp32 [N]: += column sums of the output (bias gradient), atomic */
   int relu;           /* apply ReLU */
   int accumulate;     /* out_f32 += result instead of = */
+  int a_mn, b_mn;     /* operand stored transposed: A as [K, lda>=M], B as [K, ldb>=N] (MN-major UMMA operands) */
+  int split_k;        /* > 1: split the K loop over grid.z, atomically adding into out_f32 (which must hold 0 or the running sum) */
 } b2_gemm_args;
 int b2_gemm_bf16(const b2_gemm_args* args, void* stream);
 /* fp32 [R,C] (pitch lds) -> bf16 row-major copy (pitch ldd, optional), bf16 transposed copy [C,R] (pitch ldt, optional),
  * column sums += (optional, atomic).  Staging step of the GEMMs above; the reference has no counterpart (it trains in fp32
  * through torch autograd). */
 int b2_cast_transpose(const float* src, int R, int C, int lds, void* dst_bf16, int ldd, void* dst_bf16_t, int ldt, float* colsum, void* stream);
+
+/* T4/T5 convolution building blocks (NHWC bf16 activations = the [pixels, channels] matrices b2_gemm_bf16 reads and writes).
+ * Patch index order is (c, kh, kw) = PyTorch's [Cout, Cin, KH, KW] weights flattened, so weights are used in place.
+ * Reference path: torch conv2d / max_pool2d via autograd (the reference ships no CNN; BASELINE.json configs 2-4 name one). */
+int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H, int W, int C, void* stream);
+/* dz = dp routed to the remembered maximum, times the ReLU mask (y > 0) of the pre-pool activation */
+int b2_maxpool2_relu_bwd(const void* dp_bf16, const void* idx_u8, const void* y_bf16, void* dz_bf16, int B, int H, int W, int C, void* stream);
+int b2_colsum_bf16(const void* z_bf16, int M, int C, int ld, float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -209,10 +209,15 @@ class TorchP2PFLModel(P2PFLModel):
             self.model.to(device)
             self._int_entries = []
             self._adopt_module(self.model)
-            if getattr(self.model, "native", None) is not None or (device.type == "cuda" and getattr(self.model, "wants_native", False)):
-                from myfyp_b200.models.native_mlp import attach_native_mlp
+            if device.type == "cuda" and (getattr(self.model, "native", None) is not None or getattr(self.model, "wants_native", False)):
+                if hasattr(self.model, "features"):
+                    from myfyp_b200.models.native_cnn import attach_native_cnn
 
-                attach_native_mlp(self)
+                    attach_native_cnn(self, getattr(self.model, "image_size", 32))
+                else:
+                    from myfyp_b200.models.native_mlp import attach_native_mlp
+
+                    attach_native_mlp(self)
         else:
             self.slab = self.slab.to(device)
         return self

@@ -26,9 +26,21 @@ class CNN(nn.Module):
         return self.classifier(self.features(x.float()))
 
 
-def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, channels_last: bool = True, **kwargs):
+def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, native: Optional[bool] = None, **kwargs):
+    """``TorchP2PFLModel`` around a fresh CNN; ``native`` (default: on CUDA) attaches the hand-written training step
+    (patch gather + tcgen05 GEMMs, :mod:`myfyp_b200.models.native_cnn`) which the learner prefers over autograd / cuDNN."""
     from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
 
     if seed is not None:
         torch.manual_seed(seed)
-    return TorchP2PFLModel(CNN(**kwargs), device=device)
+    module = CNN(**kwargs)
+    module.image_size = kwargs.get("image_size", 32)
+    model = TorchP2PFLModel(module, device=device)
+    if native is None:
+        module.wants_native = True
+        native = model.device.type == "cuda"
+    if native:
+        from myfyp_b200.models.native_cnn import attach_native_cnn
+
+        attach_native_cnn(model, module.image_size)
+    return model

@@ -4,15 +4,14 @@ Attached to a CUDA ``TorchP2PFLModel`` wrapping :class:`~myfyp_b200.models.mlp.M
 slab (that is what gets aggregated / published); every step stages bf16 copies for the tensor cores.
 
 Per step (kernel ids from SURVEY section 8):
-  staging   ``cast_transpose``: X -> X16, X16^T ; W_l -> W16_l, W16_l^T               (bf16, both orientations)
-  forward   T1 ``gemm_bf16`` x L: H_l = relu(H_{l-1} W_l^T + b_l) -> H_l and H_l^T ; last layer -> fp32 logits
+  staging   ``cast_transpose``: X -> bf16 ; W_l -> bf16
+  forward   T1 ``gemm_bf16`` x L: H_l = relu(H_{l-1} W_l^T + b_l) (bf16) ; last layer -> fp32 logits
   loss      T3 ``xent_fwd_bwd``: loss, dlogits (already scaled by 1/B)
-  backward  T2 wgrad: dW_l = dZ_l^T H_{l-1}  (fp32 straight into the gradient slab)
-            T2 dgrad: dZ_{l-1} = (dZ_l W_l) * (H_{l-1} > 0) -> dZ and dZ^T, column sums -> db_{l-1}
+  backward  T2 wgrad: dW_l = dZ_l^T H_{l-1}  (fp32 straight into the gradient slab; both operands MN-major)
+            T2 dgrad: dZ_{l-1} = (dZ_l W_l) * (H_{l-1} > 0), column sums -> db_{l-1}     (W_l MN-major)
   (the fused optimizer T6 then runs over the whole slab - called by the learner)
 
-Keeping both orientations of every activation / gradient (a free, coalesced extra store in the producing
-epilogue) means every GEMM operand is K-major, so one TMA + UMMA descriptor layout serves all three GEMM kinds.
+The backward GEMMs read the forward pass's buffers as MN-major tensor-core operands, so nothing is ever transposed.
 
 Reference path for the same math: three ``nn.Linear`` + ReLU + ``log_softmax`` + ``cross_entropy`` through
 Lightning / autograd in fp32 (p2pfl/learning/frameworks/pytorch/lightning_model.py:169-191).
@@ -46,12 +45,9 @@ class NativeMLP:
             self.b.append(model.slab[eb.offset : eb.offset + eb.numel])
             self.gw.append(model.grad_slab[ew.offset : ew.offset + ew.numel].view(ew.shape))
             self.gb.append(model.grad_slab[eb.offset : eb.offset + eb.numel])
-        bf = torch.bfloat16
-        # bf16 weights, both orientations: W16[l] = [out, pad8(in)], W16T[l] = [in, pad8(out)]
-        self.w16 = [torch.zeros(self.sizes[i + 1], _pad8(self.sizes[i]), dtype=bf, device=dev) for i in range(self.L)]
-        self.w16t = [torch.zeros(self.sizes[i], _pad8(self.sizes[i + 1]), dtype=bf, device=dev) for i in range(self.L)]
+        # bf16 working copy of the weights: W16[l] = [out, pad8(in)]
+        self.w16 = [torch.zeros(self.sizes[i + 1], _pad8(self.sizes[i]), dtype=torch.bfloat16, device=dev) for i in range(self.L)]
         self._bufs: Dict[int, dict] = {}
-        self._weights_version = -1
 
     # ------------------------------------------------------------------ buffers per batch capacity
     def _buffers(self, batch: int) -> dict:
@@ -59,21 +55,17 @@ class NativeMLP:
         if cap not in self._bufs:
             dev, bf, s = self.model.device, torch.bfloat16, self.sizes
             self._bufs[cap] = {
-                # activations H_0 (=X) .. H_{L-1}: [B, pad8(f)] and transposed [f, pad8(B)]
-                "h": [torch.zeros(cap, _pad8(s[i]), dtype=bf, device=dev) for i in range(self.L)],
-                "ht": [torch.zeros(s[i], cap, dtype=bf, device=dev) for i in range(self.L)],
-                # dZ_1 .. dZ_L (gradient w.r.t. pre-activations): [B, pad8(f)] and [f, pad8(B)]
-                "dz": [torch.zeros(cap, _pad8(s[i + 1]), dtype=bf, device=dev) for i in range(self.L)],
-                "dzt": [torch.zeros(s[i + 1], cap, dtype=bf, device=dev) for i in range(self.L)],
+                "h": [torch.zeros(cap, _pad8(s[i]), dtype=bf, device=dev) for i in range(self.L)],  # H_0 (=X) .. H_{L-1}
+                "dz": [torch.zeros(cap, _pad8(s[i + 1]), dtype=bf, device=dev) for i in range(self.L)],  # dZ_1 .. dZ_L
                 "logits": torch.zeros(cap, s[-1], dtype=torch.float32, device=dev),
                 "dlogits": torch.zeros(cap, s[-1], dtype=torch.float32, device=dev),
             }
         return self._bufs[cap]
 
     def refresh_weights(self) -> None:
-        """fp32 slab -> bf16 W and W^T (after every optimizer step / model load)."""
+        """fp32 slab -> bf16 working copy (after every optimizer step / model load)."""
         for i in range(self.L):
-            ops.cast_transpose(self.w[i], self.sizes[i + 1], self.sizes[i], dst=self.w16[i], dst_t=self.w16t[i])
+            ops.cast_transpose(self.w[i], self.sizes[i + 1], self.sizes[i], dst=self.w16[i])
 
     # ------------------------------------------------------------------ forward
     def _forward(self, x: torch.Tensor, buf: dict) -> int:
@@ -82,29 +74,26 @@ class NativeMLP:
         if x2.dtype != torch.float32 or not x2.is_contiguous():
             x2 = x2.float().contiguous()
         s = self.sizes
-        ops.cast_transpose(x2, bsz, s[0], dst=buf["h"][0], dst_t=buf["ht"][0])
+        ops.cast_transpose(x2, bsz, s[0], dst=buf["h"][0])
         for i in range(self.L):
             last = i == self.L - 1
             ops.gemm_bf16(
                 buf["h"][i], self.w16[i], bsz, s[i + 1], s[i],
-                out_f32=buf["logits"] if last else None,
-                out_bf16=None if last else buf["h"][i + 1],
-                out_bf16_t=None if last else buf["ht"][i + 1],
-                bias=self.b[i], relu=not last,
+                out_f32=buf["logits"] if last else None, out_bf16=None if last else buf["h"][i + 1], bias=self.b[i], relu=not last,
             )
         return bsz
 
     # ------------------------------------------------------------------ public hooks used by TorchLearner
     def train_step(self, x: torch.Tensor, y: torch.Tensor, loss_out: torch.Tensor) -> None:
         """Forward + loss + backward; gradients land in the model's gradient slab, mean loss in ``loss_out[0]``."""
+        import ctypes
+
         self.refresh_weights()
         buf = self._buffers(x.shape[0])
         bsz = self._forward(x, buf)
         s, L = self.sizes, self.L
         native = ops.native
         lib = native.load()
-        import ctypes
-
         loss_out.zero_()
         with native.device_guard(x.device):
             native.check(
@@ -112,16 +101,14 @@ class NativeMLP:
                 "b2_xent_fwd_bwd",
             )
         native.count_launch()
-        # dZ_L = dlogits: bf16 in both orientations + bias gradient of the last layer (column sums)
-        ops.cast_transpose(buf["dlogits"], bsz, s[-1], dst=buf["dz"][L - 1], dst_t=buf["dzt"][L - 1], colsum=self.gb[L - 1])
+        # dZ_L = dlogits in bf16 + bias gradient of the last layer (column sums)
+        ops.cast_transpose(buf["dlogits"], bsz, s[-1], dst=buf["dz"][L - 1], colsum=self.gb[L - 1])
         for i in range(L - 1, -1, -1):
-            # wgrad: dW_i[out,in] = dZ_i^T[out,B] @ H_i^T[in,B]^T
-            ops.gemm_bf16(buf["dzt"][i], buf["ht"][i], s[i + 1], s[i], bsz, out_f32=self.gw[i])
+            # wgrad: dW_i[out,in] = dZ_i^T H_i      - dZ_i [B,out] and H_i [B,in] consumed as MN-major operands (K = batch)
+            ops.gemm_bf16(buf["dz"][i], buf["h"][i], s[i + 1], s[i], bsz, out_f32=self.gw[i], a_mn=True, b_mn=True)
             if i > 0:
-                # dgrad: dZ_{i-1}[B,in] = (dZ_i[B,out] @ W_i^T[in,out]^T) * (H_i > 0); column sums -> db_{i-1}
-                ops.gemm_bf16(
-                    buf["dz"][i], self.w16t[i], bsz, s[i], s[i + 1], out_bf16=buf["dz"][i - 1], out_bf16_t=buf["dzt"][i - 1], mask=buf["h"][i], colsum=self.gb[i - 1]
-                )
+                # dgrad: dZ_{i-1}[B,in] = (dZ_i[B,out] W_i[out,in]) * (H_i > 0) - W_i consumed MN-major; column sums -> db_{i-1}
+                ops.gemm_bf16(buf["dz"][i], self.w16[i], bsz, s[i], s[i + 1], out_bf16=buf["dz"][i - 1], mask=buf["h"][i], colsum=self.gb[i - 1], b_mn=True)
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:

@@ -343,7 +343,7 @@ def test_cnn_learner_trains_and_gradients_live_in_the_slab(dev):
     from myfyp_b200.models import cnn_model
 
     data = P2PFLDataset.synthetic_cifar10(1024, 256, seed=2)
-    model = cnn_model(device="cuda:0", seed=0)
+    model = cnn_model(device="cuda:0", seed=0, native=False)
     learner = TorchLearner(model, data, "n0", batch_size=64)
     learner.set_epochs(2)
     before = learner.evaluate()["test_metric"]
@@ -363,7 +363,7 @@ def test_cuda_graph_epoch_equals_eager_epoch(dev, kind):
     from myfyp_b200.learning.torch_learner import TorchLearner
     from myfyp_b200.models import cnn_model, mlp_model
 
-    mk = (lambda: mlp_model(device="cuda:0", seed=5, native=True)) if kind == "mlp" else (lambda: cnn_model(device="cuda:0", seed=5))
+    mk = (lambda: mlp_model(device="cuda:0", seed=5, native=True)) if kind == "mlp" else (lambda: cnn_model(device="cuda:0", seed=5, native=False))
     data = P2PFLDataset.synthetic_mnist(300, 64, seed=3) if kind == "mlp" else P2PFLDataset.synthetic_cifar10(300, 64, seed=3)
     outs = []
     for graph in (False, True):
@@ -414,3 +414,182 @@ def test_twoshot_fedavg_emulated_ranks(dev, world, n):
         ref = sum(x.double() * wi for x, wi in zip(xs, w)).float()
         for r in range(world):
             torch.testing.assert_close(coll.outs[r], ref, rtol=1e-5, atol=1e-5, msg=f"rank {r} call {call}")
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (256, 784, 32), (10, 128, 24), (300, 130, 200), (64, 27, 4096)])
+def test_gemm_tcgen05_mn_major_operands(dev, a_mn, b_mn, m, n, k):
+    """Operands stored transposed ([K, M] / [K, N]) consumed as MN-major UMMA operands: D = A B^T must not change."""
+    from myfyp_b200 import ops
+
+    pad8 = lambda x: (x + 7) // 8 * 8  # noqa: E731
+    a = _bf(torch.randn(m, k, device=dev))
+    b = _bf(torch.randn(n, k, device=dev))
+    a_store = torch.zeros(k, pad8(m), dtype=torch.bfloat16, device=dev) if a_mn else torch.zeros(m, pad8(k), dtype=torch.bfloat16, device=dev)
+    b_store = torch.zeros(k, pad8(n), dtype=torch.bfloat16, device=dev) if b_mn else torch.zeros(n, pad8(k), dtype=torch.bfloat16, device=dev)
+    if a_mn:
+        a_store[:, :m] = a.T
+    else:
+        a_store[:, :k] = a
+    if b_mn:
+        b_store[:, :n] = b.T
+    else:
+        b_store[:, :k] = b
+    out = torch.full((m, n), float("nan"), device=dev)
+    ops.gemm_bf16(a_store, b_store, m, n, k, out_f32=out, a_mn=a_mn, b_mn=b_mn)
+    ref = a.float() @ b.float().T
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=1e-3 * math.sqrt(k))
+
+
+@pytest.mark.parametrize("splits", [2, 7, 64])
+def test_gemm_tcgen05_split_k(dev, splits):
+    from myfyp_b200 import ops
+
+    m, n, k = 32, 27, 65536  # the wgrad shape of a first conv layer: tiny output, very long reduction
+    a_store = _bf(torch.randn(k, m, device=dev) * 0.1)  # [K, M]
+    b_store = torch.zeros(k, 32, dtype=torch.bfloat16, device=dev)
+    b_store[:, :n] = _bf(torch.randn(k, n, device=dev) * 0.1)
+    out = torch.zeros(m, n, device=dev)
+    ops.gemm_bf16(a_store, b_store, m, n, k, out_f32=out, a_mn=True, b_mn=True, split_k=splits)
+    ref = a_store.float().T @ b_store[:, :n].float()
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-2)
+
+
+@pytest.mark.parametrize("B,C,H,k,stride,pad,first", [(4, 3, 32, 3, 1, 1, True), (3, 32, 16, 3, 1, 1, False), (2, 64, 8, 3, 2, 1, False), (5, 128, 4, 4, 1, 0, False), (2, 16, 8, 1, 2, 0, False)])
+def test_im2col_col2im_match_unfold_fold(dev, B, C, H, k, stride, pad, first):
+    from myfyp_b200 import ops
+
+    F = torch.nn.functional
+    x = torch.randn(B, C, H, H, device=dev)
+    xq = x.to(torch.bfloat16).float()
+    oh = (H + 2 * pad - k) // stride + 1
+    kd = C * k * k
+    ld = (kd + 7) // 8 * 8
+    col = torch.zeros(B * oh * oh, ld, dtype=torch.bfloat16, device=dev)
+    src = x.contiguous() if first else xq.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+    ops.im2col(src, col, B, H, H, C, k, k, stride, pad, nchw_f32=first)
+    ref = F.unfold(xq, k, padding=pad, stride=stride).transpose(1, 2).reshape(B * oh * oh, kd)
+    assert torch.equal(col[:, :kd].float(), ref)
+    # col2im == fold (sum of overlapping patches), NHWC out
+    dcol = torch.zeros_like(col)
+    dcol[:, :kd] = torch.randn(B * oh * oh, kd, device=dev).to(torch.bfloat16)
+    dx = torch.empty(B, H, H, C, dtype=torch.bfloat16, device=dev)
+    ops.col2im(dcol, dx, B, H, H, C, k, k, stride, pad)
+    folded = F.fold(dcol[:, :kd].float().reshape(B, oh * oh, kd).transpose(1, 2), (H, H), k, padding=pad, stride=stride)
+    torch.testing.assert_close(dx.float().permute(0, 3, 1, 2), folded, rtol=2e-2, atol=2e-2)
+
+
+def test_maxpool_and_colsum(dev):
+    from myfyp_b200 import ops
+
+    F = torch.nn.functional
+    B, H, C = 3, 8, 32
+    y = torch.relu(torch.randn(B, H, H, C, device=dev)).to(torch.bfloat16)
+    p = torch.empty(B, H // 2, H // 2, C, dtype=torch.bfloat16, device=dev)
+    idx = torch.empty(B, H // 2, H // 2, C, dtype=torch.uint8, device=dev)
+    ops.maxpool2_fwd(y, p, idx, B, H, H, C)
+    yt = y.float().permute(0, 3, 1, 2).requires_grad_(True)
+    ref = F.max_pool2d(yt, 2)
+    assert torch.equal(p.float().permute(0, 3, 1, 2), ref.detach())
+    dp = torch.randn(B, H // 2, H // 2, C, device=dev).to(torch.bfloat16)
+    dz = torch.empty_like(y)
+    ops.maxpool2_relu_bwd(dp, idx, y, dz, B, H, H, C)
+    ref.backward(dp.float().permute(0, 3, 1, 2))
+    expect = (yt.grad * (yt.detach() > 0)).permute(0, 2, 3, 1)
+    torch.testing.assert_close(dz.float(), expect, rtol=0, atol=0)
+    out = torch.zeros(C, device=dev)
+    ops.colsum_bf16(dz.view(-1, C), B * H * H, C, out)
+    torch.testing.assert_close(out, dz.float().view(-1, C).sum(0), rtol=1e-4, atol=1e-4)
+
+
+class _RoundFwd(torch.autograd.Function):
+    """bf16 rounding in the forward pass only (where our kernels store an activation as bf16)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+class _RoundBwd(torch.autograd.Function):
+    """bf16 rounding of the gradient only (where our kernels store a gradient tensor as bf16)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).float()
+
+
+def _cnn_bf16_emulation(module, x, y):
+    """The CNN step in plain PyTorch fp32 math with bf16 rounding where the hand-written path rounds (weights, stored
+    activations, stored gradients); gradients w.r.t. the fp32 master weights by straight-through."""
+    F = torch.nn.functional
+    convs = [m for m in module.features if isinstance(m, torch.nn.Conv2d)]
+    fcs = [m for m in module.classifier if isinstance(m, torch.nn.Linear)]
+    params = [p for m in convs + fcs for p in (m.weight, m.bias)]
+    w = lambda m: m.weight + (m.weight.to(torch.bfloat16).float() - m.weight).detach()  # noqa: E731  value = bf16(W), grad -> W
+    a = _RoundFwd.apply(x.float())
+    for m in convs:
+        z = F.conv2d(_RoundBwd.apply(a), w(m), m.bias, stride=m.stride, padding=m.padding)
+        a = F.max_pool2d(_RoundFwd.apply(torch.relu(_RoundBwd.apply(z))), 2)
+    h = _RoundFwd.apply(torch.relu(_RoundBwd.apply(F.linear(_RoundBwd.apply(a.flatten(1)), w(fcs[0]), fcs[0].bias))))
+    logits = _RoundBwd.apply(F.linear(h, w(fcs[1]), fcs[1].bias))
+    loss = F.cross_entropy(logits, y)
+    grads = torch.autograd.grad(loss, params)
+    return loss.detach(), logits.detach(), dict(zip([n for m_ in ("features", "classifier") for n, _ in getattr(module, m_).named_parameters(prefix=m_)], grads))
+
+
+@pytest.mark.parametrize("batch", [16, 64])
+def test_native_cnn_step_matches_reference(dev, batch):
+    """Hand-written CNN forward/backward (patch gather + tcgen05 GEMMs): tight against the fp32 PyTorch restatement that
+    rounds to bf16 where the kernels do, loose against true-fp32 autograd / cuDNN."""
+    from myfyp_b200.models import cnn_model
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    model = cnn_model(device="cuda:0", seed=2, native=True)
+    module = model.get_model()
+    x = torch.randn(batch, 3, 32, 32, device=dev)
+    y = torch.randint(0, 10, (batch,), device=dev)
+    loss = torch.zeros(1, device=dev)
+    module.native_train_step(x, y, loss)
+    grads = model.grad_slab.clone()
+    model.grad_slab.zero_()
+    logits_native = module.native.logits(x)
+    emu_loss, emu_logits, emu_grads = _cnn_bf16_emulation(module, x, y)
+    model.grad_slab.zero_()
+    torch.testing.assert_close(logits_native, emu_logits, rtol=2e-2, atol=2e-3)
+    assert abs(loss.item() - emu_loss.item()) < 1e-3 * max(1.0, abs(emu_loss.item()))
+    for e in model.layout.in_order():
+        a, b = grads[e.offset : e.offset + e.numel], emu_grads[e.name].reshape(-1)
+        rel = ((a - b).norm() / (b.norm() + 1e-12)).item()
+        assert rel < 3e-2, (e.name, rel)
+    # true fp32 autograd: direction of the whole gradient
+    ref_loss = torch.nn.functional.cross_entropy(module(x), y)
+    ref_loss.backward()
+    ref = model.grad_slab.clone()
+    model.grad_slab.zero_()
+    assert abs(loss.item() - ref_loss.item()) < 2e-2 * max(1.0, abs(ref_loss.item()))
+    assert torch.nn.functional.cosine_similarity(grads, ref, dim=0).item() > 0.98
+
+
+def test_native_cnn_learns(dev):
+    from myfyp_b200.learning.dataset import P2PFLDataset
+    from myfyp_b200.learning.torch_learner import TorchLearner
+    from myfyp_b200.models import cnn_model
+
+    data = P2PFLDataset.synthetic_cifar10(2048, 512, seed=4)
+    model = cnn_model(device="cuda:0", seed=1, native=True)
+    assert getattr(model.get_model(), "native_train_step", None) is not None
+    learner = TorchLearner(model, data, "n0", batch_size=64)
+    learner.set_epochs(2)
+    before = learner.evaluate()["test_metric"]
+    learner.fit()
+    after = learner.evaluate()
+    assert after["test_metric"] > max(0.9, before), (before, after)
