@@ -72,6 +72,8 @@ class TorchLearner(Learner):
         self._graphs: Dict[Any, Any] = {}
         self._stream: Optional[torch.cuda.Stream] = None
         self._global_step = 0
+        self._rng = torch.Generator()
+        self._rng.manual_seed(torch.initial_seed() ^ (hash(self_addr) & 0xFFFFFFF))
 
     def get_framework(self) -> str:
         return "pytorch"
@@ -213,7 +215,9 @@ class TorchLearner(Learner):
                     if self._interrupt:
                         break
                     if self.shuffle:
-                        perm.copy_(torch.randperm(n, device=dev))
+                        # host-side generator: the device RNG must not be touched while ANOTHER node's thread is
+                        # capturing its graph (PyTorch registers the CUDA generator with an active capture)
+                        perm.copy_(torch.randperm(n, generator=self._rng))
                     g = self._graph_for(gkey, lambda: self._epoch_body(x, y, perm, losses, steps_per_epoch, st, terms))
                     g.replay()
                     all_losses[e * steps_per_epoch : (e + 1) * steps_per_epoch].copy_(losses)
@@ -222,7 +226,7 @@ class TorchLearner(Learner):
                     ops.native.count_launch(g.native_kernels)
             else:
                 for e in range(self.epochs):
-                    perm = torch.randperm(n, device=dev) if self.shuffle else torch.arange(n, device=dev)
+                    perm = torch.randperm(n, generator=self._rng).to(dev) if self.shuffle else torch.arange(n, device=dev)
                     steps += self._epoch_body(x, y, perm, all_losses[e * steps_per_epoch :], steps_per_epoch, st, terms)
             for cb in self.callbacks:
                 cb.on_fit_end(self, steps, self.lr)
