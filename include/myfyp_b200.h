@@ -99,6 +99,10 @@ int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momen
  * Reference: F.cross_entropy(log_softmax(x)) lightning_model.py:178,189 and torchmetrics Accuracy :204. */
 int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out, float* dlogits, float* correct, int B, int C, float scale, void* stream);
 
+/* confusion[label*C + argmax(logits)] += 1 (fp32 counts) - statistic behind accuracy / precision / recall / F1.
+ * Reference: the fork author's extended MLP metrics (mlp_pytorch.txt, torchmetrics F1/Precision/Recall). */
+int b2_confusion(const float* logits, const int64_t* labels, float* conf, int B, int C, void* stream);
+
 /* T1/T2 bf16 GEMM on tcgen05 + TMA: D[M,N] = epilogue(A[M,K] * B[N,K]^T).  See csrc/gemm.cu for the epilogue flags.
  * Reference: the three nn.Linear GEMMs of the MLP and their autograd backward (lightning_model.py:169-179). */
 typedef struct {

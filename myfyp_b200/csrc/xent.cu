@@ -55,7 +55,39 @@ __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ log
   }
 }
 
+// confusion[label * C + argmax] += 1 : the sufficient statistic for accuracy, per-class precision / recall / F1
+// (the fork author's extended MLP logs test_f1 / test_precision / test_recall, mlp_pytorch.txt)
+__global__ void __launch_bounds__(256) confusion_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ conf, int B, int C) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int row = blockIdx.x * 8 + warp; row < B; row += gridDim.x * 8) {
+    const float* x = logits + (int64_t)row * C;
+    float mx = -INFINITY;
+    int amax = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) {
+      const float v = x[c];
+      if (v > mx) { mx = v; amax = c; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, amax, o);
+      if (om > mx || (om == mx && oa < amax)) { mx = om; amax = oa; }
+    }
+    if (lane == 0) atomicAdd(conf + (int64_t)labels[row] * C + amax, 1.f);
+  }
+}
+
 }  // namespace b2
+
+extern "C" int b2_confusion(const float* logits, const int64_t* labels, float* conf, int B, int C, void* stream) {
+  if (B <= 0 || C <= 0) return 0;
+  int grid = (B + 7) / 8;
+  const int cap = b2::sm_count() * 8;
+  if (grid > cap) grid = cap;
+  b2::confusion_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, labels, conf, B, C);
+  B2_LAUNCH_CHECK("confusion_kernel");
+  return 0;
+}
 
 extern "C" int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out, float* dlogits, float* correct, int B, int C, float scale, void* stream) {
   if (B <= 0 || C <= 0) return 0;

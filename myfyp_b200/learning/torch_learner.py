@@ -52,6 +52,7 @@ class TorchLearner(Learner):
         max_steps_per_epoch: Optional[int] = None,
         data_on_host: bool = False,
         use_cuda_graph: bool = True,
+        extra_metrics: bool = False,
     ) -> None:
         super().__init__(model, data, self_addr, aggregator)
         self.batch_size, self.lr, self.optimizer = batch_size, lr, optimizer
@@ -59,6 +60,8 @@ class TorchLearner(Learner):
         self.persist_optimizer, self.shuffle = persist_optimizer, shuffle
         self.max_steps_per_epoch = max_steps_per_epoch
         self.use_cuda_graph = use_cuda_graph
+        # extra_metrics: also report macro test_precision / test_recall / test_f1 (the fork author's MLP logs them)
+        self.extra_metrics = extra_metrics
         # data_on_host: the partition stays in pinned host memory and is copied to the GPU at every fit /
         # evaluate (the end-to-end mode of bench.py); default is device-resident data
         self.data_on_host = data_on_host
@@ -245,17 +248,24 @@ class TorchLearner(Learner):
     def interrupt_fit(self) -> None:
         self._interrupt = True
 
-    def _eval_body(self, x, y, acc) -> None:
+    def _eval_body(self, x, y, acc, conf=None) -> None:
         module = self.model.get_model()
         native = getattr(module, "native_eval", None)
         acc.zero_()
+        if conf is not None:
+            conf.zero_()
         bs = max(self.batch_size, 256)
         for s in range(0, x.shape[0], bs):
             xb, yb = x[s : s + bs], y[s : s + bs]
             if native is not None:
                 native(xb, yb, acc)
+                if conf is not None:
+                    ops.confusion(module.native.logits(xb), yb, conf)
             else:
-                ops.cross_entropy_eval(module(xb), yb, acc)
+                logits = module(xb)
+                ops.cross_entropy_eval(logits, yb, acc)
+                if conf is not None:
+                    ops.confusion(logits, yb, conf)
 
     @torch.no_grad()
     def evaluate(self) -> Dict[str, float]:
@@ -279,17 +289,25 @@ class TorchLearner(Learner):
             if "acc" not in self._static:
                 self._static["acc"] = torch.zeros(2, device=dev)  # [sum loss, correct]
             acc = self._static["acc"]
+            conf = None
+            if self.extra_metrics:
+                ncls = int(y.max().item()) + 1 if "conf" not in self._static else self._static["conf"].shape[0]
+                if "conf" not in self._static:
+                    self._static["conf"] = torch.zeros(ncls, ncls, device=dev)
+                conf = self._static["conf"]
             if cuda and self.use_cuda_graph:
                 self._state(model.layout.n_trainable, dev)
-                g = self._graph_for(("eval", x.shape[0], x.data_ptr()), lambda: self._eval_body(x, y, acc))
+                g = self._graph_for(("eval", x.shape[0], x.data_ptr(), conf is not None), lambda: self._eval_body(x, y, acc, conf))
                 g.replay()
                 ops.native.count_launch(g.native_kernels)
             else:
-                self._eval_body(x, y, acc)
+                self._eval_body(x, y, acc, conf)
             module.train()
             tot = acc.tolist()
         self.d2h_bytes += 8
         results = {"test_loss": tot[0] / x.shape[0], "test_metric": tot[1] / x.shape[0]}
+        if conf is not None:
+            results.update(ops.prf_from_confusion(conf))
         for k, v in results.items():
             logger.log_metric(self._self_addr, k, v)
         return results

@@ -86,6 +86,23 @@ class P2PFLogger:
     def add_handler(self, handler: logging.Handler) -> None:
         self._logger.addHandler(handler)
 
+    def enable_async(self) -> None:
+        """Hand records to a background thread through a queue (the reference's AsyncLogger decorator,
+        management/logger/decorators/async_logger.py:29-58): formatting and I/O leave the learning threads."""
+        import queue
+        from logging.handlers import QueueHandler, QueueListener
+
+        if getattr(self, "_listener", None) is not None:
+            return
+        q: "queue.Queue" = queue.Queue(-1)
+        handlers = list(self._logger.handlers)
+        for h in handlers:
+            self._logger.removeHandler(h)
+        self._listener = QueueListener(q, *handlers, respect_handler_level=True)
+        self._listener.start()
+        self._logger.addHandler(QueueHandler(q))
+        atexit.register(self._listener.stop)
+
     def connect_web(self, url: str, key: str) -> None:
         """Push logs/metrics to a P2PFL-web-services-compatible REST endpoint."""
         from myfyp_b200.management.web_services import P2pflWebServices, WebLogHandler

@@ -79,6 +79,10 @@ class Node:
         self.learner: Learner = learner(model, data, self.addr, self.aggregator, **kwargs) if isinstance(learner, type) else learner
         if not isinstance(learner, type):
             self.learner.set_addr(self.addr)
+        if simulation:
+            from myfyp_b200.learning.simulation import try_init_learner_with_simulation
+
+            self.learner = try_init_learner_with_simulation(self.learner)
 
         self.__running = False
         self.state = NodeState(self.addr, simulation=simulation)

@@ -338,6 +338,31 @@ def cross_entropy_eval(logits: torch.Tensor, labels: torch.Tensor, acc: torch.Te
         acc[1] += (logits.argmax(dim=1) == labels).sum()
 
 
+def confusion(logits: torch.Tensor, labels: torch.Tensor, conf: torch.Tensor) -> None:
+    """``conf[label, argmax] += 1`` (``conf`` is a C x C fp32 matrix)."""
+    b, c = logits.shape
+    if logits.is_cuda:
+        lg = logits.contiguous().float()
+        lib = native.load()
+        with native.device_guard(logits.device):
+            native.check(lib.b2_confusion(native.ptr(lg), native.ptr(labels), native.ptr(conf), b, c, native.stream_ptr(logits.device)), "b2_confusion")
+        native.count_launch()
+    else:
+        idx = labels * c + logits.argmax(dim=1)
+        conf.view(-1).index_add_(0, idx, torch.ones_like(idx, dtype=conf.dtype))
+
+
+def prf_from_confusion(conf: torch.Tensor) -> dict:
+    """Macro precision / recall / F1 from a confusion matrix (rows = true class, columns = predicted)."""
+    conf = conf.double().cpu()
+    tp = conf.diag()
+    prec = tp / conf.sum(0).clamp_min(1e-12)
+    rec = tp / conf.sum(1).clamp_min(1e-12)
+    f1 = 2 * prec * rec / (prec + rec).clamp_min(1e-12)
+    present = conf.sum(1) > 0
+    return {"test_precision": float(prec[present].mean()), "test_recall": float(rec[present].mean()), "test_f1": float(f1[present].mean())}
+
+
 # ====================================================================== T1/T2: tcgen05 GEMM + staging
 class _GemmArgs(ctypes.Structure):
     _fields_ = [

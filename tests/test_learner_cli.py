@@ -1,0 +1,152 @@
+"""Learner, callbacks, simulation pool, CLI and settings behaviour on the CPU path."""
+
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from myfyp_b200.learning.aggregators import FedProx, Scaffold
+from myfyp_b200.learning.callbacks import CallbackFactory, FedProxCallback, SCAFFOLDCallback
+from myfyp_b200.learning.dataset import P2PFLDataset
+from myfyp_b200.learning.learner import LearnerFactory
+from myfyp_b200.learning.simulation import FitPool, VirtualNodeLearner
+from myfyp_b200.learning.torch_learner import TorchLearner
+from myfyp_b200.models import cnn_model, mlp_model
+from myfyp_b200.settings import Settings
+
+
+def test_fit_and_evaluate_learn_and_log_metrics():
+    from myfyp_b200.experiment import Experiment
+    from myfyp_b200.management.logger import logger
+
+    data = P2PFLDataset.synthetic_mnist(512, 128, seed=3)
+    model = mlp_model(seed=0)
+    assert LearnerFactory.create_learner(model) is TorchLearner
+    learner = TorchLearner(model, data, "learner-node", batch_size=32, extra_metrics=True)
+    logger.register_node("learner-node", False)
+    logger.experiment_started("learner-node", Experiment("experiment", 1))
+    before = learner.evaluate()
+    learner.set_epochs(2)
+    learner.fit()
+    after = learner.evaluate()
+    assert after["test_metric"] > max(0.9, before["test_metric"]) and after["test_loss"] < before["test_loss"]
+    assert {"test_precision", "test_recall", "test_f1"} <= set(after) and after["test_f1"] > 0.9
+    assert model.get_contributors() == ["learner-node"] and model.get_num_samples() == 512
+    local = logger.get_local_logs()["experiment"][0]["learner-node"]["train_loss"]
+    assert len(local) == 2 * 16 and local[-1][1] < local[0][1]
+    assert "test_metric" in logger.get_global_logs()["experiment"]["learner-node"]
+
+
+def test_cnn_learner_cpu_path():
+    data = P2PFLDataset.synthetic_cifar10(512, 64, seed=1)
+    learner = TorchLearner(cnn_model(seed=0), data, "n", batch_size=32, lr=2e-3)
+    learner.set_epochs(5)
+    before = learner.evaluate()["test_loss"]
+    learner.fit()
+    after = learner.evaluate()
+    assert after["test_loss"] < 0.5 * before and after["test_metric"] > 0.6
+
+
+def test_interrupt_fit_stops_early():
+    data = P2PFLDataset.synthetic_mnist(4096, 64)
+    learner = TorchLearner(mlp_model(seed=0), data, "n", batch_size=8)
+    learner.set_epochs(50)
+    import threading
+
+    t = threading.Thread(target=learner.fit)
+    t.start()
+    learner.interrupt_fit()
+    t.join(20)
+    assert not t.is_alive()
+
+
+def test_fedprox_term_pulls_towards_the_global_model():
+    data = P2PFLDataset.synthetic_mnist(256, 32, seed=2)
+    drift = {}
+    for mu in (0.0, 10.0):
+        torch.manual_seed(0)
+        model = mlp_model(seed=0)
+        start = model.slab.clone()
+        learner = TorchLearner(model, data, "n", aggregator=FedProx(mu=mu), batch_size=32, shuffle=False)
+        assert [c.get_name() for c in learner.callbacks] == ["fedprox"] and learner.callbacks[0].mu == mu
+        learner.set_epochs(3)
+        learner.fit()
+        drift[mu] = float((model.slab - start).norm())
+    assert drift[10.0] < 0.7 * drift[0.0]
+
+
+def test_scaffold_callback_produces_the_deltas_the_aggregator_needs():
+    data = P2PFLDataset.synthetic_mnist(128, 32, seed=2)
+    model = mlp_model(seed=0)
+    learner = TorchLearner(model, data, "n", aggregator=Scaffold(), batch_size=32, lr=1e-2, optimizer="sgd")
+    cb = learner.callbacks[0]
+    assert isinstance(cb, SCAFFOLDCallback)
+    x = model.slab.clone()
+    learner.fit()
+    info = model.get_info("scaffold")
+    n = model.layout.n_trainable
+    torch.testing.assert_close(info["delta_y_i"][:n], (model.slab - x)[:n])
+    steps = 4
+    torch.testing.assert_close(info["delta_c_i"][:n], ((x - model.slab) / (steps * 1e-2))[:n], rtol=1e-4, atol=1e-5)  # c_i started at 0
+    torch.testing.assert_close(cb.c_i, info["delta_c_i"][:n])
+    # the wire form is NumPy (reference-compatible pickle)
+    import pickle
+
+    blob = pickle.loads(model.encode_parameters())
+    assert isinstance(blob["additional_info"]["scaffold"]["delta_y_i"], np.ndarray)
+    # a global_c coming back from the aggregator is picked up at the next fit
+    model.add_info("scaffold", {"global_c": torch.ones_like(model.slab)})
+    learner.update_callbacks_with_model_info()
+    learner.fit()
+    assert float(cb.c.mean()) == 1.0
+    with pytest.raises(ValueError):
+        CallbackFactory.create_callbacks("pytorch", type("A", (), {"get_required_callbacks": lambda self: ["nope"]})())
+    assert FedProxCallback.get_name() == "fedprox"
+
+
+def test_virtual_learner_admission_control():
+    FitPool.configure(1)
+    data = P2PFLDataset.synthetic_mnist(64, 16)
+    v = VirtualNodeLearner(TorchLearner(mlp_model(seed=0), data, "n"))
+    v.set_epochs(1)
+    v.fit()
+    assert v.evaluate()["test_metric"] >= 0.0 and v.get_framework() == "pytorch"
+    v.interrupt_fit()  # the reference raises NotImplementedError here
+    FitPool.configure(16)
+
+
+def test_settings_follow_mutation():
+    Settings.HEARTBEAT_TIMEOUT = 50
+    assert Settings.WAIT_HEARTBEATS_CONVERGENCE == 10.0  # derived at read time (the reference freezes it at import)
+    Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.5
+    assert Settings.WAIT_HEARTBEATS_CONVERGENCE == 0.5
+
+
+def test_cli_lists_and_runs_examples():
+    out = subprocess.run([sys.executable, "-m", "myfyp_b200", "experiment", "list"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "mnist" in out.stdout and "byzantine" in out.stdout
+    out = subprocess.run([sys.executable, "-m", "myfyp_b200", "experiment", "run", "nope"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 1
+    out = subprocess.run([sys.executable, "-m", "myfyp_b200", "launch"], capture_output=True, text=True, timeout=120)
+    assert "Not implemented yet" in out.stdout
+    out = subprocess.run(
+        [sys.executable, "-m", "myfyp_b200", "experiment", "run", "mnist", "--nodes", "2", "--rounds", "1", "--measure_time", "--log-level", "ERROR", "--samples-per-node", "100"],
+        capture_output=True, text=True, timeout=300,
+    )
+    assert out.returncode == 0 and "seconds" in out.stdout
+
+
+def test_native_library_loads_without_a_gpu():
+    from myfyp_b200.ops import native
+
+    lib = native.load()
+    assert lib.b2_version() >= 100
+    assert lib.b2_device_count() >= 0
+
+
+def test_build_entry_point():
+    import __graft_entry__ as g
+
+    g.build()
