@@ -7,8 +7,8 @@ One *step* = one full federated round of the whole federation (vote -> evaluate 
 gossip -> FedAvg -> diffusion) through the public API: ``Node(...)``, ``connect``, ``set_start_learning(rounds, 1)``.
 The federation is fixed (8 nodes, CNN on CIFAR-10-shaped synthetic data, fully connected, FedAvg, every node in the
 train set) and is spread over the N GPUs ("strong" scaling; N = 8 is exactly "one node per B200").
-N = 1 uses the in-memory protocol in one process; N > 1 uses the gRPC protocol between ranks for the control plane
-and CUDA-IPC slab descriptors + peer loads over NVLink for the data plane.
+N = 1 uses the in-memory protocol in one process; N > 1 uses the unix-socket protocol between ranks for the control
+plane (B2_BENCH_PROTOCOL=grpc selects gRPC) and CUDA-IPC slab descriptors + peer loads over NVLink for the data plane.
 
 `value` is device-timed (CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks)
 with device-resident data; `e2e` repeats the same K rounds with every node's partition coming from pinned host
@@ -155,13 +155,19 @@ def run_ours(args) -> None:
     parts = make_data(args.model, n_nodes)
     if multi:
         job = os.environ.get("MASTER_PORT", "29500")
-        addrs = [f"unix:///tmp/b2bench-{job}-{i}.sock" for i in range(n_nodes)]
-        for i in mine:
-            try:
-                os.unlink(addrs[i][len("unix://"):])
-            except OSError:
-                pass
-        proto = GrpcCommunicationProtocol
+        if os.environ.get("B2_BENCH_PROTOCOL", "uds") == "grpc":
+            addrs = [f"unix:///tmp/b2bench-{job}-{i}.sock" for i in range(n_nodes)]
+            for i in mine:
+                try:
+                    os.unlink(addrs[i][len("unix://"):])
+                except OSError:
+                    pass
+            proto = GrpcCommunicationProtocol
+        else:  # the box-local control plane: pickled frames over unix sockets
+            from myfyp_b200.communication.protocols.uds.uds_communication_protocol import UdsCommunicationProtocol
+
+            addrs = [f"uds:///tmp/b2bench-{job}-{i}.sock" for i in range(n_nodes)]
+            proto = UdsCommunicationProtocol
     else:
         addrs = [f"node-{i}" for i in range(n_nodes)]
         proto = InMemoryCommunicationProtocol
@@ -246,10 +252,25 @@ def run_ours(args) -> None:
     native.reset_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    for n in nodes.values():
+        n.learning_workflow.timings.clear()
+    from myfyp_b200.management.logger import logger as _lg
+
+    _lg.reset_metrics()
     e0.record(torch.cuda.current_stream(dev))
     run_rounds(args.steps)
     e1.record(torch.cuda.current_stream(dev))
     barrier()
+    stage_ms = {}
+    if nodes:
+        from collections import defaultdict
+
+        acc_t = defaultdict(float)
+        for n in nodes.values():
+            for name, dt in n.learning_workflow.timings:
+                acc_t[name] += dt
+        stage_ms = {k: round(1e3 * v / len(nodes) / args.steps, 2) for k, v in acc_t.items()}
+        stage_ms.update({k: round(sum(v) / max(len(v), 1), 2) for k, v in _lg.get_device_times().items()})
     ms = allmax(e0.elapsed_time(e1))
     launches = int(allsum(native.launches()))
     clocks = sampler.stop(world) if rank == 0 else {}
@@ -271,16 +292,6 @@ def run_ours(args) -> None:
         e2e = {"value": args.steps / wall, "unit": "rounds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * wall / args.steps}
         set_host_mode(False)
 
-    stage_ms = {}
-    if nodes:
-        from collections import defaultdict
-
-        acc = defaultdict(float)
-        for n in nodes.values():
-            for name, dt in n.learning_workflow.timings:
-                acc[name] += dt
-        rounds_run = args.warmup + args.steps + (0 if args.no_e2e else args.steps + max(1, min(args.warmup, 2)))
-        stage_ms = {k: round(1e3 * v / len(nodes) / rounds_run, 2) for k, v in acc.items()}
     for n in nodes.values():
         n.stop()
     if multi:
@@ -301,7 +312,7 @@ def run_ours(args) -> None:
                 "model": {"cnn": "CNN (3 conv + 2 fc, 0.55M params) on CIFAR-10-shaped data", "mlp": "MLP 784-256-128-10 on MNIST-shaped data", "resnet18": "ResNet-18 CIFAR"}[args.model],
                 "nodes": n_nodes, "nodes_per_gpu": n_nodes / world, "train_set_size": n_nodes, "topology": "full", "aggregator": "FedAvg",
                 "samples_per_node": SAMPLES_PER_NODE, "global_batch": BATCH * n_nodes, "batch_per_node": BATCH, "local_epochs": 1, "seq_len": None,
-                "protocol": "grpc+cuda-ipc" if multi else "in-memory", "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
+                "protocol": (os.environ.get("B2_BENCH_PROTOCOL", "uds") + "+cuda-ipc") if multi else "in-memory", "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
                 "step": "one federated round of all nodes",
             },
             "clocks": clocks, "gpu_launches": launches, "stage_ms_per_round_rank0": stage_ms,

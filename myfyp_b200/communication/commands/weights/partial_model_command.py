@@ -43,8 +43,9 @@ class PartialModelCommand(Command):
             if models_added != []:
                 # we are inside the sender's RPC / call stack: announce from the gossiper thread, never block here
                 # (a synchronous fan-out from inside a handler can exhaust the peers' RPC workers)
+                # announcements are cumulative (receivers merge them), so a newer one supersedes an unsent older one
                 self.communication_protocol.broadcast_async(
-                    self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round)
+                    self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round), coalesce=True
                 )
         except DecodingParamsError:
             handle_bad_model(st, self.stop, source, "Error decoding parameters", self.communication_protocol)

@@ -52,10 +52,24 @@ class Gossiper(threading.Thread):
             self.__cv.notify_all()
 
     # ------------------------------------------------------------------ flood
-    def add_message(self, msg: Any, pending_neis: List[str]) -> None:
+    def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None) -> None:
+        """Queue ``msg`` for ``pending_neis``.  With a ``coalesce_key`` a still-unsent message queued under the same key is
+        *replaced* (its remaining recipients get the newer message instead): a burst of state announcements costs one
+        message per neighbour, not one per state change."""
         if not pending_neis:
             return
         with self.__cv:
+            if coalesce_key is not None:
+                for i, (old, neis) in enumerate(self.__pending):
+                    if isinstance(old, dict) and old.get("_ckey") == coalesce_key:
+                        merged = list(dict.fromkeys([*neis, *pending_neis]))
+                        tagged = dict(msg)
+                        tagged["_ckey"] = coalesce_key
+                        self.__pending[i] = (tagged, merged)
+                        self.__cv.notify()
+                        return
+                msg = dict(msg)
+                msg["_ckey"] = coalesce_key
             self.__pending.append((msg, list(pending_neis)))
             self.__cv.notify()
 

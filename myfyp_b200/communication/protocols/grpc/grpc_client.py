@@ -8,7 +8,7 @@ from typing import Any, Dict, List, Optional
 
 from myfyp_b200.communication.protocols.client import Client
 from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError
-from myfyp_b200.communication.protocols.grpc.grpc_neighbors import GrpcNeighbors, make_stub
+from myfyp_b200.communication.protocols.grpc.grpc_neighbors import GrpcNeighbors
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
 
@@ -47,7 +47,7 @@ class GrpcClient(Client):
             except KeyError as e:
                 raise NeighborNotConnectedError(f"Neighbor {nei} not found.") from e
             if stub is None and create_connection:
-                channel, stub = make_stub(nei)  # temporary channel to a non-direct neighbour
+                channel, stub = self.__neighbors.make_stub(nei)  # temporary channel to a non-direct neighbour
             if stub is None:
                 raise NeighborNotConnectedError("Neighbor not directly connected (no stub and create_connection is false).")
             payload = msg

@@ -72,14 +72,16 @@ class GrpcCommunicationProtocol(CommunicationProtocol):
         self._client.broadcast(msg, node_list)
 
     @running
-    def broadcast_async(self, msg: Any) -> None:
-        """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers)."""
+    def broadcast_async(self, msg: Any, coalesce: bool = False) -> None:
+        """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers).
+        ``coalesce``: a queued, not yet sent message of the same command and round is superseded by this one."""
         if isinstance(msg, dict) and "hash" in msg:
             self._gossiper.check_and_set_processed(msg["hash"])
         nodes = list(self._neighbors.get_all(only_direct=True))
         if isinstance(msg, dict) and "hash" in msg:
             msg["seen"] = [self.addr, *nodes]
-        self._gossiper.add_message(msg, nodes)
+        key = (msg.get("cmd"), msg.get("round")) if coalesce and isinstance(msg, dict) else None
+        self._gossiper.add_message(msg, nodes, coalesce_key=key)
 
     @running
     def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]:

@@ -77,6 +77,10 @@ def make_stub(addr: str) -> Tuple[Optional[grpc.Channel], Any]:
 
 
 class GrpcNeighbors(Neighbors):
+    def make_stub(self, addr: str) -> Tuple[Any, Any]:
+        """``(closable channel or None, stub)`` for ``addr`` - the transport hook subclasses override."""
+        return make_stub(addr)
+
     def refresh_or_add(self, addr: str, time: float) -> None:
         with self.neis_lock:
             cur = self.neis.get(addr)
@@ -90,7 +94,7 @@ class GrpcNeighbors(Neighbors):
             logger.debug(self.self_addr, f"🔍 Found node {addr}")
             return (None, None, _time.time())
         logger.debug(self.self_addr, f"🤝 Adding {addr}")
-        channel, stub = make_stub(addr)
+        channel, stub = self.make_stub(addr)
         try:
             if handshake_msg:
                 err = stub.handshake(self.self_addr, Settings.GRPC_TIMEOUT)

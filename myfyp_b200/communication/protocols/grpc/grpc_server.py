@@ -36,34 +36,34 @@ def local_server(addr: str) -> Optional["GrpcServer"]:
 class GrpcServer:
     def __init__(self, addr: str, gossiper: Gossiper, neighbors, commands: Optional[List[Command]] = None) -> None:
         self.addr = addr
-        self.__commands: Dict[str, Command] = {c.get_name(): c for c in (commands or [])}
-        self.__gossiper = gossiper
-        self.__neighbors = neighbors
-        self.__server: Optional[grpc.Server] = None
-        self.__started = False
-        self.__terminated = threading.Event()
+        self._commands: Dict[str, Command] = {c.get_name(): c for c in (commands or [])}
+        self._gossiper = gossiper
+        self._neighbors = neighbors
+        self._server: Optional[grpc.Server] = None
+        self._started = False
+        self._terminated = threading.Event()
 
     @property
     def gossiper(self) -> Gossiper:
-        return self.__gossiper
+        return self._gossiper
 
     # ------------------------------------------------------------------ lifecycle
     def start(self, wait: bool = False) -> None:
         opts = [("grpc.max_send_message_length", MAX_MSG), ("grpc.max_receive_message_length", MAX_MSG), ("grpc.so_reuseport", 0)]
-        self.__server = grpc.server(futures.ThreadPoolExecutor(max_workers=32, thread_name_prefix=f"grpc-{self.addr}"), options=opts)
+        self._server = grpc.server(futures.ThreadPoolExecutor(max_workers=32, thread_name_prefix=f"grpc-{self.addr}"), options=opts)
         handlers = {
             "handshake": grpc.unary_unary_rpc_method_handler(self._rpc_handshake, request_deserializer=wire.decode_handshake, response_serializer=wire.encode_response),
             "disconnect": grpc.unary_unary_rpc_method_handler(self._rpc_disconnect, request_deserializer=wire.decode_handshake, response_serializer=wire.encode_empty),
             "send": grpc.unary_unary_rpc_method_handler(self._rpc_send, request_deserializer=wire.decode_root, response_serializer=wire.encode_response),
         }
-        self.__server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(SERVICE, handlers),))
+        self._server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(SERVICE, handlers),))
         creds = self._server_credentials()
-        port = self.__server.add_secure_port(self.addr, creds) if creds is not None else self.__server.add_insecure_port(self.addr)
+        port = self._server.add_secure_port(self.addr, creds) if creds is not None else self._server.add_insecure_port(self.addr)
         if port == 0 and not self.addr.startswith("unix:"):
             raise RuntimeError(f"cannot bind {self.addr}")
-        self.__server.start()
-        self.__started = True
-        self.__terminated.clear()
+        self._server.start()
+        self._started = True
+        self._terminated.clear()
         with _local_lock:
             _local_servers[self.addr] = self
         logger.debug(self.addr, f"gRPC started at {self.addr}")
@@ -81,44 +81,44 @@ class GrpcServer:
         with _local_lock:
             if _local_servers.get(self.addr) is self:
                 del _local_servers[self.addr]
-        self.__started = False
-        if self.__server is not None:
-            self.__server.stop(0)
-            self.__server = None
-        self.__terminated.set()
+        self._started = False
+        if self._server is not None:
+            self._server.stop(0)
+            self._server = None
+        self._terminated.set()
 
     def wait_for_termination(self) -> None:
-        self.__terminated.wait()
+        self._terminated.wait()
 
     def is_running(self) -> bool:
-        return self.__started
+        return self._started
 
     def add_command(self, cmds: Union[Command, List[Command]]) -> None:
         for c in cmds if isinstance(cmds, list) else [cmds]:
-            self.__commands[c.get_name()] = c
+            self._commands[c.get_name()] = c
 
     # ------------------------------------------------------------------ servicer logic (also called in-process)
     def handshake(self, addr: str) -> Optional[str]:
-        if not self.__started:
+        if not self._started:
             return "server not running"
-        if self.__neighbors.add(addr, non_direct=False, handshake_msg=False) or self.__neighbors.exists(addr):
+        if self._neighbors.add(addr, non_direct=False, handshake_msg=False) or self._neighbors.exists(addr):
             return None
         return "Cannot add the node (duplicated or wrong direction)"
 
     def disconnect(self, addr: str) -> None:
-        self.__neighbors.remove(addr, disconnect_msg=False)
+        self._neighbors.remove(addr, disconnect_msg=False)
 
     def send(self, msg: Dict[str, Any]) -> Optional[str]:
         """Dedupe -> dispatch -> TTL re-gossip (order of the reference's gRPC server, grpc_server.py:161-217)."""
-        if not self.__started:
+        if not self._started:
             return "server not running"
         is_weights = "weight" in msg
-        if not is_weights and not self.__gossiper.check_and_set_processed(msg["hash"]):
+        if not is_weights and not self._gossiper.check_and_set_processed(msg["hash"]):
             return None
         cmd = msg["cmd"]
         if cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS:
             logger.debug(self.addr, f"📫 {cmd.upper()} received from {msg['source']}")
-        handler = self.__commands.get(cmd)
+        handler = self._commands.get(cmd)
         if handler is None:
             logger.error(self.addr, f"Unknown command: {cmd} from {msg['source']}")
             return f"Unknown command: {cmd}"
@@ -135,9 +135,9 @@ class GrpcServer:
             fwd = dict(msg)
             fwd["ttl"] = msg["ttl"] - 1
             seen = msg.get("seen") or []
-            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n != msg["source"] and n not in seen]
+            pending = [n for n in self._neighbors.get_all(only_direct=True) if n != msg["source"] and n not in seen]
             fwd["seen"] = [*seen, *pending]
-            self.__gossiper.add_message(fwd, pending)
+            self._gossiper.add_message(fwd, pending)
         return None
 
     # ------------------------------------------------------------------ RPC adapters

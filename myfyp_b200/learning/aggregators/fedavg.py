@@ -38,7 +38,8 @@ def weighted_average(models: List[P2PFLModel], weights: List[float], num_samples
     if all(isinstance(m, TorchP2PFLModel) for m in models):
         first: TorchP2PFLModel = models[0]  # type: ignore[assignment]
         if len(models) == 1 and abs(weights[0] - 1.0) < 1e-12:
-            return first.build_copy(params=first.slab if first.model is None else first.publish(), num_samples=num_samples, contributors=contributors)
+            # one model, weight 1: hand out the same immutable slab (with its arena coordinates, if any) - no kernel, no copy
+            return first.build_copy(params=first.as_ref() if first.model is None else first.publish(), num_samples=num_samples, contributors=contributors)
         out = ops.fedavg([m.slab for m in models], weights, device=ops.pick_device([m.slab for m in models], prefer=first.slab.device))  # type: ignore[attr-defined]
         return first.build_copy(params=out, num_samples=num_samples, contributors=contributors)
     # generic (non-torch) models: per-layer NumPy, like the reference

@@ -10,6 +10,7 @@ aggregation kernel pulls it out of our HBM when it reduces.  Off-fabric peers ge
 
 from __future__ import annotations
 
+import time
 from typing import Any, List, Set, Type, Union
 
 from myfyp_b200.communication.commands.message.metrics_command import MetricsCommand
@@ -18,6 +19,7 @@ from myfyp_b200.communication.commands.message.models_ready_command import Model
 from myfyp_b200.communication.commands.weights.partial_model_command import PartialModelCommand
 from myfyp_b200.learning.aggregators.aggregator import NoModelsToAggregateError
 from myfyp_b200.management.logger import logger
+from myfyp_b200.settings import Settings
 from myfyp_b200.stages.base_node.start_learning_stage import _transport
 from myfyp_b200.stages.stage import EarlyStopException, Stage, check_early_stop
 from myfyp_b200.stages.stage_factory import StageFactory
@@ -32,25 +34,37 @@ class TrainStage(Stage):
     def execute(state=None, communication_protocol=None, learner=None, aggregator=None, **kwargs) -> Union[Type[Stage], None]:
         if state is None or communication_protocol is None or aggregator is None or learner is None:
             raise Exception("Invalid parameters on TrainStage.")
+        t = [time.perf_counter()]
+
+        def lap(name: str) -> None:  # wall-time split of the stage, read by benchmarks (logger.get_device_times())
+            t.append(time.perf_counter())
+            logger.log_device_time(f"train_stage/{name}", 1e3 * (t[-1] - t[-2]))
+
         try:
             check_early_stop(state)
             aggregator.set_nodes_to_aggregate(state.train_set)
             check_early_stop(state)
             evaluate_and_broadcast(state, learner, communication_protocol)
             check_early_stop(state)
+            lap("evaluate")
 
             logger.info(state.addr, "🏋️‍♀️ Training...")
             learner.fit()
             check_early_stop(state)
+            lap("fit")
 
             models_added = aggregator.add_model(learner.get_model().snapshot_model())
             communication_protocol.broadcast(communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=state.round))
+            lap("publish")
             TrainStage.__gossip_model_aggregation(state, communication_protocol, aggregator)
             check_early_stop(state)
+            lap("gossip")
 
             agg_model = aggregator.wait_and_get_aggregation()
+            lap("aggregate")
             learner.set_model(agg_model)
             communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
+            lap("adopt")
             return StageFactory.get_stage("GossipModelStage")
         except EarlyStopException:
             return None
@@ -72,6 +86,13 @@ class TrainStage(Stage):
         def status_fn() -> Any:
             return [(n, aggregated_by(n)) for n in communication_protocol.get_neighbors(only_direct=False) if n in state.train_set]
 
+        # What was already offered to whom in this round.  The loop below is event driven (it runs again as soon as any
+        # announcement arrives), so without this memory every wake-up would re-send the same model to every peer that
+        # has not finished yet - O(n^3) transfers per round in a full mesh.  An identical offer is repeated only after
+        # `reoffer_after` seconds (covers a lost message, like the reference's periodic re-send does).
+        offered: dict = {}
+        reoffer_after = max(1.0, 20 * Settings.GOSSIP_MODELS_PERIOD)
+
         def model_fn(node: str) -> Any:
             try:
                 model = aggregator.get_model(aggregated_by(node))
@@ -80,6 +101,11 @@ class TrainStage(Stage):
                 return None
             if state.round is None:
                 raise Exception("Round not initialized.")
+            key = (node, frozenset(model.get_contributors()))
+            now = time.monotonic()
+            if now - offered.get(key, -1e9) < reoffer_after:
+                return None
+            offered[key] = now
             return communication_protocol.build_weights(
                 PartialModelCommand.get_name(), state.round, _transport(model, communication_protocol, node), model.get_contributors(), model.get_num_samples()
             )

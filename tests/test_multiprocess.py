@@ -8,7 +8,7 @@ import time
 import numpy as np
 
 
-def _worker(rank, addrs, q, rounds):
+def _worker(rank, addrs, q, rounds, proto_name="grpc"):
     import torch
 
     torch.set_num_threads(1)
@@ -23,7 +23,10 @@ def _worker(rank, addrs, q, rounds):
 
     logger.set_level("ERROR")
     data = P2PFLDataset.synthetic_mnist(400, 100, seed=0).generate_partitions(2, RandomIIDPartitionStrategy)[rank]
-    node = Node(mlp_model(seed=rank), data, address=addrs[rank], protocol=GrpcCommunicationProtocol, batch_size=32)
+    from myfyp_b200.communication.protocols.uds.uds_communication_protocol import UdsCommunicationProtocol
+
+    proto = GrpcCommunicationProtocol if proto_name == "grpc" else UdsCommunicationProtocol
+    node = Node(mlp_model(seed=rank), data, address=addrs[rank], protocol=proto, batch_size=32)
     node.start()
     q.put(("up", rank))
     if rank == 0:
@@ -44,12 +47,16 @@ def _worker(rank, addrs, q, rounds):
     node.stop()
 
 
-def test_two_processes_grpc_unix_sockets():
+import pytest
+
+
+@pytest.mark.parametrize("proto_name", ["grpc", "uds"])
+def test_two_processes_over_sockets(proto_name):
     ctx = mp.get_context("spawn")
     d = tempfile.mkdtemp()
-    addrs = [f"unix://{d}/n{i}.sock" for i in range(2)]
+    addrs = [f"unix://{d}/n{i}.sock" if proto_name == "grpc" else f"uds://{d}/n{i}.sock" for i in range(2)]
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, addrs, q, 2)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, addrs, q, 2, proto_name)) for r in range(2)]
     for p in procs:
         p.start()
     results = {}

@@ -8,6 +8,7 @@ from myfyp_b200.communication.commands.command import Command
 from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError, ProtocolNotStartedError
 from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
 from myfyp_b200.communication.protocols.memory.memory_communication_protocol import InMemoryCommunicationProtocol
+from myfyp_b200.communication.protocols.uds.uds_communication_protocol import UdsCommunicationProtocol
 from myfyp_b200.settings import Settings
 from myfyp_b200.utils.utils import set_test_settings
 
@@ -20,7 +21,15 @@ class GrpcOverSockets(GrpcCommunicationProtocol):
         super().__init__(addr, commands)
 
 
-PROTOCOLS = [GrpcCommunicationProtocol, GrpcOverSockets, InMemoryCommunicationProtocol]
+class UdsOverSockets(UdsCommunicationProtocol):
+    """Unix-socket protocol with the in-process shortcut off (frames really cross the socket)."""
+
+    def __init__(self, addr=None, commands=None):
+        Settings.GRPC_LOCAL_SHORTCUT = False
+        super().__init__(addr, commands)
+
+
+PROTOCOLS = [GrpcCommunicationProtocol, GrpcOverSockets, InMemoryCommunicationProtocol, UdsOverSockets]
 
 
 class MockCommand(Command):
