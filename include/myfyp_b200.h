@@ -88,17 +88,25 @@ int b2_krum_select(const float* dist, int K, int f, float* scores, int* order, v
 /* T6 fused Adam over a flat slab; g' = g + wd*p + prox_mu*(p - prox_ref) + cv_scale*(cv_global - cv_local); clears g.
  * Reference: torch.optim.Adam (lightning_model.py:181-183), Scaffold term scaffold_callback.py:90-110. */
 int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
-                 float bias_corr2, const float* dev_state, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale,
-                 int zero_grad, void* stream);
+                 float bias_corr2, const float* dev_state, float step_offset, void* p_bf16, float prox_mu, const float* prox_ref, const float* cv_global,
+                 const float* cv_local, float cv_scale, int zero_grad, void* stream);
 /* Device-resident Adam step state {step, 1-beta1^step, 1-beta2^step}: advance it by one step.  When `dev_state` is passed to
  * b2_adam_step the bias corrections are read from it (so a captured CUDA graph of an epoch replays correctly). */
 int b2_adam_prepare(float* state, float beta1, float beta2, void* stream);
+/* Graph-friendly stepping: with `dev_state` and step_offset > 0 the step number is dev_state[0] + step_offset (steps finished
+ * before this graph replay, kept on the device, plus the index inside the captured epoch, baked into the launch);
+ * b2_adam_advance adds the epoch's step count once per replay.  `p_bf16` (optional) receives a bf16 mirror of the updated
+ * parameters - the tensor-core operands of the next step; b2_cast_slab (re)builds the whole mirror after a model load. */
+int b2_adam_advance(float* state, float n_steps, void* stream);
+int b2_cast_slab(const float* p, void* p_bf16, int64_t n, void* stream);
 int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momentum, float weight_decay, float prox_mu, const float* prox_ref,
                 const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream);
 /* T3+T8 fused log-softmax + NLL (+ gradient, + argmax accuracy).  loss_out/correct are accumulated atomically.
  * Reference: F.cross_entropy(log_softmax(x)) lightning_model.py:178,189 and torchmetrics Accuracy :204. */
 int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float* loss_out, float* dlogits, float* correct, int B, int C, float scale, void* stream);
 
+/* Training variant in one block: loss written, dlogits as bf16 (pitch ld16) for the backward GEMMs, bias gradient added. */
+int b2_xent_train(const float* logits, const int64_t* labels, float* loss_out, void* dlogits_bf16, int ld16, float* bias_grad, int B, int C, float scale, void* stream);
 /* confusion[label*C + argmax(logits)] += 1 (fp32 counts) - statistic behind accuracy / precision / recall / F1.
  * Reference: the fork author's extended MLP metrics (mlp_pytorch.txt, torchmetrics F1/Precision/Recall). */
 int b2_confusion(const float* logits, const int64_t* labels, float* conf, int B, int C, void* stream);
@@ -138,6 +146,13 @@ int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H
 /* dz = dp routed to the remembered maximum, times the ReLU mask (y > 0) of the pre-pool activation */
 int b2_maxpool2_relu_bwd(const void* dp_bf16, const void* idx_u8, const void* y_bf16, void* dz_bf16, int B, int H, int W, int C, void* stream);
 int b2_colsum_bf16(const void* z_bf16, int M, int C, int ld, float* out, void* stream);
+/* Fused forward tail: 2x2 max-pool of y [B,2PH,2PW,C] (winner index kept) scattered straight into the NEXT layer's col matrix
+ * (geometry KH,KW,stride,pad over the pooled [B,PH,PW,C] map); the pooled tensor is never materialised. */
+int b2_pool_im2col(const void* y_bf16, void* idx_u8, void* col_bf16, int ldc, int B, int PH, int PW, int C, int KH, int KW, int stride, int pad, void* stream);
+/* Fused backward head: col2im of the next layer's dcol -> unpool to the remembered winner -> ReLU mask -> dz [B,2PH,2PW,C],
+ * bias_grad[c] += column sums of dz. */
+int b2_unpool_col2im(const void* dcol_bf16, int ldc, const void* idx_u8, const void* y_bf16, void* dz_bf16, float* bias_grad, int B, int PH, int PW, int C, int KH, int KW,
+                     int stride, int pad, void* stream);
 
 #ifdef __cplusplus
 }

@@ -118,6 +118,86 @@ __global__ void __launch_bounds__(256) maxpool2_relu_bwd_kernel(const __nv_bfloa
   }
 }
 
+// Fused forward tail of a conv block: 2x2 max-pool of Y (remembering the winner) AND the patch gather of the NEXT layer in
+// one pass - the pooled value is scattered straight into the next layer's col matrix (up to KH*KW positions), the
+// pooled activation itself is never materialised.  `g` is the NEXT layer's geometry over the pooled map [B, g.H, g.W, g.C].
+// Entries of col that correspond to padding taps are never written and keep the zero they were allocated with.
+__global__ void __launch_bounds__(256) pool_im2col_kernel(const __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ idx, __nv_bfloat16* __restrict__ col, ConvGeom g, int ldc) {
+  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, KK = g.KH * g.KW;
+  const int64_t total = (int64_t)g.B * g.H * g.W * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int64_t q = i / C;
+    const int pw = (int)(q % g.W), ph = (int)((q / g.W) % g.H), b = (int)(q / ((int64_t)g.W * g.H));
+    const __nv_bfloat16* src = y + (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + c;
+    __nv_bfloat16 bv = src[0];
+    float best = __bfloat162float(bv);
+    int bi = 0;
+    const __nv_bfloat16 r1 = src[C], r2 = src[(int64_t)W2 * C], r3 = src[(int64_t)W2 * C + C];
+    if (__bfloat162float(r1) > best) { best = __bfloat162float(r1); bv = r1; bi = 1; }
+    if (__bfloat162float(r2) > best) { best = __bfloat162float(r2); bv = r2; bi = 2; }
+    if (__bfloat162float(r3) > best) { best = __bfloat162float(r3); bv = r3; bi = 3; }
+    idx[i] = (uint8_t)bi;
+    for (int kh = 0; kh < g.KH; ++kh) {
+      const int th = ph + g.pad - kh;
+      if (th < 0 || th % g.stride) continue;
+      const int oh = th / g.stride;
+      if (oh >= g.OH) continue;
+      for (int kw = 0; kw < g.KW; ++kw) {
+        const int tw = pw + g.pad - kw;
+        if (tw < 0 || tw % g.stride) continue;
+        const int ow = tw / g.stride;
+        if (ow >= g.OW) continue;
+        col[(((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)c * KK + kh * g.KW + kw] = bv;
+      }
+    }
+  }
+}
+
+// Fused backward head of a conv block: col2im of the NEXT layer's dcol (gather over its taps) -> gradient of the pooled
+// activation -> routed to the remembered max position, times the ReLU mask -> dZ [B, 2H, 2W, C], plus the bias gradient
+// (column sums of dZ) reduced per block in shared memory.  One pass, no dP / P buffers.
+__global__ void __launch_bounds__(256) unpool_col2im_kernel(const __nv_bfloat16* __restrict__ dcol, const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ y,
+                                                            __nv_bfloat16* __restrict__ dz, float* __restrict__ bias_grad, ConvGeom g, int ldc) {
+  extern __shared__ float s_db[];  // C floats
+  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, KK = g.KH * g.KW;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
+  __syncthreads();
+  const int64_t total = (int64_t)g.B * g.H * g.W * C;
+  const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int64_t q = i / C;
+    const int pw = (int)(q % g.W), ph = (int)((q / g.W) % g.H), b = (int)(q / ((int64_t)g.W * g.H));
+    float acc = 0.f;
+    for (int kh = 0; kh < g.KH; ++kh) {
+      const int th = ph + g.pad - kh;
+      if (th < 0 || th % g.stride) continue;
+      const int oh = th / g.stride;
+      if (oh >= g.OH) continue;
+      for (int kw = 0; kw < g.KW; ++kw) {
+        const int tw = pw + g.pad - kw;
+        if (tw < 0 || tw % g.stride) continue;
+        const int ow = tw / g.stride;
+        if (ow >= g.OW) continue;
+        acc += __bfloat162float(dcol[(((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)c * KK + kh * g.KW + kw]);
+      }
+    }
+    const int win = idx[i];
+    const int64_t base = (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + c;
+    const int64_t offs[4] = {0, C, (int64_t)W2 * C, (int64_t)W2 * C + C};
+    const __nv_bfloat16 gq = __float2bfloat16_rn(acc);  // the value the unfused path stores as dP
+    const bool live = __bfloat162float(y[base + offs[win]]) > 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dz[base + offs[k]] = (k == win && live) ? gq : zero;
+    if (live && bias_grad != nullptr) atomicAdd(&s_db[c], __bfloat162float(gq));
+  }
+  __syncthreads();
+  if (bias_grad != nullptr)
+    for (int c = threadIdx.x; c < C; c += blockDim.x)
+      if (s_db[c] != 0.f) atomicAdd(bias_grad + c, s_db[c]);
+}
+
 // out[c] += sum_m z[m, c]   (bias gradient of a conv layer): each block reduces a slab of rows in shared memory
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ z, int M, int C, int ld, float* __restrict__ out, int rows_per_block) {
   extern __shared__ float s_acc[];  // C floats
@@ -181,6 +261,34 @@ int b2_maxpool2_relu_bwd(const void* dp_bf16, const void* idx_u8, const void* y_
   maxpool2_relu_bwd_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dp_bf16), static_cast<const uint8_t*>(idx_u8), static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(dz_bf16), B, H, W, C);
   B2_LAUNCH_CHECK("maxpool2_relu_bwd_kernel");
+  return 0;
+}
+
+int b2_pool_im2col(const void* y_bf16, void* idx_u8, void* col_bf16, int ldc, int B, int PH, int PW, int C, int KH, int KW, int stride, int pad, void* stream) {
+  ConvGeom g{B, PH, PW, C, KH, KW, stride, pad, (PH + 2 * pad - KH) / stride + 1, (PW + 2 * pad - KW) / stride + 1};
+  if (g.OH <= 0 || g.OW <= 0 || ldc < C * KH * KW) {
+    set_error("pool_im2col: bad geometry");
+    return 1;
+  }
+  const int64_t total = (int64_t)B * PH * PW * C;
+  pool_im2col_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(y_bf16), static_cast<uint8_t*>(idx_u8),
+                                                                                            static_cast<__nv_bfloat16*>(col_bf16), g, ldc);
+  B2_LAUNCH_CHECK("pool_im2col_kernel");
+  return 0;
+}
+
+int b2_unpool_col2im(const void* dcol_bf16, int ldc, const void* idx_u8, const void* y_bf16, void* dz_bf16, float* bias_grad, int B, int PH, int PW, int C, int KH, int KW,
+                     int stride, int pad, void* stream) {
+  ConvGeom g{B, PH, PW, C, KH, KW, stride, pad, (PH + 2 * pad - KH) / stride + 1, (PW + 2 * pad - KW) / stride + 1};
+  if (C > 8192) {
+    set_error("unpool_col2im: C=%d too wide", C);
+    return 1;
+  }
+  const int64_t total = (int64_t)B * PH * PW * C;
+  unpool_col2im_kernel<<<stream_grid(total, 256, 2), 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dcol_bf16), static_cast<const uint8_t*>(idx_u8), static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(dz_bf16), bias_grad, g,
+      ldc);
+  B2_LAUNCH_CHECK("unpool_col2im_kernel");
   return 0;
 }
 

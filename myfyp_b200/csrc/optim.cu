@@ -3,6 +3,8 @@
 //   g' = g + wd*p + mu*(p - p_ref) + cv_scale*(c - c_i)
 // Reference path: torch.optim.Adam(lr=1e-3) per Lightning fit (lightning_model.py:181-183) plus a Python
 // callback for Scaffold (scaffold_callback.py:90-110); FedProx does not exist there.
+#include <cuda_bf16.h>
+
 #include "../../include/myfyp_b200.h"
 #include "common.cuh"
 
@@ -38,12 +40,20 @@ __global__ void adam_prepare_kernel(float* __restrict__ state, float b1, float b
   state[2] = 1.f - powf(b2, step);
 }
 
+__global__ void adam_advance_kernel(float* __restrict__ state, float n) { state[0] += n; }
+
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4, float lr,
-                                                   float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, const float* __restrict__ state, FusedTerms t,
-                                                   int zero_grad) {
+                                                   float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, const float* __restrict__ state, float step_offset,
+                                                   __nv_bfloat16* __restrict__ p16, FusedTerms t, int zero_grad) {
   if (state != nullptr) {
-    inv_bc1 = 1.f / state[1];
-    inv_sqrt_bc2 = rsqrtf(state[2]);
+    if (step_offset > 0.f) {  // step = (steps finished before this graph replay, on the device) + (index inside the graph, baked)
+      const float step = state[0] + step_offset;
+      inv_bc1 = 1.f / (1.f - powf(b1, step));
+      inv_sqrt_bc2 = rsqrtf(1.f - powf(b2, step));
+    } else {
+      inv_bc1 = 1.f / state[1];
+      inv_sqrt_bc2 = rsqrtf(state[2]);
+    }
   }
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -56,7 +66,26 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float
     B2_ADAM1(x) B2_ADAM1(y) B2_ADAM1(z) B2_ADAM1(w)
 #undef B2_ADAM1
     p[i] = pv; m[i] = mv; v[i] = vv;
+    if (p16 != nullptr) {  // bf16 mirror of the parameters = the tensor-core operands of the next step (no separate cast kernels)
+      __nv_bfloat162 lo = __floats2bfloat162_rn(pv.x, pv.y), hi = __floats2bfloat162_rn(pv.z, pv.w);
+      uint2 w;
+      w.x = *reinterpret_cast<uint32_t*>(&lo);
+      w.y = *reinterpret_cast<uint32_t*>(&hi);
+      reinterpret_cast<uint2*>(p16)[i] = w;
+    }
     if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256) cast_slab_kernel(const float4* __restrict__ p, __nv_bfloat16* __restrict__ p16, int64_t n4) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 pv = p[i];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(pv.x, pv.y), hi = __floats2bfloat162_rn(pv.z, pv.w);
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&lo);
+    w.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(p16)[i] = w;
   }
 }
 
@@ -98,15 +127,34 @@ int b2_adam_prepare(float* state, float beta1, float beta2, void* stream) {
   return 0;
 }
 
+int b2_adam_advance(float* state, float n_steps, void* stream) {
+  adam_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, n_steps);
+  B2_LAUNCH_CHECK("adam_advance_kernel");
+  return 0;
+}
+
+int b2_cast_slab(const float* p, void* p_bf16, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  if ((n & 3) || !aligned16(p) || (reinterpret_cast<uintptr_t>(p_bf16) & 7u)) {
+    set_error("cast_slab: n %% 4 == 0 and aligned slabs required");
+    return 1;
+  }
+  cast_slab_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(p), static_cast<__nv_bfloat16*>(p_bf16), n / 4);
+  B2_LAUNCH_CHECK("cast_slab_kernel");
+  return 0;
+}
+
 int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
-                 const float* dev_state, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale, int zero_grad, void* stream) {
+                 const float* dev_state, float step_offset, void* p_bf16, float prox_mu, const float* prox_ref, const float* cv_global, const float* cv_local, float cv_scale,
+                 int zero_grad, void* stream) {
   if (n <= 0) return 0;
   if (check_slab(p, g, m, v, n) || check_slab(p, p, prox_ref, cv_global, n) || check_slab(p, p, cv_local, nullptr, n)) return 1;
   FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
                reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
   adam_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
                                                                                       reinterpret_cast<float4*>(v), n / 4, lr, beta1, beta2, eps, 1.f / bias_corr1,
-                                                                                      rsqrtf(bias_corr2), dev_state, t, zero_grad);
+                                                                                      rsqrtf(bias_corr2), dev_state, step_offset, static_cast<__nv_bfloat16*>(p_bf16), t,
+                                                                                      zero_grad);
   B2_LAUNCH_CHECK("adam_kernel");
   return 0;
 }

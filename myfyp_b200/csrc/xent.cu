@@ -4,6 +4,8 @@
 //   loss_out   += scale * sum_rows ( logsumexp(row) - row[label] )        (atomic, one add per CTA)
 //   dlogits[r] = scale * (softmax(row) - onehot(label))                   (optional)
 //   correct    += #rows with argmax == label                              (optional; first max wins, like torch)
+#include <cuda_bf16.h>
+
 #include "../../include/myfyp_b200.h"
 #include "common.cuh"
 
@@ -55,6 +57,47 @@ __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ log
   }
 }
 
+// Training variant, ONE block: loss written (not accumulated), dlogits emitted directly as the bf16 operand of the backward
+// GEMMs (row pitch ld16), bias gradient of the last layer (column sums of dlogits) added - replaces memset + xent +
+// cast + column-sum (4 launches) by one.  B <= a few thousand rows (a batch).
+__global__ void __launch_bounds__(256) xent_train_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_out,
+                                                         __nv_bfloat16* __restrict__ dl16, int ld16, float* __restrict__ bias_grad, int B, int C, float scale) {
+  extern __shared__ float s_mem[];  // C column sums + 8 warp losses
+  float* s_db = s_mem;
+  float* s_loss = s_mem + C;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
+  __syncthreads();
+  float wl = 0.f;
+  for (int row = warp; row < B; row += 8) {
+    const float* x = logits + (int64_t)row * C;
+    const int lab = (int)labels[row];
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, x[c]);
+    mx = warp_max(mx);
+    float se = 0.f;
+    for (int c = lane; c < C; c += 32) se += __expf(x[c] - mx);
+    se = warp_sum(se);
+    const float inv = scale / se;
+    for (int c = lane; c < C; c += 32) {
+      const float d = __expf(x[c] - mx) * inv - (c == lab ? scale : 0.f);
+      dl16[(int64_t)row * ld16 + c] = __float2bfloat16_rn(d);
+      atomicAdd(&s_db[c], d);
+    }
+    if (lane == 0) wl += mx + __logf(se) - x[lab];
+  }
+  if (lane == 0) s_loss[warp] = wl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_loss[w];
+    *loss_out = t * scale;
+  }
+  if (bias_grad != nullptr)
+    for (int c = threadIdx.x; c < C; c += blockDim.x) bias_grad[c] += s_db[c];
+}
+
 // confusion[label * C + argmax] += 1 : the sufficient statistic for accuracy, per-class precision / recall / F1
 // (the fork author's extended MLP logs test_f1 / test_precision / test_recall, mlp_pytorch.txt)
 __global__ void __launch_bounds__(256) confusion_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ conf, int B, int C) {
@@ -78,6 +121,19 @@ __global__ void __launch_bounds__(256) confusion_kernel(const float* __restrict_
 }
 
 }  // namespace b2
+
+extern "C" int b2_xent_train(const float* logits, const int64_t* labels, float* loss_out, void* dlogits_bf16, int ld16, float* bias_grad, int B, int C, float scale,
+                             void* stream) {
+  if (B <= 0 || C <= 0) return 0;
+  if (C > 8192) {
+    b2::set_error("xent_train: C=%d too wide for the single-block variant", C);
+    return 1;
+  }
+  b2::xent_train_kernel<<<1, 256, (C + 8) * sizeof(float), static_cast<cudaStream_t>(stream)>>>(logits, labels, loss_out, static_cast<__nv_bfloat16*>(dlogits_bf16), ld16, bias_grad,
+                                                                                                B, C, scale);
+  B2_LAUNCH_CHECK("xent_train_kernel");
+  return 0;
+}
 
 extern "C" int b2_confusion(const float* logits, const int64_t* labels, float* conf, int B, int C, void* stream) {
   if (B <= 0 || C <= 0) return 0;

@@ -116,19 +116,28 @@ class TorchLearner(Learner):
             self._graphs.clear()
         return st
 
-    def _optimizer_step(self, st: Dict[str, Any], terms: Dict[str, Any]) -> None:
+    def _optimizer_step(self, st: Dict[str, Any], terms: Dict[str, Any], step_in_epoch: int, p16=None) -> None:
         model: TorchP2PFLModel = self.model  # type: ignore[assignment]
         n = model.layout.n_trainable
-        st["step"] += 1
         if self.optimizer == "adam":
-            ops.adam_step(model.slab[:n], model.grad_slab[:n], st["m"], st["v"], st["step"], lr=self.lr, weight_decay=self.weight_decay, dev_state=st["dev_state"], **terms)
+            # step = (steps of earlier epochs, on the device) + (index inside this epoch, baked): one launch per step
+            ops.adam_step(
+                model.slab[:n], model.grad_slab[:n], st["m"], st["v"], 0, lr=self.lr, weight_decay=self.weight_decay, dev_state=st["dev_state"], step_offset=step_in_epoch,
+                p16=None if p16 is None else p16[:n], **terms,
+            )
         else:
             ops.sgd_step(model.slab[:n], model.grad_slab[:n], st["m"], lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay, **terms)
+            if p16 is not None:
+                ops.cast_slab(model.slab[:n], p16[:n])
 
     # ------------------------------------------------------------------ one epoch (eager, or the body that gets captured)
     def _epoch_body(self, x, y, perm, losses, steps: int, st, terms) -> int:
         module = self.model.get_model()
         native = getattr(module, "native_train_step", None)
+        nat = getattr(module, "native", None)
+        p16 = getattr(nat, "p16", None)
+        if nat is not None:
+            nat.refresh_weights()  # bf16 mirror of the (possibly just aggregated) parameters; Adam keeps it current afterwards
         done = 0
         for s in range(steps):
             if self._interrupt:
@@ -141,8 +150,10 @@ class TorchLearner(Learner):
                 loss = ops.cross_entropy(module(xb), yb)
                 loss.backward()
                 losses[s : s + 1].copy_(loss.detach().reshape(1))
-            self._optimizer_step(st, terms)
+            self._optimizer_step(st, terms, s + 1, p16)
             done += 1
+        if self.optimizer == "adam" and done:
+            ops.adam_advance(st["dev_state"], done)
         return done
 
     def _graph_for(self, key, build):
@@ -224,7 +235,6 @@ class TorchLearner(Learner):
                     g = self._graph_for(gkey, lambda: self._epoch_body(x, y, perm, losses, steps_per_epoch, st, terms))
                     g.replay()
                     all_losses[e * steps_per_epoch : (e + 1) * steps_per_epoch].copy_(losses)
-                    st["step"] += steps_per_epoch
                     steps += steps_per_epoch
                     ops.native.count_launch(g.native_kernels)
             else:
@@ -251,6 +261,8 @@ class TorchLearner(Learner):
     def _eval_body(self, x, y, acc, conf=None) -> None:
         module = self.model.get_model()
         native = getattr(module, "native_eval", None)
+        if getattr(module, "native", None) is not None:
+            module.native.refresh_weights()
         acc.zero_()
         if conf is not None:
             conf.zero_()

@@ -6,10 +6,10 @@ and are only *read* here (bf16 working copies per step, no permutation: the patc
 
 Activations are NHWC bf16, i.e. the ``[pixels, channels]`` matrices the GEMM reads and writes.  Per conv block:
 
-    forward   col = im2col(P_prev)            Y = relu(col W^T + b)  (GEMM epilogue)        P = maxpool2(Y), argmax kept
-    backward  dZ  = unpool(dP) * (Y > 0)      db = colsum(dZ)
+    forward   Y = relu(col W^T + b)  (GEMM epilogue)       col_next = im2col(maxpool2(Y))  (ONE kernel, argmax kept, P never stored)
+    backward  dZ = unpool(col2im(dcol_next)) * (Y > 0), db = colsum(dZ)                     (ONE kernel)
               dW  = dZ^T col                  (MN-major operands, split-K over pixels, fp32 atomics into the gradient slab)
-              dcol = dZ W  (W MN-major)       dP_prev = col2im(dcol)
+              dcol = dZ W  (W MN-major)
 
 The first linear layer after the feature map is a convolution whose kernel covers the whole map, which reproduces
 ``nn.Flatten``'s NCHW feature order on NHWC data.  Reference path: the same ``nn.Module`` through torch autograd / cuDNN.
@@ -81,7 +81,17 @@ class NativeCNN:
 
         self.params = {s.name: views(s.name, s.cout, s.kdim) for s in self.convs + [self.fc1]}
         self.params[self.fc2_name] = views(self.fc2_name, self.fc2_out, self.fc2_in)
-        self.w16 = {n: torch.zeros(p[0].shape[0], _pad8(p[0].shape[1]), dtype=torch.bfloat16, device=dev) for n, p in self.params.items()}
+        # bf16 mirror of the whole slab, kept current by the fused optimizer; weights with a row length that is a multiple of
+        # 8 are TMA operands in place, the others (the 27-wide first conv) get a padded private copy
+        self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
+        self.w16, self._padded = {}, []
+        for n, (w, _, _, _) in self.params.items():
+            ew = lay.entries[n + ".weight"]
+            if w.shape[1] % 8 == 0:
+                self.w16[n] = self.p16[ew.offset : ew.offset + ew.numel].view(w.shape)
+            else:
+                self.w16[n] = torch.zeros(w.shape[0], _pad8(w.shape[1]), dtype=torch.bfloat16, device=dev)
+                self._padded.append(n)
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers
@@ -93,58 +103,60 @@ class NativeCNN:
             for s in self.convs:
                 m = B * s.oh * s.ow
                 buf["conv"].append({
-                    "col": z(m, _pad8(s.kdim)), "y": z(m, s.cout), "p": z(B * (s.oh // 2) * (s.ow // 2), s.cout), "idx": z(B * (s.oh // 2) * (s.ow // 2), s.cout, dtype=torch.uint8),
-                    "dz": z(m, s.cout), "dcol": z(m, _pad8(s.kdim)), "dp": z(B * (s.oh // 2) * (s.ow // 2), s.cout),
+                    "col": z(m, _pad8(s.kdim)), "y": z(m, s.cout), "idx": z(B * (s.oh // 2) * (s.ow // 2), s.cout, dtype=torch.uint8),
+                    "dz": z(m, s.cout), "dcol": z(m, _pad8(s.kdim)),
                 })
             f = self.fc1
             buf.update(
                 col_fc1=z(B, _pad8(f.kdim)), h1=z(B, _pad8(f.cout)), dh1=z(B, _pad8(f.cout)), dcol_fc1=z(B, _pad8(f.kdim)),
-                logits=z(B, self.fc2_out, dtype=torch.float32), dlogits=z(B, self.fc2_out, dtype=torch.float32), dz2=z(B, _pad8(self.fc2_out)),
+                logits=z(B, self.fc2_out, dtype=torch.float32), dz2=z(B, _pad8(self.fc2_out)),
             )
             self._bufs[B] = buf
         return self._bufs[B]
 
     def refresh_weights(self) -> None:
-        for n, (w, _, _, _) in self.params.items():
+        """fp32 slab -> bf16 mirror, once per fit / evaluation (the optimizer updates the mirror after every step)."""
+        ops.cast_slab(self.model.slab, self.p16)
+        self._refresh_padded()
+
+    def _refresh_padded(self) -> None:
+        for n in self._padded:
+            w = self.params[n][0]
             ops.cast_transpose(w, w.shape[0], w.shape[1], dst=self.w16[n])
+
+    def _next_geom(self, li: int):
+        """Geometry of the layer that consumes conv block ``li``'s pooled output (the next conv, or fc1 as a full-map conv)."""
+        nxt = self.convs[li + 1] if li + 1 < len(self.convs) else self.fc1
+        return nxt, (nxt.h, nxt.w, nxt.cin, nxt.k, nxt.k, nxt.stride, nxt.pad)
 
     # ------------------------------------------------------------------ forward
     def _forward(self, x: torch.Tensor, buf: dict) -> int:
         B = x.shape[0]
         if x.dtype != torch.float32 or not x.is_contiguous():
             x = x.float().contiguous()
-        prev = x
+        s0 = self.convs[0]
+        ops.im2col(x, buf["conv"][0]["col"], B, s0.h, s0.w, s0.cin, s0.k, s0.k, s0.stride, s0.pad, nchw_f32=True)
         for li, s in enumerate(self.convs):
             cb = buf["conv"][li]
-            ops.im2col(prev, cb["col"], B, s.h, s.w, s.cin, s.k, s.k, s.stride, s.pad, nchw_f32=(li == 0))
-            w, b, _, _ = self.params[s.name]
-            ops.gemm_bf16(cb["col"], self.w16[s.name], B * s.oh * s.ow, s.cout, s.kdim, out_bf16=cb["y"], bias=b, relu=True)
-            ops.maxpool2_fwd(cb["y"], cb["p"], cb["idx"], B, s.oh, s.ow, s.cout)
-            prev = cb["p"]
+            ops.gemm_bf16(cb["col"], self.w16[s.name], B * s.oh * s.ow, s.cout, s.kdim, out_bf16=cb["y"], bias=self.params[s.name][1], relu=True)
+            # max-pool + the next layer's patch gather in one pass (the pooled activation is never stored)
+            nxt, (h, w, c, kh, kw, st, pd) = self._next_geom(li)
+            dst = buf["conv"][li + 1]["col"] if li + 1 < len(self.convs) else buf["col_fc1"]
+            ops.pool_im2col(cb["y"], cb["idx"], dst, B, h, w, c, kh, kw, st, pd)
         f = self.fc1
-        ops.im2col(prev, buf["col_fc1"], B, f.h, f.w, f.cin, f.k, f.k, 1, 0)
         ops.gemm_bf16(buf["col_fc1"], self.w16[f.name], B, f.cout, f.kdim, out_bf16=buf["h1"], bias=self.params[f.name][1], relu=True)
         ops.gemm_bf16(buf["h1"], self.w16[self.fc2_name], B, self.fc2_out, self.fc2_in, out_f32=buf["logits"], bias=self.params[self.fc2_name][1])
         return B
 
     # ------------------------------------------------------------------ training step
     def train_step(self, x: torch.Tensor, y: torch.Tensor, loss_out: torch.Tensor) -> None:
-        self.refresh_weights()
+        self._refresh_padded()
         B = x.shape[0]
         buf = self._buffers(B)
         self._forward(x, buf)
-        native = ops.native
-        lib = native.load()
-        loss_out.zero_()
-        with native.device_guard(x.device):
-            native.check(
-                lib.b2_xent_fwd_bwd(native.ptr(buf["logits"]), native.ptr(y), native.ptr(loss_out), native.ptr(buf["dlogits"]), native.ptr(None), B, self.fc2_out, ctypes.c_float(1.0 / B), native.stream_ptr(x.device)),
-                "b2_xent_fwd_bwd",
-            )
-        native.count_launch()
-        # ---- fc2
+        # ---- loss + dlogits (bf16) + fc2 bias gradient: one launch
         _, _, gw2, gb2 = self.params[self.fc2_name]
-        ops.cast_transpose(buf["dlogits"], B, self.fc2_out, dst=buf["dz2"], colsum=gb2)
+        ops.xent_train(buf["logits"], y, loss_out, buf["dz2"], gb2, B, self.fc2_out)
         ops.gemm_bf16(buf["dz2"], buf["h1"], self.fc2_out, self.fc2_in, B, out_f32=gw2, a_mn=True, b_mn=True)
         # ---- fc1 (dgrad of fc2 with the ReLU mask of h1; its column sums are fc1's bias gradient)
         f = self.fc1
@@ -152,23 +164,22 @@ class NativeCNN:
         ops.gemm_bf16(buf["dz2"], self.w16[self.fc2_name], B, self.fc2_in, self.fc2_out, out_bf16=buf["dh1"], mask=buf["h1"], colsum=gb1, b_mn=True)
         ops.gemm_bf16(buf["dh1"], buf["col_fc1"], f.cout, f.kdim, B, out_f32=gw1, a_mn=True, b_mn=True)
         ops.gemm_bf16(buf["dh1"], self.w16[f.name], B, f.kdim, f.cout, out_bf16=buf["dcol_fc1"], b_mn=True)
-        last = buf["conv"][-1]
-        ops.col2im(buf["dcol_fc1"], last["dp"], B, f.h, f.w, f.cin, f.k, f.k, 1, 0)
         # ---- conv blocks, last to first
         for li in range(len(self.convs) - 1, -1, -1):
             s, cb = self.convs[li], buf["conv"][li]
             m = B * s.oh * s.ow
             _, _, gw, gb = self.params[s.name]
-            ops.maxpool2_relu_bwd(cb["dp"], cb["idx"], cb["y"], cb["dz"], B, s.oh, s.ow, s.cout)
-            ops.colsum_bf16(cb["dz"], m, s.cout, gb)
+            nxt, (h, w, c, kh, kw, st, pd) = self._next_geom(li)
+            next_dcol = buf["conv"][li + 1]["dcol"] if li + 1 < len(self.convs) else buf["dcol_fc1"]
+            # col2im of the next layer's dcol + unpool + ReLU mask + bias gradient: one launch
+            ops.unpool_col2im(next_dcol, cb["idx"], cb["y"], cb["dz"], gb, B, h, w, c, kh, kw, st, pd)
             ops.gemm_bf16(cb["dz"], cb["col"], s.cout, s.kdim, m, out_f32=gw, a_mn=True, b_mn=True, split_k=max(1, min(64, m // 1024)))
             if li > 0:
                 ops.gemm_bf16(cb["dz"], self.w16[s.name], m, s.kdim, s.cout, out_bf16=cb["dcol"], b_mn=True)
-                ops.col2im(cb["dcol"], buf["conv"][li - 1]["dp"], B, s.h, s.w, s.cin, s.k, s.k, s.stride, s.pad)
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:
-        self.refresh_weights()
+        """``acc[0] += sum NLL``, ``acc[1] += #correct``  (the caller refreshed the bf16 mirror)."""
         buf = self._buffers(x.shape[0])
         B = self._forward(x, buf)
         ops.cross_entropy_eval(buf["logits"][:B], y, acc)

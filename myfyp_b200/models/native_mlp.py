@@ -4,9 +4,9 @@ Attached to a CUDA ``TorchP2PFLModel`` wrapping :class:`~myfyp_b200.models.mlp.M
 slab (that is what gets aggregated / published); every step stages bf16 copies for the tensor cores.
 
 Per step (kernel ids from SURVEY section 8):
-  staging   ``cast_transpose``: X -> bf16 ; W_l -> bf16
+  staging   ``cast_transpose``: X -> bf16 (the weights' bf16 mirror is written by the fused optimizer itself)
   forward   T1 ``gemm_bf16`` x L: H_l = relu(H_{l-1} W_l^T + b_l) (bf16) ; last layer -> fp32 logits
-  loss      T3 ``xent_fwd_bwd``: loss, dlogits (already scaled by 1/B)
+  loss      T3 ``xent_train``: loss, bf16 dlogits (already scaled by 1/B), bias gradient of the last layer
   backward  T2 wgrad: dW_l = dZ_l^T H_{l-1}  (fp32 straight into the gradient slab; both operands MN-major)
             T2 dgrad: dZ_{l-1} = (dZ_l W_l) * (H_{l-1} > 0), column sums -> db_{l-1}     (W_l MN-major)
   (the fused optimizer T6 then runs over the whole slab - called by the learner)
@@ -45,8 +45,17 @@ class NativeMLP:
             self.b.append(model.slab[eb.offset : eb.offset + eb.numel])
             self.gw.append(model.grad_slab[ew.offset : ew.offset + ew.numel].view(ew.shape))
             self.gb.append(model.grad_slab[eb.offset : eb.offset + eb.numel])
-        # bf16 working copy of the weights: W16[l] = [out, pad8(in)]
-        self.w16 = [torch.zeros(self.sizes[i + 1], _pad8(self.sizes[i]), dtype=torch.bfloat16, device=dev) for i in range(self.L)]
+        # bf16 mirror of the whole slab (kept current by the fused optimizer); weights whose row length is a multiple of 8
+        # are used in place as TMA operands, the others get a padded private copy
+        self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
+        self.w16, self._padded = [], []
+        for i in range(self.L):
+            ew = lay.entries[f"layers.{i}.weight"]
+            if self.sizes[i] % 8 == 0:
+                self.w16.append(self.p16[ew.offset : ew.offset + ew.numel].view(ew.shape))
+            else:
+                self.w16.append(torch.zeros(self.sizes[i + 1], _pad8(self.sizes[i]), dtype=torch.bfloat16, device=dev))
+                self._padded.append(i)
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers per batch capacity
@@ -63,8 +72,12 @@ class NativeMLP:
         return self._bufs[cap]
 
     def refresh_weights(self) -> None:
-        """fp32 slab -> bf16 working copy (after every optimizer step / model load)."""
-        for i in range(self.L):
+        """fp32 slab -> bf16 mirror, once per fit / evaluation (the optimizer updates the mirror after every step)."""
+        ops.cast_slab(self.model.slab, self.p16)
+        self._refresh_padded()
+
+    def _refresh_padded(self) -> None:
+        for i in self._padded:
             ops.cast_transpose(self.w[i], self.sizes[i + 1], self.sizes[i], dst=self.w16[i])
 
     # ------------------------------------------------------------------ forward
@@ -86,23 +99,12 @@ class NativeMLP:
     # ------------------------------------------------------------------ public hooks used by TorchLearner
     def train_step(self, x: torch.Tensor, y: torch.Tensor, loss_out: torch.Tensor) -> None:
         """Forward + loss + backward; gradients land in the model's gradient slab, mean loss in ``loss_out[0]``."""
-        import ctypes
-
-        self.refresh_weights()
+        self._refresh_padded()
         buf = self._buffers(x.shape[0])
         bsz = self._forward(x, buf)
         s, L = self.sizes, self.L
-        native = ops.native
-        lib = native.load()
-        loss_out.zero_()
-        with native.device_guard(x.device):
-            native.check(
-                lib.b2_xent_fwd_bwd(native.ptr(buf["logits"]), native.ptr(y), native.ptr(loss_out), native.ptr(buf["dlogits"]), native.ptr(None), bsz, s[-1], ctypes.c_float(1.0 / bsz), native.stream_ptr(x.device)),
-                "b2_xent_fwd_bwd",
-            )
-        native.count_launch()
-        # dZ_L = dlogits in bf16 + bias gradient of the last layer (column sums)
-        ops.cast_transpose(buf["dlogits"], bsz, s[-1], dst=buf["dz"][L - 1], colsum=self.gb[L - 1])
+        # loss, dZ_L = dlogits/B as bf16, bias gradient of the last layer: one launch
+        ops.xent_train(buf["logits"], y, loss_out, buf["dz"][L - 1], self.gb[L - 1], bsz, s[-1])
         for i in range(L - 1, -1, -1):
             # wgrad: dW_i[out,in] = dZ_i^T H_i      - dZ_i [B,out] and H_i [B,in] consumed as MN-major operands (K = batch)
             ops.gemm_bf16(buf["dz"][i], buf["h"][i], s[i + 1], s[i], bsz, out_f32=self.gw[i], a_mn=True, b_mn=True)
@@ -112,8 +114,7 @@ class NativeMLP:
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:
-        """``acc[0] += sum NLL``, ``acc[1] += #correct``."""
-        self.refresh_weights()
+        """``acc[0] += sum NLL``, ``acc[1] += #correct``  (the caller refreshed the bf16 mirror)."""
         buf = self._buffers(x.shape[0])
         bsz = self._forward(x, buf)
         ops.cross_entropy_eval(buf["logits"][:bsz], y, acc)

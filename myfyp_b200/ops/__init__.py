@@ -217,23 +217,28 @@ def adam_step(
     p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,
     weight_decay: float = 0.0, prox_mu: float = 0.0, prox_ref: Optional[torch.Tensor] = None, cv_global: Optional[torch.Tensor] = None,
     cv_local: Optional[torch.Tensor] = None, cv_scale: float = 1.0, zero_grad: bool = True, dev_state: Optional[torch.Tensor] = None,
+    step_offset: int = 0, p16: Optional[torch.Tensor] = None,
 ) -> None:
     """Adam over the flat slab.  ``g' = g + wd*p + mu*(p - ref) + cv_scale*(c - c_i)``; clears ``g`` afterwards.
 
-    ``dev_state`` (3 floats on the device: step, 1-b1^step, 1-b2^step) replaces the host-side ``step``: it is advanced
-    by a 1-thread kernel and read by the update kernel, which is what makes a whole epoch CUDA-graph-capturable.
+    ``dev_state`` (floats on the device: step, 1-b1^step, 1-b2^step) replaces the host-side ``step``, which is what makes a
+    whole epoch CUDA-graph-capturable.  Two ways: ``step_offset == 0`` - a 1-thread kernel advances the state before the
+    update; ``step_offset = k > 0`` - the step is ``dev_state[0] + k`` (k = index inside the captured epoch, baked into
+    the launch) and :func:`adam_advance` adds the epoch's length once per replay (one launch per step instead of two).
+    ``p16``: bf16 mirror of ``p`` written in the same pass (the tensor-core operands of the next step).
     """
     if p.is_cuda:
         lib = native.load()
         bc1, bc2 = (1.0 - beta1**step, 1.0 - beta2**step) if dev_state is None else (1.0, 1.0)
         with native.device_guard(p.device):
-            if dev_state is not None:
+            if dev_state is not None and step_offset == 0:
                 native.check(lib.b2_adam_prepare(native.ptr(dev_state), ctypes.c_float(beta1), ctypes.c_float(beta2), native.stream_ptr(p.device)), "b2_adam_prepare")
                 native.count_launch()
             native.check(
                 lib.b2_adam_step(
                     native.ptr(p), native.ptr(g), native.ptr(m), native.ptr(v), ctypes.c_int64(p.numel()), ctypes.c_float(lr), ctypes.c_float(beta1), ctypes.c_float(beta2),
-                    ctypes.c_float(eps), ctypes.c_float(weight_decay), ctypes.c_float(bc1), ctypes.c_float(bc2), native.ptr(dev_state), ctypes.c_float(prox_mu if prox_ref is not None else 0.0),
+                    ctypes.c_float(eps), ctypes.c_float(weight_decay), ctypes.c_float(bc1), ctypes.c_float(bc2), native.ptr(dev_state), ctypes.c_float(float(step_offset)), native.ptr(p16),
+                    ctypes.c_float(prox_mu if prox_ref is not None else 0.0),
                     native.ptr(prox_ref), native.ptr(cv_global), native.ptr(cv_local), ctypes.c_float(cv_scale), ctypes.c_int(1 if zero_grad else 0), native.stream_ptr(p.device),
                 ),
                 "b2_adam_step",
@@ -241,15 +246,42 @@ def adam_step(
         native.count_launch()
         return
     if dev_state is not None:
-        dev_state[0] += 1
-        step = int(dev_state[0].item())
+        if step_offset > 0:
+            step = int(dev_state[0].item()) + step_offset
+        else:
+            dev_state[0] += 1
+            step = int(dev_state[0].item())
     gg = _effective_grad(p, g, weight_decay, prox_mu, prox_ref, cv_global, cv_local, cv_scale)
     m.mul_(beta1).add_(gg, alpha=1 - beta1)
     v.mul_(beta2).addcmul_(gg, gg, value=1 - beta2)
     denom = (v / (1 - beta2**step)).sqrt_().add_(eps)
     p.data.addcdiv_(m / (1 - beta1**step), denom, value=-lr)
+    if p16 is not None:
+        p16.copy_(p.data)
     if zero_grad:
         g.zero_()
+
+
+def adam_advance(dev_state: torch.Tensor, n_steps: int) -> None:
+    """``dev_state[0] += n_steps`` (once per epoch replay, see :func:`adam_step`)."""
+    if dev_state.is_cuda:
+        lib = native.load()
+        with native.device_guard(dev_state.device):
+            native.check(lib.b2_adam_advance(native.ptr(dev_state), ctypes.c_float(float(n_steps)), native.stream_ptr(dev_state.device)), "b2_adam_advance")
+        native.count_launch()
+    else:
+        dev_state[0] += n_steps
+
+
+def cast_slab(p: torch.Tensor, p16: torch.Tensor) -> None:
+    """bf16 mirror of a whole fp32 slab in one pass."""
+    if p.is_cuda:
+        lib = native.load()
+        with native.device_guard(p.device):
+            native.check(lib.b2_cast_slab(native.ptr(p), native.ptr(p16), ctypes.c_int64(p.numel()), native.stream_ptr(p.device)), "b2_cast_slab")
+        native.count_launch()
+    else:
+        p16.copy_(p)
 
 
 def sgd_step(
@@ -445,3 +477,24 @@ def maxpool2_relu_bwd(dp: torch.Tensor, idx: torch.Tensor, y: torch.Tensor, dz: 
 
 def colsum_bf16(z: torch.Tensor, M: int, C: int, out: torch.Tensor) -> None:
     _conv_call("b2_colsum_bf16", z.device, native.ptr(z), M, C, int(z.stride(0)), native.ptr(out))
+
+
+def pool_im2col(y: torch.Tensor, idx: torch.Tensor, col: torch.Tensor, B: int, PH: int, PW: int, C: int, KH: int, KW: int, stride: int, pad: int) -> None:
+    """Fused 2x2 max-pool of ``y [B,2PH,2PW,C]`` + patch gather of the next layer (geometry over the pooled map)."""
+    _conv_call("b2_pool_im2col", y.device, native.ptr(y), native.ptr(idx), native.ptr(col), int(col.stride(0)), B, PH, PW, C, KH, KW, stride, pad)
+
+
+def unpool_col2im(dcol: torch.Tensor, idx: torch.Tensor, y: torch.Tensor, dz: torch.Tensor, bias_grad: Optional[torch.Tensor], B: int, PH: int, PW: int, C: int, KH: int, KW: int, stride: int, pad: int) -> None:
+    """Fused col2im of the next layer's ``dcol`` + unpool to the winners + ReLU mask -> ``dz``; ``bias_grad += colsum(dz)``."""
+    _conv_call("b2_unpool_col2im", dcol.device, native.ptr(dcol), int(dcol.stride(0)), native.ptr(idx), native.ptr(y), native.ptr(dz), native.ptr(bias_grad), B, PH, PW, C, KH, KW, stride, pad)
+
+
+def xent_train(logits: torch.Tensor, labels: torch.Tensor, loss_out: torch.Tensor, dl16: torch.Tensor, bias_grad: Optional[torch.Tensor], B: int, C: int) -> None:
+    """One launch: ``loss_out[0] = mean NLL``, ``dl16 = bf16(dlogits / B)``, ``bias_grad += colsum(dlogits / B)``."""
+    lib = native.load()
+    with native.device_guard(logits.device):
+        native.check(
+            lib.b2_xent_train(native.ptr(logits), native.ptr(labels), native.ptr(loss_out), native.ptr(dl16), int(dl16.stride(0)), native.ptr(bias_grad), B, C, ctypes.c_float(1.0 / B), native.stream_ptr(logits.device)),
+            "b2_xent_train",
+        )
+    native.count_launch()

@@ -301,6 +301,7 @@ def test_native_mlp_step_matches_reference(dev, batch):
     x = torch.randn(batch, 28, 28, device=dev)
     y = torch.randint(0, 10, (batch,), device=dev)
     loss = torch.zeros(1, device=dev)
+    module.native.refresh_weights()
     module.native_train_step(x, y, loss)
     grads = model.grad_slab.clone()
     model.grad_slab.zero_()
@@ -558,6 +559,7 @@ def test_native_cnn_step_matches_reference(dev, batch):
     x = torch.randn(batch, 3, 32, 32, device=dev)
     y = torch.randint(0, 10, (batch,), device=dev)
     loss = torch.zeros(1, device=dev)
+    module.native.refresh_weights()
     module.native_train_step(x, y, loss)
     grads = model.grad_slab.clone()
     model.grad_slab.zero_()
@@ -593,3 +595,81 @@ def test_native_cnn_learns(dev):
     learner.fit()
     after = learner.evaluate()
     assert after["test_metric"] > max(0.9, before), (before, after)
+
+
+def test_fused_pool_im2col_and_unpool_col2im_match_the_unfused_kernels(dev):
+    from myfyp_b200 import ops
+
+    B, H, C, k, pad = 3, 16, 32, 3, 1  # Y is [B,H,H,C]; the next conv works on the pooled [B,H/2,H/2,C] map
+    PH = H // 2
+    y = torch.relu(torch.randn(B, H, H, C, device=dev)).to(torch.bfloat16)
+    # unfused: pool -> im2col
+    p = torch.empty(B, PH, PH, C, dtype=torch.bfloat16, device=dev)
+    idx = torch.empty(B, PH, PH, C, dtype=torch.uint8, device=dev)
+    ops.maxpool2_fwd(y, p, idx, B, H, H, C)
+    kd = C * k * k
+    col = torch.zeros(B * PH * PH, kd, dtype=torch.bfloat16, device=dev)
+    ops.im2col(p, col, B, PH, PH, C, k, k, 1, pad)
+    # fused
+    idx2 = torch.empty_like(idx)
+    col2 = torch.zeros_like(col)
+    ops.pool_im2col(y, idx2, col2, B, PH, PH, C, k, k, 1, pad)
+    assert torch.equal(idx, idx2) and torch.equal(col, col2)
+    # backward: unfused col2im -> unpool+mask -> colsum  vs fused
+    dcol = torch.randn(B * PH * PH, kd, device=dev).to(torch.bfloat16)
+    dp = torch.empty_like(p)
+    ops.col2im(dcol, dp, B, PH, PH, C, k, k, 1, pad)
+    dz = torch.empty_like(y)
+    ops.maxpool2_relu_bwd(dp, idx, y, dz, B, H, H, C)
+    db = torch.zeros(C, device=dev)
+    ops.colsum_bf16(dz.view(-1, C), B * H * H, C, db)
+    dz2 = torch.full_like(y, float("nan"))
+    db2 = torch.zeros(C, device=dev)
+    ops.unpool_col2im(dcol, idx, y, dz2, db2, B, PH, PH, C, k, k, 1, pad)
+    assert torch.equal(dz, dz2)
+    torch.testing.assert_close(db, db2, rtol=1e-4, atol=1e-4)
+
+
+def test_xent_train_matches_xent_plus_cast(dev):
+    from myfyp_b200 import ops
+
+    b, c = 64, 10
+    logits = torch.randn(b, c, device=dev) * 2
+    labels = torch.randint(0, c, (b,), device=dev)
+    loss = torch.full((1,), 123.0, device=dev)
+    dl16 = torch.zeros(b, 16, dtype=torch.bfloat16, device=dev)
+    db = torch.zeros(c, device=dev)
+    ops.xent_train(logits, labels, loss, dl16, db, b, c)
+    ref_logits = logits.clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(ref_logits, labels)
+    ref.backward()
+    torch.testing.assert_close(loss[0], ref.detach(), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(dl16[:, :c].float(), ref_logits.grad, rtol=1e-2, atol=1e-4)
+    torch.testing.assert_close(db, ref_logits.grad.sum(0), rtol=1e-3, atol=1e-5)
+
+
+def test_adam_baked_step_with_device_base_and_bf16_mirror(dev):
+    """Two 'epochs' of 3 steps with step = device base + baked offset must equal torch.optim.Adam's 6 steps; the mirror tracks p."""
+    from myfyp_b200 import ops
+
+    n = 4096
+    p0 = _slabs(1, n, dev)[0]
+    p, pt = p0.clone(), p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([pt], lr=1e-3)
+    m, v, st = torch.zeros(n, device=dev), torch.zeros(n, device=dev), torch.zeros(4, device=dev)
+    p16 = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+    k = 0
+    for epoch in range(2):
+        for s in range(3):
+            k += 1
+            g = _slabs(1, n, dev, seed=100 + k)[0]
+            pt.grad = g.clone()
+            opt.step()
+            ops.adam_step(p, g.clone(), m, v, 0, lr=1e-3, dev_state=st, step_offset=s + 1, p16=p16)
+        ops.adam_advance(st, 3)
+    assert st[0].item() == 6.0
+    torch.testing.assert_close(p, pt.detach(), rtol=1e-4, atol=1e-6)
+    assert torch.equal(p16, p.to(torch.bfloat16))
+    full = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+    ops.cast_slab(p, full)
+    assert torch.equal(full, p16)

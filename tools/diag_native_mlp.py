@@ -12,6 +12,7 @@ for batch in (32, 256):
     x = torch.randn(batch, 28, 28, device=dev)
     y = torch.randint(0, 10, (batch,), device=dev)
     loss = torch.zeros(1, device=dev)
+    module.native.refresh_weights()
     module.native_train_step(x, y, loss)
     g_nat = model.grad_slab.clone(); model.grad_slab.zero_()
     l32 = torch.nn.functional.cross_entropy(module(x), y); l32.backward()

@@ -20,9 +20,10 @@ if mode == "step":
     from myfyp_b200 import ops
     n = model.layout.n_trainable
     m, v, st = torch.zeros(n, device=dev), torch.zeros(n, device=dev), torch.zeros(4, device=dev)
+    module.native.refresh_weights()
     for it in range(5):
         module.native_train_step(x, y, loss)
-        ops.adam_step(model.slab[:n], model.grad_slab[:n], m, v, it + 1, dev_state=st)
+        ops.adam_step(model.slab[:n], model.grad_slab[:n], m, v, 0, dev_state=st, step_offset=it + 1, p16=module.native.p16[:n])
     torch.cuda.synchronize()
     print("step ok", loss.item())
 else:
