@@ -9,10 +9,11 @@
 //   dgrad    dX = (dY W) * (Xact > 0)  A = dY [B,out]    B = W^T [in,out]   -> dX bf16 [B,in] and dX^T [in,B], colsum -> db
 //   wgrad    dW = dY^T X               A = dY^T [out,B]  B = X^T [in,B]     -> dW fp32 [out,in]
 //
-// Structure (warp specialised, one 128 x 64 output tile per CTA):
-//   warp 0     : TMA producer  - cp.async.bulk.tensor.2d (128B-swizzled boxes) into a 4-stage ring, mbarrier expect_tx
-//   warp 1     : MMA issuer    - one elected thread, tcgen05.mma kind::f16 M=128 N=64 K=16, accumulator in TMEM
-//   warps 2..5 : epilogue      - tcgen05.ld (32 lanes x 32 columns per warp), bias / mask / ReLU, stores, column sums
+// Structure (persistent, warp specialised; 128 x BN output tiles, BN = 64 or 256, one CTA per SM walking the tile list):
+//   warp 0     : TMA producer  - cp.async.bulk.tensor.2d (128B-swizzled boxes) into a 4-6 stage ring, mbarrier expect_tx
+//   warp 1     : MMA issuer    - one elected thread, tcgen05.mma kind::f16 M=128 N=BN K=16, two accumulators in TMEM
+//   warps 2..5 : epilogue      - tcgen05.ld (32 lanes x 32 columns per warp), bias / mask / ReLU, stores, column sums;
+//                                drains accumulator i while the tensor core fills accumulator i+1
 // TMA zero-fills out-of-bounds rows and the K tail, so M, N, K need no padding (only 16-byte row pitches).
 //
 // Operand majors.  Either operand may instead be stored "MN-major" = transposed, i.e. as [K, M] (resp. [K, N]) row-major
@@ -33,13 +34,19 @@
 
 namespace b2 {
 
-constexpr int GM_BM = 128, GM_BN = 64, GM_BK = 64;
-constexpr int GM_STAGES = 4;
+constexpr int GM_BM = 128, GM_BK = 64;
 constexpr int GM_A_BYTES = GM_BM * GM_BK * 2;  // 16 KB
-constexpr int GM_B_BYTES = GM_BN * GM_BK * 2;  //  8 KB
-constexpr int GM_STAGE_BYTES = GM_A_BYTES + GM_B_BYTES;
-constexpr int GM_SMEM = GM_STAGES * GM_STAGE_BYTES + 1024;
 constexpr int GM_THREADS = 192;
+constexpr int GM_ACC_STAGES = 2;  // TMEM accumulators: the epilogue drains one while the tensor core fills the other
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int B_BYTES = BN * GM_BK * 2;
+  static constexpr int STAGE_BYTES = GM_A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 256) ? 4 : 6;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
+  static constexpr uint32_t TMEM_COLS = (uint32_t)(GM_ACC_STAGES * BN) < 32u ? 32u : (uint32_t)(GM_ACC_STAGES * BN);
+};
 
 struct GemmEpilogue {
   float* out_f32;
@@ -58,165 +65,205 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t smem_addr, uint3
   return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
 
-template <bool A_MN, bool B_MN>
+// Persistent, warp-specialised: every CTA walks work items w = blockIdx.x, blockIdx.x + gridDim.x, ...  where
+// w = (output tile, k-split).  Three pipelines: smem ring (TMA -> MMA), TMEM accumulator ring (MMA -> epilogue), tile loop.
+template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GM_THREADS, 1) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
-                                                                   int kb_per_split, GemmEpilogue ep) {
+                                                                   int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep) {
+  using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[GM_STAGES], empty_bar[GM_STAGES], done_bar;
+  __shared__ __align__(8) uint64_t full_bar[Cfg::STAGES], empty_bar[Cfg::STAGES], acc_full[GM_ACC_STAGES], acc_empty[GM_ACC_STAGES];
   __shared__ uint32_t tmem_base_s;
 
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m0 = blockIdx.y * GM_BM, n0 = blockIdx.x * GM_BN;
   const int total_k = (K + GM_BK - 1) / GM_BK;
-  const int kb0 = blockIdx.z * kb_per_split;
-  const int num_k = (total_k - kb0 < kb_per_split) ? (total_k - kb0 > 0 ? total_k - kb0 : 0) : kb_per_split;
-  const bool split = gridDim.z > 1;
+  const int n_work = tiles_m * tiles_n * splits;
+  const bool split = splits > 1;
 
   if (tid == 0) {
     tc::tma_prefetch_desc(&tmap_a);
     tc::tma_prefetch_desc(&tmap_b);
-    for (int s = 0; s < GM_STAGES; ++s) {
+    for (int s = 0; s < Cfg::STAGES; ++s) {
       tc::mbar_init(&full_bar[s], 1);
       tc::mbar_init(&empty_bar[s], 1);
     }
-    tc::mbar_init(&done_bar, 1);
+    for (int a = 0; a < GM_ACC_STAGES; ++a) {
+      tc::mbar_init(&acc_full[a], 1);
+      tc::mbar_init(&acc_empty[a], 4);  // one arrival per epilogue warp
+    }
     tc::mbar_fence_init();
   }
-  if (warp == 1) tc::tmem_alloc<64>(&tmem_base_s);
+  if (warp == 1) tc::tmem_alloc<Cfg::TMEM_COLS>(&tmem_base_s);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = tmem_base_s;
 
+  auto work_coords = [&](int w, int& m0, int& n0, int& kb0, int& nk) {
+    const int z = w % splits;
+    const int t = w / splits;
+    m0 = (t / tiles_n) * GM_BM;  // consecutive work items share the A row block
+    n0 = (t % tiles_n) * BN;
+    kb0 = z * kb_per_split;
+    nk = total_k - kb0;
+    nk = nk < 0 ? 0 : (nk < kb_per_split ? nk : kb_per_split);
+  };
+
   if (warp == 0) {
+    // ================================ TMA producer
     if (tc::elect_one()) {
-      for (int kb = 0; kb < num_k; ++kb) {
-        const int s = kb % GM_STAGES;
-        const uint32_t ph = (uint32_t)((kb / GM_STAGES) & 1);
-        tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-        uint8_t* a_dst = tiles + s * GM_STAGE_BYTES;
-        uint8_t* b_dst = a_dst + GM_A_BYTES;
-        tc::mbar_arrive_expect_tx(&full_bar[s], GM_STAGE_BYTES);
-        const int k0 = (kb0 + kb) * GM_BK;
-        if constexpr (A_MN) {  // stored [K, M]: two 64(K) x 64(M) boxes side by side
-          tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], m0, k0);
-          tc::tma_load_2d(a_dst + GM_BK * 128, &tmap_a, &full_bar[s], m0 + 64, k0);
-        } else {
-          tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], k0, m0);
-        }
-        if constexpr (B_MN) {
-          tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], n0, k0);
-        } else {
-          tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);
+      uint32_t it = 0;
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+        int m0, n0, kb0, nk;
+        work_coords(w, m0, n0, kb0, nk);
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % Cfg::STAGES;
+          tc::mbar_wait(&empty_bar[s], ((it / Cfg::STAGES) & 1u) ^ 1u);
+          uint8_t* a_dst = tiles + s * Cfg::STAGE_BYTES;
+          uint8_t* b_dst = a_dst + GM_A_BYTES;
+          tc::mbar_arrive_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+          const int k0 = (kb0 + kb) * GM_BK;
+          if constexpr (A_MN) {  // stored [K, M]: 64(K) x 64(M) boxes side by side
+            tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], m0, k0);
+            tc::tma_load_2d(a_dst + GM_BK * 128, &tmap_a, &full_bar[s], m0 + 64, k0);
+          } else {
+            tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], k0, m0);
+          }
+          if constexpr (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tc::tma_load_2d(b_dst + j * GM_BK * 128, &tmap_b, &full_bar[s], n0 + 64 * j, k0);
+          } else {
+            tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);
+          }
         }
       }
     }
   } else if (warp == 1) {
+    // ================================ MMA issuer (one thread)
     if (tc::elect_one()) {
-      constexpr uint32_t idesc = tc::make_idesc(tc::FMT_BF16, GM_BM, GM_BN) | (A_MN ? (1u << 15) : 0u) | (B_MN ? (1u << 16) : 0u);
-      for (int kb = 0; kb < num_k; ++kb) {
-        const int s = kb % GM_STAGES;
-        const uint32_t ph = (uint32_t)((kb / GM_STAGES) & 1);
-        tc::mbar_wait(&full_bar[s], ph);
+      constexpr uint32_t idesc = tc::make_idesc(tc::FMT_BF16, GM_BM, BN) | (A_MN ? (1u << 15) : 0u) | (B_MN ? (1u << 16) : 0u);
+      uint32_t it = 0, acc_it = 0;
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++acc_it) {
+        int m0, n0, kb0, nk;
+        work_coords(w, m0, n0, kb0, nk);
+        const uint32_t as = acc_it % GM_ACC_STAGES;
+        tc::mbar_wait(&acc_empty[as], ((acc_it / GM_ACC_STAGES) & 1u) ^ 1u);  // epilogue has drained this accumulator
         tc::fence_after_sync();
-        const uint32_t a_addr = tc::smem_u32(tiles + s * GM_STAGE_BYTES);
-        const uint32_t b_addr = a_addr + GM_A_BYTES;
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % Cfg::STAGES;
+          tc::mbar_wait(&full_bar[s], (it / Cfg::STAGES) & 1u);
+          tc::fence_after_sync();
+          const uint32_t a_addr = tc::smem_u32(tiles + s * Cfg::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + GM_A_BYTES;
 #pragma unroll
-        for (int ks = 0; ks < GM_BK / 16; ++ks) {  // UMMA_K = 16 bf16 = 32 bytes inside the 128-byte swizzle row
-          // K-major: 16 elements = 32 bytes along the swizzle row; MN-major: 16 K-rows = 2048 bytes down the tile
-          const uint64_t da = A_MN ? smem_desc_sw128_mn(a_addr + ks * 2048, GM_BK * 128) : tc::smem_desc_sw128(a_addr + ks * 32);
-          const uint64_t db = B_MN ? smem_desc_sw128_mn(b_addr + ks * 2048, GM_BK * 128) : tc::smem_desc_sw128(b_addr + ks * 32);
-          tc::mma_bf16(tmem_base, da, db, idesc, (kb | ks) != 0 ? 1u : 0u);
+          for (int ks = 0; ks < GM_BK / 16; ++ks) {
+            // K-major: 16 elements = 32 bytes along the swizzle row; MN-major: 16 K-rows = 2048 bytes down the tile
+            const uint64_t da = A_MN ? smem_desc_sw128_mn(a_addr + ks * 2048, GM_BK * 128) : tc::smem_desc_sw128(a_addr + ks * 32);
+            const uint64_t db = B_MN ? smem_desc_sw128_mn(b_addr + ks * 2048, GM_BK * 128) : tc::smem_desc_sw128(b_addr + ks * 32);
+            tc::mma_bf16(d_tmem, da, db, idesc, (kb | ks) != 0 ? 1u : 0u);
+          }
+          tc::mma_commit(&empty_bar[s]);
         }
-        tc::mma_commit(&empty_bar[s]);
+        tc::mma_commit(&acc_full[as]);
       }
-      tc::mma_commit(&done_bar);
     }
   } else {
     // ================================ epilogue: this warp owns TMEM lanes [32q, 32q+32), q = warp % 4
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
-    tc::mbar_wait(&done_bar, 0);
-    tc::fence_after_sync();
-#pragma unroll
-    for (int cb = 0; cb < GM_BN / 32; ++cb) {
-      float v[32];
-      if (num_k > 0) {
-        tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cb * 32), v);
-      } else {
-#pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = 0.f;
-      }
-      const int nb = n0 + cb * 32;
+    uint32_t acc_it = 0;
+    for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++acc_it) {
+      int m0, n0, kb0, nk;
+      work_coords(w, m0, n0, kb0, nk);
+      const uint32_t as = acc_it % GM_ACC_STAGES;
+      const int row = m0 + q * 32 + lane;
       const bool row_ok = row < M;
-#pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const int n = nb + e;
-        float x = v[e];
-        if (ep.bias != nullptr && n < N) x += __ldg(ep.bias + n);
-        if (ep.relu) x = fmaxf(x, 0.f);
-        if (ep.mask != nullptr && row_ok && n < N) x = (__bfloat162float(ep.mask[(int64_t)row * ep.ldm + n]) > 0.f) ? x : 0.f;
-        v[e] = (row_ok && n < N) ? x : 0.f;
-      }
-      if (ep.out_f32 != nullptr && row_ok) {
-        float* o = ep.out_f32 + (int64_t)row * ep.ldo + nb;
-        if (split) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e)
-            if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
-        } else if (nb + 32 <= N && (ep.ldo & 3) == 0) {
-#pragma unroll
-          for (int e = 0; e < 32; e += 4) {
-            float4 w = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
-            if (ep.accumulate) {
-              const float4 old = *reinterpret_cast<const float4*>(o + e);
-              w.x += old.x; w.y += old.y; w.z += old.z; w.w += old.w;
-            }
-            *reinterpret_cast<float4*>(o + e) = w;
-          }
+      tc::mbar_wait(&acc_full[as], (acc_it / GM_ACC_STAGES) & 1u);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int cb = 0; cb < BN / 32; ++cb) {
+        const int nb = n0 + cb * 32;
+        if (nb >= N) break;  // warp-uniform
+        float v[32];
+        if (nk > 0) {
+          tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(cb * 32), v);
         } else {
 #pragma unroll
-          for (int e = 0; e < 32; ++e)
-            if (nb + e < N) o[e] = ep.accumulate ? o[e] + v[e] : v[e];
+          for (int e = 0; e < 32; ++e) v[e] = 0.f;
         }
-      }
-      if (ep.out_bf16 != nullptr && row_ok) {
-        __nv_bfloat16* o = ep.out_bf16 + (int64_t)row * ep.ldo16 + nb;
-        if (nb + 32 <= N && (ep.ldo16 & 7) == 0) {
-#pragma unroll
-          for (int e = 0; e < 32; e += 8) {
-            __nv_bfloat162 p0 = __floats2bfloat162_rn(v[e], v[e + 1]), p1 = __floats2bfloat162_rn(v[e + 2], v[e + 3]);
-            __nv_bfloat162 p2 = __floats2bfloat162_rn(v[e + 4], v[e + 5]), p3 = __floats2bfloat162_rn(v[e + 6], v[e + 7]);
-            uint4 w;
-            w.x = *reinterpret_cast<uint32_t*>(&p0); w.y = *reinterpret_cast<uint32_t*>(&p1);
-            w.z = *reinterpret_cast<uint32_t*>(&p2); w.w = *reinterpret_cast<uint32_t*>(&p3);
-            *reinterpret_cast<uint4*>(o + e) = w;
-          }
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e)
-            if (nb + e < N) o[e] = __float2bfloat16_rn(v[e]);
-        }
-      }
-      if (ep.out_bf16_t != nullptr) {
-        // transposed copy: for a fixed column the 32 lanes hold 32 consecutive rows -> one 64-byte row segment
-#pragma unroll
-        for (int e = 0; e < 32; ++e)
-          if (nb + e < N && row_ok) ep.out_bf16_t[(int64_t)(nb + e) * ep.ldt + row] = __float2bfloat16_rn(v[e]);
-      }
-      if (ep.colsum != nullptr) {
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          const float sum = warp_sum(v[e]);
-          if (lane == 0 && nb + e < N && sum != 0.f) atomicAdd(ep.colsum + nb + e, sum);
+          const int n = nb + e;
+          float x = v[e];
+          if (ep.bias != nullptr && n < N) x += __ldg(ep.bias + n);
+          if (ep.relu) x = fmaxf(x, 0.f);
+          if (ep.mask != nullptr && row_ok && n < N) x = (__bfloat162float(ep.mask[(int64_t)row * ep.ldm + n]) > 0.f) ? x : 0.f;
+          v[e] = (row_ok && n < N) ? x : 0.f;
+        }
+        if (ep.out_f32 != nullptr && row_ok) {
+          float* o = ep.out_f32 + (int64_t)row * ep.ldo + nb;
+          if (split) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+          } else if (nb + 32 <= N && (ep.ldo & 3) == 0) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              float4 wv = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+              if (ep.accumulate) {
+                const float4 old = *reinterpret_cast<const float4*>(o + e);
+                wv.x += old.x; wv.y += old.y; wv.z += old.z; wv.w += old.w;
+              }
+              *reinterpret_cast<float4*>(o + e) = wv;
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (nb + e < N) o[e] = ep.accumulate ? o[e] + v[e] : v[e];
+          }
+        }
+        if (ep.out_bf16 != nullptr && row_ok) {
+          __nv_bfloat16* o = ep.out_bf16 + (int64_t)row * ep.ldo16 + nb;
+          if (nb + 32 <= N && (ep.ldo16 & 7) == 0) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 8) {
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(v[e], v[e + 1]), p1 = __floats2bfloat162_rn(v[e + 2], v[e + 3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(v[e + 4], v[e + 5]), p3 = __floats2bfloat162_rn(v[e + 6], v[e + 7]);
+              uint4 wv;
+              wv.x = *reinterpret_cast<uint32_t*>(&p0); wv.y = *reinterpret_cast<uint32_t*>(&p1);
+              wv.z = *reinterpret_cast<uint32_t*>(&p2); wv.w = *reinterpret_cast<uint32_t*>(&p3);
+              *reinterpret_cast<uint4*>(o + e) = wv;
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (nb + e < N) o[e] = __float2bfloat16_rn(v[e]);
+          }
+        }
+        if (ep.out_bf16_t != nullptr) {
+          // transposed copy: for a fixed column the 32 lanes hold 32 consecutive rows -> one 64-byte row segment
+#pragma unroll
+          for (int e = 0; e < 32; ++e)
+            if (nb + e < N && row_ok) ep.out_bf16_t[(int64_t)(nb + e) * ep.ldt + row] = __float2bfloat16_rn(v[e]);
+        }
+        if (ep.colsum != nullptr) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float sum = warp_sum(v[e]);
+            if (lane == 0 && nb + e < N && sum != 0.f) atomicAdd(ep.colsum + nb + e, sum);
+          }
         }
       }
+      // every tcgen05.ld of this warp has completed (tmem_ld32 waits): hand the accumulator back to the MMA warp
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[as]);
     }
-    tc::fence_before_sync();
   }
+  tc::fence_before_sync();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc<64>(tmem_base);
+  if (warp == 1) tc::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ---------------------------------------------------------------------------------------------- host: tensor maps
@@ -246,7 +293,7 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int 
   }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)GM_BK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)GM_BK, (cuuint32_t)box_rows};  // box_rows <= 256 (TMA limit)
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -261,25 +308,44 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int 
 
 using namespace b2;
 
+template <int BN>
+static int launch_gemm(const b2_gemm_args* a, const CUtensorMap& ta, const CUtensorMap& tb, int splits, int kb_per_split, const GemmEpilogue& ep, cudaStream_t st) {
+  using Cfg = GemmCfg<BN>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set[dev] = true;
+  }
+  const int tiles_m = (a->M + GM_BM - 1) / GM_BM, tiles_n = (a->N + BN - 1) / BN;
+  const int n_work = tiles_m * tiles_n * splits;
+  int grid = sm_count();
+  if (n_work < grid) grid = n_work;
+  if (a->a_mn && a->b_mn) gemm_bf16_kernel<BN, true, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
+  else if (a->a_mn) gemm_bf16_kernel<BN, true, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
+  else if (a->b_mn) gemm_bf16_kernel<BN, false, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
+  else gemm_bf16_kernel<BN, false, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
+  B2_LAUNCH_CHECK("gemm_bf16_kernel");
+  return 0;
+}
+
 extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
   if (a == nullptr || a->M <= 0 || a->N <= 0 || a->K < 0) {
     set_error("gemm: bad shape");
     return 1;
   }
+  // tile width: 256 columns when the problem is big enough to fill the chip with such tiles (halves the shared-memory
+  // traffic per MMA, the limiter at N=64), 64 columns for the small / skinny GEMMs of federated local training
+  const int64_t big_tiles = (int64_t)((a->M + GM_BM - 1) / GM_BM) * ((a->N + 255) / 256);
+  const int bn = (a->N >= 256 && big_tiles >= sm_count() && !a->b_mn) ? 256 : 64;
   CUtensorMap ta, tb;
   // K-major operand: [M, K] rows = M; MN-major operand: stored [K, M], rows = K, 64 x 64 boxes
   if (a->a_mn ? make_tmap(&ta, a->A, a->K, a->M, a->lda, GM_BK) : make_tmap(&ta, a->A, a->M, a->K, a->lda, GM_BM)) return 1;
-  if (a->b_mn ? make_tmap(&tb, a->B, a->K, a->N, a->ldb, GM_BK) : make_tmap(&tb, a->B, a->N, a->K, a->ldb, GM_BN)) return 1;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  B2_CUDA(cudaGetDevice(&dev));
-  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM));
-    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM));
-    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM));
-    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM));
-    attr_set[dev] = true;
-  }
+  if (a->b_mn ? make_tmap(&tb, a->B, a->K, a->N, a->ldb, GM_BK) : make_tmap(&tb, a->B, a->N, a->K, a->ldb, bn)) return 1;
   const int total_k = (a->K + GM_BK - 1) / GM_BK;
   int splits = a->split_k > 1 ? a->split_k : 1;
   if (splits > total_k) splits = total_k > 0 ? total_k : 1;
@@ -287,17 +353,12 @@ extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
     set_error("gemm: split_k only combines with a plain fp32 (accumulating) output");
     return 1;
   }
-  const int kb_per_split = (total_k + splits - 1) / splits;
-  splits = kb_per_split > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
+  int kb_per_split = (total_k + splits - 1) / splits;
+  if (kb_per_split < 1) kb_per_split = 1;
+  splits = total_k > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
   GemmEpilogue ep{a->out_f32, static_cast<__nv_bfloat16*>(a->out_bf16), static_cast<__nv_bfloat16*>(a->out_bf16_t), a->bias, static_cast<const __nv_bfloat16*>(a->mask),
                   a->colsum, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate};
-  dim3 grid((a->N + GM_BN - 1) / GM_BN, (a->M + GM_BM - 1) / GM_BM, splits > 0 ? splits : 1);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int kps = kb_per_split > 0 ? kb_per_split : 1;
-  if (a->a_mn && a->b_mn) gemm_bf16_kernel<true, true><<<grid, GM_THREADS, GM_SMEM, st>>>(ta, tb, a->M, a->N, a->K, kps, ep);
-  else if (a->a_mn) gemm_bf16_kernel<true, false><<<grid, GM_THREADS, GM_SMEM, st>>>(ta, tb, a->M, a->N, a->K, kps, ep);
-  else if (a->b_mn) gemm_bf16_kernel<false, true><<<grid, GM_THREADS, GM_SMEM, st>>>(ta, tb, a->M, a->N, a->K, kps, ep);
-  else gemm_bf16_kernel<false, false><<<grid, GM_THREADS, GM_SMEM, st>>>(ta, tb, a->M, a->N, a->K, kps, ep);
-  B2_LAUNCH_CHECK("gemm_bf16_kernel");
-  return 0;
+  if (bn == 256) return launch_gemm<256>(a, ta, tb, splits, kb_per_split, ep, st);
+  return launch_gemm<64>(a, ta, tb, splits, kb_per_split, ep, st);
 }

@@ -58,6 +58,21 @@ class Aggregator:
     def on_model_added(self, fn: Callable[[], None]) -> None:
         self._listeners.append(fn)
 
+    def drop_node(self, addr: str) -> bool:
+        """A train-set member is known to be dead (evicted by the failure detector): stop waiting for its model.
+
+        The reference only learns this by sitting out ``AGGREGATION_TIMEOUT`` (aggregator.py:192-208).  A model the node
+        already delivered (alone or inside a partial aggregate) stays in; returns True if the train set shrank."""
+        with self.__agg_lock:
+            if addr not in self.__train_set or addr in self.get_aggregated_models():
+                return False
+            self.__train_set = [n for n in self.__train_set if n != addr]
+            if self.__train_set and len(self.get_aggregated_models()) >= len(self.__train_set):
+                self._finish_aggregation_event.set()
+        for fn in self._listeners:
+            fn()
+        return True
+
     # -- collection ------------------------------------------------------------------
     def get_aggregated_models(self) -> List[str]:
         out: List[str] = []

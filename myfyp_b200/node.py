@@ -126,6 +126,17 @@ class Node:
         self._communication_protocol.disconnect(addr, disconnect_msg=True)
 
     def _on_neighbors_changed(self) -> None:
+        st = self.state
+        if st.round is not None and st.train_set:
+            # failure detector -> aggregation: a train-set member that is no longer a neighbour will not deliver its model
+            try:
+                alive = set(self._communication_protocol.get_neighbors(only_direct=False)) | {self.addr}
+                for dead in [n for n in st.train_set if n not in alive]:
+                    if self.aggregator.drop_node(dead):
+                        st.train_set = [n for n in st.train_set if n != dead]
+                        logger.info(self.addr, f"☠️ {dead} left during the round: aggregating without it.")
+            except Exception:  # noqa: BLE001
+                pass
         self.state.notify()
         if Settings.ALLOW_REJOIN and self.state.round is not None and self._learning_args is not None:
             self._invite_newcomers()

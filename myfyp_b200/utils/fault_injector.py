@@ -98,6 +98,29 @@ class FaultInjector:
         t.start()
         self._threads.append(t)
 
+    def rejoin_at(self, make_node: Callable[[], object], connect_to: List[str], watch_node, round: int, poll: float = 0.005, on_joined: Optional[Callable[[object], None]] = None) -> None:
+        """Bring a (new) node up and connect it once ``watch_node`` has reached ``round``."""
+
+        def watch():
+            while True:
+                r = watch_node.state.round
+                if r is not None and r >= round:
+                    break
+                if watch_node.learning_workflow.finished and len(watch_node.learning_workflow.history) > 1:
+                    return
+                time.sleep(poll)
+            node = make_node()
+            node.start()
+            for a in connect_to:
+                node.connect(a)
+            self.events.append(("rejoin", node.addr, round, None, time.time()))
+            if on_joined is not None:
+                on_joined(node)
+
+        t = threading.Thread(target=watch, daemon=True, name="fault-rejoin")
+        t.start()
+        self._threads.append(t)
+
     def join(self, timeout: float = 60) -> None:
         for t in self._threads:
             t.join(timeout)
