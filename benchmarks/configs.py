@@ -25,7 +25,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples, train_set, device_mode, byzantine=0, faults=None, seed=0, batch=64):
+def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples, train_set, device_mode, byzantine=0, faults=None, seed=0, batch=64, graphs=None):
     import numpy as np
     import torch
 
@@ -56,12 +56,15 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
     parts = data.generate_partitions(n_nodes, RandomIIDPartitionStrategy, seed=seed)
     mk = {"mlp": mlp_model, "cnn": cnn_model, "resnet18": resnet18_model}[model_name]
     gpus = torch.cuda.device_count() if device_mode == "cuda" else 0
+    if graphs is None:  # capturing 32-64 ResNet graphs costs minutes; short scenario runs train eagerly
+        graphs = model_name != "resnet18"
+    Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS = 60
     if gpus > 1:
         Fabric.get().enable_peer_access()
     nodes = []
     for i in range(n_nodes):
         dev = f"cuda:{i % gpus}" if gpus else "cpu"
-        nodes.append(Node(mk(device=dev, seed=seed + i), parts[i], address=f"{name}-{i}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch))
+        nodes.append(Node(mk(device=dev, seed=seed + i), parts[i], address=f"{name}-{i}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs))
     for n in nodes:
         n.start()
     for n in nodes[n_nodes - byzantine :]:
@@ -79,7 +82,7 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
             fi.drop_at(nodes[idx], round=rnd, stage="TrainStage")
         for idx, at_round in faults.get("rejoin", []):
             def make(idx=idx):
-                n = Node(mk(device=f"cuda:{idx % gpus}" if gpus else "cpu", seed=1000 + idx), parts[idx], address=f"{name}-re-{idx}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch)
+                n = Node(mk(device=f"cuda:{idx % gpus}" if gpus else "cpu", seed=1000 + idx), parts[idx], address=f"{name}-re-{idx}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs)
                 late.append(n)
                 return n
             targets = [nodes[j].addr for j in range(min(4, n_nodes)) if j != idx]

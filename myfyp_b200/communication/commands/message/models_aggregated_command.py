@@ -21,5 +21,9 @@ class ModelsAggregatedCommand(Command):
             cur = self.state.models_aggregated.get(source, [])
             self.state.models_aggregated[source] = cur + [a for a in args if a not in cur]
             self.state.notify()
+        elif self.state.round is not None and round == self.state.round + 1:
+            # the sender is already one round ahead of us: keep its announcement for when we get there
+            nxt = self.state.models_aggregated_next.setdefault(source, [])
+            nxt += [a for a in args if a not in nxt]
         else:
             logger.debug(self.state.addr, f"models_aggregated from {source} in a late round ({round} != {self.state.round}). Ignored.")

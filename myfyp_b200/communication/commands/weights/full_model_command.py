@@ -26,8 +26,14 @@ class FullModelCommand(Command):
             logger.debug(st.addr, "❌ Tried to add a model while learning is not running")
             return
         if round != st.round:
-            logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
-            return
+            if st.rejoining and round > st.round and st.experiment is not None:
+                # we joined a running experiment believing it was in round st.round, but the network has moved on:
+                # fast-forward to the round this aggregate belongs to
+                logger.info(st.addr, f"⏩ Rejoining: fast-forward from round {st.round} to {round}.")
+                st.experiment.round = round
+            else:
+                logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
+                return
         try:
             with self._mutex:
                 if st.aggregated_model_event.is_set():
@@ -35,6 +41,7 @@ class FullModelCommand(Command):
                     return
                 logger.info(st.addr, "📦 Aggregated model received.")
                 self.learner.set_model(weights)
+                st.rejoining = False
                 st.aggregated_model_event.set()
             st.notify()
         except DecodingParamsError:

@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import os
 import threading
+import time
 from concurrent import futures
 from typing import Any, Dict, List, Optional, Union
 
@@ -116,6 +117,9 @@ class GrpcServer:
         if not is_weights and not self._gossiper.check_and_set_processed(msg["hash"]):
             return None
         cmd = msg["cmd"]
+        if not is_weights and cmd != "beat" and msg["source"] != self.addr:
+            # any message proves its origin is alive: learn about it now rather than at its next heartbeat
+            self._neighbors.refresh_or_add(msg["source"], time.time())
         if cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS:
             logger.debug(self.addr, f"📫 {cmd.upper()} received from {msg['source']}")
         handler = self._commands.get(cmd)

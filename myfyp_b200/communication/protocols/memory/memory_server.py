@@ -5,6 +5,7 @@ Reference: communication/protocols/memory/memory_server.py:40-222.
 
 from __future__ import annotations
 
+import time
 from typing import Any, Dict, List, Optional, Union
 
 from myfyp_b200.communication.commands.command import Command
@@ -62,6 +63,10 @@ class InMemoryServer:
         if not self.__gossiper.check_and_set_processed(request["hash"]):
             return {}
         cmd = request["cmd"]
+        if cmd != "beat" and request["source"] != self.addr:
+            # any message proves its origin is alive: learn about it now rather than at its next heartbeat (a node that
+            # just (re)joined would otherwise be missing from some nodes' vote bookkeeping -> diverging train sets)
+            self.__neighbors.refresh_or_add(request["source"], time.time())
         if cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS:
             logger.debug(self.addr, f"📫 {cmd.upper()} received from {request['source']} (ttl={request['ttl']})")
         # re-gossip first (same order as the reference, memory_server.py:155-165)

@@ -127,6 +127,18 @@ class Aggregator:
     def get_missing_models(self) -> set:
         return set(self.__train_set) - set(self.get_aggregated_models())
 
+    def peek_offer(self, except_nodes: List[str]) -> List[str]:
+        """Contributors of what :meth:`get_model` would return for a peer holding ``except_nodes`` - without aggregating."""
+        usable = [m for m in self._held() if all(n not in except_nodes for n in m.get_contributors())]
+        if not usable:
+            return []
+        if self.partial_aggregation:
+            out: List[str] = []
+            for m in usable:
+                out += m.get_contributors()
+            return out
+        return list(usable[0].get_contributors())
+
     def get_model(self, except_nodes: List[str]) -> P2PFLModel:
         """What to offer a peer that already holds ``except_nodes``."""
         usable = [m for m in self._held() if all(n not in except_nodes for n in m.get_contributors())]

@@ -254,6 +254,11 @@ class Node:
                 logger.experiment_started(self.addr, self.state.experiment)
                 with contextlib.suppress(RuntimeError):
                     self.state.model_initialized_lock.release()
+                self.state.rejoining = True
+                # we do not vote in the round we enter: tell everybody, so nobody waits VOTE_TIMEOUT for our ballot
+                p = self._communication_protocol
+                with contextlib.suppress(Exception):
+                    p.broadcast(p.build_msg(VoteTrainSetCommand.get_name(), [], round=start_round))
                 first = "WaitAggregatedModelsStage"
                 kw: Dict[str, Any] = {"first_stage": first}
             else:

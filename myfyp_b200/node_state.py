@@ -24,9 +24,11 @@ class NodeState:
         self.simulation = simulation
         self.experiment_config = None
         self.experiment: Optional[Experiment] = None
+        self.rejoining = False  # entered a running experiment and still waits for its first aggregated model
 
         # learning bookkeeping
         self.models_aggregated: Dict[str, List[str]] = {}
+        self.models_aggregated_next: Dict[str, List[str]] = {}  # announcements of peers that are one round ahead
         self.nei_status: Dict[str, int] = {}
         self.train_set: List[str] = []
         self.train_set_votes: Dict[str, Dict[str, int]] = {}
@@ -86,7 +88,7 @@ class NodeState:
         if self.experiment is None:
             raise ValueError("Experiment not initialized")
         self.experiment.increase_round()
-        self.models_aggregated = {}
+        self.models_aggregated, self.models_aggregated_next = self.models_aggregated_next, {}
         self.notify()
 
     def clear(self) -> None:

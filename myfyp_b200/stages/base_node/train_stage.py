@@ -80,7 +80,13 @@ class TrainStage(Stage):
         def remaining(node: str) -> Set[str]:
             return set(state.train_set) - set(aggregated_by(node))
 
+        def fresh_offer(node: str) -> bool:
+            key = (node, frozenset(aggregator.peek_offer(aggregated_by(node))))
+            return bool(key[1]) and time.monotonic() - offered.get(key, -1e9) >= reoffer_after
+
         def get_candidates_fn() -> List[str]:
+            # the loop ends on the peers' ANNOUNCEMENTS, not on what we offered: an offer can be refused (overlap with
+            # something the peer got meanwhile), and only its next announcement tells us what it still lacks
             return [n for n in set(state.train_set) - {state.addr} if len(remaining(n)) != 0]
 
         def status_fn() -> Any:
@@ -94,6 +100,8 @@ class TrainStage(Stage):
         reoffer_after = max(1.0, 20 * Settings.GOSSIP_MODELS_PERIOD)
 
         def model_fn(node: str) -> Any:
+            if not fresh_offer(node):  # nothing new for this peer: do not even run the partial-aggregation kernel
+                return None
             try:
                 model = aggregator.get_model(aggregated_by(node))
             except NoModelsToAggregateError:
@@ -101,11 +109,7 @@ class TrainStage(Stage):
                 return None
             if state.round is None:
                 raise Exception("Round not initialized.")
-            key = (node, frozenset(model.get_contributors()))
-            now = time.monotonic()
-            if now - offered.get(key, -1e9) < reoffer_after:
-                return None
-            offered[key] = now
+            offered[(node, frozenset(model.get_contributors()))] = time.monotonic()
             return communication_protocol.build_weights(
                 PartialModelCommand.get_name(), state.round, _transport(model, communication_protocol, node), model.get_contributors(), model.get_num_samples()
             )
