@@ -267,6 +267,10 @@ class Node:
                 rounds=rounds, epochs=epochs, state=self.state, learner=self.learner, communication_protocol=self._communication_protocol, aggregator=self.aggregator, **kw
             )
         except Exception as e:  # noqa: BLE001
+            if not self.__running:  # the node was stopped (or crashed on purpose) under its own learning thread
+                logger.debug(self.addr, f"learning thread ended after stop: {type(e).__name__}: {e}")
+                self.learning_workflow.finished = True
+                return
             logger.error(self.addr, f"Error {type(e).__name__}: {e}\n{traceback.format_exc()}")
             self.stop()
 
