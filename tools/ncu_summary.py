@@ -29,6 +29,31 @@ def main():
             print("no data in", rep)
             continue
         hdr, units, vals = rows[0], rows[1], rows[-1]
+        if len(rows) > 3:  # several kernels in one report: one table row per launch
+            col = {h: i for i, h in enumerate(hdr)}
+            pick = ["gpu__time_duration.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+                    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+                    "launch__grid_size", "dram__bytes_read.sum", "dram__bytes_write.sum"]
+            with open(os.path.join(out_dir, name + ".md"), "w") as f:
+                f.write(f"# ncu --set full, every launch of `{os.path.basename(rep)}`\n\n| kernel | time | dram % | sm % | tensor % | warps active % | regs | grid | dram read | dram write |\n|---|---|---|---|---|---|---|---|---|---|\n")
+                for r in rows[2:]:
+                    kn = r[col["Kernel Name"]].split("(")[0].replace("void ", "").replace("b2::", "")
+                    cells = []
+                    for k in pick:
+                        if k in col:
+                            v = r[col[k]]
+                            try:
+                                v = f"{float(v.replace(',', '')):.2f}"
+                            except ValueError:
+                                pass
+                            cells.append(f"{v} {units[col[k]]}".strip())
+                        else:
+                            cells.append("-")
+                    f.write(f"| `{kn}` | " + " | ".join(cells) + " |\n")
+            with open(os.path.join(out_dir, name + ".raw.csv"), "w") as f:
+                f.write(raw)
+            print("wrote", name, f"({len(rows) - 2} launches)")
+            continue
         with open(os.path.join(out_dir, name + ".raw.csv"), "w") as f:
             w = csv.writer(f)
             w.writerow(["metric", "unit", "value"])
