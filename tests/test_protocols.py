@@ -244,3 +244,41 @@ def test_address_parser():
     assert AddressParser("unix:///tmp/x.sock").get_parsed_address() == "unix:///tmp/x.sock"
     with pytest.raises(ValueError):
         AddressParser("not an address:99999999").get_parsed_address()
+
+
+def test_grpc_mutual_tls(tmp_path):
+    """gRPC over mTLS with certificates from certificates/gen-certs.sh (the reference's CI generates its own the same way)."""
+    import os
+    import shutil
+    import subprocess
+
+    if shutil.which("openssl") is None:
+        pytest.skip("openssl not available")
+    script = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "myfyp_b200", "certificates", "gen-certs.sh")
+    shutil.copy(script, tmp_path / "gen-certs.sh")
+    subprocess.run(["bash", str(tmp_path / "gen-certs.sh")], check=True, capture_output=True)
+    Settings.USE_SSL = True
+    Settings.GRPC_LOCAL_SHORTCUT = False
+    Settings.CA_CRT, Settings.SERVER_CRT, Settings.SERVER_KEY = str(tmp_path / "ca.crt"), str(tmp_path / "server.crt"), str(tmp_path / "server.key")
+    Settings.CLIENT_CRT, Settings.CLIENT_KEY = str(tmp_path / "client.crt"), str(tmp_path / "client.key")
+    cmd = MockCommand()
+    p1, p2 = GrpcCommunicationProtocol("127.0.0.1"), GrpcCommunicationProtocol("127.0.0.1", commands=[cmd])
+    p1.start()
+    p2.start()
+    try:
+        assert p1.connect(p2.get_address())
+        p1.send(p2.get_address(), p1.build_msg("mock", ["secret"]), raise_error=True)
+        assert cmd.calls[-1][2] == ("secret",)
+        # a client without certificates cannot talk to the TLS server
+        import grpc
+
+        from myfyp_b200.communication.protocols.grpc import wire
+
+        ch = grpc.insecure_channel(p2.get_address())
+        call = ch.unary_unary("/node.NodeServices/handshake", request_serializer=wire.encode_handshake, response_deserializer=wire.decode_response)
+        with pytest.raises(grpc.RpcError):
+            call("intruder", timeout=1.0)
+        ch.close()
+    finally:
+        p1.stop()
+        p2.stop()
