@@ -130,6 +130,7 @@ typedef struct {
   int accumulate;     /* out_f32 += result instead of = */
   int a_mn, b_mn;     /* operand stored transposed: A as [K, lda>=M], B as [K, ldb>=N] (MN-major UMMA operands) */
   int split_k;        /* > 1: split the K loop over grid.z, atomically adding into out_f32 (which must hold 0 or the running sum) */
+  float* colsumsq;    /* optional fp32 [N]: += column sums of squares (batch-norm statistics of the output), atomic */
 } b2_gemm_args;
 int b2_gemm_bf16(const b2_gemm_args* args, void* stream);
 /* fp32 [R,C] (pitch lds) -> bf16 row-major copy (pitch ldd, optional), bf16 transposed copy [C,R] (pitch ldt, optional),
@@ -141,7 +142,19 @@ int b2_cast_transpose(const float* src, int R, int C, int lds, void* dst_bf16, i
  * Patch index order is (c, kh, kw) = PyTorch's [Cout, Cin, KH, KW] weights flattened, so weights are used in place.
  * Reference path: torch conv2d / max_pool2d via autograd (the reference ships no CNN; BASELINE.json configs 2-4 name one). */
 int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
-int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+/* dx = col2im(dcol) (+ add, when the activation has a second consumer such as a residual / shortcut branch) */
+int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, const void* add_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+/* T5 batch normalisation on [M, C] NHWC bf16.  Training: `stats` = [sum[C], sumsq[C]] as accumulated by b2_gemm_bf16 (colsum / colsumsq);
+ * y = act(gamma (z - mean) invstd + beta (+ residual)); running statistics and the batch counter are updated with PyTorch semantics.
+ * Eval: stats == NULL, the running statistics are used.  Reference path: torch batch_norm via autograd (ResNet-18 is not in the reference). */
+int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, const float* stats, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                float* num_batches, float eps, float momentum, int M, int C, int relu, void* stream);
+/* g = dy * (y > 0 if relu) (stored: it is also the gradient of the residual branch); dz = gamma invstd (g - mean g - xhat mean(g xhat));
+ * dgamma += sum g xhat, dbeta += sum g.  `red2c` is a 2C-float scratch. */
+int b2_bn_backward(const void* dy_bf16, const void* y_bf16, const void* z_bf16, void* g_bf16, void* dz_bf16, float* red2c, const float* stats, const float* gamma, float* dgamma,
+                   float* dbeta, float eps, int M, int C, int relu, void* stream);
+int b2_avgpool_fwd(const void* x_bf16, void* out_bf16, int ldo, int B, int HW, int C, void* stream);
+int b2_avgpool_bwd(const void* dout_bf16, int ldo, void* dx_bf16, int B, int HW, int C, void* stream);
 int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H, int W, int C, void* stream);
 /* dz = dp routed to the remembered maximum, times the ReLU mask (y > 0) of the pre-pool activation */
 int b2_maxpool2_relu_bwd(const void* dp_bf16, const void* idx_u8, const void* y_bf16, void* dz_bf16, int B, int H, int W, int C, void* stream);

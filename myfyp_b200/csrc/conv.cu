@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(256) im2col_kernel(const void* __restrict__ xi
 }
 
 // dx[b,h,w,c] = sum over the taps (kh,kw) whose output pixel exists of dcol[(b,oh,ow), c*KK + kh*KW + kw]
-__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int ldc) {
+__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int ldc,
+                                                     const __nv_bfloat16* __restrict__ add) {
   const int64_t total = (int64_t)g.B * g.H * g.W * g.C;
   const int KK = g.KH * g.KW;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -74,7 +75,126 @@ __global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __rest
         acc += __bfloat162float(dcol[m * ldc + (int64_t)c * KK + kh * g.KW + kw]);
       }
     }
+    if (add != nullptr) acc += __bfloat162float(add[i]);  // second consumer of the same activation (residual / shortcut branch)
     dx[i] = __float2bfloat16_rn(acc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ T5: batch normalisation
+// Training statistics come for free from the producing GEMM's epilogue (column sums and sums of squares of the fp32
+// accumulators, `stats` = [sum[C], sumsq[C]]).  mean / invstd are recomputed from them wherever needed (2 loads + rsqrt).
+struct BnArgs {
+  const float* stats;     // [2C] batch sums (training) - nullptr in eval mode
+  const float* gamma;     // [C]
+  const float* beta;      // [C]
+  float* running_mean;    // [C] (updated by block 0 in training, read in eval)
+  float* running_var;     // [C]
+  float* num_batches;     // fp32 mirror slot of num_batches_tracked (may be null)
+  float eps, momentum;
+  int M, C, relu;
+};
+
+// y = act(gamma * (z - mean) * invstd + beta (+ residual))
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y, BnArgs a) {
+  const int64_t total = (int64_t)a.M * a.C;
+  const float invM = 1.f / (float)a.M;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % a.C);
+    float mean, var;
+    if (a.stats != nullptr) {
+      mean = a.stats[c] * invM;
+      var = fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f);
+    } else {
+      mean = a.running_mean[c];
+      var = a.running_var[c];
+    }
+    float v = (__bfloat162float(z[i]) - mean) * rsqrtf(var + a.eps) * a.gamma[c] + a.beta[c];
+    if (residual != nullptr) v += __bfloat162float(residual[i]);
+    if (a.relu) v = fmaxf(v, 0.f);
+    y[i] = __float2bfloat16_rn(v);
+  }
+  if (a.stats != nullptr && blockIdx.x == 0) {  // running statistics (PyTorch semantics: unbiased variance, momentum)
+    for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+      const float mean = a.stats[c] * invM;
+      const float var = fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f);
+      const float unbiased = a.M > 1 ? var * (float)a.M / (float)(a.M - 1) : var;
+      a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+      a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * unbiased;
+    }
+    if (threadIdx.x == 0 && a.num_batches != nullptr) a.num_batches[0] += 1.f;
+  }
+}
+
+// pass 1 of the backward: g = dy * (y > 0 if relu);  red[c] += sum g, red[C + c] += sum g * xhat;  g is stored for pass 2
+// (and is at the same time the gradient that flows into the residual branch)
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ z,
+                                                            __nv_bfloat16* __restrict__ gbuf, float* __restrict__ red, BnArgs a, int rows_per_block) {
+  extern __shared__ float s_red[];  // 2C
+  for (int c = threadIdx.x; c < 2 * a.C; c += blockDim.x) s_red[c] = 0.f;
+  __syncthreads();
+  const float invM = 1.f / (float)a.M;
+  const int m0 = blockIdx.x * rows_per_block, m1 = min(a.M, m0 + rows_per_block);
+  const int cols = blockDim.x < a.C ? blockDim.x : a.C;
+  const int groups = blockDim.x / cols, gid = threadIdx.x / cols, lane = threadIdx.x % cols;
+  if (gid < groups) {
+    for (int c = lane; c < a.C; c += cols) {
+      const float mean = a.stats[c] * invM;
+      const float invstd = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f) + a.eps);
+      float sg = 0.f, sgx = 0.f;
+      for (int m = m0 + gid; m < m1; m += groups) {
+        const int64_t i = (int64_t)m * a.C + c;
+        float g = __bfloat162float(dy[i]);
+        if (a.relu && !(__bfloat162float(y[i]) > 0.f)) g = 0.f;
+        const __nv_bfloat16 gq = __float2bfloat16_rn(g);
+        gbuf[i] = gq;
+        g = __bfloat162float(gq);
+        sg += g;
+        sgx += g * (__bfloat162float(z[i]) - mean) * invstd;
+      }
+      atomicAdd(&s_red[c], sg);
+      atomicAdd(&s_red[a.C + c], sgx);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * a.C; c += blockDim.x)
+    if (s_red[c] != 0.f) atomicAdd(red + c, s_red[c]);
+}
+
+// pass 2: dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat));  block 0 adds dgamma / dbeta into the gradient slab
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ gbuf, const __nv_bfloat16* __restrict__ z, const float* __restrict__ red,
+                                                           __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta, BnArgs a) {
+  const int64_t total = (int64_t)a.M * a.C;
+  const float invM = 1.f / (float)a.M;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % a.C);
+    const float mean = a.stats[c] * invM;
+    const float invstd = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f) + a.eps);
+    const float xhat = (__bfloat162float(z[i]) - mean) * invstd;
+    const float v = a.gamma[c] * invstd * (__bfloat162float(gbuf[i]) - red[c] * invM - xhat * red[a.C + c] * invM);
+    dz[i] = __float2bfloat16_rn(v);
+  }
+  if (blockIdx.x == 0)
+    for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+      dbeta[c] += red[c];
+      dgamma[c] += red[a.C + c];
+    }
+}
+
+// global average pooling over the H*W pixels of an NHWC map, and its backward (broadcast / HW)
+__global__ void __launch_bounds__(256) avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int HW, int C, int ldo) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B * C; i += gridDim.x * blockDim.x) {
+    const int c = i % C, b = i / C;
+    float acc = 0.f;
+    for (int p = 0; p < HW; ++p) acc += __bfloat162float(x[((int64_t)b * HW + p) * C + c]);
+    out[(int64_t)b * ldo + c] = __float2bfloat16_rn(acc / (float)HW);
+  }
+}
+__global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int ldo, __nv_bfloat16* __restrict__ dx, int B, int HW, int C) {
+  const int64_t total = (int64_t)B * HW * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int b = (int)(i / ((int64_t)HW * C));
+    dx[i] = __float2bfloat16_rn(__bfloat162float(dout[(int64_t)b * ldo + c]) / (float)HW);
   }
 }
 
@@ -240,11 +360,63 @@ int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, 
   return 0;
 }
 
-int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream) {
+int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, const void* add_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream) {
   ConvGeom g{B, H, W, C, KH, KW, stride, pad, (H + 2 * pad - KH) / stride + 1, (W + 2 * pad - KW) / stride + 1};
   const int64_t total = (int64_t)B * H * W * C;
-  col2im_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dcol_bf16), static_cast<__nv_bfloat16*>(dx_bf16), g, ldc);
+  col2im_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dcol_bf16), static_cast<__nv_bfloat16*>(dx_bf16), g, ldc,
+                                                                                       static_cast<const __nv_bfloat16*>(add_bf16));
   B2_LAUNCH_CHECK("col2im_kernel");
+  return 0;
+}
+
+static BnArgs bn_args(const float* stats, const float* gamma, const float* beta, float* rm, float* rv, float* nb, float eps, float momentum, int M, int C, int relu) {
+  return BnArgs{stats, gamma, beta, rm, rv, nb, eps, momentum, M, C, relu};
+}
+
+int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, const float* stats, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                float* num_batches, float eps, float momentum, int M, int C, int relu, void* stream) {
+  if (M <= 0 || C <= 0) return 0;
+  bn_apply_kernel<<<stream_grid((int64_t)M * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(z_bf16), static_cast<const __nv_bfloat16*>(residual_bf16), static_cast<__nv_bfloat16*>(y_bf16),
+      bn_args(stats, gamma, beta, running_mean, running_var, num_batches, eps, momentum, M, C, relu));
+  B2_LAUNCH_CHECK("bn_apply_kernel");
+  return 0;
+}
+
+int b2_bn_backward(const void* dy_bf16, const void* y_bf16, const void* z_bf16, void* g_bf16, void* dz_bf16, float* red2c, const float* stats, const float* gamma, float* dgamma,
+                   float* dbeta, float eps, int M, int C, int relu, void* stream) {
+  if (M <= 0 || C <= 0) return 0;
+  if (C > 4096) {
+    set_error("bn_backward: C=%d too wide", C);
+    return 1;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  BnArgs a = bn_args(stats, gamma, nullptr, nullptr, nullptr, nullptr, eps, 0.f, M, C, relu);
+  B2_CUDA(cudaMemsetAsync(red2c, 0, 2 * C * sizeof(float), s));
+  int blocks = sm_count() * 2;
+  int rows_per_block = (M + blocks - 1) / blocks;
+  if (rows_per_block < 16) rows_per_block = 16;
+  blocks = (M + rows_per_block - 1) / rows_per_block;
+  bn_bwd_reduce_kernel<<<blocks, 256, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(dy_bf16), static_cast<const __nv_bfloat16*>(y_bf16),
+                                                                  static_cast<const __nv_bfloat16*>(z_bf16), static_cast<__nv_bfloat16*>(g_bf16), red2c, a, rows_per_block);
+  B2_LAUNCH_CHECK("bn_bwd_reduce_kernel");
+  bn_bwd_apply_kernel<<<stream_grid((int64_t)M * C, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(g_bf16), static_cast<const __nv_bfloat16*>(z_bf16), red2c,
+                                                                       static_cast<__nv_bfloat16*>(dz_bf16), dgamma, dbeta, a);
+  B2_LAUNCH_CHECK("bn_bwd_apply_kernel");
+  return 0;
+}
+
+int b2_avgpool_fwd(const void* x_bf16, void* out_bf16, int ldo, int B, int HW, int C, void* stream) {
+  avgpool_fwd_kernel<<<stream_grid((int64_t)B * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x_bf16), static_cast<__nv_bfloat16*>(out_bf16), B,
+                                                                                                     HW, C, ldo);
+  B2_LAUNCH_CHECK("avgpool_fwd_kernel");
+  return 0;
+}
+
+int b2_avgpool_bwd(const void* dout_bf16, int ldo, void* dx_bf16, int B, int HW, int C, void* stream) {
+  avgpool_bwd_kernel<<<stream_grid((int64_t)B * HW * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout_bf16), ldo,
+                                                                                                          static_cast<__nv_bfloat16*>(dx_bf16), B, HW, C);
+  B2_LAUNCH_CHECK("avgpool_bwd_kernel");
   return 0;
 }
 

@@ -43,7 +43,8 @@ template <int BN>
 struct GemmCfg {
   static constexpr int B_BYTES = BN * GM_BK * 2;
   static constexpr int STAGE_BYTES = GM_A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 256) ? 4 : 6;
+  static constexpr int STAGES = 4;
+  static constexpr int CTAS_PER_SM = (BN >= 256) ? 1 : 2;  // small tiles: two CTAs per SM double the epilogue warps per SM
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
   static constexpr uint32_t TMEM_COLS = (uint32_t)(GM_ACC_STAGES * BN) < 32u ? 32u : (uint32_t)(GM_ACC_STAGES * BN);
 };
@@ -55,6 +56,7 @@ struct GemmEpilogue {
   const float* bias;
   const __nv_bfloat16* mask;
   float* colsum;
+  float* colsumsq;
   int ldo, ldo16, ldt, ldm;
   int relu, accumulate;
 };
@@ -68,7 +70,7 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t smem_addr, uint3
 // Persistent, warp-specialised: every CTA walks work items w = blockIdx.x, blockIdx.x + gridDim.x, ...  where
 // w = (output tile, k-split).  Three pipelines: smem ring (TMA -> MMA), TMEM accumulator ring (MMA -> epilogue), tile loop.
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(GM_THREADS, 1) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
+__global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
                                                                    int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -254,6 +256,13 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_bf16_kernel(const __grid_c
             if (lane == 0 && nb + e < N && sum != 0.f) atomicAdd(ep.colsum + nb + e, sum);
           }
         }
+        if (ep.colsumsq != nullptr) {  // batch-norm statistics of the layer output, from the fp32 accumulators
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float sq = warp_sum(v[e] * v[e]);
+            if (lane == 0 && nb + e < N && sq != 0.f) atomicAdd(ep.colsumsq + nb + e, sq);
+          }
+        }
       }
       // every tcgen05.ld of this warp has completed (tmem_ld32 waits): hand the accumulator back to the MMA warp
       tc::fence_before_sync();
@@ -323,7 +332,7 @@ static int launch_gemm(const b2_gemm_args* a, const CUtensorMap& ta, const CUten
   }
   const int tiles_m = (a->M + GM_BM - 1) / GM_BM, tiles_n = (a->N + BN - 1) / BN;
   const int n_work = tiles_m * tiles_n * splits;
-  int grid = sm_count();
+  int grid = sm_count() * Cfg::CTAS_PER_SM;
   if (n_work < grid) grid = n_work;
   if (a->a_mn && a->b_mn) gemm_bf16_kernel<BN, true, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
   else if (a->a_mn) gemm_bf16_kernel<BN, true, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
@@ -357,7 +366,7 @@ extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
   if (kb_per_split < 1) kb_per_split = 1;
   splits = total_k > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
   GemmEpilogue ep{a->out_f32, static_cast<__nv_bfloat16*>(a->out_bf16), static_cast<__nv_bfloat16*>(a->out_bf16_t), a->bias, static_cast<const __nv_bfloat16*>(a->mask),
-                  a->colsum, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate};
+                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (bn == 256) return launch_gemm<256>(a, ta, tb, splits, kb_per_split, ep, st);
   return launch_gemm<64>(a, ta, tb, splits, kb_per_split, ep, st);

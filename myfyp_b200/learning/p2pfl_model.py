@@ -214,6 +214,10 @@ class TorchP2PFLModel(P2PFLModel):
                     from myfyp_b200.models.native_cnn import attach_native_cnn
 
                     attach_native_cnn(self, getattr(self.model, "image_size", 32))
+                elif hasattr(self.model, "layers") and hasattr(self.model, "bn1"):
+                    from myfyp_b200.models.native_resnet import attach_native_resnet
+
+                    attach_native_resnet(self, getattr(self.model, "image_size", 32))
                 else:
                     from myfyp_b200.models.native_mlp import attach_native_mlp
 

@@ -251,6 +251,8 @@ class TorchLearner(Learner):
             for i, v in enumerate(vals):
                 logger.log_metric(self._self_addr, "train_loss", v, step=self._global_step + i)
             self._global_step += steps
+        if getattr(module, "native", None) is not None:
+            model.sync_mirrors_from_slab()  # e.g. BatchNorm's integer batch counter, advanced on the device in its fp32 slab slot
         model.set_contribution([self._self_addr], self.data.get_num_samples(train=True))
         self.add_callback_info_to_model()
         return model

@@ -1,0 +1,219 @@
+"""Hand-written training step for ResNet-18 (CIFAR variant): no autograd, no cuDNN.
+
+Every convolution is a patch gather + the tcgen05 GEMM (``csrc/gemm.cu``); the GEMM epilogue also accumulates the batch-norm
+statistics (column sums and sums of squares of the fp32 accumulators), so batch normalisation costs one elementwise kernel
+forward (normalise + scale/shift + residual add + ReLU fused) and two backward (reduce, apply).  Activations are NHWC bf16;
+parameters stay the fp32 slab in PyTorch's layouts (bf16 mirror written by the fused optimizer); BatchNorm running statistics
+live in the slab too and are updated in place with PyTorch semantics, so what the nodes exchange and aggregate is exactly the
+``state_dict`` of the ``nn.Module``.
+
+    conv + bn (+res) (+relu)   col = im2col(x);  z = col W^T  [+ stats];  y = act(bn(z) + res)
+    backward                   g = dy * (y > 0);  dz = bn'(g);  dW = dz^T col;  dcol = dz W;  dx = col2im(dcol) (+ second consumer)
+
+Reference path: the same ``nn.Module`` through torch autograd / cuDNN (ResNet-18 is not in the reference itself; BASELINE.json
+configs 3-4 name it).
+"""
+
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from myfyp_b200 import ops
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+class _ConvBN:
+    def __init__(self, conv: str, bn: str, cin: int, cout: int, k: int, stride: int, pad: int, h: int, w: int, relu: bool) -> None:
+        self.conv, self.bn, self.cin, self.cout, self.k, self.stride, self.pad, self.h, self.w, self.relu = conv, bn, cin, cout, k, stride, pad, h, w, relu
+        self.oh = (h + 2 * pad - k) // stride + 1
+        self.ow = (w + 2 * pad - k) // stride + 1
+        self.kdim = cin * k * k
+
+
+class NativeResNet:
+    def __init__(self, model, image_size: int = 32) -> None:
+        self.model = model
+        m = model.get_model()
+        dev, lay = model.device, model.layout
+        self.layers: List[_ConvBN] = []
+        self.blocks: List[dict] = []
+        h = w = image_size
+        stem = _ConvBN("conv1", "bn1", m.conv1.in_channels, m.conv1.out_channels, 3, 1, 1, h, w, True)
+        self.layers.append(stem)
+        self.stem = stem
+        for bi, blk in enumerate(m.layers):
+            s = blk.conv1.stride[0]
+            c1 = _ConvBN(f"layers.{bi}.conv1", f"layers.{bi}.bn1", blk.conv1.in_channels, blk.conv1.out_channels, 3, s, 1, h, w, True)
+            c2 = _ConvBN(f"layers.{bi}.conv2", f"layers.{bi}.bn2", blk.conv2.in_channels, blk.conv2.out_channels, 3, 1, 1, c1.oh, c1.ow, True)
+            sc = None
+            if blk.shortcut is not None:
+                sc = _ConvBN(f"layers.{bi}.shortcut.0", f"layers.{bi}.shortcut.1", blk.conv1.in_channels, blk.conv2.out_channels, 1, s, 0, h, w, False)
+            self.blocks.append({"c1": c1, "c2": c2, "sc": sc})
+            self.layers += [c1, c2] + ([sc] if sc is not None else [])
+            h, w = c1.oh, c1.ow
+        self.final_hw, self.final_c = h * w, self.blocks[-1]["c2"].cout
+        self.fc_in, self.fc_out = m.fc.in_features, m.fc.out_features
+
+        def pv(name: str, shape=None):
+            e = lay.entries[name]
+            v = model.slab[e.offset : e.offset + e.numel]
+            return v.view(shape) if shape is not None else v
+
+        def gv(name: str, shape=None):
+            e = lay.entries[name]
+            v = model.grad_slab[e.offset : e.offset + e.numel]
+            return v.view(shape) if shape is not None else v
+
+        self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
+        self.par: Dict[str, dict] = {}
+        self._padded: List[str] = []
+        for L in self.layers:
+            e = lay.entries[L.conv + ".weight"]
+            d = {
+                "w": pv(L.conv + ".weight", (L.cout, L.kdim)), "gw": gv(L.conv + ".weight", (L.cout, L.kdim)),
+                "gamma": pv(L.bn + ".weight"), "beta": pv(L.bn + ".bias"), "dgamma": gv(L.bn + ".weight"), "dbeta": gv(L.bn + ".bias"),
+                "rm": pv(L.bn + ".running_mean"), "rv": pv(L.bn + ".running_var"), "nb": pv(L.bn + ".num_batches_tracked"),
+            }
+            if L.kdim % 8 == 0:
+                d["w16"] = self.p16[e.offset : e.offset + e.numel].view(L.cout, L.kdim)
+            else:
+                d["w16"] = torch.zeros(L.cout, _pad8(L.kdim), dtype=torch.bfloat16, device=dev)
+                self._padded.append(L.conv)
+            self.par[L.conv] = d
+        efc = lay.entries["fc.weight"]
+        self.fc = {"w": pv("fc.weight", (self.fc_out, self.fc_in)), "b": pv("fc.bias"), "gw": gv("fc.weight", (self.fc_out, self.fc_in)), "gb": gv("fc.bias"),
+                   "w16": self.p16[efc.offset : efc.offset + efc.numel].view(self.fc_out, self.fc_in)}
+        self._bufs: Dict[int, dict] = {}
+
+    # ------------------------------------------------------------------ buffers
+    def _buffers(self, B: int) -> dict:
+        if B in self._bufs:
+            return self._bufs[B]
+        dev, bf = self.model.device, torch.bfloat16
+        z = lambda *shape, dtype=bf: torch.zeros(*shape, dtype=dtype, device=dev)  # noqa: E731
+        total_c = sum(L.cout for L in self.layers)
+        stats = z(2 * total_c, dtype=torch.float32)  # one arena, zeroed once per step
+        buf: dict = {"L": {}, "stats": stats, "red": z(2 * max(L.cout for L in self.layers), dtype=torch.float32)}
+        off = 0
+        max_dcol = 0
+        for L in self.layers:
+            M = B * L.oh * L.ow
+            buf["L"][L.conv] = {
+                "col": z(M, _pad8(L.kdim)), "z": z(M, L.cout), "y": z(M, L.cout), "g": z(M, L.cout), "dz": z(M, L.cout), "dy": z(M, L.cout),
+                "stats": stats[off : off + 2 * L.cout], "M": M,
+            }
+            off += 2 * L.cout
+            max_dcol = max(max_dcol, M * _pad8(L.kdim))
+        buf["dcol"] = z(max_dcol)  # transient: one shared buffer
+        buf["tmp_dx"] = z(max(B * L.h * L.w * L.cin for L in self.layers))
+        buf.update(pool=z(B, _pad8(self.fc_in)), dpool=z(B, _pad8(self.fc_in)), logits=z(B, self.fc_out, dtype=torch.float32), dzfc=z(B, _pad8(self.fc_out)))
+        self._bufs[B] = buf
+        return buf
+
+    def refresh_weights(self) -> None:
+        ops.cast_slab(self.model.slab, self.p16)
+        self._refresh_padded()
+
+    def _refresh_padded(self) -> None:
+        for n in self._padded:
+            w = self.par[n]["w"]
+            ops.cast_transpose(w, w.shape[0], w.shape[1], dst=self.par[n]["w16"])
+
+    # ------------------------------------------------------------------ forward
+    def _convbn(self, L: _ConvBN, x, B: int, buf: dict, train: bool, residual=None, first: bool = False):
+        lb, p = buf["L"][L.conv], self.par[L.conv]
+        M = lb["M"]
+        ops.im2col(x, lb["col"], B, L.h, L.w, L.cin, L.k, L.k, L.stride, L.pad, nchw_f32=first)
+        st = lb["stats"] if train else None
+        ops.gemm_bf16(lb["col"], p["w16"], M, L.cout, L.kdim, out_bf16=lb["z"], colsum=None if st is None else st[: L.cout], colsumsq=None if st is None else st[L.cout :])
+        ops.bn_apply(lb["z"], residual, lb["y"], st, p["gamma"], p["beta"], p["rm"], p["rv"], p["nb"] if train else None, M, L.cout, L.relu or residual is not None)
+        return lb["y"]
+
+    def _forward(self, x: torch.Tensor, buf: dict, train: bool) -> int:
+        B = x.shape[0]
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        if train:
+            buf["stats"].zero_()
+        a = self._convbn(self.stem, x, B, buf, train, first=True)
+        for blk in self.blocks:
+            inp = a
+            y1 = self._convbn(blk["c1"], inp, B, buf, train)
+            sc = self._convbn(blk["sc"], inp, B, buf, train) if blk["sc"] is not None else inp
+            a = self._convbn(blk["c2"], y1, B, buf, train, residual=sc)
+        ops.avgpool_fwd(a, buf["pool"], B, self.final_hw, self.final_c)
+        ops.gemm_bf16(buf["pool"], self.fc["w16"], B, self.fc_out, self.fc_in, out_f32=buf["logits"], bias=self.fc["b"])
+        return B
+
+    # ------------------------------------------------------------------ backward helpers
+    def _bn_conv_backward(self, L: _ConvBN, dy, B: int, buf: dict, relu: bool, x_prev, need_dx: bool):
+        """dy = gradient w.r.t. this layer's output.  Returns (g, dcol view or None): g is the masked gradient (= gradient of the
+        residual branch), dcol the gradient of this layer's patch matrix (col2im is left to the caller, who knows the consumers)."""
+        lb, p = buf["L"][L.conv], self.par[L.conv]
+        M = lb["M"]
+        ops.bn_backward(dy, lb["y"], lb["z"], lb["g"], lb["dz"], buf["red"], lb["stats"], p["gamma"], p["dgamma"], p["dbeta"], M, L.cout, relu)
+        ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)))
+        dcol = None
+        if need_dx:
+            dcol = buf["dcol"][: M * _pad8(L.kdim)].view(M, _pad8(L.kdim))
+            ops.gemm_bf16(lb["dz"], p["w16"], M, L.kdim, L.cout, out_bf16=dcol, b_mn=True)
+        return lb["g"], dcol
+
+    # ------------------------------------------------------------------ training step
+    def train_step(self, x: torch.Tensor, y: torch.Tensor, loss_out: torch.Tensor) -> None:
+        self._refresh_padded()
+        B = x.shape[0]
+        buf = self._buffers(B)
+        self._forward(x, buf, train=True)
+        ops.xent_train(buf["logits"], y, loss_out, buf["dzfc"], self.fc["gb"], B, self.fc_out)
+        ops.gemm_bf16(buf["dzfc"], buf["pool"], self.fc_out, self.fc_in, B, out_f32=self.fc["gw"], a_mn=True, b_mn=True)
+        ops.gemm_bf16(buf["dzfc"], self.fc["w16"], B, self.fc_in, self.fc_out, out_bf16=buf["dpool"], b_mn=True)
+        last = self.blocks[-1]["c2"]
+        ops.avgpool_bwd(buf["dpool"], buf["L"][last.conv]["dy"], B, self.final_hw, self.final_c)
+        for bi in range(len(self.blocks) - 1, -1, -1):
+            blk = self.blocks[bi]
+            c1, c2, sc = blk["c1"], blk["c2"], blk["sc"]
+            prev = self.blocks[bi - 1]["c2"] if bi > 0 else self.stem  # the layer whose output is this block's input
+            d_in = buf["L"][prev.conv]["dy"]  # gradient w.r.t. the block input goes here
+            # conv2 + bn2 (+ residual) + relu
+            g2, dcol2 = self._bn_conv_backward(c2, buf["L"][c2.conv]["dy"], B, buf, True, None, True)
+            ops.col2im(dcol2, buf["L"][c1.conv]["dy"], B, c2.h, c2.w, c2.cin, 3, 3, 1, 1)
+            # shortcut branch receives g2
+            add = g2
+            if sc is not None:
+                _, dcol_sc = self._bn_conv_backward(sc, g2, B, buf, False, None, True)
+                tmp = buf["tmp_dx"][: B * sc.h * sc.w * sc.cin]
+                ops.col2im(dcol_sc, tmp, B, sc.h, sc.w, sc.cin, 1, 1, sc.stride, 0)
+                add = tmp
+            # conv1 + bn1 + relu ; its input gradient plus the shortcut's gradient = gradient of the block input
+            _, dcol1 = self._bn_conv_backward(c1, buf["L"][c1.conv]["dy"], B, buf, True, None, True)
+            ops.col2im(dcol1, d_in, B, c1.h, c1.w, c1.cin, 3, 3, c1.stride, 1, add=add)
+        self._bn_conv_backward(self.stem, buf["L"][self.stem.conv]["dy"], B, buf, True, None, False)
+
+    @torch.no_grad()
+    def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:
+        buf = self._buffers(x.shape[0])
+        B = self._forward(x, buf, train=False)
+        ops.cross_entropy_eval(buf["logits"][:B], y, acc)
+
+    def logits(self, x: torch.Tensor, train: bool = False) -> torch.Tensor:
+        self.refresh_weights()
+        buf = self._buffers(x.shape[0])
+        B = self._forward(x, buf, train)
+        return buf["logits"][:B].clone()
+
+
+def attach_native_resnet(model, image_size: int = 32) -> NativeResNet:
+    if model.device.type != "cuda":
+        raise RuntimeError("the native ResNet path needs a CUDA device")
+    nr = NativeResNet(model, image_size)
+    module = model.get_model()
+    module.native_train_step = nr.train_step
+    module.native_eval = nr.eval_step
+    module.native = nr
+    return nr

@@ -46,9 +46,21 @@ class ResNet18(nn.Module):
         return self.fc(torch.flatten(torch.nn.functional.adaptive_avg_pool2d(x, 1), 1))
 
 
-def resnet18_model(device: Optional[str] = None, seed: Optional[int] = None, **kwargs):
+def resnet18_model(device: Optional[str] = None, seed: Optional[int] = None, native: Optional[bool] = None, image_size: int = 32, **kwargs):
+    """``TorchP2PFLModel`` around a fresh ResNet-18; ``native`` (default: on CUDA) attaches the hand-written training step
+    (:mod:`myfyp_b200.models.native_resnet`) which the learner prefers over autograd / cuDNN."""
     from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
 
     if seed is not None:
         torch.manual_seed(seed)
-    return TorchP2PFLModel(ResNet18(**kwargs), device=device)
+    module = ResNet18(**kwargs)
+    module.image_size = image_size
+    model = TorchP2PFLModel(module, device=device)
+    if native is None:
+        module.wants_native = True
+        native = model.device.type == "cuda"
+    if native:
+        from myfyp_b200.models.native_resnet import attach_native_resnet
+
+        attach_native_resnet(model, image_size)
+    return model

@@ -401,14 +401,14 @@ class _GemmArgs(ctypes.Structure):
         ("A", ctypes.c_void_p), ("B", ctypes.c_void_p), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int), ("lda", ctypes.c_int), ("ldb", ctypes.c_int),
         ("out_f32", ctypes.c_void_p), ("out_bf16", ctypes.c_void_p), ("out_bf16_t", ctypes.c_void_p), ("ldo", ctypes.c_int), ("ldo16", ctypes.c_int), ("ldt", ctypes.c_int),
         ("bias", ctypes.c_void_p), ("mask", ctypes.c_void_p), ("ldm", ctypes.c_int), ("colsum", ctypes.c_void_p), ("relu", ctypes.c_int), ("accumulate", ctypes.c_int),
-        ("a_mn", ctypes.c_int), ("b_mn", ctypes.c_int), ("split_k", ctypes.c_int),
+        ("a_mn", ctypes.c_int), ("b_mn", ctypes.c_int), ("split_k", ctypes.c_int), ("colsumsq", ctypes.c_void_p),
     ]
 
 
 def gemm_bf16(
     a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
     out_bf16_t: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
-    relu: bool = False, accumulate: bool = False, a_mn: bool = False, b_mn: bool = False, split_k: int = 1,
+    relu: bool = False, accumulate: bool = False, a_mn: bool = False, b_mn: bool = False, split_k: int = 1, colsumsq: Optional[torch.Tensor] = None,
 ) -> None:
     """``D[m,n] = epilogue(A[m,k] @ B[n,k]^T)`` on tcgen05 tensor cores (bf16 in, fp32 accumulate); see csrc/gemm.cu.
 
@@ -428,7 +428,7 @@ def gemm_bf16(
         a.data_ptr(), b.data_ptr(), m, n, k, ld(a), ld(b), 0 if out_f32 is None else out_f32.data_ptr(), 0 if out_bf16 is None else out_bf16.data_ptr(),
         0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld(out_f32), ld(out_bf16), ld(out_bf16_t), 0 if bias is None else bias.data_ptr(),
         0 if mask is None else mask.data_ptr(), ld(mask), 0 if colsum is None else colsum.data_ptr(), int(relu), int(accumulate),
-        int(a_mn), int(b_mn), int(split_k),
+        int(a_mn), int(b_mn), int(split_k), 0 if colsumsq is None else colsumsq.data_ptr(),
     )
     lib = native.load()
     with native.device_guard(a.device):
@@ -463,8 +463,30 @@ def im2col(x: torch.Tensor, col: torch.Tensor, B: int, H: int, W: int, C: int, K
     _conv_call("b2_im2col", x.device, native.ptr(x), int(nchw_f32), native.ptr(col), int(col.stride(0)), B, H, W, C, KH, KW, stride, pad)
 
 
-def col2im(dcol: torch.Tensor, dx: torch.Tensor, B: int, H: int, W: int, C: int, KH: int, KW: int, stride: int, pad: int) -> None:
-    _conv_call("b2_col2im", dcol.device, native.ptr(dcol), int(dcol.stride(0)), native.ptr(dx), B, H, W, C, KH, KW, stride, pad)
+def col2im(dcol: torch.Tensor, dx: torch.Tensor, B: int, H: int, W: int, C: int, KH: int, KW: int, stride: int, pad: int, add: Optional[torch.Tensor] = None) -> None:
+    """``dx = col2im(dcol) (+ add)`` - gather form, no atomics."""
+    _conv_call("b2_col2im", dcol.device, native.ptr(dcol), int(dcol.stride(0)), native.ptr(dx), native.ptr(add), B, H, W, C, KH, KW, stride, pad)
+
+
+def bn_apply(z, residual, y, stats, gamma, beta, running_mean, running_var, num_batches, M: int, C: int, relu: bool, eps: float = 1e-5, momentum: float = 0.1) -> None:
+    """Batch-norm apply on ``[M, C]`` bf16 (training when ``stats`` = [sum, sumsq] is given, else running statistics)."""
+    _conv_call("b2_bn_apply", z.device, native.ptr(z), native.ptr(residual), native.ptr(y), native.ptr(stats), native.ptr(gamma), native.ptr(beta), native.ptr(running_mean),
+               native.ptr(running_var), native.ptr(num_batches), ctypes.c_float(eps), ctypes.c_float(momentum), M, C, int(relu))
+
+
+def bn_backward(dy, y, z, g, dz, red, stats, gamma, dgamma, dbeta, M: int, C: int, relu: bool, eps: float = 1e-5) -> None:
+    """Batch-norm backward (two launches): ``g = dy*(y>0)``, ``dz``, ``dgamma +=``, ``dbeta +=``."""
+    _conv_call("b2_bn_backward", dy.device, native.ptr(dy), native.ptr(y), native.ptr(z), native.ptr(g), native.ptr(dz), native.ptr(red), native.ptr(stats), native.ptr(gamma),
+               native.ptr(dgamma), native.ptr(dbeta), ctypes.c_float(eps), M, C, int(relu))
+    native.count_launch(1)
+
+
+def avgpool_fwd(x, out, B: int, HW: int, C: int) -> None:
+    _conv_call("b2_avgpool_fwd", x.device, native.ptr(x), native.ptr(out), int(out.stride(0)), B, HW, C)
+
+
+def avgpool_bwd(dout, dx, B: int, HW: int, C: int) -> None:
+    _conv_call("b2_avgpool_bwd", dout.device, native.ptr(dout), int(dout.stride(0)), native.ptr(dx), B, HW, C)
 
 
 def maxpool2_fwd(y: torch.Tensor, p: torch.Tensor, idx: torch.Tensor, B: int, H: int, W: int, C: int) -> None:
