@@ -133,6 +133,35 @@ typedef struct {
   float* colsumsq;    /* optional fp32 [N]: += column sums of squares (batch-norm statistics of the output), atomic */
 } b2_gemm_args;
 int b2_gemm_bf16(const b2_gemm_args* args, void* stream);
+
+/* Implicit-GEMM convolution on the same tcgen05 kernel (stride 1, pad = ksize / 2, cin % 64 == 0): the patch matrix is never
+ * written - 4-D TMA boxes of the NHWC activation, shifted per filter tap and zero-filled outside the image, are the operand tiles.
+ * `weights` is bf16 [cout, ksize*ksize*cin] in (kh, kw, cin) order (b2_repack_conv_weights).  Epilogue fields as in b2_gemm_args.
+ *   B2_CONV_FWD    act = x  [batch,h,w,cin]   -> out [batch*h*w, cout]   (+ colsum / colsumsq: batch-norm statistics)
+ *   B2_CONV_DGRAD  act = dz [batch,h,w,cout]  -> out [batch*h*w, cin]    (+ add_bf16: gradient arriving through a second consumer)
+ *   B2_CONV_WGRAD  act = x, dz = [batch*h*w, cout] -> out_f32 [cout, cin, ksize, ksize] (PyTorch's layout), split-K over pixels
+ * Reference path: torch conv2d through autograd / cuDNN (the reference ships no CNN; BASELINE.json configs 2-4 name CNN / ResNet-18). */
+#define B2_CONV_FWD 0
+#define B2_CONV_DGRAD 1
+#define B2_CONV_WGRAD 2
+typedef struct {
+  int mode;
+  const void* act;      /* bf16 NHWC 4-D operand */
+  const void* weights;  /* bf16 [cout, taps*cin] (fwd, dgrad) */
+  const void* dz;       /* bf16 [batch*h*w, cout] (wgrad) */
+  int batch, h, w, cin, cout, ksize;
+  float* out_f32;
+  void* out_bf16;
+  const float* bias;
+  const void* add_bf16;
+  float* colsum;
+  float* colsumsq;
+  int relu, accumulate, split_k;
+} b2_conv_gemm_args;
+int b2_conv_gemm(const b2_conv_gemm_args* args, void* stream);
+/* fp32 [cout, cin, taps] (PyTorch conv weight inside the slab) -> bf16 [cout, taps, cin] for every layer of `table` in one launch;
+ * table = n_layers x {src offset, dst offset, cout, cin, taps} (int64, device memory). */
+int b2_repack_conv_weights(const float* slab, void* dst_bf16, const int64_t* table, int n_layers, int64_t max_elems, void* stream);
 /* fp32 [R,C] (pitch lds) -> bf16 row-major copy (pitch ldd, optional), bf16 transposed copy [C,R] (pitch ldt, optional),
  * column sums += (optional, atomic).  Staging step of the GEMMs above; the reference has no counterpart (it trains in fp32
  * through torch autograd). */

@@ -340,6 +340,18 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
     if (s_acc[c] != 0.f) atomicAdd(out + c, s_acc[c]);
 }
 
+// conv weights fp32 [cout][cin][taps] -> bf16 [cout][taps][cin]; blockIdx.y = layer
+__global__ void repack_conv_weights_kernel(const float* __restrict__ slab, __nv_bfloat16* __restrict__ dst, const int64_t* __restrict__ table) {
+  const int64_t* t = table + 5 * blockIdx.y;
+  const float* src = slab + t[0];
+  __nv_bfloat16* out = dst + t[1];
+  const int64_t cin = t[3], taps = t[4], n = t[2] * cin * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i % cin, r = i / cin, tp = r % taps, co = r / taps;
+    out[i] = __float2bfloat16_rn(src[(co * cin + c) * taps + tp]);
+  }
+}
+
 }  // namespace b2
 
 using namespace b2;
@@ -480,3 +492,13 @@ int b2_colsum_bf16(const void* z_bf16, int M, int C, int ld, float* out, void* s
 }
 
 }  // extern "C"
+
+extern "C" int b2_repack_conv_weights(const float* slab, void* dst_bf16, const int64_t* table, int n_layers, int64_t max_elems, void* stream) {
+  if (n_layers <= 0) return 0;
+  int64_t blocks = (max_elems + 255) / 256;
+  if (blocks > 592) blocks = 592;
+  if (blocks < 1) blocks = 1;
+  repack_conv_weights_kernel<<<dim3((unsigned)blocks, (unsigned)n_layers), 256, 0, static_cast<cudaStream_t>(stream)>>>(slab, static_cast<__nv_bfloat16*>(dst_bf16), table);
+  B2_LAUNCH_CHECK("repack_conv_weights_kernel");
+  return 0;
+}

@@ -25,6 +25,16 @@
 //   dgrad  dX[B,in]   = dY W     : A = dY [B,out] K-major,     B = W [out,in] as MN-major
 // Split-K (grid.z): each z-slice reduces a range of k-blocks and atomically adds into the (pre-zeroed / accumulated) fp32
 // output - used by wgrad where K = batch x pixels is long and M x N is small.
+//
+// Implicit-GEMM convolution (template parameter CONV; entry point b2_conv_gemm; stride 1, "same" padding, channels % 64 == 0).
+// The patch matrix is never materialised: the producer warp fetches, per (filter tap, 64-channel block), a 4-D TMA box
+// {64 channels, tile_w, tile_h, tile_n} straight out of the NHWC activation tensor, shifted by the tap offset - TMA's
+// out-of-bounds zero fill IS the padding - and the box lands in shared memory in exactly the 128B-swizzled [pixels, 64]
+// layout the UMMA descriptors already describe.  Weights are kept as bf16 [Cout, (kh, kw, cin)] (b2_repack_conv_weights).
+//   CONV=1  fwd    z[pix, co]  = sum_{tap, ci} x[pix + tap, ci]  w[co, tap, ci]      A = 4-D boxes of x,  B = w K-major
+//           dgrad  dx[pix, ci] = sum_{tap, co} dz[pix - tap, co] w[co, tap, ci]      A = 4-D boxes of dz, B = w MN-major
+//   CONV=2  wgrad  dw[co, tap, ci] = sum_pix dz[pix, co] x[pix + tap, ci]            A = dz MN-major, B = 4-D boxes of x (MN-major),
+//                  split-K over pixel blocks; the epilogue scatters into PyTorch's [Cout, Cin, KH, KW] gradient layout
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -59,7 +69,30 @@ struct GemmEpilogue {
   float* colsumsq;
   int ldo, ldo16, ldt, ldm;
   int relu, accumulate;
+  const __nv_bfloat16* add16;  // optional bf16 [M, ldadd] added to the result (second consumer of an activation: residual branch gradient)
+  int ldadd;
+  int perm_cin, perm_taps;  // wgrad of a convolution: column j = tap * cin + c is stored at c * taps + tap (PyTorch's [Cout, Cin, KH, KW])
 };
+
+// Geometry of the 4-D activation operand of an implicit-GEMM convolution (stride 1, pad = k / 2)
+struct ConvGeom {
+  int cblocks;    // channels of the 4-D tensor / 64
+  int kw;         // filter width (taps = kh * kw)
+  int off, sign;  // input coordinate = output coordinate + off + sign * tap index   (fwd / wgrad: -pad, +1; dgrad: +pad, -1)
+  int hw_tiles;   // pixel tiles per image (tile = tile_h full rows), or 0 when a tile spans tile_n whole images
+  int tile_h, tile_n;
+  int ncols;      // CONV=1 with B MN-major (dgrad): columns per tap of the weight matrix (= cin); CONV=2: cin
+};
+
+__device__ __forceinline__ void conv_pixel_tile(const ConvGeom& cg, int pt, int& n, int& h0) {
+  if (cg.hw_tiles > 0) {
+    n = pt / cg.hw_tiles;
+    h0 = (pt % cg.hw_tiles) * cg.tile_h;
+  } else {
+    n = pt * cg.tile_n;
+    h0 = 0;
+  }
+}
 
 __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
   // MN-major canonical SWIZZLE_128B: rows are K (128 bytes = 64 MN elements each), 8-row groups 1024 bytes apart (SBO),
@@ -69,9 +102,9 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t smem_addr, uint3
 
 // Persistent, warp-specialised: every CTA walks work items w = blockIdx.x, blockIdx.x + gridDim.x, ...  where
 // w = (output tile, k-split).  Three pipelines: smem ring (TMA -> MMA), TMEM accumulator ring (MMA -> epilogue), tile loop.
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CONV = 0>
 __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
-                                                                   int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep) {
+                                                                   int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep, ConvGeom cg) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[Cfg::STAGES], empty_bar[Cfg::STAGES], acc_full[GM_ACC_STAGES], acc_empty[GM_ACC_STAGES];
@@ -126,17 +159,38 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
           uint8_t* b_dst = a_dst + GM_A_BYTES;
           tc::mbar_arrive_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
           const int k0 = (kb0 + kb) * GM_BK;
-          if constexpr (A_MN) {  // stored [K, M]: 64(K) x 64(M) boxes side by side
+          if constexpr (CONV == 1) {
+            // A = activation patches: k-block -> (tap, channel block); one 4-D box {64 ch, W, tile_h, tile_n} shifted by the tap
+            const int t = (kb0 + kb) / cg.cblocks, cb = (kb0 + kb) % cg.cblocks;
+            int n_img, h0;
+            conv_pixel_tile(cg, m0 / GM_BM, n_img, h0);
+            tc::tma_load_4d(a_dst, &tmap_a, &full_bar[s], cb * GM_BK, cg.off + cg.sign * (t % cg.kw), h0 + cg.off + cg.sign * (t / cg.kw), n_img);
+            if constexpr (B_MN) {  // dgrad: weights [Cout, taps * cin] read as [K = co, N = ci] of this tap
+              tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], t * cg.ncols + n0, cb * GM_BK);
+            } else {
+              tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);
+            }
+          } else if constexpr (CONV == 2) {
+            // wgrad: A = dz [pixels, co] MN-major; B = activation patches [64 pixels, 64 channels of tap t] MN-major
             tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], m0, k0);
             tc::tma_load_2d(a_dst + GM_BK * 128, &tmap_a, &full_bar[s], m0 + 64, k0);
+            const int t = n0 / cg.ncols, c0 = n0 % cg.ncols;
+            int n_img, h0;
+            conv_pixel_tile(cg, kb0 + kb, n_img, h0);
+            tc::tma_load_4d(b_dst, &tmap_b, &full_bar[s], c0, cg.off + cg.sign * (t % cg.kw), h0 + cg.off + cg.sign * (t / cg.kw), n_img);
           } else {
-            tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], k0, m0);
-          }
-          if constexpr (B_MN) {
+            if constexpr (A_MN) {  // stored [K, M]: 64(K) x 64(M) boxes side by side
+              tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], m0, k0);
+              tc::tma_load_2d(a_dst + GM_BK * 128, &tmap_a, &full_bar[s], m0 + 64, k0);
+            } else {
+              tc::tma_load_2d(a_dst, &tmap_a, &full_bar[s], k0, m0);
+            }
+            if constexpr (B_MN) {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j) tc::tma_load_2d(b_dst + j * GM_BK * 128, &tmap_b, &full_bar[s], n0 + 64 * j, k0);
-          } else {
-            tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);
+              for (int j = 0; j < BN / 64; ++j) tc::tma_load_2d(b_dst + j * GM_BK * 128, &tmap_b, &full_bar[s], n0 + 64 * j, k0);
+            } else {
+              tc::tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);
+            }
           }
         }
       }
@@ -199,13 +253,27 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
           const int n = nb + e;
           float x = v[e];
           if (ep.bias != nullptr && n < N) x += __ldg(ep.bias + n);
+          if (ep.add16 != nullptr && row_ok && n < N) x += __bfloat162float(ep.add16[(int64_t)row * ep.ldadd + n]);
           if (ep.relu) x = fmaxf(x, 0.f);
           if (ep.mask != nullptr && row_ok && n < N) x = (__bfloat162float(ep.mask[(int64_t)row * ep.ldm + n]) > 0.f) ? x : 0.f;
           v[e] = (row_ok && n < N) ? x : 0.f;
         }
         if (ep.out_f32 != nullptr && row_ok) {
           float* o = ep.out_f32 + (int64_t)row * ep.ldo + nb;
-          if (split) {
+          if (ep.perm_cin > 0) {
+            // 32 consecutive columns lie inside one tap (cin % 64 == 0): scatter to [row][c][tap]
+            float* op = ep.out_f32 + (int64_t)row * ep.ldo + (int64_t)(nb % ep.perm_cin) * ep.perm_taps + nb / ep.perm_cin;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              if (nb + e < N) {
+                if (split) {
+                  if (v[e] != 0.f) atomicAdd(op + e * ep.perm_taps, v[e]);
+                } else {
+                  op[e * ep.perm_taps] = ep.accumulate ? op[e * ep.perm_taps] + v[e] : v[e];
+                }
+              }
+            }
+          } else if (split) {
 #pragma unroll
             for (int e = 0; e < 32; ++e)
               if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
@@ -313,6 +381,48 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int 
   return 0;
 }
 
+// bf16 NHWC activation [Nimg, H, W, C] as a 4-D tensor {C, W, H, N}; box = {64, W, tile_h, tile_n}, 128-byte swizzle, zero fill outside
+static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n_img, int h, int w, int c, int tile_h, int tile_n) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return 1;
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15u) || (c & 63)) {
+    set_error("conv_gemm: activation must be 16-byte aligned with channels %% 64 == 0 (c=%d)", c);
+    return 1;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n_img};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
+  cuuint32_t box[4] = {(cuuint32_t)GM_BK, (cuuint32_t)w, (cuuint32_t)tile_h, (cuuint32_t)tile_n};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (4-D) failed with CUresult %d (n=%d h=%d w=%d c=%d box %dx%dx%d)", (int)r, n_img, h, w, c, w, tile_h, tile_n);
+    return 1;
+  }
+  return 0;
+}
+
+// pixel tile of `pixels` (128 or 64) output positions = full rows of one image, or whole images
+static int conv_tile_shape(int h, int w, int pixels, int* tile_h, int* tile_n, int* hw_tiles) {
+  if (w <= 0 || h <= 0 || pixels % w != 0) return 1;
+  int th = pixels / w;
+  if (th <= h) {
+    if (h % th != 0) return 1;
+    *tile_h = th;
+    *tile_n = 1;
+    *hw_tiles = h / th;
+    return 0;
+  }
+  if (pixels % (h * w) != 0) return 1;
+  *tile_h = h;
+  *tile_n = pixels / (h * w);
+  *hw_tiles = 0;
+  return 0;
+}
+
 }  // namespace b2
 
 using namespace b2;
@@ -334,10 +444,10 @@ static int launch_gemm(const b2_gemm_args* a, const CUtensorMap& ta, const CUten
   const int n_work = tiles_m * tiles_n * splits;
   int grid = sm_count() * Cfg::CTAS_PER_SM;
   if (n_work < grid) grid = n_work;
-  if (a->a_mn && a->b_mn) gemm_bf16_kernel<BN, true, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
-  else if (a->a_mn) gemm_bf16_kernel<BN, true, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
-  else if (a->b_mn) gemm_bf16_kernel<BN, false, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
-  else gemm_bf16_kernel<BN, false, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep);
+  if (a->a_mn && a->b_mn) gemm_bf16_kernel<BN, true, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else if (a->a_mn) gemm_bf16_kernel<BN, true, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else if (a->b_mn) gemm_bf16_kernel<BN, false, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else gemm_bf16_kernel<BN, false, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
   B2_LAUNCH_CHECK("gemm_bf16_kernel");
   return 0;
 }
@@ -366,8 +476,113 @@ extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
   if (kb_per_split < 1) kb_per_split = 1;
   splits = total_k > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
   GemmEpilogue ep{a->out_f32, static_cast<__nv_bfloat16*>(a->out_bf16), static_cast<__nv_bfloat16*>(a->out_bf16_t), a->bias, static_cast<const __nv_bfloat16*>(a->mask),
-                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate};
+                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate, nullptr, 0, 0, 0};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (bn == 256) return launch_gemm<256>(a, ta, tb, splits, kb_per_split, ep, st);
   return launch_gemm<64>(a, ta, tb, splits, kb_per_split, ep, st);
+}
+
+// ---------------------------------------------------------------------------------------------- implicit-GEMM convolution
+template <bool A_MN, bool B_MN, int CONV>
+static int launch_conv(int M, int N, int K, const CUtensorMap& ta, const CUtensorMap& tb, int splits, int kb_per_split, const GemmEpilogue& ep, const ConvGeom& cg, cudaStream_t st) {
+  using Cfg = GemmCfg<64>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    B2_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<64, A_MN, B_MN, CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set[dev] = true;
+  }
+  const int tiles_m = (M + GM_BM - 1) / GM_BM, tiles_n = (N + 63) / 64;
+  const int n_work = tiles_m * tiles_n * splits;
+  int grid = sm_count() * Cfg::CTAS_PER_SM;
+  if (n_work < grid) grid = n_work;
+  gemm_bf16_kernel<64, A_MN, B_MN, CONV><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, M, N, K, tiles_m, tiles_n, splits, kb_per_split, ep, cg);
+  B2_LAUNCH_CHECK("gemm_bf16_kernel (conv)");
+  return 0;
+}
+
+extern "C" int b2_conv_gemm(const b2_conv_gemm_args* a, void* stream) {
+  if (a == nullptr || a->batch <= 0 || a->h <= 0 || a->w <= 0 || a->cin <= 0 || a->cout <= 0 || a->ksize <= 0 || (a->ksize & 1) == 0) {
+    set_error("conv_gemm: bad shape");
+    return 1;
+  }
+  if ((a->cin & 63) || (a->mode == B2_CONV_DGRAD && (a->cout & 63))) {
+    set_error("conv_gemm: channel counts must be multiples of 64 (cin=%d cout=%d)", a->cin, a->cout);
+    return 1;
+  }
+  const int taps = a->ksize * a->ksize, pad = a->ksize / 2;
+  const int pixels = a->batch * a->h * a->w;
+  const int kdim = taps * a->cin;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap ta, tb;
+  ConvGeom cg{};
+  cg.kw = a->ksize;
+  GemmEpilogue ep{};
+  ep.out_f32 = a->out_f32;
+  ep.out_bf16 = static_cast<__nv_bfloat16*>(a->out_bf16);
+  ep.bias = a->bias;
+  ep.colsum = a->colsum;
+  ep.colsumsq = a->colsumsq;
+  ep.relu = a->relu;
+  ep.accumulate = a->accumulate;
+  ep.add16 = static_cast<const __nv_bfloat16*>(a->add_bf16);
+  const int tile_pixels = a->mode == B2_CONV_WGRAD ? GM_BK : GM_BM;
+  if (conv_tile_shape(a->h, a->w, tile_pixels, &cg.tile_h, &cg.tile_n, &cg.hw_tiles)) {
+    set_error("conv_gemm: a %d-pixel tile must be whole rows of one image or whole images (h=%d w=%d)", tile_pixels, a->h, a->w);
+    return 1;
+  }
+  if (cg.tile_h > 256 || cg.tile_n > 256 || a->w > 256) {
+    set_error("conv_gemm: TMA box limit (w=%d)", a->w);
+    return 1;
+  }
+  if (a->mode == B2_CONV_FWD) {
+    // z[pixels, cout] = patches(x)[pixels, taps * cin] * w[cout, taps * cin]^T
+    cg.cblocks = a->cin / 64;
+    cg.off = -pad;
+    cg.sign = 1;
+    if (make_tmap_nhwc(&ta, a->act, a->batch, a->h, a->w, a->cin, cg.tile_h, cg.tile_n)) return 1;
+    if (make_tmap(&tb, a->weights, a->cout, kdim, kdim, 64)) return 1;
+    ep.ldo = ep.ldo16 = a->cout;
+    ep.ldadd = a->cout;
+    return launch_conv<false, false, 1>(pixels, a->cout, kdim, ta, tb, 1, taps * cg.cblocks, ep, cg, st);
+  }
+  if (a->mode == B2_CONV_DGRAD) {
+    // dx[pixels, cin] = patches'(dz)[pixels, taps * cout] * w'[cin, taps * cout]^T, taps mirrored
+    cg.cblocks = a->cout / 64;
+    cg.off = pad;
+    cg.sign = -1;
+    cg.ncols = a->cin;
+    if (make_tmap_nhwc(&ta, a->act, a->batch, a->h, a->w, a->cout, cg.tile_h, cg.tile_n)) return 1;
+    if (make_tmap(&tb, a->weights, a->cout, kdim, kdim, GM_BK)) return 1;
+    ep.ldo = ep.ldo16 = a->cin;
+    ep.ldadd = a->cin;
+    return launch_conv<false, true, 1>(pixels, a->cin, taps * a->cout, ta, tb, 1, taps * cg.cblocks, ep, cg, st);
+  }
+  if (a->mode == B2_CONV_WGRAD) {
+    // dw[cout, taps * cin] = dz[pixels, cout]^T * patches(x)[pixels, taps * cin]; K = pixels in 64-pixel blocks
+    if (a->out_f32 == nullptr || a->out_bf16 != nullptr || a->bias != nullptr || a->relu || a->add_bf16 != nullptr || a->colsum != nullptr || a->colsumsq != nullptr) {
+      set_error("conv_gemm: wgrad writes a plain fp32 gradient");
+      return 1;
+    }
+    cg.cblocks = a->cin / 64;
+    cg.off = -pad;
+    cg.sign = 1;
+    cg.ncols = a->cin;
+    const int n_img_padded = cg.hw_tiles > 0 ? a->batch : (a->batch + cg.tile_n - 1) / cg.tile_n * cg.tile_n;
+    const int kpix = n_img_padded * a->h * a->w;  // pixel blocks past the batch are zero-filled by TMA on both operands
+    if (make_tmap(&ta, a->dz, pixels, a->cout, a->cout, GM_BK)) return 1;
+    if (make_tmap_nhwc(&tb, a->act, a->batch, a->h, a->w, a->cin, cg.tile_h, cg.tile_n)) return 1;
+    const int total_k = kpix / GM_BK;
+    int splits = a->split_k > 1 ? a->split_k : 1;
+    if (splits > total_k) splits = total_k;
+    int kb_per_split = (total_k + splits - 1) / splits;
+    splits = (total_k + kb_per_split - 1) / kb_per_split;
+    ep.ldo = kdim;
+    ep.perm_cin = a->cin;
+    ep.perm_taps = taps;
+    return launch_conv<true, true, 2>(a->cout, kdim, kpix, ta, tb, splits, kb_per_split, ep, cg, st);
+  }
+  set_error("conv_gemm: unknown mode %d", a->mode);
+  return 1;
 }

@@ -33,6 +33,8 @@ class _ConvBN:
         self.oh = (h + 2 * pad - k) // stride + 1
         self.ow = (w + 2 * pad - k) // stride + 1
         self.kdim = cin * k * k
+        # stride-1 "same" convolutions with 64-channel multiples run as implicit GEMMs (4-D TMA boxes, no patch matrix)
+        self.implicit = ops.conv_gemm_supported(h, w, cin, cout, k, stride, pad)
 
 
 class NativeResNet:
@@ -72,6 +74,11 @@ class NativeResNet:
         self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
         self.par: Dict[str, dict] = {}
         self._padded: List[str] = []
+        # implicit-GEMM layers read their weights as bf16 [cout, (kh, kw, cin)]: one repack launch per step fills this arena
+        implicit = [L for L in self.layers if L.implicit]
+        self.p16r = torch.zeros(sum(L.cout * L.kdim for L in implicit), dtype=torch.bfloat16, device=dev)
+        table, roff = [], 0
+        self._repack_max = max([L.cout * L.kdim for L in implicit], default=0)
         for L in self.layers:
             e = lay.entries[L.conv + ".weight"]
             d = {
@@ -79,12 +86,18 @@ class NativeResNet:
                 "gamma": pv(L.bn + ".weight"), "beta": pv(L.bn + ".bias"), "dgamma": gv(L.bn + ".weight"), "dbeta": gv(L.bn + ".bias"),
                 "rm": pv(L.bn + ".running_mean"), "rv": pv(L.bn + ".running_var"), "nb": pv(L.bn + ".num_batches_tracked"),
             }
-            if L.kdim % 8 == 0:
+            if L.implicit:
+                d["w16"] = self.p16r[roff : roff + e.numel].view(L.cout, L.kdim)
+                table += [e.offset, roff, L.cout, L.cin, L.k * L.k]
+                roff += e.numel
+            elif L.kdim % 8 == 0:
                 d["w16"] = self.p16[e.offset : e.offset + e.numel].view(L.cout, L.kdim)
             else:
                 d["w16"] = torch.zeros(L.cout, _pad8(L.kdim), dtype=torch.bfloat16, device=dev)
                 self._padded.append(L.conv)
             self.par[L.conv] = d
+        self._repack_table = torch.tensor(table, dtype=torch.int64, device=dev) if table else None
+        self._n_repack = len(table) // 5
         efc = lay.entries["fc.weight"]
         self.fc = {"w": pv("fc.weight", (self.fc_out, self.fc_in)), "b": pv("fc.bias"), "gw": gv("fc.weight", (self.fc_out, self.fc_in)), "gb": gv("fc.bias"),
                    "w16": self.p16[efc.offset : efc.offset + efc.numel].view(self.fc_out, self.fc_in)}
@@ -104,11 +117,12 @@ class NativeResNet:
         for L in self.layers:
             M = B * L.oh * L.ow
             buf["L"][L.conv] = {
-                "col": z(M, _pad8(L.kdim)), "z": z(M, L.cout), "y": z(M, L.cout), "g": z(M, L.cout), "dz": z(M, L.cout), "dy": z(M, L.cout),
+                "col": None if L.implicit else z(M, _pad8(L.kdim)), "z": z(M, L.cout), "y": z(M, L.cout), "g": z(M, L.cout), "dz": z(M, L.cout), "dy": z(M, L.cout),
                 "stats": stats[off : off + 2 * L.cout], "M": M,
             }
             off += 2 * L.cout
-            max_dcol = max(max_dcol, M * _pad8(L.kdim))
+            if not L.implicit:
+                max_dcol = max(max_dcol, M * _pad8(L.kdim))
         buf["dcol"] = z(max_dcol)  # transient: one shared buffer
         buf["tmp_dx"] = z(max(B * L.h * L.w * L.cin for L in self.layers))
         buf.update(pool=z(B, _pad8(self.fc_in)), dpool=z(B, _pad8(self.fc_in)), logits=z(B, self.fc_out, dtype=torch.float32), dzfc=z(B, _pad8(self.fc_out)))
@@ -123,14 +137,21 @@ class NativeResNet:
         for n in self._padded:
             w = self.par[n]["w"]
             ops.cast_transpose(w, w.shape[0], w.shape[1], dst=self.par[n]["w16"])
+        if self._n_repack:
+            ops.repack_conv_weights(self.model.slab, self.p16r, self._repack_table, self._n_repack, self._repack_max)
 
     # ------------------------------------------------------------------ forward
     def _convbn(self, L: _ConvBN, x, B: int, buf: dict, train: bool, residual=None, first: bool = False):
         lb, p = buf["L"][L.conv], self.par[L.conv]
         M = lb["M"]
-        ops.im2col(x, lb["col"], B, L.h, L.w, L.cin, L.k, L.k, L.stride, L.pad, nchw_f32=first)
         st = lb["stats"] if train else None
-        ops.gemm_bf16(lb["col"], p["w16"], M, L.cout, L.kdim, out_bf16=lb["z"], colsum=None if st is None else st[: L.cout], colsumsq=None if st is None else st[L.cout :])
+        cs, cq = (None, None) if st is None else (st[: L.cout], st[L.cout :])
+        if L.implicit:
+            lb["x"] = x  # the backward weight-gradient GEMM reads the input activation itself
+            ops.conv_gemm(ops.CONV_FWD, x, B, L.h, L.w, L.cin, L.cout, L.k, weights=p["w16"], out_bf16=lb["z"], colsum=cs, colsumsq=cq)
+        else:
+            ops.im2col(x, lb["col"], B, L.h, L.w, L.cin, L.k, L.k, L.stride, L.pad, nchw_f32=first)
+            ops.gemm_bf16(lb["col"], p["w16"], M, L.cout, L.kdim, out_bf16=lb["z"], colsum=cs, colsumsq=cq)
         ops.bn_apply(lb["z"], residual, lb["y"], st, p["gamma"], p["beta"], p["rm"], p["rv"], p["nb"] if train else None, M, L.cout, L.relu or residual is not None)
         return lb["y"]
 
@@ -151,18 +172,25 @@ class NativeResNet:
         return B
 
     # ------------------------------------------------------------------ backward helpers
-    def _bn_conv_backward(self, L: _ConvBN, dy, B: int, buf: dict, relu: bool, x_prev, need_dx: bool):
-        """dy = gradient w.r.t. this layer's output.  Returns (g, dcol view or None): g is the masked gradient (= gradient of the
-        residual branch), dcol the gradient of this layer's patch matrix (col2im is left to the caller, who knows the consumers)."""
+    def _bn_conv_backward(self, L: _ConvBN, dy, B: int, buf: dict, relu: bool, dx=None, add=None):
+        """``dy`` = gradient w.r.t. this layer's output.  Accumulates the parameter gradients, writes the gradient of the layer
+        input (plus ``add``, the gradient arriving through a second consumer of that input) into ``dx`` when given, and returns
+        g, the masked gradient (= the gradient of the residual branch)."""
         lb, p = buf["L"][L.conv], self.par[L.conv]
         M = lb["M"]
         ops.bn_backward(dy, lb["y"], lb["z"], lb["g"], lb["dz"], buf["red"], lb["stats"], p["gamma"], p["dgamma"], p["dbeta"], M, L.cout, relu)
+        if L.implicit:
+            tiles = ((L.cout + 127) // 128) * (L.kdim // 64)
+            ops.conv_gemm(ops.CONV_WGRAD, lb["x"], B, L.h, L.w, L.cin, L.cout, L.k, dz=lb["dz"], out_f32=p["gw"], split_k=max(1, min(296 // tiles, M // 128)))
+            if dx is not None:
+                ops.conv_gemm(ops.CONV_DGRAD, lb["dz"], B, L.h, L.w, L.cin, L.cout, L.k, weights=p["w16"], out_bf16=dx, add=add)
+            return lb["g"]
         ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)))
-        dcol = None
-        if need_dx:
+        if dx is not None:
             dcol = buf["dcol"][: M * _pad8(L.kdim)].view(M, _pad8(L.kdim))
             ops.gemm_bf16(lb["dz"], p["w16"], M, L.kdim, L.cout, out_bf16=dcol, b_mn=True)
-        return lb["g"], dcol
+            ops.col2im(dcol, dx, B, L.h, L.w, L.cin, L.k, L.k, L.stride, L.pad, add=add)
+        return lb["g"]
 
     # ------------------------------------------------------------------ training step
     def train_step(self, x: torch.Tensor, y: torch.Tensor, loss_out: torch.Tensor) -> None:
@@ -181,19 +209,15 @@ class NativeResNet:
             prev = self.blocks[bi - 1]["c2"] if bi > 0 else self.stem  # the layer whose output is this block's input
             d_in = buf["L"][prev.conv]["dy"]  # gradient w.r.t. the block input goes here
             # conv2 + bn2 (+ residual) + relu
-            g2, dcol2 = self._bn_conv_backward(c2, buf["L"][c2.conv]["dy"], B, buf, True, None, True)
-            ops.col2im(dcol2, buf["L"][c1.conv]["dy"], B, c2.h, c2.w, c2.cin, 3, 3, 1, 1)
-            # shortcut branch receives g2
+            g2 = self._bn_conv_backward(c2, buf["L"][c2.conv]["dy"], B, buf, True, dx=buf["L"][c1.conv]["dy"])
+            # the shortcut branch receives g2 (through its own conv + bn when the block changes shape)
             add = g2
             if sc is not None:
-                _, dcol_sc = self._bn_conv_backward(sc, g2, B, buf, False, None, True)
-                tmp = buf["tmp_dx"][: B * sc.h * sc.w * sc.cin]
-                ops.col2im(dcol_sc, tmp, B, sc.h, sc.w, sc.cin, 1, 1, sc.stride, 0)
-                add = tmp
+                add = buf["tmp_dx"][: B * sc.h * sc.w * sc.cin]
+                self._bn_conv_backward(sc, g2, B, buf, False, dx=add)
             # conv1 + bn1 + relu ; its input gradient plus the shortcut's gradient = gradient of the block input
-            _, dcol1 = self._bn_conv_backward(c1, buf["L"][c1.conv]["dy"], B, buf, True, None, True)
-            ops.col2im(dcol1, d_in, B, c1.h, c1.w, c1.cin, 3, 3, c1.stride, 1, add=add)
-        self._bn_conv_backward(self.stem, buf["L"][self.stem.conv]["dy"], B, buf, True, None, False)
+            self._bn_conv_backward(c1, buf["L"][c1.conv]["dy"], B, buf, True, dx=d_in, add=add)
+        self._bn_conv_backward(self.stem, buf["L"][self.stem.conv]["dy"], B, buf, True)
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:

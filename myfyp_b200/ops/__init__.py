@@ -436,6 +436,61 @@ def gemm_bf16(
     native.count_launch()
 
 
+class _ConvGemmArgs(ctypes.Structure):
+    _fields_ = [
+        ("mode", ctypes.c_int), ("act", ctypes.c_void_p), ("weights", ctypes.c_void_p), ("dz", ctypes.c_void_p), ("batch", ctypes.c_int), ("h", ctypes.c_int),
+        ("w", ctypes.c_int), ("cin", ctypes.c_int), ("cout", ctypes.c_int), ("ksize", ctypes.c_int), ("out_f32", ctypes.c_void_p), ("out_bf16", ctypes.c_void_p),
+        ("bias", ctypes.c_void_p), ("add_bf16", ctypes.c_void_p), ("colsum", ctypes.c_void_p), ("colsumsq", ctypes.c_void_p), ("relu", ctypes.c_int),
+        ("accumulate", ctypes.c_int), ("split_k", ctypes.c_int),
+    ]
+
+
+CONV_FWD, CONV_DGRAD, CONV_WGRAD = 0, 1, 2
+
+
+def conv_gemm_supported(h: int, w: int, cin: int, cout: int, ksize: int, stride: int, pad: int) -> bool:
+    """Geometries the implicit-GEMM convolution takes (everything else goes through im2col + gemm_bf16)."""
+    if stride != 1 or ksize % 2 == 0 or pad != ksize // 2 or cin % 64 or cout % 64 or w > 128 or 128 % w:
+        return False
+    for pixels in (128, 64):
+        th = pixels // w
+        if th <= h:
+            if h % th:
+                return False
+        elif pixels % (h * w):
+            return False
+    return True
+
+
+def conv_gemm(
+    mode: int, act: torch.Tensor, batch: int, h: int, w: int, cin: int, cout: int, ksize: int, weights: Optional[torch.Tensor] = None, dz: Optional[torch.Tensor] = None,
+    out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, add: Optional[torch.Tensor] = None,
+    colsum: Optional[torch.Tensor] = None, colsumsq: Optional[torch.Tensor] = None, relu: bool = False, accumulate: bool = False, split_k: int = 1,
+) -> None:
+    """Implicit-GEMM convolution (stride 1, "same" padding) on the tcgen05 GEMM: 4-D TMA boxes of the NHWC activation are the operand
+    tiles, no patch matrix is written.  ``weights``: bf16 ``[cout, k*k*cin]`` in (kh, kw, cin) order (:func:`repack_conv_weights`).
+
+    ``CONV_FWD``: ``act`` = x -> ``out[batch*h*w, cout]``; ``CONV_DGRAD``: ``act`` = dz -> ``out[batch*h*w, cin]`` (+ ``add``);
+    ``CONV_WGRAD``: ``act`` = x, ``dz`` -> ``out_f32[cout, cin, k, k]``."""
+    args = _ConvGemmArgs(
+        mode, act.data_ptr(), 0 if weights is None else weights.data_ptr(), 0 if dz is None else dz.data_ptr(), batch, h, w, cin, cout, ksize,
+        0 if out_f32 is None else out_f32.data_ptr(), 0 if out_bf16 is None else out_bf16.data_ptr(), 0 if bias is None else bias.data_ptr(),
+        0 if add is None else add.data_ptr(), 0 if colsum is None else colsum.data_ptr(), 0 if colsumsq is None else colsumsq.data_ptr(), int(relu), int(accumulate), int(split_k),
+    )
+    lib = native.load()
+    with native.device_guard(act.device):
+        native.check(lib.b2_conv_gemm(ctypes.byref(args), native.stream_ptr(act.device)), "b2_conv_gemm")
+    native.count_launch()
+
+
+def repack_conv_weights(slab: torch.Tensor, dst: torch.Tensor, table: torch.Tensor, n_layers: int, max_elems: int) -> None:
+    """fp32 conv weights ``[cout, cin, taps]`` inside ``slab`` -> bf16 ``[cout, taps, cin]`` in ``dst`` for all layers of ``table`` (one launch)."""
+    lib = native.load()
+    with native.device_guard(slab.device):
+        native.check(lib.b2_repack_conv_weights(native.ptr(slab), native.ptr(dst), native.ptr(table), n_layers, ctypes.c_int64(max_elems), native.stream_ptr(slab.device)), "b2_repack_conv_weights")
+    native.count_launch()
+
+
 def cast_transpose(src: torch.Tensor, rows: int, cols: int, dst: Optional[torch.Tensor] = None, dst_t: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None) -> None:
     """fp32 ``src[rows, cols]`` -> bf16 copy ``dst`` and/or transposed bf16 copy ``dst_t`` (+ column sums), one pass."""
     lib = native.load()

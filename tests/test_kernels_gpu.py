@@ -712,6 +712,51 @@ def test_batchnorm_kernels_match_torch(dev):
     torch.testing.assert_close(y2.float(), ref2, rtol=2e-2, atol=2e-2)
 
 
+@pytest.mark.parametrize("B,H,cin,cout", [(4, 32, 64, 64), (3, 16, 128, 64), (5, 8, 64, 128), (6, 8, 256, 256), (11, 4, 128, 192), (8, 4, 512, 512)])
+def test_implicit_gemm_conv_matches_conv2d(dev, B, H, cin, cout):
+    """Implicit-GEMM 3x3 convolution (4-D TMA boxes as operand tiles): forward, input gradient and weight gradient against
+    torch conv2d + autograd in fp32 on the same bf16-rounded operands."""
+    from myfyp_b200 import ops
+
+    torch.backends.cudnn.allow_tf32 = False
+    g = torch.Generator(device="cpu").manual_seed(B * 1000 + H + cin)
+    x = torch.randn(B, cin, H, H, generator=g).to(dev).bfloat16().float()
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin**0.5)).to(dev)
+    dz = torch.randn(B, cout, H, H, generator=g).to(dev).bfloat16().float()
+    extra = torch.randn(B, cin, H, H, generator=g).to(dev).bfloat16().float()
+    assert ops.conv_gemm_supported(H, H, cin, cout, 3, 1, 1)
+    # weights: slab-style fp32 [cout, cin, 9] -> bf16 [cout, 9, cin]
+    w16 = torch.zeros(cout, 9 * cin, dtype=torch.bfloat16, device=dev)
+    table = torch.tensor([0, 0, cout, cin, 9], dtype=torch.int64, device=dev)
+    ops.repack_conv_weights(w.reshape(-1), w16.reshape(-1), table, 1, w.numel())
+    torch.testing.assert_close(w16.float().view(cout, 9, cin), w.bfloat16().float().view(cout, cin, 9).transpose(1, 2))
+    wr = w.bfloat16().float().requires_grad_(True)
+    xr = x.clone().requires_grad_(True)
+    z_ref = torch.nn.functional.conv2d(xr, wr, padding=1)
+    z_ref.backward(dz)
+    M = B * H * H
+    x_nhwc = x.permute(0, 2, 3, 1).contiguous().bfloat16()
+    dz_nhwc = dz.permute(0, 2, 3, 1).contiguous().bfloat16()
+    # forward (+ batch-norm statistics in the epilogue)
+    z = torch.zeros(M, cout, dtype=torch.bfloat16, device=dev)
+    cs, cq = torch.zeros(cout, device=dev), torch.zeros(cout, device=dev)
+    ops.conv_gemm(ops.CONV_FWD, x_nhwc, B, H, H, cin, cout, 3, weights=w16, out_bf16=z, colsum=cs, colsumsq=cq)
+    zr = z_ref.detach().permute(0, 2, 3, 1).reshape(M, cout)
+    torch.testing.assert_close(z.float(), zr, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(cs, zr.sum(0), rtol=1e-2, atol=5e-2)
+    torch.testing.assert_close(cq, (zr * zr).sum(0), rtol=1e-2, atol=5e-2)
+    # input gradient (+ the gradient of a second consumer)
+    dx = torch.zeros(M, cin, dtype=torch.bfloat16, device=dev)
+    ops.conv_gemm(ops.CONV_DGRAD, dz_nhwc, B, H, H, cin, cout, 3, weights=w16, out_bf16=dx, add=extra.permute(0, 2, 3, 1).contiguous().bfloat16())
+    dxr = (xr.grad + extra).permute(0, 2, 3, 1).reshape(M, cin)
+    torch.testing.assert_close(dx.float(), dxr, rtol=2e-2, atol=3e-2)
+    # weight gradient straight into PyTorch's layout, split-K over pixel blocks
+    for split in (1, 4):
+        dw = torch.zeros(cout, cin, 3, 3, device=dev)
+        ops.conv_gemm(ops.CONV_WGRAD, x_nhwc, B, H, H, cin, cout, 3, dz=dz_nhwc, out_f32=dw, split_k=split)
+        torch.testing.assert_close(dw, wr.grad, rtol=1e-2, atol=1e-2 * float(wr.grad.abs().max()))
+
+
 def test_native_resnet18_step_matches_autograd(dev):
     """Hand-written ResNet-18 step vs torch autograd / cuDNN in fp32 on the same weights (bf16-operand tolerances)."""
     from myfyp_b200.models import resnet18_model

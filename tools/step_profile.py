@@ -5,16 +5,16 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from myfyp_b200.learning.dataset import P2PFLDataset
 from myfyp_b200.learning.torch_learner import TorchLearner
-from myfyp_b200.models import cnn_model, mlp_model
+from myfyp_b200.models import cnn_model, mlp_model, resnet18_model
 
 which = sys.argv[1] if len(sys.argv) > 1 else "cnn"
 mode = sys.argv[2] if len(sys.argv) > 2 else "step"
 dev = torch.device("cuda:0")
-mk = cnn_model if which == "cnn" else mlp_model
+mk = {"cnn": cnn_model, "mlp": mlp_model, "resnet": resnet18_model}[which]
 if mode == "step":
     model = mk(device="cuda:0", seed=0, native=True)
     module = model.get_model()
-    x = torch.randn(64, *( (3, 32, 32) if which == "cnn" else (28, 28)), device=dev)
+    x = torch.randn(64, *((28, 28) if which == "mlp" else (3, 32, 32)), device=dev)
     y = torch.randint(0, 10, (64,), device=dev)
     loss = torch.zeros(1, device=dev)
     from myfyp_b200 import ops
@@ -28,7 +28,7 @@ if mode == "step":
     print("step ok", loss.item())
 else:
     N = 8
-    shape_fn = P2PFLDataset.synthetic_cifar10 if which == "cnn" else P2PFLDataset.synthetic_mnist
+    shape_fn = P2PFLDataset.synthetic_mnist if which == "mlp" else P2PFLDataset.synthetic_cifar10
     learners = [TorchLearner(mk(device="cuda:0", seed=i, native=True), shape_fn(6250, 256, seed=i), f"n{i}", batch_size=64) for i in range(N)]
     for l in learners:
         l.fit()  # capture
