@@ -179,9 +179,10 @@ int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, const void* add_bf1
 int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, const float* stats, const float* gamma, const float* beta, float* running_mean, float* running_var,
                 float* num_batches, float eps, float momentum, int M, int C, int relu, void* stream);
 /* g = dy * (y > 0 if relu) (stored: it is also the gradient of the residual branch); dz = gamma invstd (g - mean g - xhat mean(g xhat));
- * dgamma += sum g xhat, dbeta += sum g.  `red2c` is a 2C-float scratch. */
+ * dgamma += sum g xhat, dbeta += sum g.  `red2c` is a 2C-float scratch (zeroed here unless the caller says it already is:
+ * a training step zeroes one arena for all its layers).  C % 8 == 0, C <= 2048. */
 int b2_bn_backward(const void* dy_bf16, const void* y_bf16, const void* z_bf16, void* g_bf16, void* dz_bf16, float* red2c, const float* stats, const float* gamma, float* dgamma,
-                   float* dbeta, float eps, int M, int C, int relu, void* stream);
+                   float* dbeta, float eps, int M, int C, int relu, int red_is_zero, void* stream);
 int b2_avgpool_fwd(const void* x_bf16, void* out_bf16, int ldo, int B, int HW, int C, void* stream);
 int b2_avgpool_bwd(const void* dout_bf16, int ldo, void* dx_bf16, int B, int HW, int C, void* stream);
 int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H, int W, int C, void* stream);

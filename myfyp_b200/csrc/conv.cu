@@ -94,24 +94,72 @@ struct BnArgs {
   int M, C, relu;
 };
 
+// All three kernels use the same thread layout: a thread owns 8 consecutive channels (one 16-byte bf16 vector) and walks rows;
+// a block covers `rows_per_iter = 256 / (C / 8)` rows per iteration (C % 8 == 0, C / 8 <= 256 -> C <= 2048).
+struct Bf16x8 {
+  uint4 raw;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { raw = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+  __device__ __forceinline__ void unpack(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __bfloat1622float2(h[i]);
+      f[2 * i] = t.x;
+      f[2 * i + 1] = t.y;
+    }
+  }
+  __device__ __forceinline__ void pack(const float (&f)[8]) {
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  }
+};
+
 // y = act(gamma * (z - mean) * invstd + beta (+ residual))
 __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y, BnArgs a) {
-  const int64_t total = (int64_t)a.M * a.C;
+  const int groups = a.C >> 3, rows_per_iter = blockDim.x / groups;
+  const int cg = threadIdx.x % groups, r = threadIdx.x / groups;
   const float invM = 1.f / (float)a.M;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % a.C);
-    float mean, var;
-    if (a.stats != nullptr) {
-      mean = a.stats[c] * invM;
-      var = fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f);
-    } else {
-      mean = a.running_mean[c];
-      var = a.running_var[c];
+  if (r < rows_per_iter) {
+    float scale[8], shift[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cg * 8 + j;
+      float mean, var;
+      if (a.stats != nullptr) {
+        mean = a.stats[c] * invM;
+        var = fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f);
+      } else {
+        mean = a.running_mean[c];
+        var = a.running_var[c];
+      }
+      scale[j] = rsqrtf(var + a.eps) * a.gamma[c];
+      shift[j] = a.beta[c] - mean * scale[j];
     }
-    float v = (__bfloat162float(z[i]) - mean) * rsqrtf(var + a.eps) * a.gamma[c] + a.beta[c];
-    if (residual != nullptr) v += __bfloat162float(residual[i]);
-    if (a.relu) v = fmaxf(v, 0.f);
-    y[i] = __float2bfloat16_rn(v);
+    for (int m = blockIdx.x * rows_per_iter + r; m < a.M; m += gridDim.x * rows_per_iter) {
+      const int64_t i = (int64_t)m * a.C + cg * 8;
+      Bf16x8 v;
+      float f[8];
+      v.load(z + i);
+      v.unpack(f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
+      if (residual != nullptr) {
+        Bf16x8 rv;
+        float rf[8];
+        rv.load(residual + i);
+        rv.unpack(rf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] += rf[j];
+      }
+      if (a.relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      v.pack(f);
+      v.store(y + i);
+    }
   }
   if (a.stats != nullptr && blockIdx.x == 0) {  // running statistics (PyTorch semantics: unbiased variance, momentum)
     for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
@@ -128,31 +176,51 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 // pass 1 of the backward: g = dy * (y > 0 if relu);  red[c] += sum g, red[C + c] += sum g * xhat;  g is stored for pass 2
 // (and is at the same time the gradient that flows into the residual branch)
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ z,
-                                                            __nv_bfloat16* __restrict__ gbuf, float* __restrict__ red, BnArgs a, int rows_per_block) {
+                                                            __nv_bfloat16* __restrict__ gbuf, float* __restrict__ red, BnArgs a) {
   extern __shared__ float s_red[];  // 2C
   for (int c = threadIdx.x; c < 2 * a.C; c += blockDim.x) s_red[c] = 0.f;
   __syncthreads();
+  const int groups = a.C >> 3, rows_per_iter = blockDim.x / groups;
+  const int cg = threadIdx.x % groups, r = threadIdx.x / groups;
   const float invM = 1.f / (float)a.M;
-  const int m0 = blockIdx.x * rows_per_block, m1 = min(a.M, m0 + rows_per_block);
-  const int cols = blockDim.x < a.C ? blockDim.x : a.C;
-  const int groups = blockDim.x / cols, gid = threadIdx.x / cols, lane = threadIdx.x % cols;
-  if (gid < groups) {
-    for (int c = lane; c < a.C; c += cols) {
-      const float mean = a.stats[c] * invM;
-      const float invstd = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f) + a.eps);
-      float sg = 0.f, sgx = 0.f;
-      for (int m = m0 + gid; m < m1; m += groups) {
-        const int64_t i = (int64_t)m * a.C + c;
-        float g = __bfloat162float(dy[i]);
-        if (a.relu && !(__bfloat162float(y[i]) > 0.f)) g = 0.f;
-        const __nv_bfloat16 gq = __float2bfloat16_rn(g);
-        gbuf[i] = gq;
-        g = __bfloat162float(gq);
-        sg += g;
-        sgx += g * (__bfloat162float(z[i]) - mean) * invstd;
+  if (r < rows_per_iter) {
+    float mean[8], invstd[8], sg[8], sgx[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cg * 8 + j;
+      mean[j] = a.stats[c] * invM;
+      invstd[j] = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean[j] * mean[j], 0.f) + a.eps);
+      sg[j] = sgx[j] = 0.f;
+    }
+    for (int m = blockIdx.x * rows_per_iter + r; m < a.M; m += gridDim.x * rows_per_iter) {
+      const int64_t i = (int64_t)m * a.C + cg * 8;
+      Bf16x8 vd, vz;
+      float g[8], zf[8];
+      vd.load(dy + i);
+      vz.load(z + i);
+      vd.unpack(g);
+      vz.unpack(zf);
+      if (a.relu) {
+        Bf16x8 vy;
+        float yf[8];
+        vy.load(y + i);
+        vy.unpack(yf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (!(yf[j] > 0.f)) g[j] = 0.f;
+        vd.pack(g);
       }
-      atomicAdd(&s_red[c], sg);
-      atomicAdd(&s_red[a.C + c], sgx);
+      vd.store(gbuf + i);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        sg[j] += g[j];
+        sgx[j] += g[j] * (zf[j] - mean[j]) * invstd[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_red[cg * 8 + j], sg[j]);
+      atomicAdd(&s_red[a.C + cg * 8 + j], sgx[j]);
     }
   }
   __syncthreads();
@@ -163,15 +231,35 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
 // pass 2: dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat));  block 0 adds dgamma / dbeta into the gradient slab
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ gbuf, const __nv_bfloat16* __restrict__ z, const float* __restrict__ red,
                                                            __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta, BnArgs a) {
-  const int64_t total = (int64_t)a.M * a.C;
+  const int groups = a.C >> 3, rows_per_iter = blockDim.x / groups;
+  const int cg = threadIdx.x % groups, r = threadIdx.x / groups;
   const float invM = 1.f / (float)a.M;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % a.C);
-    const float mean = a.stats[c] * invM;
-    const float invstd = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f) + a.eps);
-    const float xhat = (__bfloat162float(z[i]) - mean) * invstd;
-    const float v = a.gamma[c] * invstd * (__bfloat162float(gbuf[i]) - red[c] * invM - xhat * red[a.C + c] * invM);
-    dz[i] = __float2bfloat16_rn(v);
+  if (r < rows_per_iter) {
+    // dz = k1 * g + k2 * z + k3   with xhat = (z - mean) * invstd
+    float k1[8], k2[8], k3[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cg * 8 + j;
+      const float mean = a.stats[c] * invM;
+      const float invstd = rsqrtf(fmaxf(a.stats[a.C + c] * invM - mean * mean, 0.f) + a.eps);
+      const float gi = a.gamma[c] * invstd, mg = red[c] * invM, mgx = red[a.C + c] * invM;
+      k1[j] = gi;
+      k2[j] = -gi * mgx * invstd;
+      k3[j] = -gi * mg + gi * mgx * invstd * mean;
+    }
+    for (int m = blockIdx.x * rows_per_iter + r; m < a.M; m += gridDim.x * rows_per_iter) {
+      const int64_t i = (int64_t)m * a.C + cg * 8;
+      Bf16x8 vg, vz;
+      float g[8], zf[8];
+      vg.load(gbuf + i);
+      vz.load(z + i);
+      vg.unpack(g);
+      vz.unpack(zf);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = k1[j] * g[j] + k2[j] * zf[j] + k3[j];
+      vg.pack(g);
+      vg.store(dz + i);
+    }
   }
   if (blockIdx.x == 0)
     for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
@@ -381,6 +469,15 @@ int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, const void* add_bf1
   return 0;
 }
 
+// blocks of 256 threads covering 256 / (C / 8) rows per iteration; enough blocks to fill the chip, at least ~4 rows per thread
+static int bn_grid(int M, int C, int ctas_per_sm = 8) {
+  const int rows_per_iter = 256 / (C >> 3) > 0 ? 256 / (C >> 3) : 1;
+  int64_t need = ((int64_t)M + rows_per_iter * 4 - 1) / (rows_per_iter * 4);
+  const int64_t cap = (int64_t)sm_count() * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
 static BnArgs bn_args(const float* stats, const float* gamma, const float* beta, float* rm, float* rv, float* nb, float eps, float momentum, int M, int C, int relu) {
   return BnArgs{stats, gamma, beta, rm, rv, nb, eps, momentum, M, C, relu};
 }
@@ -388,7 +485,11 @@ static BnArgs bn_args(const float* stats, const float* gamma, const float* beta,
 int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, const float* stats, const float* gamma, const float* beta, float* running_mean, float* running_var,
                 float* num_batches, float eps, float momentum, int M, int C, int relu, void* stream) {
   if (M <= 0 || C <= 0) return 0;
-  bn_apply_kernel<<<stream_grid((int64_t)M * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  if ((C & 7) || C > 2048) {
+    set_error("bn: C=%d must be a multiple of 8, at most 2048", C);
+    return 1;
+  }
+  bn_apply_kernel<<<bn_grid(M, C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(z_bf16), static_cast<const __nv_bfloat16*>(residual_bf16), static_cast<__nv_bfloat16*>(y_bf16),
       bn_args(stats, gamma, beta, running_mean, running_var, num_batches, eps, momentum, M, C, relu));
   B2_LAUNCH_CHECK("bn_apply_kernel");
@@ -396,24 +497,21 @@ int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, con
 }
 
 int b2_bn_backward(const void* dy_bf16, const void* y_bf16, const void* z_bf16, void* g_bf16, void* dz_bf16, float* red2c, const float* stats, const float* gamma, float* dgamma,
-                   float* dbeta, float eps, int M, int C, int relu, void* stream) {
+                   float* dbeta, float eps, int M, int C, int relu, int red_is_zero, void* stream) {
   if (M <= 0 || C <= 0) return 0;
-  if (C > 4096) {
-    set_error("bn_backward: C=%d too wide", C);
+  if ((C & 7) || C > 2048) {
+    set_error("bn_backward: C=%d must be a multiple of 8, at most 2048", C);
     return 1;
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   BnArgs a = bn_args(stats, gamma, nullptr, nullptr, nullptr, nullptr, eps, 0.f, M, C, relu);
-  B2_CUDA(cudaMemsetAsync(red2c, 0, 2 * C * sizeof(float), s));
-  int blocks = sm_count() * 2;
-  int rows_per_block = (M + blocks - 1) / blocks;
-  if (rows_per_block < 16) rows_per_block = 16;
-  blocks = (M + rows_per_block - 1) / rows_per_block;
-  bn_bwd_reduce_kernel<<<blocks, 256, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(dy_bf16), static_cast<const __nv_bfloat16*>(y_bf16),
-                                                                  static_cast<const __nv_bfloat16*>(z_bf16), static_cast<__nv_bfloat16*>(g_bf16), red2c, a, rows_per_block);
+  if (!red_is_zero) B2_CUDA(cudaMemsetAsync(red2c, 0, 2 * C * sizeof(float), s));
+  // the reduce pass ends in 2C atomics per block: fewer, longer blocks than the pure streaming passes
+  bn_bwd_reduce_kernel<<<bn_grid(M, C, 2), 256, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(dy_bf16), static_cast<const __nv_bfloat16*>(y_bf16),
+                                                                            static_cast<const __nv_bfloat16*>(z_bf16), static_cast<__nv_bfloat16*>(g_bf16), red2c, a);
   B2_LAUNCH_CHECK("bn_bwd_reduce_kernel");
-  bn_bwd_apply_kernel<<<stream_grid((int64_t)M * C, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(g_bf16), static_cast<const __nv_bfloat16*>(z_bf16), red2c,
-                                                                       static_cast<__nv_bfloat16*>(dz_bf16), dgamma, dbeta, a);
+  bn_bwd_apply_kernel<<<bn_grid(M, C), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(g_bf16), static_cast<const __nv_bfloat16*>(z_bf16), red2c,
+                                                    static_cast<__nv_bfloat16*>(dz_bf16), dgamma, dbeta, a);
   B2_LAUNCH_CHECK("bn_bwd_apply_kernel");
   return 0;
 }

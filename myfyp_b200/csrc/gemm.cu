@@ -94,6 +94,30 @@ __device__ __forceinline__ void conv_pixel_tile(const ConvGeom& cg, int pt, int&
   }
 }
 
+// v[e] = value of column e in this lane's row; returns the sum over the 32 lanes (rows) of column `lane` (of squares when `sq`)
+__device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane, bool sq) {
+  float w[16];
+  {
+    const bool hi = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float a = v[i], b = v[i + 16];
+      if (sq) {
+        a *= a;
+        b *= b;
+      }
+      w[i] = (hi ? b : a) + __shfl_xor_sync(0xffffffffu, hi ? a : b, 16);
+    }
+  }
+#pragma unroll
+  for (int half = 8; half >= 1; half >>= 1) {
+    const bool hi = lane & half;
+#pragma unroll
+    for (int i = 0; i < half; ++i) w[i] = (hi ? w[i + half] : w[i]) + __shfl_xor_sync(0xffffffffu, hi ? w[i] : w[i + half], half);
+  }
+  return w[0];
+}
+
 __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
   // MN-major canonical SWIZZLE_128B: rows are K (128 bytes = 64 MN elements each), 8-row groups 1024 bytes apart (SBO),
   // further 64-element MN blocks `lbo_bytes` apart (LBO)
@@ -317,18 +341,16 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
           for (int e = 0; e < 32; ++e)
             if (nb + e < N && row_ok) ep.out_bf16_t[(int64_t)(nb + e) * ep.ldt + row] = __float2bfloat16_rn(v[e]);
         }
-        if (ep.colsum != nullptr) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const float sum = warp_sum(v[e]);
-            if (lane == 0 && nb + e < N && sum != 0.f) atomicAdd(ep.colsum + nb + e, sum);
+        if (ep.colsum != nullptr || ep.colsumsq != nullptr) {
+          // column sums (bias gradient / batch-norm statistics) of this warp's 32 x 32 block: a transposing butterfly leaves the
+          // total of column `lane` in lane `lane` (31 shuffles instead of 32 full reductions), then ONE coalesced 32-wide atomic
+          if (ep.colsum != nullptr) {
+            const float t = warp_colsum32(v, lane, false);
+            if (nb + lane < N && t != 0.f) atomicAdd(ep.colsum + nb + lane, t);
           }
-        }
-        if (ep.colsumsq != nullptr) {  // batch-norm statistics of the layer output, from the fp32 accumulators
-#pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const float sq = warp_sum(v[e] * v[e]);
-            if (lane == 0 && nb + e < N && sq != 0.f) atomicAdd(ep.colsumsq + nb + e, sq);
+          if (ep.colsumsq != nullptr) {
+            const float t = warp_colsum32(v, lane, true);
+            if (nb + lane < N && t != 0.f) atomicAdd(ep.colsumsq + nb + lane, t);
           }
         }
       }

@@ -110,17 +110,18 @@ class NativeResNet:
         dev, bf = self.model.device, torch.bfloat16
         z = lambda *shape, dtype=bf: torch.zeros(*shape, dtype=dtype, device=dev)  # noqa: E731
         total_c = sum(L.cout for L in self.layers)
-        stats = z(2 * total_c, dtype=torch.float32)  # one arena, zeroed once per step
-        buf: dict = {"L": {}, "stats": stats, "red": z(2 * max(L.cout for L in self.layers), dtype=torch.float32)}
+        # one fp32 arena, zeroed once per step: per layer [sum, sumsq] of the forward and [sum g, sum g xhat] of the backward
+        stats = z(4 * total_c, dtype=torch.float32)
+        buf: dict = {"L": {}, "stats": stats}
         off = 0
         max_dcol = 0
         for L in self.layers:
             M = B * L.oh * L.ow
             buf["L"][L.conv] = {
                 "col": None if L.implicit else z(M, _pad8(L.kdim)), "z": z(M, L.cout), "y": z(M, L.cout), "g": z(M, L.cout), "dz": z(M, L.cout), "dy": z(M, L.cout),
-                "stats": stats[off : off + 2 * L.cout], "M": M,
+                "stats": stats[off : off + 2 * L.cout], "red": stats[off + 2 * L.cout : off + 4 * L.cout], "M": M,
             }
-            off += 2 * L.cout
+            off += 4 * L.cout
             if not L.implicit:
                 max_dcol = max(max_dcol, M * _pad8(L.kdim))
         buf["dcol"] = z(max_dcol)  # transient: one shared buffer
@@ -178,7 +179,7 @@ class NativeResNet:
         g, the masked gradient (= the gradient of the residual branch)."""
         lb, p = buf["L"][L.conv], self.par[L.conv]
         M = lb["M"]
-        ops.bn_backward(dy, lb["y"], lb["z"], lb["g"], lb["dz"], buf["red"], lb["stats"], p["gamma"], p["dgamma"], p["dbeta"], M, L.cout, relu)
+        ops.bn_backward(dy, lb["y"], lb["z"], lb["g"], lb["dz"], lb["red"], lb["stats"], p["gamma"], p["dgamma"], p["dbeta"], M, L.cout, relu, red_is_zero=True)
         if L.implicit:
             tiles = ((L.cout + 127) // 128) * (L.kdim // 64)
             ops.conv_gemm(ops.CONV_WGRAD, lb["x"], B, L.h, L.w, L.cin, L.cout, L.k, dz=lb["dz"], out_f32=p["gw"], split_k=max(1, min(296 // tiles, M // 128)))

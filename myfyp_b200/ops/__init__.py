@@ -529,10 +529,11 @@ def bn_apply(z, residual, y, stats, gamma, beta, running_mean, running_var, num_
                native.ptr(running_var), native.ptr(num_batches), ctypes.c_float(eps), ctypes.c_float(momentum), M, C, int(relu))
 
 
-def bn_backward(dy, y, z, g, dz, red, stats, gamma, dgamma, dbeta, M: int, C: int, relu: bool, eps: float = 1e-5) -> None:
-    """Batch-norm backward (two launches): ``g = dy*(y>0)``, ``dz``, ``dgamma +=``, ``dbeta +=``."""
+def bn_backward(dy, y, z, g, dz, red, stats, gamma, dgamma, dbeta, M: int, C: int, relu: bool, eps: float = 1e-5, red_is_zero: bool = False) -> None:
+    """Batch-norm backward (two launches): ``g = dy*(y>0)``, ``dz``, ``dgamma +=``, ``dbeta +=``.  ``red`` (2C floats of scratch) is
+    zeroed first unless ``red_is_zero`` (a training step clears one arena for all its layers instead)."""
     _conv_call("b2_bn_backward", dy.device, native.ptr(dy), native.ptr(y), native.ptr(z), native.ptr(g), native.ptr(dz), native.ptr(red), native.ptr(stats), native.ptr(gamma),
-               native.ptr(dgamma), native.ptr(dbeta), ctypes.c_float(eps), M, C, int(relu))
+               native.ptr(dgamma), native.ptr(dbeta), ctypes.c_float(eps), M, C, int(relu), int(red_is_zero))
     native.count_launch(1)
 
 
