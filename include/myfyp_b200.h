@@ -131,6 +131,8 @@ typedef struct {
   int a_mn, b_mn;     /* operand stored transposed: A as [K, lda>=M], B as [K, ldb>=N] (MN-major UMMA operands) */
   int split_k;        /* > 1: split the K loop over grid.z, atomically adding into out_f32 (which must hold 0 or the running sum) */
   float* colsumsq;    /* optional fp32 [N]: += column sums of squares (batch-norm statistics of the output), atomic */
+  int perm_cin, perm_taps; /* > 0: out_f32 column j = tap * cin + c is stored at c * taps + tap - the weight gradient of a convolution
+                              whose patch matrix is in (tap, c) order lands in PyTorch's [Cout, Cin, KH, KW] layout */
 } b2_gemm_args;
 int b2_gemm_bf16(const b2_gemm_args* args, void* stream);
 
@@ -160,7 +162,7 @@ typedef struct {
 } b2_conv_gemm_args;
 int b2_conv_gemm(const b2_conv_gemm_args* args, void* stream);
 /* fp32 [cout, cin, taps] (PyTorch conv weight inside the slab) -> bf16 [cout, taps, cin] for every layer of `table` in one launch;
- * table = n_layers x {src offset, dst offset, cout, cin, taps} (int64, device memory). */
+ * table = n_layers x {src offset, dst offset, cout, cin, taps, dst row pitch >= taps*cin} (int64, device memory). */
 int b2_repack_conv_weights(const float* slab, void* dst_bf16, const int64_t* table, int n_layers, int64_t max_elems, void* stream);
 /* fp32 [R,C] (pitch lds) -> bf16 row-major copy (pitch ldd, optional), bf16 transposed copy [C,R] (pitch ldt, optional),
  * column sums += (optional, atomic).  Staging step of the GEMMs above; the reference has no counterpart (it trains in fp32
@@ -168,7 +170,8 @@ int b2_repack_conv_weights(const float* slab, void* dst_bf16, const int64_t* tab
 int b2_cast_transpose(const float* src, int R, int C, int lds, void* dst_bf16, int ldd, void* dst_bf16_t, int ldt, float* colsum, void* stream);
 
 /* T4/T5 convolution building blocks (NHWC bf16 activations = the [pixels, channels] matrices b2_gemm_bf16 reads and writes).
- * Patch index order is (c, kh, kw) = PyTorch's [Cout, Cin, KH, KW] weights flattened, so weights are used in place.
+ * Patch index order is (kh, kw, c): a tap's channels are contiguous like the activations (16-byte vector gathers); weights are
+ * repacked to bf16 [Cout, taps, Cin] by b2_repack_conv_weights and the weight-gradient GEMM scatters back (perm_cin / perm_taps).
  * Reference path: torch conv2d / max_pool2d via autograd (the reference ships no CNN; BASELINE.json configs 2-4 name one). */
 int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
 /* dx = col2im(dcol) (+ add, when the activation has a second consumer such as a residual / shortcut branch) */

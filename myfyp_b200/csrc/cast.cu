@@ -10,6 +10,7 @@ namespace b2 {
 
 __global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __restrict__ src, int R, int C, int lds, __nv_bfloat16* __restrict__ dst, int ldd,
                                                              __nv_bfloat16* __restrict__ dst_t, int ldt, float* __restrict__ colsum) {
+  grid_dep_sync();
   __shared__ float tile[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
   const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __rest
 extern "C" int b2_cast_transpose(const float* src, int R, int C, int lds, void* dst_bf16, int ldd, void* dst_bf16_t, int ldt, float* colsum, void* stream) {
   if (R <= 0 || C <= 0) return 0;
   dim3 grid((C + 31) / 32, (R + 31) / 32);
-  b2::cast_transpose_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, R, C, lds, static_cast<__nv_bfloat16*>(dst_bf16), ldd,
+  b2::launch_pdl(b2::cast_transpose_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), src, R, C, lds, static_cast<__nv_bfloat16*>(dst_bf16), ldd,
                                                                                 static_cast<__nv_bfloat16*>(dst_bf16_t), ldt, colsum);
   B2_LAUNCH_CHECK("cast_transpose_kernel");
   return 0;

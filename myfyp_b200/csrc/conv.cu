@@ -4,9 +4,12 @@
 //     forward   col = im2col(X)                      Y = relu(col W^T + b)           (GEMM epilogue: bias + ReLU, bf16 out)
 //     wgrad     dW  = dZ^T col                       (both operands MN-major, split-K over the pixels, fp32 atomics into the gradient slab)
 //     dgrad     dcol = dZ W                          dX = col2im(dcol)               (gather form: no atomics)
-// The patch (K) index is ordered (c, kh, kw) - PyTorch's own [Cout, Cin, KH, KW] weight layout flattened - so the weights
-// need no permutation in either direction and dW lands directly in the slab.  A fully connected layer after a feature
-// map is the same thing with a kernel as large as the map, which also reproduces nn.Flatten's NCHW feature order.
+// The patch (K) index is ordered (kh, kw, c): a tap's channels are contiguous, exactly like the NHWC activations, so every
+// gather / scatter below moves 16-byte vectors of 8 channels with fully coalesced warps (the PyTorch order (c, kh, kw) would
+// put a tap's channels 2*KH*KW bytes apart).  The price is paid on the small side: weights are repacked fp32 [Cout, Cin, taps]
+// -> bf16 [Cout, taps, Cin] once per step for all layers (b2_repack_conv_weights) and the weight-gradient GEMM's epilogue
+// scatters back into PyTorch's layout (gemm.cu, perm_cin).  A fully connected layer after a feature map is the same thing
+// with a kernel as large as the map (nn.Flatten's NCHW feature order falls out of the same repack).
 // Reference path: torch conv2d / max_pool2d through autograd (cuDNN); the reference itself ships no CNN.
 #include <cuda_bf16.h>
 
@@ -19,48 +22,90 @@ struct ConvGeom {
   int B, H, W, C, KH, KW, stride, pad, OH, OW;
 };
 
-// one thread per (output pixel m, input channel c): KH*KW taps -> KH*KW consecutive columns of row m
-template <bool NCHW_F32>
-__global__ void __launch_bounds__(256) im2col_kernel(const void* __restrict__ xin, __nv_bfloat16* __restrict__ col, ConvGeom g, int ldc) {
-  const int64_t total = (int64_t)g.B * g.OH * g.OW * g.C;
-  const int KK = g.KH * g.KW;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % g.C);
-    const int64_t m = i / g.C;
-    const int ow = (int)(m % g.OW);
-    const int oh = (int)((m / g.OW) % g.OH);
-    const int b = (int)(m / ((int64_t)g.OW * g.OH));
-    __nv_bfloat16* dst = col + m * ldc + (int64_t)c * KK;
-    for (int kh = 0; kh < g.KH; ++kh) {
-      const int ih = oh * g.stride - g.pad + kh;
-      for (int kw = 0; kw < g.KW; ++kw) {
-        const int iw = ow * g.stride - g.pad + kw;
-        __nv_bfloat16 v = __float2bfloat16_rn(0.f);
-        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) {
-          if constexpr (NCHW_F32) {
-            v = __float2bfloat16_rn(static_cast<const float*>(xin)[(((int64_t)b * g.C + c) * g.H + ih) * g.W + iw]);
-          } else {
-            v = static_cast<const __nv_bfloat16*>(xin)[(((int64_t)b * g.H + ih) * g.W + iw) * g.C + c];
-          }
-        }
-        dst[kh * g.KW + kw] = v;
-      }
+// V consecutive channels (V = 8: one 16-byte vector, V = 1: scalar fallback for channel counts that are not multiples of 8)
+template <int V>
+struct ChanVec;
+template <>
+struct ChanVec<8> {
+  uint4 raw;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { raw = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+  __device__ __forceinline__ void zero() { raw = make_uint4(0u, 0u, 0u, 0u); }
+  __device__ __forceinline__ void unpack(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __bfloat1622float2(h[i]);
+      f[2 * i] = t.x;
+      f[2 * i + 1] = t.y;
     }
+  }
+  __device__ __forceinline__ void pack(const float (&f)[8]) {
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  }
+};
+template <>
+struct ChanVec<1> {
+  __nv_bfloat16 raw;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { raw = *p; }
+  __device__ __forceinline__ void store(__nv_bfloat16* p) const { *p = raw; }
+  __device__ __forceinline__ void zero() { raw = __float2bfloat16_rn(0.f); }
+  __device__ __forceinline__ void unpack(float (&f)[1]) const { f[0] = __bfloat162float(raw); }
+  __device__ __forceinline__ void pack(const float (&f)[1]) { raw = __float2bfloat16_rn(f[0]); }
+};
+
+// one thread per (output pixel m, tap, channel group): col[m, tap * C + c] = x[pixel + tap, c]  (zero outside the image)
+template <int V>
+__global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g, int ldc) {
+  grid_dep_sync();
+  const int KK = g.KH * g.KW, CG = g.C / V;
+  const int64_t total = (int64_t)g.B * g.OH * g.OW * KK * CG;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CG);
+    const int t = (int)((i / CG) % KK);
+    const int64_t m = i / ((int64_t)CG * KK);
+    const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH), b = (int)(m / ((int64_t)g.OW * g.OH));
+    const int ih = oh * g.stride - g.pad + t / g.KW, iw = ow * g.stride - g.pad + t % g.KW;
+    ChanVec<V> v;
+    if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) v.load(x + (((int64_t)b * g.H + ih) * g.W + iw) * g.C + cg * V);
+    else v.zero();
+    v.store(col + m * ldc + (int64_t)t * g.C + cg * V);
   }
 }
 
-// dx[b,h,w,c] = sum over the taps (kh,kw) whose output pixel exists of dcol[(b,oh,ow), c*KK + kh*KW + kw]
-__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int ldc,
-                                                     const __nv_bfloat16* __restrict__ add) {
-  const int64_t total = (int64_t)g.B * g.H * g.W * g.C;
+// the input layer: NCHW fp32 images -> the same (tap, c) patch rows
+__global__ void __launch_bounds__(256) im2col_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g, int ldc) {
+  grid_dep_sync();
   const int KK = g.KH * g.KW;
+  const int64_t total = (int64_t)g.B * g.OH * g.OW * KK * g.C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % g.C);
-    const int64_t p = i / g.C;
-    const int w = (int)(p % g.W);
-    const int h = (int)((p / g.W) % g.H);
-    const int b = (int)(p / ((int64_t)g.W * g.H));
-    float acc = 0.f;
+    const int t = (int)((i / g.C) % KK);
+    const int64_t m = i / ((int64_t)g.C * KK);
+    const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH), b = (int)(m / ((int64_t)g.OW * g.OH));
+    const int ih = oh * g.stride - g.pad + t / g.KW, iw = ow * g.stride - g.pad + t % g.KW;
+    float v = 0.f;
+    if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) v = x[(((int64_t)b * g.C + c) * g.H + ih) * g.W + iw];
+    col[m * ldc + (int64_t)t * g.C + c] = __float2bfloat16_rn(v);
+  }
+}
+
+// dx[b,h,w,c] = sum over the taps (kh,kw) whose output pixel exists of dcol[(b,oh,ow), (kh*KW + kw) * C + c]  (gather form, no atomics)
+template <int V>
+__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int ldc,
+                                                     const __nv_bfloat16* __restrict__ add) {
+  grid_dep_sync();
+  const int CG = g.C / V;
+  const int64_t total = (int64_t)g.B * g.H * g.W * CG;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CG);
+    const int64_t p = i / CG;
+    const int w = (int)(p % g.W), h = (int)((p / g.W) % g.H), b = (int)(p / ((int64_t)g.W * g.H));
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
     for (int kh = 0; kh < g.KH; ++kh) {
       const int th = h + g.pad - kh;
       if (th < 0 || th % g.stride) continue;
@@ -71,12 +116,24 @@ __global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __rest
         if (tw < 0 || tw % g.stride) continue;
         const int ow = tw / g.stride;
         if (ow >= g.OW) continue;
-        const int64_t m = ((int64_t)b * g.OH + oh) * g.OW + ow;
-        acc += __bfloat162float(dcol[m * ldc + (int64_t)c * KK + kh * g.KW + kw]);
+        ChanVec<V> v;
+        float f[V];
+        v.load(dcol + (((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)(kh * g.KW + kw) * g.C + cg * V);
+        v.unpack(f);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += f[j];
       }
     }
-    if (add != nullptr) acc += __bfloat162float(add[i]);  // second consumer of the same activation (residual / shortcut branch)
-    dx[i] = __float2bfloat16_rn(acc);
+    ChanVec<V> o;
+    if (add != nullptr) {  // second consumer of the same activation (residual / shortcut branch)
+      float f[V];
+      o.load(add + p * g.C + cg * V);
+      o.unpack(f);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += f[j];
+    }
+    o.pack(acc);
+    o.store(dx + p * g.C + cg * V);
   }
 }
 
@@ -118,6 +175,7 @@ struct Bf16x8 {
 
 // y = act(gamma * (z - mean) * invstd + beta (+ residual))
 __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y, BnArgs a) {
+  grid_dep_sync();
   const int groups = a.C >> 3, rows_per_iter = blockDim.x / groups;
   const int cg = threadIdx.x % groups, r = threadIdx.x / groups;
   const float invM = 1.f / (float)a.M;
@@ -177,6 +235,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 // (and is at the same time the gradient that flows into the residual branch)
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ z,
                                                             __nv_bfloat16* __restrict__ gbuf, float* __restrict__ red, BnArgs a) {
+  grid_dep_sync();
   extern __shared__ float s_red[];  // 2C
   for (int c = threadIdx.x; c < 2 * a.C; c += blockDim.x) s_red[c] = 0.f;
   __syncthreads();
@@ -231,6 +290,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
 // pass 2: dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat));  block 0 adds dgamma / dbeta into the gradient slab
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ gbuf, const __nv_bfloat16* __restrict__ z, const float* __restrict__ red,
                                                            __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta, BnArgs a) {
+  grid_dep_sync();
   const int groups = a.C >> 3, rows_per_iter = blockDim.x / groups;
   const int cg = threadIdx.x % groups, r = threadIdx.x / groups;
   const float invM = 1.f / (float)a.M;
@@ -270,6 +330,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
 
 // global average pooling over the H*W pixels of an NHWC map, and its backward (broadcast / HW)
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int HW, int C, int ldo) {
+  grid_dep_sync();
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B * C; i += gridDim.x * blockDim.x) {
     const int c = i % C, b = i / C;
     float acc = 0.f;
@@ -278,6 +339,7 @@ __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const __nv_bfloat16* _
   }
 }
 __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dout, int ldo, __nv_bfloat16* __restrict__ dx, int B, int HW, int C) {
+  grid_dep_sync();
   const int64_t total = (int64_t)B * HW * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
@@ -289,6 +351,7 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* _
 // 2x2 / stride 2 max pooling over NHWC, remembering which of the four inputs won (first maximum, like PyTorch)
 __global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ p, uint8_t* __restrict__ idx, int B, int H, int W,
                                                            int C) {
+  grid_dep_sync();
   const int OH = H / 2, OW = W / 2;
   const int64_t total = (int64_t)B * OH * OW * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -310,6 +373,7 @@ __global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const __nv_bfloat16* 
 // dz[b,h,w,c] = dp[b,h/2,w/2,c] where (h,w) is the remembered maximum and the pre-pool activation is positive (ReLU)
 __global__ void __launch_bounds__(256) maxpool2_relu_bwd_kernel(const __nv_bfloat16* __restrict__ dp, const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ y,
                                                                 __nv_bfloat16* __restrict__ dz, int B, int H, int W, int C) {
+  grid_dep_sync();
   const int OH = H / 2, OW = W / 2;
   const int64_t total = (int64_t)B * H * W * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -330,22 +394,45 @@ __global__ void __launch_bounds__(256) maxpool2_relu_bwd_kernel(const __nv_bfloa
 // one pass - the pooled value is scattered straight into the next layer's col matrix (up to KH*KW positions), the
 // pooled activation itself is never materialised.  `g` is the NEXT layer's geometry over the pooled map [B, g.H, g.W, g.C].
 // Entries of col that correspond to padding taps are never written and keep the zero they were allocated with.
+template <int V>
 __global__ void __launch_bounds__(256) pool_im2col_kernel(const __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ idx, __nv_bfloat16* __restrict__ col, ConvGeom g, int ldc) {
-  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, KK = g.KH * g.KW;
-  const int64_t total = (int64_t)g.B * g.H * g.W * C;
+  grid_dep_sync();
+  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, CG = C / V;
+  const int64_t total = (int64_t)g.B * g.H * g.W * CG;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const int64_t q = i / C;
+    const int cg = (int)(i % CG);
+    const int64_t q = i / CG;
     const int pw = (int)(q % g.W), ph = (int)((q / g.W) % g.H), b = (int)(q / ((int64_t)g.W * g.H));
-    const __nv_bfloat16* src = y + (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + c;
-    __nv_bfloat16 bv = src[0];
-    float best = __bfloat162float(bv);
-    int bi = 0;
-    const __nv_bfloat16 r1 = src[C], r2 = src[(int64_t)W2 * C], r3 = src[(int64_t)W2 * C + C];
-    if (__bfloat162float(r1) > best) { best = __bfloat162float(r1); bv = r1; bi = 1; }
-    if (__bfloat162float(r2) > best) { best = __bfloat162float(r2); bv = r2; bi = 2; }
-    if (__bfloat162float(r3) > best) { best = __bfloat162float(r3); bv = r3; bi = 3; }
-    idx[i] = (uint8_t)bi;
+    const __nv_bfloat16* src = y + (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + cg * V;
+    const int64_t offs[4] = {0, C, (int64_t)W2 * C, (int64_t)W2 * C + C};
+    float best[V];
+    uint8_t bi[V];
+    ChanVec<V> v;
+    v.load(src);
+    v.unpack(best);
+#pragma unroll
+    for (int j = 0; j < V; ++j) bi[j] = 0;
+#pragma unroll
+    for (int k = 1; k < 4; ++k) {
+      float f[V];
+      v.load(src + offs[k]);
+      v.unpack(f);
+#pragma unroll
+      for (int j = 0; j < V; ++j)
+        if (f[j] > best[j]) {
+          best[j] = f[j];
+          bi[j] = (uint8_t)k;
+        }
+    }
+    v.pack(best);  // exact: the maxima are bf16 values
+    if constexpr (V == 8) {
+      uint2 packed;
+      packed.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+      packed.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+      *reinterpret_cast<uint2*>(idx + q * C + cg * 8) = packed;
+    } else {
+      idx[q * C + cg] = bi[0];
+    }
     for (int kh = 0; kh < g.KH; ++kh) {
       const int th = ph + g.pad - kh;
       if (th < 0 || th % g.stride) continue;
@@ -356,7 +443,7 @@ __global__ void __launch_bounds__(256) pool_im2col_kernel(const __nv_bfloat16* _
         if (tw < 0 || tw % g.stride) continue;
         const int ow = tw / g.stride;
         if (ow >= g.OW) continue;
-        col[(((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)c * KK + kh * g.KW + kw] = bv;
+        v.store(col + (((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)(kh * g.KW + kw) * C + cg * V);
       }
     }
   }
@@ -365,19 +452,22 @@ __global__ void __launch_bounds__(256) pool_im2col_kernel(const __nv_bfloat16* _
 // Fused backward head of a conv block: col2im of the NEXT layer's dcol (gather over its taps) -> gradient of the pooled
 // activation -> routed to the remembered max position, times the ReLU mask -> dZ [B, 2H, 2W, C], plus the bias gradient
 // (column sums of dZ) reduced per block in shared memory.  One pass, no dP / P buffers.
+template <int V>
 __global__ void __launch_bounds__(256) unpool_col2im_kernel(const __nv_bfloat16* __restrict__ dcol, const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ y,
                                                             __nv_bfloat16* __restrict__ dz, float* __restrict__ bias_grad, ConvGeom g, int ldc) {
+  grid_dep_sync();
   extern __shared__ float s_db[];  // C floats
-  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, KK = g.KH * g.KW;
+  const int H2 = g.H * 2, W2 = g.W * 2, C = g.C, CG = C / V;
   for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
   __syncthreads();
-  const int64_t total = (int64_t)g.B * g.H * g.W * C;
-  const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
+  const int64_t total = (int64_t)g.B * g.H * g.W * CG;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const int64_t q = i / C;
+    const int cg = (int)(i % CG);
+    const int64_t q = i / CG;
     const int pw = (int)(q % g.W), ph = (int)((q / g.W) % g.H), b = (int)(q / ((int64_t)g.W * g.H));
-    float acc = 0.f;
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
     for (int kh = 0; kh < g.KH; ++kh) {
       const int th = ph + g.pad - kh;
       if (th < 0 || th % g.stride) continue;
@@ -388,17 +478,45 @@ __global__ void __launch_bounds__(256) unpool_col2im_kernel(const __nv_bfloat16*
         if (tw < 0 || tw % g.stride) continue;
         const int ow = tw / g.stride;
         if (ow >= g.OW) continue;
-        acc += __bfloat162float(dcol[(((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)c * KK + kh * g.KW + kw]);
+        ChanVec<V> v;
+        float f[V];
+        v.load(dcol + (((int64_t)b * g.OH + oh) * g.OW + ow) * ldc + (int64_t)(kh * g.KW + kw) * C + cg * V);
+        v.unpack(f);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += f[j];
       }
     }
-    const int win = idx[i];
-    const int64_t base = (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + c;
-    const int64_t offs[4] = {0, C, (int64_t)W2 * C, (int64_t)W2 * C + C};
-    const __nv_bfloat16 gq = __float2bfloat16_rn(acc);  // the value the unfused path stores as dP
-    const bool live = __bfloat162float(y[base + offs[win]]) > 0.f;
+    uint8_t win[V];
+    if constexpr (V == 8) {
+      const uint2 packed = *reinterpret_cast<const uint2*>(idx + q * C + cg * 8);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) dz[base + offs[k]] = (k == win && live) ? gq : zero;
-    if (live && bias_grad != nullptr) atomicAdd(&s_db[c], __bfloat162float(gq));
+      for (int j = 0; j < 4; ++j) {
+        win[j] = (packed.x >> (8 * j)) & 0xFF;
+        win[4 + j] = (packed.y >> (8 * j)) & 0xFF;
+      }
+    } else {
+      win[0] = idx[q * C + cg];
+    }
+    ChanVec<V> gq;
+    gq.pack(acc);  // the value the unfused path stores as dP
+    gq.unpack(acc);
+    const int64_t base = (((int64_t)b * H2 + 2 * ph) * W2 + 2 * pw) * C + cg * V;
+    const int64_t offs[4] = {0, C, (int64_t)W2 * C, (int64_t)W2 * C + C};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      ChanVec<V> yv, o;
+      float yf[V], of[V];
+      yv.load(y + base + offs[k]);
+      yv.unpack(yf);
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const bool live = (win[j] == k) && yf[j] > 0.f;
+        of[j] = live ? acc[j] : 0.f;
+        if (live && bias_grad != nullptr) atomicAdd(&s_db[cg * V + j], acc[j]);
+      }
+      o.pack(of);
+      o.store(dz + base + offs[k]);
+    }
   }
   __syncthreads();
   if (bias_grad != nullptr)
@@ -408,6 +526,7 @@ __global__ void __launch_bounds__(256) unpool_col2im_kernel(const __nv_bfloat16*
 
 // out[c] += sum_m z[m, c]   (bias gradient of a conv layer): each block reduces a slab of rows in shared memory
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ z, int M, int C, int ld, float* __restrict__ out, int rows_per_block) {
+  grid_dep_sync();
   extern __shared__ float s_acc[];  // C floats
   for (int c = threadIdx.x; c < C; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
@@ -428,15 +547,16 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
     if (s_acc[c] != 0.f) atomicAdd(out + c, s_acc[c]);
 }
 
-// conv weights fp32 [cout][cin][taps] -> bf16 [cout][taps][cin]; blockIdx.y = layer
+// conv weights fp32 [cout][cin][taps] -> bf16 [cout][taps][cin] (row pitch ld >= taps * cin); blockIdx.y = layer
 __global__ void repack_conv_weights_kernel(const float* __restrict__ slab, __nv_bfloat16* __restrict__ dst, const int64_t* __restrict__ table) {
-  const int64_t* t = table + 5 * blockIdx.y;
+  grid_dep_sync();
+  const int64_t* t = table + 6 * blockIdx.y;
   const float* src = slab + t[0];
   __nv_bfloat16* out = dst + t[1];
-  const int64_t cin = t[3], taps = t[4], n = t[2] * cin * taps;
+  const int64_t cin = t[3], taps = t[4], ld = t[5], n = t[2] * cin * taps;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t c = i % cin, r = i / cin, tp = r % taps, co = r / taps;
-    out[i] = __float2bfloat16_rn(src[(co * cin + c) * taps + tp]);
+    out[co * ld + tp * cin + c] = __float2bfloat16_rn(src[(co * cin + c) * taps + tp]);
   }
 }
 
@@ -452,10 +572,13 @@ int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, 
     set_error("im2col: bad geometry (OH=%d OW=%d ldc=%d < %d)", g.OH, g.OW, ldc, C * KH * KW);
     return 1;
   }
-  const int64_t total = (int64_t)B * g.OH * g.OW * C;
+  const int64_t total = (int64_t)B * g.OH * g.OW * KH * KW * C;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (x_is_nchw_f32) im2col_kernel<true><<<stream_grid(total, 256), 256, 0, s>>>(x, static_cast<__nv_bfloat16*>(col_bf16), g, ldc);
-  else im2col_kernel<false><<<stream_grid(total, 256), 256, 0, s>>>(x, static_cast<__nv_bfloat16*>(col_bf16), g, ldc);
+  __nv_bfloat16* col = static_cast<__nv_bfloat16*>(col_bf16);
+  const bool vec = (C % 8 == 0) && (ldc % 8 == 0) && aligned16(x) && aligned16(col_bf16);
+  if (x_is_nchw_f32) launch_pdl(im2col_nchw_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, s, static_cast<const float*>(x), col, g, ldc);
+  else if (vec) launch_pdl(im2col_kernel<8>, dim3(stream_grid(total / 8, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), col, g, ldc);
+  else launch_pdl(im2col_kernel<1>, dim3(stream_grid(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), col, g, ldc);
   B2_LAUNCH_CHECK("im2col_kernel");
   return 0;
 }
@@ -463,8 +586,12 @@ int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, 
 int b2_col2im(const void* dcol_bf16, int ldc, void* dx_bf16, const void* add_bf16, int B, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream) {
   ConvGeom g{B, H, W, C, KH, KW, stride, pad, (H + 2 * pad - KH) / stride + 1, (W + 2 * pad - KW) / stride + 1};
   const int64_t total = (int64_t)B * H * W * C;
-  col2im_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dcol_bf16), static_cast<__nv_bfloat16*>(dx_bf16), g, ldc,
-                                                                                       static_cast<const __nv_bfloat16*>(add_bf16));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16 *dcol = static_cast<const __nv_bfloat16*>(dcol_bf16), *add = static_cast<const __nv_bfloat16*>(add_bf16);
+  __nv_bfloat16* dx = static_cast<__nv_bfloat16*>(dx_bf16);
+  const bool vec = (C % 8 == 0) && (ldc % 8 == 0) && aligned16(dcol_bf16) && aligned16(dx_bf16) && aligned16(add_bf16);
+  if (vec) launch_pdl(col2im_kernel<8>, dim3(stream_grid(total / 8, 256)), dim3(256), 0, s, dcol, dx, g, ldc, add);
+  else launch_pdl(col2im_kernel<1>, dim3(stream_grid(total, 256)), dim3(256), 0, s, dcol, dx, g, ldc, add);
   B2_LAUNCH_CHECK("col2im_kernel");
   return 0;
 }
@@ -489,7 +616,7 @@ int b2_bn_apply(const void* z_bf16, const void* residual_bf16, void* y_bf16, con
     set_error("bn: C=%d must be a multiple of 8, at most 2048", C);
     return 1;
   }
-  bn_apply_kernel<<<bn_grid(M, C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_pdl(bn_apply_kernel, dim3(bn_grid(M, C)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(z_bf16), static_cast<const __nv_bfloat16*>(residual_bf16), static_cast<__nv_bfloat16*>(y_bf16),
       bn_args(stats, gamma, beta, running_mean, running_var, num_batches, eps, momentum, M, C, relu));
   B2_LAUNCH_CHECK("bn_apply_kernel");
@@ -507,24 +634,24 @@ int b2_bn_backward(const void* dy_bf16, const void* y_bf16, const void* z_bf16, 
   BnArgs a = bn_args(stats, gamma, nullptr, nullptr, nullptr, nullptr, eps, 0.f, M, C, relu);
   if (!red_is_zero) B2_CUDA(cudaMemsetAsync(red2c, 0, 2 * C * sizeof(float), s));
   // the reduce pass ends in 2C atomics per block: fewer, longer blocks than the pure streaming passes
-  bn_bwd_reduce_kernel<<<bn_grid(M, C, 2), 256, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(dy_bf16), static_cast<const __nv_bfloat16*>(y_bf16),
+  launch_pdl(bn_bwd_reduce_kernel, dim3(bn_grid(M, C, 2)), dim3(256), 2 * C * sizeof(float), s, static_cast<const __nv_bfloat16*>(dy_bf16), static_cast<const __nv_bfloat16*>(y_bf16),
                                                                             static_cast<const __nv_bfloat16*>(z_bf16), static_cast<__nv_bfloat16*>(g_bf16), red2c, a);
   B2_LAUNCH_CHECK("bn_bwd_reduce_kernel");
-  bn_bwd_apply_kernel<<<bn_grid(M, C), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(g_bf16), static_cast<const __nv_bfloat16*>(z_bf16), red2c,
+  launch_pdl(bn_bwd_apply_kernel, dim3(bn_grid(M, C)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(g_bf16), static_cast<const __nv_bfloat16*>(z_bf16), red2c,
                                                     static_cast<__nv_bfloat16*>(dz_bf16), dgamma, dbeta, a);
   B2_LAUNCH_CHECK("bn_bwd_apply_kernel");
   return 0;
 }
 
 int b2_avgpool_fwd(const void* x_bf16, void* out_bf16, int ldo, int B, int HW, int C, void* stream) {
-  avgpool_fwd_kernel<<<stream_grid((int64_t)B * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x_bf16), static_cast<__nv_bfloat16*>(out_bf16), B,
+  launch_pdl(avgpool_fwd_kernel, dim3(stream_grid((int64_t)B * C, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x_bf16), static_cast<__nv_bfloat16*>(out_bf16), B,
                                                                                                      HW, C, ldo);
   B2_LAUNCH_CHECK("avgpool_fwd_kernel");
   return 0;
 }
 
 int b2_avgpool_bwd(const void* dout_bf16, int ldo, void* dx_bf16, int B, int HW, int C, void* stream) {
-  avgpool_bwd_kernel<<<stream_grid((int64_t)B * HW * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dout_bf16), ldo,
+  launch_pdl(avgpool_bwd_kernel, dim3(stream_grid((int64_t)B * HW * C, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dout_bf16), ldo,
                                                                                                           static_cast<__nv_bfloat16*>(dx_bf16), B, HW, C);
   B2_LAUNCH_CHECK("avgpool_bwd_kernel");
   return 0;
@@ -532,7 +659,7 @@ int b2_avgpool_bwd(const void* dout_bf16, int ldo, void* dx_bf16, int B, int HW,
 
 int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H, int W, int C, void* stream) {
   const int64_t total = (int64_t)B * (H / 2) * (W / 2) * C;
-  maxpool2_fwd_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(p_bf16),
+  launch_pdl(maxpool2_fwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(p_bf16),
                                                                                              static_cast<uint8_t*>(idx_u8), B, H, W, C);
   B2_LAUNCH_CHECK("maxpool2_fwd_kernel");
   return 0;
@@ -540,7 +667,7 @@ int b2_maxpool2_fwd(const void* y_bf16, void* p_bf16, void* idx_u8, int B, int H
 
 int b2_maxpool2_relu_bwd(const void* dp_bf16, const void* idx_u8, const void* y_bf16, void* dz_bf16, int B, int H, int W, int C, void* stream) {
   const int64_t total = (int64_t)B * H * W * C;
-  maxpool2_relu_bwd_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_pdl(maxpool2_relu_bwd_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(dp_bf16), static_cast<const uint8_t*>(idx_u8), static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(dz_bf16), B, H, W, C);
   B2_LAUNCH_CHECK("maxpool2_relu_bwd_kernel");
   return 0;
@@ -553,8 +680,13 @@ int b2_pool_im2col(const void* y_bf16, void* idx_u8, void* col_bf16, int ldc, in
     return 1;
   }
   const int64_t total = (int64_t)B * PH * PW * C;
-  pool_im2col_kernel<<<stream_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(y_bf16), static_cast<uint8_t*>(idx_u8),
-                                                                                            static_cast<__nv_bfloat16*>(col_bf16), g, ldc);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* y = static_cast<const __nv_bfloat16*>(y_bf16);
+  uint8_t* idx = static_cast<uint8_t*>(idx_u8);
+  __nv_bfloat16* col = static_cast<__nv_bfloat16*>(col_bf16);
+  const bool vec = (C % 8 == 0) && (ldc % 8 == 0) && aligned16(y_bf16) && aligned16(col_bf16) && aligned16(idx_u8);
+  if (vec) launch_pdl(pool_im2col_kernel<8>, dim3(stream_grid(total / 8, 256)), dim3(256), 0, s, y, idx, col, g, ldc);
+  else launch_pdl(pool_im2col_kernel<1>, dim3(stream_grid(total, 256)), dim3(256), 0, s, y, idx, col, g, ldc);
   B2_LAUNCH_CHECK("pool_im2col_kernel");
   return 0;
 }
@@ -567,9 +699,13 @@ int b2_unpool_col2im(const void* dcol_bf16, int ldc, const void* idx_u8, const v
     return 1;
   }
   const int64_t total = (int64_t)B * PH * PW * C;
-  unpool_col2im_kernel<<<stream_grid(total, 256, 2), 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dcol_bf16), static_cast<const uint8_t*>(idx_u8), static_cast<const __nv_bfloat16*>(y_bf16), static_cast<__nv_bfloat16*>(dz_bf16), bias_grad, g,
-      ldc);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16 *dcol = static_cast<const __nv_bfloat16*>(dcol_bf16), *y = static_cast<const __nv_bfloat16*>(y_bf16);
+  const uint8_t* idx = static_cast<const uint8_t*>(idx_u8);
+  __nv_bfloat16* dz = static_cast<__nv_bfloat16*>(dz_bf16);
+  const bool vec = (C % 8 == 0) && (ldc % 8 == 0) && aligned16(dcol_bf16) && aligned16(y_bf16) && aligned16(dz_bf16) && aligned16(idx_u8);
+  if (vec) launch_pdl(unpool_col2im_kernel<8>, dim3(stream_grid(total / 8, 256, 2)), dim3(256), C * sizeof(float), s, dcol, idx, y, dz, bias_grad, g, ldc);
+  else launch_pdl(unpool_col2im_kernel<1>, dim3(stream_grid(total, 256, 2)), dim3(256), C * sizeof(float), s, dcol, idx, y, dz, bias_grad, g, ldc);
   B2_LAUNCH_CHECK("unpool_col2im_kernel");
   return 0;
 }
@@ -584,7 +720,7 @@ int b2_colsum_bf16(const void* z_bf16, int M, int C, int ld, float* out, void* s
   int rows_per_block = (M + blocks - 1) / blocks;
   if (rows_per_block < 32) rows_per_block = 32;
   blocks = (M + rows_per_block - 1) / rows_per_block;
-  colsum_bf16_kernel<<<blocks, 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(z_bf16), M, C, ld, out, rows_per_block);
+  launch_pdl(colsum_bf16_kernel, dim3(blocks), dim3(256), C * sizeof(float), static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(z_bf16), M, C, ld, out, rows_per_block);
   B2_LAUNCH_CHECK("colsum_bf16_kernel");
   return 0;
 }
@@ -596,7 +732,7 @@ extern "C" int b2_repack_conv_weights(const float* slab, void* dst_bf16, const i
   int64_t blocks = (max_elems + 255) / 256;
   if (blocks > 592) blocks = 592;
   if (blocks < 1) blocks = 1;
-  repack_conv_weights_kernel<<<dim3((unsigned)blocks, (unsigned)n_layers), 256, 0, static_cast<cudaStream_t>(stream)>>>(slab, static_cast<__nv_bfloat16*>(dst_bf16), table);
+  launch_pdl(repack_conv_weights_kernel, dim3(dim3((unsigned)blocks, (unsigned)n_layers)), dim3(256), 0, static_cast<cudaStream_t>(stream), slab, static_cast<__nv_bfloat16*>(dst_bf16), table);
   B2_LAUNCH_CHECK("repack_conv_weights_kernel");
   return 0;
 }

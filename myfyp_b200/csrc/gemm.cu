@@ -130,6 +130,7 @@ template <int BN, bool A_MN, bool B_MN, int CONV = 0>
 __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
                                                                    int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep, ConvGeom cg) {
   using Cfg = GemmCfg<BN>;
+  grid_dep_launch();  // the next kernel of the step may become resident and run its own prologue while this one works
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[Cfg::STAGES], empty_bar[Cfg::STAGES], acc_full[GM_ACC_STAGES], acc_empty[GM_ACC_STAGES];
   __shared__ uint32_t tmem_base_s;
@@ -158,6 +159,7 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = tmem_base_s;
+  grid_dep_wait();  // barriers, TMEM and tensor maps are ready: now wait for the producer of our operands to complete
 
   auto work_coords = [&](int w, int& m0, int& n0, int& kb0, int& nk) {
     const int z = w % splits;
@@ -285,15 +287,17 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
         if (ep.out_f32 != nullptr && row_ok) {
           float* o = ep.out_f32 + (int64_t)row * ep.ldo + nb;
           if (ep.perm_cin > 0) {
-            // 32 consecutive columns lie inside one tap (cin % 64 == 0): scatter to [row][c][tap]
+            // column j = tap * cin + c goes to [row][c][tap]; with cin % 32 == 0 the 32 columns of this block share one tap
+            const bool one_tap = (ep.perm_cin & 31) == 0;
             float* op = ep.out_f32 + (int64_t)row * ep.ldo + (int64_t)(nb % ep.perm_cin) * ep.perm_taps + nb / ep.perm_cin;
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
               if (nb + e < N) {
+                float* o1 = one_tap ? op + e * ep.perm_taps : ep.out_f32 + (int64_t)row * ep.ldo + (int64_t)((nb + e) % ep.perm_cin) * ep.perm_taps + (nb + e) / ep.perm_cin;
                 if (split) {
-                  if (v[e] != 0.f) atomicAdd(op + e * ep.perm_taps, v[e]);
+                  if (v[e] != 0.f) atomicAdd(o1, v[e]);
                 } else {
-                  op[e * ep.perm_taps] = ep.accumulate ? op[e * ep.perm_taps] + v[e] : v[e];
+                  *o1 = ep.accumulate ? *o1 + v[e] : v[e];
                 }
               }
             }
@@ -466,10 +470,10 @@ static int launch_gemm(const b2_gemm_args* a, const CUtensorMap& ta, const CUten
   const int n_work = tiles_m * tiles_n * splits;
   int grid = sm_count() * Cfg::CTAS_PER_SM;
   if (n_work < grid) grid = n_work;
-  if (a->a_mn && a->b_mn) gemm_bf16_kernel<BN, true, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
-  else if (a->a_mn) gemm_bf16_kernel<BN, true, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
-  else if (a->b_mn) gemm_bf16_kernel<BN, false, true><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
-  else gemm_bf16_kernel<BN, false, false><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  if (a->a_mn && a->b_mn) launch_pdl(gemm_bf16_kernel<BN, true, true>, dim3(grid), dim3(GM_THREADS), Cfg::SMEM, st, ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else if (a->a_mn) launch_pdl(gemm_bf16_kernel<BN, true, false>, dim3(grid), dim3(GM_THREADS), Cfg::SMEM, st, ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else if (a->b_mn) launch_pdl(gemm_bf16_kernel<BN, false, true>, dim3(grid), dim3(GM_THREADS), Cfg::SMEM, st, ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
+  else launch_pdl(gemm_bf16_kernel<BN, false, false>, dim3(grid), dim3(GM_THREADS), Cfg::SMEM, st, ta, tb, a->M, a->N, a->K, tiles_m, tiles_n, splits, kb_per_split, ep, ConvGeom{});
   B2_LAUNCH_CHECK("gemm_bf16_kernel");
   return 0;
 }
@@ -498,7 +502,7 @@ extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
   if (kb_per_split < 1) kb_per_split = 1;
   splits = total_k > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
   GemmEpilogue ep{a->out_f32, static_cast<__nv_bfloat16*>(a->out_bf16), static_cast<__nv_bfloat16*>(a->out_bf16_t), a->bias, static_cast<const __nv_bfloat16*>(a->mask),
-                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate, nullptr, 0, 0, 0};
+                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate, nullptr, 0, a->perm_cin, a->perm_taps};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (bn == 256) return launch_gemm<256>(a, ta, tb, splits, kb_per_split, ep, st);
   return launch_gemm<64>(a, ta, tb, splits, kb_per_split, ep, st);
@@ -519,7 +523,7 @@ static int launch_conv(int M, int N, int K, const CUtensorMap& ta, const CUtenso
   const int n_work = tiles_m * tiles_n * splits;
   int grid = sm_count() * Cfg::CTAS_PER_SM;
   if (n_work < grid) grid = n_work;
-  gemm_bf16_kernel<64, A_MN, B_MN, CONV><<<grid, GM_THREADS, Cfg::SMEM, st>>>(ta, tb, M, N, K, tiles_m, tiles_n, splits, kb_per_split, ep, cg);
+  launch_pdl(gemm_bf16_kernel<64, A_MN, B_MN, CONV>, dim3(grid), dim3(GM_THREADS), Cfg::SMEM, st, ta, tb, M, N, K, tiles_m, tiles_n, splits, kb_per_split, ep, cg);
   B2_LAUNCH_CHECK("gemm_bf16_kernel (conv)");
   return 0;
 }

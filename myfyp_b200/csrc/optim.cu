@@ -34,17 +34,20 @@ __device__ __forceinline__ float4 effective_grad(const float4 g, const float4 p,
 // state = {step, 1-beta1^step, 1-beta2^step}: the step counter lives on the device so that a captured CUDA graph of a
 // whole local epoch replays with the right bias corrections (a host-side step would be frozen into the graph).
 __global__ void adam_prepare_kernel(float* __restrict__ state, float b1, float b2) {
+  grid_dep_sync();
   const float step = state[0] + 1.f;
   state[0] = step;
   state[1] = 1.f - powf(b1, step);
   state[2] = 1.f - powf(b2, step);
 }
 
-__global__ void adam_advance_kernel(float* __restrict__ state, float n) { state[0] += n; }
+__global__ void adam_advance_kernel(float* __restrict__ state, float n) {
+  grid_dep_sync(); state[0] += n; }
 
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4, float lr,
                                                    float b1, float b2, float eps, float inv_bc1, float inv_sqrt_bc2, const float* __restrict__ state, float step_offset,
                                                    __nv_bfloat16* __restrict__ p16, FusedTerms t, int zero_grad) {
+  grid_dep_sync();
   if (state != nullptr) {
     if (step_offset > 0.f) {  // step = (steps finished before this graph replay, on the device) + (index inside the graph, baked)
       const float step = state[0] + step_offset;
@@ -78,6 +81,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ p, float
 }
 
 __global__ void __launch_bounds__(256) cast_slab_kernel(const float4* __restrict__ p, __nv_bfloat16* __restrict__ p16, int64_t n4) {
+  grid_dep_sync();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     const float4 pv = p[i];
@@ -91,6 +95,7 @@ __global__ void __launch_bounds__(256) cast_slab_kernel(const float4* __restrict
 
 __global__ void __launch_bounds__(256) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ buf, int64_t n4, float lr, float momentum,
                                                   FusedTerms t, int zero_grad) {
+  grid_dep_sync();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pv = p[i];
@@ -122,13 +127,13 @@ using namespace b2;
 extern "C" {
 
 int b2_adam_prepare(float* state, float beta1, float beta2, void* stream) {
-  adam_prepare_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, beta1, beta2);
+  launch_pdl(adam_prepare_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), state, beta1, beta2);
   B2_LAUNCH_CHECK("adam_prepare_kernel");
   return 0;
 }
 
 int b2_adam_advance(float* state, float n_steps, void* stream) {
-  adam_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, n_steps);
+  launch_pdl(adam_advance_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), state, n_steps);
   B2_LAUNCH_CHECK("adam_advance_kernel");
   return 0;
 }
@@ -139,7 +144,7 @@ int b2_cast_slab(const float* p, void* p_bf16, int64_t n, void* stream) {
     set_error("cast_slab: n %% 4 == 0 and aligned slabs required");
     return 1;
   }
-  cast_slab_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(p), static_cast<__nv_bfloat16*>(p_bf16), n / 4);
+  launch_pdl(cast_slab_kernel, dim3(stream_grid(n / 4, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(p), static_cast<__nv_bfloat16*>(p_bf16), n / 4);
   B2_LAUNCH_CHECK("cast_slab_kernel");
   return 0;
 }
@@ -151,7 +156,7 @@ int b2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, fl
   if (check_slab(p, g, m, v, n) || check_slab(p, p, prox_ref, cv_global, n) || check_slab(p, p, cv_local, nullptr, n)) return 1;
   FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
                reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
-  adam_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
+  launch_pdl(adam_kernel, dim3(stream_grid(n / 4, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
                                                                                       reinterpret_cast<float4*>(v), n / 4, lr, beta1, beta2, eps, 1.f / bias_corr1,
                                                                                       rsqrtf(bias_corr2), dev_state, step_offset, static_cast<__nv_bfloat16*>(p_bf16), t,
                                                                                       zero_grad);
@@ -165,7 +170,7 @@ int b2_sgd_step(float* p, float* g, float* buf, int64_t n, float lr, float momen
   if (check_slab(p, g, buf, prox_ref, n) || check_slab(p, p, cv_global, cv_local, n)) return 1;
   FusedTerms t{reinterpret_cast<const float4*>(prox_ref), (cv_global && cv_local) ? reinterpret_cast<const float4*>(cv_global) : nullptr,
                reinterpret_cast<const float4*>(cv_local), prox_mu, cv_scale, weight_decay};
-  sgd_kernel<<<stream_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(buf),
+  launch_pdl(sgd_kernel, dim3(stream_grid(n / 4, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(buf),
                                                                                      n / 4, lr, momentum, t, zero_grad);
   B2_LAUNCH_CHECK("sgd_kernel");
   return 0;

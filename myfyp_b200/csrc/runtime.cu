@@ -1,5 +1,6 @@
 // Library runtime: error string, device queries, peer access, IPC arenas (the native side of the fabric).
 #include <cstdarg>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/myfyp_b200.h"
@@ -33,9 +34,20 @@ int sm_count() {
   }
   return cache[dev];
 }
+static int g_pdl = -1;
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("B2_PDL");
+    g_pdl = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  return g_pdl == 1;
+}
 }  // namespace b2
 
 extern "C" {
+
+/* 1 / 0: launch the training-step kernels with / without programmatic dependent launch (default: off; B2_PDL=1) */
+void b2_set_pdl(int on) { b2::g_pdl = on ? 1 : 0; }
 
 const char* b2_last_error(void) { return b2::g_err; }
 

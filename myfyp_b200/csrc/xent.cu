@@ -13,6 +13,7 @@ namespace b2 {
 
 __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_out,
                                                    float* __restrict__ dlogits, float* __restrict__ correct, int B, int C, float scale) {
+  grid_dep_sync();
   __shared__ float s_loss[8], s_corr[8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float wl = 0.f, wc = 0.f;
@@ -62,6 +63,7 @@ __global__ void __launch_bounds__(256) xent_kernel(const float* __restrict__ log
 // cast + column-sum (4 launches) by one.  B <= a few thousand rows (a batch).
 __global__ void __launch_bounds__(256) xent_train_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_out,
                                                          __nv_bfloat16* __restrict__ dl16, int ld16, float* __restrict__ bias_grad, int B, int C, float scale) {
+  grid_dep_sync();
   extern __shared__ float s_mem[];  // C column sums + 8 warp losses
   float* s_db = s_mem;
   float* s_loss = s_mem + C;
@@ -101,6 +103,7 @@ __global__ void __launch_bounds__(256) xent_train_kernel(const float* __restrict
 // confusion[label * C + argmax] += 1 : the sufficient statistic for accuracy, per-class precision / recall / F1
 // (the fork author's extended MLP logs test_f1 / test_precision / test_recall, mlp_pytorch.txt)
 __global__ void __launch_bounds__(256) confusion_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ conf, int B, int C) {
+  grid_dep_sync();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int row = blockIdx.x * 8 + warp; row < B; row += gridDim.x * 8) {
     const float* x = logits + (int64_t)row * C;
@@ -129,7 +132,7 @@ extern "C" int b2_xent_train(const float* logits, const int64_t* labels, float* 
     b2::set_error("xent_train: C=%d too wide for the single-block variant", C);
     return 1;
   }
-  b2::xent_train_kernel<<<1, 256, (C + 8) * sizeof(float), static_cast<cudaStream_t>(stream)>>>(logits, labels, loss_out, static_cast<__nv_bfloat16*>(dlogits_bf16), ld16, bias_grad,
+  b2::launch_pdl(b2::xent_train_kernel, dim3(1), dim3(256), (C + 8) * sizeof(float), static_cast<cudaStream_t>(stream), logits, labels, loss_out, static_cast<__nv_bfloat16*>(dlogits_bf16), ld16, bias_grad,
                                                                                                 B, C, scale);
   B2_LAUNCH_CHECK("xent_train_kernel");
   return 0;
@@ -140,7 +143,7 @@ extern "C" int b2_confusion(const float* logits, const int64_t* labels, float* c
   int grid = (B + 7) / 8;
   const int cap = b2::sm_count() * 8;
   if (grid > cap) grid = cap;
-  b2::confusion_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, labels, conf, B, C);
+  b2::launch_pdl(b2::confusion_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), logits, labels, conf, B, C);
   B2_LAUNCH_CHECK("confusion_kernel");
   return 0;
 }
@@ -150,7 +153,7 @@ extern "C" int b2_xent_fwd_bwd(const float* logits, const int64_t* labels, float
   int grid = (B + 7) / 8;
   const int cap = b2::sm_count() * 8;
   if (grid > cap) grid = cap;
-  b2::xent_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, labels, loss_out, dlogits, correct, B, C, scale);
+  b2::launch_pdl(b2::xent_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), logits, labels, loss_out, dlogits, correct, B, C, scale);
   B2_LAUNCH_CHECK("xent_kernel");
   return 0;
 }

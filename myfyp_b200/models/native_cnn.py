@@ -2,7 +2,8 @@
 
 Attached to a CUDA ``TorchP2PFLModel`` wrapping :class:`~myfyp_b200.models.cnn.CNN` (conv3x3-ReLU-maxpool2 blocks followed
 by linear layers).  Parameters stay the fp32 slab in PyTorch's own layouts - that is what is aggregated and exchanged -
-and are only *read* here (bf16 working copies per step, no permutation: the patch index order is (c, kh, kw)).
+and are only *read* here: one launch per step repacks every conv / fc1 weight into bf16 ``[cout, (kh, kw, cin)]``, the patch
+order in which a tap's channels are contiguous (16-byte vector gathers), and the weight-gradient GEMMs scatter back.
 
 Activations are NHWC bf16, i.e. the ``[pixels, channels]`` matrices the GEMM reads and writes.  Per conv block:
 
@@ -11,13 +12,12 @@ Activations are NHWC bf16, i.e. the ``[pixels, channels]`` matrices the GEMM rea
               dW  = dZ^T col                  (MN-major operands, split-K over pixels, fp32 atomics into the gradient slab)
               dcol = dZ W  (W MN-major)
 
-The first linear layer after the feature map is a convolution whose kernel covers the whole map, which reproduces
-``nn.Flatten``'s NCHW feature order on NHWC data.  Reference path: the same ``nn.Module`` through torch autograd / cuDNN.
+The first linear layer after the feature map is a convolution whose kernel covers the whole map; the same weight repack
+maps ``nn.Flatten``'s NCHW feature order onto the NHWC data.  Reference path: the same ``nn.Module`` through torch autograd / cuDNN.
 """
 
 from __future__ import annotations
 
-import ctypes
 from typing import Dict, List
 
 import torch
@@ -81,17 +81,23 @@ class NativeCNN:
 
         self.params = {s.name: views(s.name, s.cout, s.kdim) for s in self.convs + [self.fc1]}
         self.params[self.fc2_name] = views(self.fc2_name, self.fc2_out, self.fc2_in)
-        # bf16 mirror of the whole slab, kept current by the fused optimizer; weights with a row length that is a multiple of
-        # 8 are TMA operands in place, the others (the 27-wide first conv) get a padded private copy
+        # bf16 mirror of the whole slab, kept current by the fused optimizer (fc2 reads it in place); conv / fc1 weights are
+        # repacked per step into [cout, (kh, kw, cin)] rows (pitch padded to 8 elements for TMA)
         self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
-        self.w16, self._padded = {}, []
-        for n, (w, _, _, _) in self.params.items():
-            ew = lay.entries[n + ".weight"]
-            if w.shape[1] % 8 == 0:
-                self.w16[n] = self.p16[ew.offset : ew.offset + ew.numel].view(w.shape)
-            else:
-                self.w16[n] = torch.zeros(w.shape[0], _pad8(w.shape[1]), dtype=torch.bfloat16, device=dev)
-                self._padded.append(n)
+        specs = self.convs + [self.fc1]
+        self.p16r = torch.zeros(sum(sp.cout * _pad8(sp.kdim) for sp in specs), dtype=torch.bfloat16, device=dev)
+        self.w16, table, roff = {}, [], 0
+        for sp in specs:
+            ew, ld = lay.entries[sp.name + ".weight"], _pad8(sp.kdim)
+            self.w16[sp.name] = self.p16r[roff : roff + sp.cout * ld].view(sp.cout, ld)
+            table += [ew.offset, roff, sp.cout, sp.cin, sp.k * sp.k, ld]
+            roff += sp.cout * ld
+        self._repack_table = torch.tensor(table, dtype=torch.int64, device=dev)
+        self._repack_max = max(sp.cout * sp.kdim for sp in specs)
+        e2 = lay.entries[self.fc2_name + ".weight"]
+        self.w16[self.fc2_name] = self.p16[e2.offset : e2.offset + e2.numel].view(self.fc2_out, self.fc2_in)
+        if self.fc2_in % 8:
+            raise ValueError("NativeCNN: the hidden width must be a multiple of 8")
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers
@@ -120,9 +126,7 @@ class NativeCNN:
         self._refresh_padded()
 
     def _refresh_padded(self) -> None:
-        for n in self._padded:
-            w = self.params[n][0]
-            ops.cast_transpose(w, w.shape[0], w.shape[1], dst=self.w16[n])
+        ops.repack_conv_weights(self.model.slab, self.p16r, self._repack_table, len(self.convs) + 1, self._repack_max)
 
     def _next_geom(self, li: int):
         """Geometry of the layer that consumes conv block ``li``'s pooled output (the next conv, or fc1 as a full-map conv)."""
@@ -162,7 +166,7 @@ class NativeCNN:
         f = self.fc1
         _, _, gw1, gb1 = self.params[f.name]
         ops.gemm_bf16(buf["dz2"], self.w16[self.fc2_name], B, self.fc2_in, self.fc2_out, out_bf16=buf["dh1"], mask=buf["h1"], colsum=gb1, b_mn=True)
-        ops.gemm_bf16(buf["dh1"], buf["col_fc1"], f.cout, f.kdim, B, out_f32=gw1, a_mn=True, b_mn=True)
+        ops.gemm_bf16(buf["dh1"], buf["col_fc1"], f.cout, f.kdim, B, out_f32=gw1, a_mn=True, b_mn=True, perm=(f.cin, f.k * f.k))
         ops.gemm_bf16(buf["dh1"], self.w16[f.name], B, f.kdim, f.cout, out_bf16=buf["dcol_fc1"], b_mn=True)
         # ---- conv blocks, last to first
         for li in range(len(self.convs) - 1, -1, -1):
@@ -173,7 +177,7 @@ class NativeCNN:
             next_dcol = buf["conv"][li + 1]["dcol"] if li + 1 < len(self.convs) else buf["dcol_fc1"]
             # col2im of the next layer's dcol + unpool + ReLU mask + bias gradient: one launch
             ops.unpool_col2im(next_dcol, cb["idx"], cb["y"], cb["dz"], gb, B, h, w, c, kh, kw, st, pd)
-            ops.gemm_bf16(cb["dz"], cb["col"], s.cout, s.kdim, m, out_f32=gw, a_mn=True, b_mn=True, split_k=max(1, min(64, m // 1024)))
+            ops.gemm_bf16(cb["dz"], cb["col"], s.cout, s.kdim, m, out_f32=gw, a_mn=True, b_mn=True, split_k=max(1, min(64, m // 1024)), perm=(s.cin, s.k * s.k))
             if li > 0:
                 ops.gemm_bf16(cb["dz"], self.w16[s.name], m, s.kdim, s.cout, out_bf16=cb["dcol"], b_mn=True)
 

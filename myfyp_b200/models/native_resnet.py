@@ -73,31 +73,23 @@ class NativeResNet:
 
         self.p16 = torch.zeros(lay.total, dtype=torch.bfloat16, device=dev)
         self.par: Dict[str, dict] = {}
-        self._padded: List[str] = []
-        # implicit-GEMM layers read their weights as bf16 [cout, (kh, kw, cin)]: one repack launch per step fills this arena
-        implicit = [L for L in self.layers if L.implicit]
-        self.p16r = torch.zeros(sum(L.cout * L.kdim for L in implicit), dtype=torch.bfloat16, device=dev)
+        # every convolution reads its weights as bf16 [cout, (kh, kw, cin)] (row pitch padded to 8): one repack launch per step
+        self.p16r = torch.zeros(sum(L.cout * _pad8(L.kdim) for L in self.layers), dtype=torch.bfloat16, device=dev)
         table, roff = [], 0
-        self._repack_max = max([L.cout * L.kdim for L in implicit], default=0)
+        self._repack_max = max(L.cout * L.kdim for L in self.layers)
         for L in self.layers:
             e = lay.entries[L.conv + ".weight"]
-            d = {
+            ld = _pad8(L.kdim)
+            self.par[L.conv] = {
                 "w": pv(L.conv + ".weight", (L.cout, L.kdim)), "gw": gv(L.conv + ".weight", (L.cout, L.kdim)),
                 "gamma": pv(L.bn + ".weight"), "beta": pv(L.bn + ".bias"), "dgamma": gv(L.bn + ".weight"), "dbeta": gv(L.bn + ".bias"),
                 "rm": pv(L.bn + ".running_mean"), "rv": pv(L.bn + ".running_var"), "nb": pv(L.bn + ".num_batches_tracked"),
+                "w16": self.p16r[roff : roff + L.cout * ld].view(L.cout, ld),
             }
-            if L.implicit:
-                d["w16"] = self.p16r[roff : roff + e.numel].view(L.cout, L.kdim)
-                table += [e.offset, roff, L.cout, L.cin, L.k * L.k]
-                roff += e.numel
-            elif L.kdim % 8 == 0:
-                d["w16"] = self.p16[e.offset : e.offset + e.numel].view(L.cout, L.kdim)
-            else:
-                d["w16"] = torch.zeros(L.cout, _pad8(L.kdim), dtype=torch.bfloat16, device=dev)
-                self._padded.append(L.conv)
-            self.par[L.conv] = d
+            table += [e.offset, roff, L.cout, L.cin, L.k * L.k, ld]
+            roff += L.cout * ld
         self._repack_table = torch.tensor(table, dtype=torch.int64, device=dev) if table else None
-        self._n_repack = len(table) // 5
+        self._n_repack = len(table) // 6
         efc = lay.entries["fc.weight"]
         self.fc = {"w": pv("fc.weight", (self.fc_out, self.fc_in)), "b": pv("fc.bias"), "gw": gv("fc.weight", (self.fc_out, self.fc_in)), "gb": gv("fc.bias"),
                    "w16": self.p16[efc.offset : efc.offset + efc.numel].view(self.fc_out, self.fc_in)}
@@ -135,11 +127,7 @@ class NativeResNet:
         self._refresh_padded()
 
     def _refresh_padded(self) -> None:
-        for n in self._padded:
-            w = self.par[n]["w"]
-            ops.cast_transpose(w, w.shape[0], w.shape[1], dst=self.par[n]["w16"])
-        if self._n_repack:
-            ops.repack_conv_weights(self.model.slab, self.p16r, self._repack_table, self._n_repack, self._repack_max)
+        ops.repack_conv_weights(self.model.slab, self.p16r, self._repack_table, self._n_repack, self._repack_max)
 
     # ------------------------------------------------------------------ forward
     def _convbn(self, L: _ConvBN, x, B: int, buf: dict, train: bool, residual=None, first: bool = False):
@@ -186,7 +174,7 @@ class NativeResNet:
             if dx is not None:
                 ops.conv_gemm(ops.CONV_DGRAD, lb["dz"], B, L.h, L.w, L.cin, L.cout, L.k, weights=p["w16"], out_bf16=dx, add=add)
             return lb["g"]
-        ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)))
+        ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)), perm=(L.cin, L.k * L.k))
         if dx is not None:
             dcol = buf["dcol"][: M * _pad8(L.kdim)].view(M, _pad8(L.kdim))
             ops.gemm_bf16(lb["dz"], p["w16"], M, L.kdim, L.cout, out_bf16=dcol, b_mn=True)

@@ -401,7 +401,7 @@ class _GemmArgs(ctypes.Structure):
         ("A", ctypes.c_void_p), ("B", ctypes.c_void_p), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int), ("lda", ctypes.c_int), ("ldb", ctypes.c_int),
         ("out_f32", ctypes.c_void_p), ("out_bf16", ctypes.c_void_p), ("out_bf16_t", ctypes.c_void_p), ("ldo", ctypes.c_int), ("ldo16", ctypes.c_int), ("ldt", ctypes.c_int),
         ("bias", ctypes.c_void_p), ("mask", ctypes.c_void_p), ("ldm", ctypes.c_int), ("colsum", ctypes.c_void_p), ("relu", ctypes.c_int), ("accumulate", ctypes.c_int),
-        ("a_mn", ctypes.c_int), ("b_mn", ctypes.c_int), ("split_k", ctypes.c_int), ("colsumsq", ctypes.c_void_p),
+        ("a_mn", ctypes.c_int), ("b_mn", ctypes.c_int), ("split_k", ctypes.c_int), ("colsumsq", ctypes.c_void_p), ("perm_cin", ctypes.c_int), ("perm_taps", ctypes.c_int),
     ]
 
 
@@ -409,11 +409,15 @@ def gemm_bf16(
     a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, out_f32: Optional[torch.Tensor] = None, out_bf16: Optional[torch.Tensor] = None,
     out_bf16_t: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
     relu: bool = False, accumulate: bool = False, a_mn: bool = False, b_mn: bool = False, split_k: int = 1, colsumsq: Optional[torch.Tensor] = None,
+    perm: Optional[tuple] = None,
 ) -> None:
     """``D[m,n] = epilogue(A[m,k] @ B[n,k]^T)`` on tcgen05 tensor cores (bf16 in, fp32 accumulate); see csrc/gemm.cu.
 
     ``a_mn`` / ``b_mn``: the operand is stored transposed (``a`` is ``[k, m]``, ``b`` is ``[k, n]``) and consumed as an
     MN-major UMMA operand - the backward GEMMs read the forward pass's buffers without transposed copies.
+
+    ``perm=(cin, taps)``: ``out_f32`` column ``tap*cin + c`` is stored at ``c*taps + tap`` (weight gradient of a convolution whose
+    patch matrix is in (tap, c) order, written in PyTorch's ``[cout, cin, kh, kw]`` layout).
 
     ``a``/``b`` are 2-D bf16 tensors whose row pitch (``stride(0)``) is the leading dimension; the logical sizes
     ``m, n, k`` may be smaller than the allocations (TMA zero-fills the tails).
@@ -428,7 +432,7 @@ def gemm_bf16(
         a.data_ptr(), b.data_ptr(), m, n, k, ld(a), ld(b), 0 if out_f32 is None else out_f32.data_ptr(), 0 if out_bf16 is None else out_bf16.data_ptr(),
         0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld(out_f32), ld(out_bf16), ld(out_bf16_t), 0 if bias is None else bias.data_ptr(),
         0 if mask is None else mask.data_ptr(), ld(mask), 0 if colsum is None else colsum.data_ptr(), int(relu), int(accumulate),
-        int(a_mn), int(b_mn), int(split_k), 0 if colsumsq is None else colsumsq.data_ptr(),
+        int(a_mn), int(b_mn), int(split_k), 0 if colsumsq is None else colsumsq.data_ptr(), 0 if perm is None else int(perm[0]), 0 if perm is None else int(perm[1]),
     )
     lib = native.load()
     with native.device_guard(a.device):
@@ -514,7 +518,7 @@ def _conv_call(name: str, dev, *args) -> None:
 
 
 def im2col(x: torch.Tensor, col: torch.Tensor, B: int, H: int, W: int, C: int, KH: int, KW: int, stride: int, pad: int, nchw_f32: bool = False) -> None:
-    """Patch gather ``col[(b,oh,ow), c*KH*KW + kh*KW + kw]`` (bf16); ``x`` is NHWC bf16, or NCHW fp32 for the input layer."""
+    """Patch gather ``col[(b,oh,ow), (kh*KW + kw)*C + c]`` (bf16); ``x`` is NHWC bf16, or NCHW fp32 for the input layer."""
     _conv_call("b2_im2col", x.device, native.ptr(x), int(nchw_f32), native.ptr(col), int(col.stride(0)), B, H, W, C, KH, KW, stride, pad)
 
 

@@ -456,7 +456,7 @@ def test_gemm_tcgen05_split_k(dev, splits):
     torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-2)
 
 
-@pytest.mark.parametrize("B,C,H,k,stride,pad,first", [(4, 3, 32, 3, 1, 1, True), (3, 32, 16, 3, 1, 1, False), (2, 64, 8, 3, 2, 1, False), (5, 128, 4, 4, 1, 0, False), (2, 16, 8, 1, 2, 0, False)])
+@pytest.mark.parametrize("B,C,H,k,stride,pad,first", [(4, 3, 32, 3, 1, 1, True), (3, 32, 16, 3, 1, 1, False), (2, 64, 8, 3, 2, 1, False), (5, 128, 4, 4, 1, 0, False), (2, 16, 8, 1, 2, 0, False), (2, 12, 8, 3, 1, 1, False)])
 def test_im2col_col2im_match_unfold_fold(dev, B, C, H, k, stride, pad, first):
     from myfyp_b200 import ops
 
@@ -469,14 +469,16 @@ def test_im2col_col2im_match_unfold_fold(dev, B, C, H, k, stride, pad, first):
     col = torch.zeros(B * oh * oh, ld, dtype=torch.bfloat16, device=dev)
     src = x.contiguous() if first else xq.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
     ops.im2col(src, col, B, H, H, C, k, k, stride, pad, nchw_f32=first)
-    ref = F.unfold(xq, k, padding=pad, stride=stride).transpose(1, 2).reshape(B * oh * oh, kd)
+    # unfold orders a patch (c, kh, kw); the kernels use (kh, kw, c) so that a tap's channels are contiguous
+    ref = F.unfold(xq, k, padding=pad, stride=stride).transpose(1, 2).reshape(B * oh * oh, C, k * k).transpose(1, 2).reshape(B * oh * oh, kd)
     assert torch.equal(col[:, :kd].float(), ref)
     # col2im == fold (sum of overlapping patches), NHWC out
     dcol = torch.zeros_like(col)
     dcol[:, :kd] = torch.randn(B * oh * oh, kd, device=dev).to(torch.bfloat16)
     dx = torch.empty(B, H, H, C, dtype=torch.bfloat16, device=dev)
     ops.col2im(dcol, dx, B, H, H, C, k, k, stride, pad)
-    folded = F.fold(dcol[:, :kd].float().reshape(B, oh * oh, kd).transpose(1, 2), (H, H), k, padding=pad, stride=stride)
+    dcol_ckk = dcol[:, :kd].float().reshape(B, oh * oh, k * k, C).transpose(2, 3).reshape(B, oh * oh, kd)
+    folded = F.fold(dcol_ckk.transpose(1, 2), (H, H), k, padding=pad, stride=stride)
     torch.testing.assert_close(dx.float().permute(0, 3, 1, 2), folded, rtol=2e-2, atol=2e-2)
 
 
@@ -727,7 +729,7 @@ def test_implicit_gemm_conv_matches_conv2d(dev, B, H, cin, cout):
     assert ops.conv_gemm_supported(H, H, cin, cout, 3, 1, 1)
     # weights: slab-style fp32 [cout, cin, 9] -> bf16 [cout, 9, cin]
     w16 = torch.zeros(cout, 9 * cin, dtype=torch.bfloat16, device=dev)
-    table = torch.tensor([0, 0, cout, cin, 9], dtype=torch.int64, device=dev)
+    table = torch.tensor([0, 0, cout, cin, 9, 9 * cin], dtype=torch.int64, device=dev)
     ops.repack_conv_weights(w.reshape(-1), w16.reshape(-1), table, 1, w.numel())
     torch.testing.assert_close(w16.float().view(cout, 9, cin), w.bfloat16().float().view(cout, cin, 9).transpose(1, 2))
     wr = w.bfloat16().float().requires_grad_(True)
