@@ -24,6 +24,7 @@ import torch
 from torch import nn
 
 from myfyp_b200 import ops
+from myfyp_b200.models._branch import WgradBranch
 
 
 def _pad8(n: int) -> int:
@@ -98,6 +99,7 @@ class NativeCNN:
         self.w16[self.fc2_name] = self.p16[e2.offset : e2.offset + e2.numel].view(self.fc2_out, self.fc2_in)
         if self.fc2_in % 8:
             raise ValueError("NativeCNN: the hidden width must be a multiple of 8")
+        self.branch = WgradBranch(dev)  # weight-gradient GEMMs run beside the dgrad chain
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers
@@ -161,12 +163,12 @@ class NativeCNN:
         # ---- loss + dlogits (bf16) + fc2 bias gradient: one launch
         _, _, gw2, gb2 = self.params[self.fc2_name]
         ops.xent_train(buf["logits"], y, loss_out, buf["dz2"], gb2, B, self.fc2_out)
-        ops.gemm_bf16(buf["dz2"], buf["h1"], self.fc2_out, self.fc2_in, B, out_f32=gw2, a_mn=True, b_mn=True)
+        self.branch.run(lambda: ops.gemm_bf16(buf["dz2"], buf["h1"], self.fc2_out, self.fc2_in, B, out_f32=gw2, a_mn=True, b_mn=True))
         # ---- fc1 (dgrad of fc2 with the ReLU mask of h1; its column sums are fc1's bias gradient)
         f = self.fc1
         _, _, gw1, gb1 = self.params[f.name]
         ops.gemm_bf16(buf["dz2"], self.w16[self.fc2_name], B, self.fc2_in, self.fc2_out, out_bf16=buf["dh1"], mask=buf["h1"], colsum=gb1, b_mn=True)
-        ops.gemm_bf16(buf["dh1"], buf["col_fc1"], f.cout, f.kdim, B, out_f32=gw1, a_mn=True, b_mn=True, perm=(f.cin, f.k * f.k))
+        self.branch.run(lambda: ops.gemm_bf16(buf["dh1"], buf["col_fc1"], f.cout, f.kdim, B, out_f32=gw1, a_mn=True, b_mn=True, perm=(f.cin, f.k * f.k)))
         ops.gemm_bf16(buf["dh1"], self.w16[f.name], B, f.kdim, f.cout, out_bf16=buf["dcol_fc1"], b_mn=True)
         # ---- conv blocks, last to first
         for li in range(len(self.convs) - 1, -1, -1):
@@ -177,9 +179,10 @@ class NativeCNN:
             next_dcol = buf["conv"][li + 1]["dcol"] if li + 1 < len(self.convs) else buf["dcol_fc1"]
             # col2im of the next layer's dcol + unpool + ReLU mask + bias gradient: one launch
             ops.unpool_col2im(next_dcol, cb["idx"], cb["y"], cb["dz"], gb, B, h, w, c, kh, kw, st, pd)
-            ops.gemm_bf16(cb["dz"], cb["col"], s.cout, s.kdim, m, out_f32=gw, a_mn=True, b_mn=True, split_k=max(1, min(64, m // 1024)), perm=(s.cin, s.k * s.k))
+            self.branch.run(lambda s=s, cb=cb, m=m, gw=gw: ops.gemm_bf16(cb["dz"], cb["col"], s.cout, s.kdim, m, out_f32=gw, a_mn=True, b_mn=True, split_k=max(1, min(64, m // 1024)), perm=(s.cin, s.k * s.k)))
             if li > 0:
                 ops.gemm_bf16(cb["dz"], self.w16[s.name], m, s.kdim, s.cout, out_bf16=cb["dcol"], b_mn=True)
+        self.branch.join()
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:

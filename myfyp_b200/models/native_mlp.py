@@ -24,6 +24,7 @@ from typing import Dict, List
 import torch
 
 from myfyp_b200 import ops
+from myfyp_b200.models._branch import WgradBranch
 
 
 def _pad8(n: int) -> int:
@@ -56,6 +57,7 @@ class NativeMLP:
             else:
                 self.w16.append(torch.zeros(self.sizes[i + 1], _pad8(self.sizes[i]), dtype=torch.bfloat16, device=dev))
                 self._padded.append(i)
+        self.branch = WgradBranch(model.device)
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers per batch capacity
@@ -106,11 +108,13 @@ class NativeMLP:
         # loss, dZ_L = dlogits/B as bf16, bias gradient of the last layer: one launch
         ops.xent_train(buf["logits"], y, loss_out, buf["dz"][L - 1], self.gb[L - 1], bsz, s[-1])
         for i in range(L - 1, -1, -1):
-            # wgrad: dW_i[out,in] = dZ_i^T H_i      - dZ_i [B,out] and H_i [B,in] consumed as MN-major operands (K = batch)
-            ops.gemm_bf16(buf["dz"][i], buf["h"][i], s[i + 1], s[i], bsz, out_f32=self.gw[i], a_mn=True, b_mn=True)
+            # wgrad: dW_i[out,in] = dZ_i^T H_i      - dZ_i [B,out] and H_i [B,in] consumed as MN-major operands (K = batch);
+            # off the critical path (side stream / parallel graph branch): only the optimizer needs it
+            self.branch.run(lambda i=i: ops.gemm_bf16(buf["dz"][i], buf["h"][i], s[i + 1], s[i], bsz, out_f32=self.gw[i], a_mn=True, b_mn=True))
             if i > 0:
                 # dgrad: dZ_{i-1}[B,in] = (dZ_i[B,out] W_i[out,in]) * (H_i > 0) - W_i consumed MN-major; column sums -> db_{i-1}
                 ops.gemm_bf16(buf["dz"][i], self.w16[i], bsz, s[i], s[i + 1], out_bf16=buf["dz"][i - 1], mask=buf["h"][i], colsum=self.gb[i - 1], b_mn=True)
+        self.branch.join()
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:

@@ -21,6 +21,7 @@ from typing import Dict, List, Optional
 import torch
 
 from myfyp_b200 import ops
+from myfyp_b200.models._branch import WgradBranch
 
 
 def _pad8(n: int) -> int:
@@ -93,6 +94,7 @@ class NativeResNet:
         efc = lay.entries["fc.weight"]
         self.fc = {"w": pv("fc.weight", (self.fc_out, self.fc_in)), "b": pv("fc.bias"), "gw": gv("fc.weight", (self.fc_out, self.fc_in)), "gb": gv("fc.bias"),
                    "w16": self.p16[efc.offset : efc.offset + efc.numel].view(self.fc_out, self.fc_in)}
+        self.branch = WgradBranch(dev)  # weight-gradient GEMMs run beside the dgrad chain
         self._bufs: Dict[int, dict] = {}
 
     # ------------------------------------------------------------------ buffers
@@ -170,11 +172,11 @@ class NativeResNet:
         ops.bn_backward(dy, lb["y"], lb["z"], lb["g"], lb["dz"], lb["red"], lb["stats"], p["gamma"], p["dgamma"], p["dbeta"], M, L.cout, relu, red_is_zero=True)
         if L.implicit:
             tiles = ((L.cout + 127) // 128) * (L.kdim // 64)
-            ops.conv_gemm(ops.CONV_WGRAD, lb["x"], B, L.h, L.w, L.cin, L.cout, L.k, dz=lb["dz"], out_f32=p["gw"], split_k=max(1, min(296 // tiles, M // 128)))
+            self.branch.run(lambda: ops.conv_gemm(ops.CONV_WGRAD, lb["x"], B, L.h, L.w, L.cin, L.cout, L.k, dz=lb["dz"], out_f32=p["gw"], split_k=max(1, min(296 // tiles, M // 128))))
             if dx is not None:
                 ops.conv_gemm(ops.CONV_DGRAD, lb["dz"], B, L.h, L.w, L.cin, L.cout, L.k, weights=p["w16"], out_bf16=dx, add=add)
             return lb["g"]
-        ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)), perm=(L.cin, L.k * L.k))
+        self.branch.run(lambda: ops.gemm_bf16(lb["dz"], lb["col"], L.cout, L.kdim, M, out_f32=p["gw"], a_mn=True, b_mn=True, split_k=max(1, min(32, M // 2048)), perm=(L.cin, L.k * L.k)))
         if dx is not None:
             dcol = buf["dcol"][: M * _pad8(L.kdim)].view(M, _pad8(L.kdim))
             ops.gemm_bf16(lb["dz"], p["w16"], M, L.kdim, L.cout, out_bf16=dcol, b_mn=True)
@@ -188,7 +190,7 @@ class NativeResNet:
         buf = self._buffers(B)
         self._forward(x, buf, train=True)
         ops.xent_train(buf["logits"], y, loss_out, buf["dzfc"], self.fc["gb"], B, self.fc_out)
-        ops.gemm_bf16(buf["dzfc"], buf["pool"], self.fc_out, self.fc_in, B, out_f32=self.fc["gw"], a_mn=True, b_mn=True)
+        self.branch.run(lambda: ops.gemm_bf16(buf["dzfc"], buf["pool"], self.fc_out, self.fc_in, B, out_f32=self.fc["gw"], a_mn=True, b_mn=True))
         ops.gemm_bf16(buf["dzfc"], self.fc["w16"], B, self.fc_in, self.fc_out, out_bf16=buf["dpool"], b_mn=True)
         last = self.blocks[-1]["c2"]
         ops.avgpool_bwd(buf["dpool"], buf["L"][last.conv]["dy"], B, self.final_hw, self.final_c)
@@ -207,6 +209,7 @@ class NativeResNet:
             # conv1 + bn1 + relu ; its input gradient plus the shortcut's gradient = gradient of the block input
             self._bn_conv_backward(c1, buf["L"][c1.conv]["dy"], B, buf, True, dx=d_in, add=add)
         self._bn_conv_backward(self.stem, buf["L"][self.stem.conv]["dy"], B, buf, True)
+        self.branch.join()
 
     @torch.no_grad()
     def eval_step(self, x: torch.Tensor, y: torch.Tensor, acc: torch.Tensor) -> None:
