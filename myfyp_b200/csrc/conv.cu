@@ -92,6 +92,32 @@ __global__ void __launch_bounds__(256) im2col_nchw_kernel(const float* __restric
   }
 }
 
+// input layer with a short patch (KH*KW*C <= 32, row pitch exactly 32 elements, e.g. 3x3x3 -> 27): one thread builds the whole
+// 64-byte patch row of an output pixel in registers and writes it with four 16-byte stores (neighbouring threads read
+// neighbouring pixels of the same channel plane, so the fp32 loads coalesce too)
+__global__ void __launch_bounds__(256) im2col_nchw_row32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g) {
+  grid_dep_sync();
+  const int64_t total = (int64_t)g.B * g.OH * g.OW;
+  const int KK = g.KH * g.KW;
+  for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < total; m += (int64_t)gridDim.x * blockDim.x) {
+    const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH), b = (int)(m / ((int64_t)g.OW * g.OH));
+    __align__(16) __nv_bfloat16 row[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) row[j] = __float2bfloat16_rn(0.f);
+    const float* img = x + (int64_t)b * g.C * g.H * g.W;
+#pragma unroll 1
+    for (int t = 0; t < KK; ++t) {
+      const int ih = oh * g.stride - g.pad + t / g.KW, iw = ow * g.stride - g.pad + t % g.KW;
+      if (ih < 0 || ih >= g.H || iw < 0 || iw >= g.W) continue;
+      for (int c = 0; c < g.C; ++c) row[t * g.C + c] = __float2bfloat16_rn(__ldg(img + ((int64_t)c * g.H + ih) * g.W + iw));
+    }
+    uint4* dst = reinterpret_cast<uint4*>(col + m * 32);
+    const uint4* src = reinterpret_cast<const uint4*>(row);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dst[j] = src[j];
+  }
+}
+
 // dx[b,h,w,c] = sum over the taps (kh,kw) whose output pixel exists of dcol[(b,oh,ow), (kh*KW + kw) * C + c]  (gather form, no atomics)
 template <int V>
 __global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int ldc,
@@ -576,7 +602,9 @@ int b2_im2col(const void* x, int x_is_nchw_f32, void* col_bf16, int ldc, int B, 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   __nv_bfloat16* col = static_cast<__nv_bfloat16*>(col_bf16);
   const bool vec = (C % 8 == 0) && (ldc % 8 == 0) && aligned16(x) && aligned16(col_bf16);
-  if (x_is_nchw_f32) launch_pdl(im2col_nchw_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, s, static_cast<const float*>(x), col, g, ldc);
+  if (x_is_nchw_f32 && KH * KW * C <= 32 && ldc == 32 && aligned16(col_bf16))
+    launch_pdl(im2col_nchw_row32_kernel, dim3(stream_grid((int64_t)B * g.OH * g.OW, 256)), dim3(256), 0, s, static_cast<const float*>(x), col, g);
+  else if (x_is_nchw_f32) launch_pdl(im2col_nchw_kernel, dim3(stream_grid(total, 256)), dim3(256), 0, s, static_cast<const float*>(x), col, g, ldc);
   else if (vec) launch_pdl(im2col_kernel<8>, dim3(stream_grid(total / 8, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), col, g, ldc);
   else launch_pdl(im2col_kernel<1>, dim3(stream_grid(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), col, g, ldc);
   B2_LAUNCH_CHECK("im2col_kernel");
