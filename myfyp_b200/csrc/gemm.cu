@@ -71,6 +71,7 @@ struct GemmEpilogue {
   int relu, accumulate;
   const __nv_bfloat16* add16;  // optional bf16 [M, ldadd] added to the result (second consumer of an activation: residual branch gradient)
   int ldadd;
+  long long* trace;  // debug (tools/gemm_trace.py): per-phase %globaltimer stamps of CTA 0, nullptr in production
   int perm_cin, perm_taps;  // wgrad of a convolution: column j = tap * cin + c is stored at c * taps + tap (PyTorch's [Cout, Cin, KH, KW])
 };
 
@@ -84,6 +85,14 @@ struct ConvGeom {
   int ncols;      // CONV=1 with B MN-major (dgrad): columns per tap of the weight matrix (= cin); CONV=2: cin
 };
 
+__device__ __forceinline__ void trace_stamp(long long* trace, int slot) {
+  if (trace != nullptr && blockIdx.x == 0) {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    trace[slot] = t;
+  }
+}
+
 __device__ __forceinline__ void conv_pixel_tile(const ConvGeom& cg, int pt, int& n, int& h0) {
   if (cg.hw_tiles > 0) {
     n = pt / cg.hw_tiles;
@@ -91,6 +100,32 @@ __device__ __forceinline__ void conv_pixel_tile(const ConvGeom& cg, int pt, int&
   } else {
     n = pt * cg.tile_n;
     h0 = 0;
+  }
+}
+
+// 32 consecutive bf16 of one row -> fp32 registers: four 16-byte loads when the row segment is complete and 16-byte aligned,
+// else independent scalar loads (all issued before any use); columns >= n_valid read as 0
+__device__ __forceinline__ void load_row32_bf16(const __nv_bfloat16* p, bool vec_ok, int n_valid, float (&out)[32]) {
+  if (vec_ok && (reinterpret_cast<uintptr_t>(p) & 15u) == 0) {
+    uint4 raw[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) raw[j] = *reinterpret_cast<const uint4*>(p + 8 * j);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[j]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 t = __bfloat1622float2(h[i]);
+        out[8 * j + 2 * i] = t.x;
+        out[8 * j + 2 * i + 1] = t.y;
+      }
+    }
+  } else {
+    __nv_bfloat16 raw[32];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) raw[e] = e < n_valid ? p[e] : __float2bfloat16_rn(0.f);
+#pragma unroll
+    for (int e = 0; e < 32; ++e) out[e] = __bfloat162float(raw[e]);
   }
 }
 
@@ -130,6 +165,7 @@ template <int BN, bool A_MN, bool B_MN, int CONV = 0>
 __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N, int K,
                                                                    int tiles_m, int tiles_n, int splits, int kb_per_split, GemmEpilogue ep, ConvGeom cg) {
   using Cfg = GemmCfg<BN>;
+  if (threadIdx.x == 0) trace_stamp(ep.trace, 0);  // kernel entry
   grid_dep_launch();  // the next kernel of the step may become resident and run its own prologue while this one works
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[Cfg::STAGES], empty_bar[Cfg::STAGES], acc_full[GM_ACC_STAGES], acc_empty[GM_ACC_STAGES];
@@ -159,6 +195,7 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = tmem_base_s;
+  if (threadIdx.x == 0) trace_stamp(ep.trace, 1);  // prologue done
   grid_dep_wait();  // barriers, TMEM and tensor maps are ready: now wait for the producer of our operands to complete
 
   auto work_coords = [&](int w, int& m0, int& n0, int& kb0, int& nk) {
@@ -237,6 +274,7 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
           const int s = it % Cfg::STAGES;
           tc::mbar_wait(&full_bar[s], (it / Cfg::STAGES) & 1u);
           tc::fence_after_sync();
+          if (it == 0) trace_stamp(ep.trace, 2);  // first operand tile landed
           const uint32_t a_addr = tc::smem_u32(tiles + s * Cfg::STAGE_BYTES);
           const uint32_t b_addr = a_addr + GM_A_BYTES;
 #pragma unroll
@@ -249,6 +287,7 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
           tc::mma_commit(&empty_bar[s]);
         }
         tc::mma_commit(&acc_full[as]);
+        if (acc_it == 0) trace_stamp(ep.trace, 3);  // all MMAs of the first tile issued
       }
     }
   } else {
@@ -263,6 +302,7 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
       const bool row_ok = row < M;
       tc::mbar_wait(&acc_full[as], (acc_it / GM_ACC_STAGES) & 1u);
       tc::fence_after_sync();
+      if (acc_it == 0 && q == 0 && lane == 0) trace_stamp(ep.trace, 4);  // first accumulator complete
 #pragma unroll 1
       for (int cb = 0; cb < BN / 32; ++cb) {
         const int nb = n0 + cb * 32;
@@ -274,16 +314,42 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
 #pragma unroll
           for (int e = 0; e < 32; ++e) v[e] = 0.f;
         }
+        // Side inputs are fetched as whole 32-column rows into their own registers BEFORE they are consumed (16-byte vector
+        // loads on the common aligned path): per-element predicated loads compile into one serial load->use chain per column.
+        const bool full = nb + 32 <= N;
+        if (ep.bias != nullptr) {
+          float bv[32];
+          if (full && (reinterpret_cast<uintptr_t>(ep.bias + nb) & 15u) == 0) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const int n = nb + e;
-          float x = v[e];
-          if (ep.bias != nullptr && n < N) x += __ldg(ep.bias + n);
-          if (ep.add16 != nullptr && row_ok && n < N) x += __bfloat162float(ep.add16[(int64_t)row * ep.ldadd + n]);
-          if (ep.relu) x = fmaxf(x, 0.f);
-          if (ep.mask != nullptr && row_ok && n < N) x = (__bfloat162float(ep.mask[(int64_t)row * ep.ldm + n]) > 0.f) ? x : 0.f;
-          v[e] = (row_ok && n < N) ? x : 0.f;
+            for (int e = 0; e < 32; e += 4) {
+              const float4 t = __ldg(reinterpret_cast<const float4*>(ep.bias + nb + e));
+              bv[e] = t.x; bv[e + 1] = t.y; bv[e + 2] = t.z; bv[e + 3] = t.w;
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) bv[e] = (nb + e < N) ? __ldg(ep.bias + nb + e) : 0.f;
+          }
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] += bv[e];
         }
+        if (ep.add16 != nullptr && row_ok) {
+          float av[32];
+          load_row32_bf16(ep.add16 + (int64_t)row * ep.ldadd + nb, full && (ep.ldadd & 7) == 0, N - nb, av);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] += av[e];
+        }
+        if (ep.relu) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = fmaxf(v[e], 0.f);
+        }
+        if (ep.mask != nullptr && row_ok) {
+          float mv[32];
+          load_row32_bf16(ep.mask + (int64_t)row * ep.ldm + nb, full && (ep.ldm & 7) == 0, N - nb, mv);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = mv[e] > 0.f ? v[e] : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = (row_ok && nb + e < N) ? v[e] : 0.f;
         if (ep.out_f32 != nullptr && row_ok) {
           float* o = ep.out_f32 + (int64_t)row * ep.ldo + nb;
           if (ep.perm_cin > 0) {
@@ -364,9 +430,11 @@ __global__ void __launch_bounds__(GM_THREADS, GemmCfg<BN>::CTAS_PER_SM) gemm_bf1
       if (lane == 0) tc::mbar_arrive(&acc_empty[as]);
     }
   }
+  if (threadIdx.x == 64) trace_stamp(ep.trace, 5);  // epilogue warp 2 done
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  if (threadIdx.x == 32) trace_stamp(ep.trace, 6);  // exit
 }
 
 // ---------------------------------------------------------------------------------------------- host: tensor maps
@@ -453,6 +521,10 @@ static int conv_tile_shape(int h, int w, int pixels, int* tile_h, int* tile_n, i
 
 using namespace b2;
 
+static long long* g_gemm_trace = nullptr;
+/* debug hook (tools/gemm_trace.py): device buffer of 8 int64 that CTA 0 of every following b2_gemm_bf16 launch stamps with %globaltimer */
+extern "C" void b2_gemm_set_trace(void* dev_buf) { g_gemm_trace = static_cast<long long*>(dev_buf); }
+
 template <int BN>
 static int launch_gemm(const b2_gemm_args* a, const CUtensorMap& ta, const CUtensorMap& tb, int splits, int kb_per_split, const GemmEpilogue& ep, cudaStream_t st) {
   using Cfg = GemmCfg<BN>;
@@ -502,7 +574,7 @@ extern "C" int b2_gemm_bf16(const b2_gemm_args* a, void* stream) {
   if (kb_per_split < 1) kb_per_split = 1;
   splits = total_k > 0 ? (total_k + kb_per_split - 1) / kb_per_split : 1;
   GemmEpilogue ep{a->out_f32, static_cast<__nv_bfloat16*>(a->out_bf16), static_cast<__nv_bfloat16*>(a->out_bf16_t), a->bias, static_cast<const __nv_bfloat16*>(a->mask),
-                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate, nullptr, 0, a->perm_cin, a->perm_taps};
+                  a->colsum, a->colsumsq, a->ldo, a->ldo16, a->ldt, a->ldm, a->relu, a->accumulate, nullptr, 0, g_gemm_trace, a->perm_cin, a->perm_taps};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (bn == 256) return launch_gemm<256>(a, ta, tb, splits, kb_per_split, ep, st);
   return launch_gemm<64>(a, ta, tb, splits, kb_per_split, ep, st);
