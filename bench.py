@@ -257,9 +257,15 @@ def run_ours(args) -> None:
     from myfyp_b200.management.logger import logger as _lg
 
     _lg.reset_metrics()
+    from myfyp_b200.management import trace as _trace
+
+    _trace.clear()
     e0.record(torch.cuda.current_stream(dev))
     run_rounds(args.steps)
     e1.record(torch.cuda.current_stream(dev))
+    if _trace.ENABLED:  # B2_TRACE=1: control-plane timeline of the timed rounds, one file per rank
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        _trace.dump(os.path.join(ROOT, "gpurun_out", f"trace_rank{rank}.json"))
     barrier()
     stage_ms = {}
     if nodes:
@@ -271,6 +277,8 @@ def run_ours(args) -> None:
                 acc_t[name] += dt
         stage_ms = {k: round(1e3 * v / len(nodes) / args.steps, 2) for k, v in acc_t.items()}
         stage_ms.update({k: round(sum(v) / max(len(v), 1), 2) for k, v in _lg.get_device_times().items()})
+        # control-plane messages handled by this rank's nodes, per round (all nodes of the rank together)
+        stage_ms.update({k: round(v / args.steps, 1) for k, v in _lg.get_bytes().items() if k.startswith("msgs/")})
     ms = allmax(e0.elapsed_time(e1))
     launches = int(allsum(native.launches()))
     clocks = sampler.stop(world) if rank == 0 else {}

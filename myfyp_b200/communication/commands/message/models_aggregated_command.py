@@ -2,6 +2,7 @@
 
 from myfyp_b200.communication.commands.command import Command
 from myfyp_b200.management.logger import logger
+from myfyp_b200.management.trace import trace
 
 
 class ModelsAggregatedCommand(Command):
@@ -13,6 +14,7 @@ class ModelsAggregatedCommand(Command):
         return "models_aggregated"
 
     def execute(self, source: str, round: int, *args, **kwargs) -> None:
+        trace(self.state.addr, f"announce<{source} {len(args)}")
         if round == self.state.round:
             # Within a round a node's held set only grows, so announcements are merged, not overwritten: two
             # announcements of one node can overtake each other (concurrent handlers, async fan-out), and a stale

@@ -13,6 +13,8 @@ from myfyp_b200.communication.commands.message.models_aggregated_command import 
 from myfyp_b200.communication.commands.weights._common import handle_bad_model
 from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
 from myfyp_b200.management.logger import logger
+from myfyp_b200.management.trace import trace
+from myfyp_b200.settings import Settings
 
 
 class PartialModelCommand(Command):
@@ -37,15 +39,23 @@ class PartialModelCommand(Command):
         if len(st.train_set) == 0:
             logger.error(st.addr, "Model Reception when there is no trainset")
             return
+        trace(st.addr, f"recv_model<{source} {len(contributors)}")
         try:
             model = self.learner.get_model().build_copy(params=weights, num_samples=num_samples, contributors=list(contributors))
             models_added = self.aggregator.add_model(model)
+            trace(st.addr, f"added<{source} held={len(models_added)}")
+            # the sender evidently holds what it sent: no need to wait for its announcement to know that
+            held = st.models_aggregated.get(source, [])
+            st.models_aggregated[source] = held + [c for c in contributors if c not in held]
             if models_added != []:
                 # we are inside the sender's RPC / call stack: announce from the gossiper thread, never block here
                 # (a synchronous fan-out from inside a handler can exhaust the peers' RPC workers)
                 # announcements are cumulative (receivers merge them), so a newer one supersedes an unsent older one
+                # and a burst of arrivals is worth one announcement: only the complete set goes out without delay
+                complete = len(set(models_added)) >= len(st.train_set)
                 self.communication_protocol.broadcast_async(
-                    self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round), coalesce=True
+                    self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round), coalesce=True,
+                    linger=0.0 if complete else Settings.ANNOUNCE_LINGER,
                 )
         except DecodingParamsError:
             handle_bad_model(st, self.stop, source, "Error decoding parameters", self.communication_protocol)

@@ -76,7 +76,7 @@ class CommunicationProtocol(abc.ABC):
         wait_fn: Optional[Callable[[float], None]] = None,
     ) -> None: ...
 
-    def broadcast_async(self, msg: Any, coalesce: bool = False) -> None:
+    def broadcast_async(self, msg: Any, coalesce: bool = False, linger: float = 0.0) -> None:
         """Like :meth:`broadcast` but never blocks the caller on the peers (default: plain broadcast)."""
         self.broadcast(msg)
 

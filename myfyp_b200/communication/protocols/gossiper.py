@@ -24,6 +24,7 @@ from typing import Any, Callable, Deque, List, Optional, Tuple
 
 from myfyp_b200.communication.protocols.client import Client
 from myfyp_b200.management.logger import logger
+from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
 
 
@@ -36,7 +37,7 @@ class Gossiper(threading.Thread):
         self.messages_per_period = messages_per_period
         self.__processed: "collections.OrderedDict[int, None]" = collections.OrderedDict()
         self.__processed_lock = threading.Lock()
-        self.__pending: Deque[Tuple[Any, List[str]]] = collections.deque()
+        self.__pending: Deque[Tuple[Any, List[str], float]] = collections.deque()  # (message, recipients, not before [monotonic])
         self.__cv = threading.Condition()
         self.__terminate = threading.Event()
 
@@ -52,25 +53,28 @@ class Gossiper(threading.Thread):
             self.__cv.notify_all()
 
     # ------------------------------------------------------------------ flood
-    def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None) -> None:
+    def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None, linger: float = 0.0) -> None:
         """Queue ``msg`` for ``pending_neis``.  With a ``coalesce_key`` a still-unsent message queued under the same key is
         *replaced* (its remaining recipients get the newer message instead): a burst of state announcements costs one
-        message per neighbour, not one per state change."""
+        message per neighbour, not one per state change.  ``linger`` holds a coalescable message back for that many
+        seconds so that a burst really does collapse (the first deadline of a key is kept: nothing is starved);
+        ``linger = 0`` with an entry already queued under the key sends the replacement at once."""
         if not pending_neis:
             return
+        now = time.monotonic()
         with self.__cv:
             if coalesce_key is not None:
-                for i, (old, neis) in enumerate(self.__pending):
+                for i, (old, neis, due) in enumerate(self.__pending):
                     if isinstance(old, dict) and old.get("_ckey") == coalesce_key:
                         merged = list(dict.fromkeys([*neis, *pending_neis]))
                         tagged = dict(msg)
                         tagged["_ckey"] = coalesce_key
-                        self.__pending[i] = (tagged, merged)
+                        self.__pending[i] = (tagged, merged, min(due, now + linger))
                         self.__cv.notify()
                         return
                 msg = dict(msg)
                 msg["_ckey"] = coalesce_key
-            self.__pending.append((msg, list(pending_neis)))
+            self.__pending.append((msg, list(pending_neis), now + (linger if coalesce_key is not None else 0.0)))
             self.__cv.notify()
 
     def check_and_set_processed(self, msg_hash: int) -> bool:
@@ -93,24 +97,34 @@ class Gossiper(threading.Thread):
             budget = Settings.GOSSIP_MESSAGES_PER_PERIOD if self.messages_per_period is None else self.messages_per_period
             batch: List[Tuple[Any, List[str]]] = []
             with self.__cv:
-                while not self.__pending and not self.__terminate.is_set():
-                    self.__cv.wait(timeout=1.0)
+                while not self.__terminate.is_set():
+                    now = time.monotonic()
+                    if any(due <= now for _, _, due in self.__pending):
+                        break
+                    nxt = min((due for _, _, due in self.__pending), default=None)
+                    self.__cv.wait(timeout=1.0 if nxt is None else max(0.0, nxt - now))
                 if self.__terminate.is_set():
                     return
-                while budget > 0 and self.__pending:
-                    msg, neis = self.__pending[0]
-                    if len(neis) <= budget:
-                        batch.append(self.__pending.popleft())
+                now = time.monotonic()
+                kept: Deque[Tuple[Any, List[str], float]] = collections.deque()
+                while self.__pending:
+                    msg, neis, due = self.__pending.popleft()
+                    if due > now or budget <= 0:  # lingering announcement, or this period's budget is spent
+                        kept.append((msg, neis, due))
+                    elif len(neis) <= budget:
+                        batch.append((msg, neis))
                         budget -= len(neis)
                     else:
                         batch.append((msg, neis[:budget]))
-                        self.__pending[0] = (msg, neis[budget:])
+                        kept.append((msg, neis[budget:], due))
                         budget = 0
+                self.__pending = kept
             t0 = time.monotonic()
             for msg, neis in batch:
                 for nei in neis:
                     if self.__terminate.is_set():
                         return
+                    trace(self.__self_addr, f"flood {msg.get('cmd') if isinstance(msg, dict) else '?'}>{nei}")
                     self.__client.send(nei, msg)
             # only a *saturated* period needs pacing; otherwise go back to waiting
             if budget == 0 and period > 0:
@@ -151,7 +165,9 @@ class Gossiper(threading.Thread):
                 if msg is None:
                     continue
                 logger.debug(self.__self_addr, f"🗣️ Gossiping model to {nei}.")
+                trace(self.__self_addr, f"send_model>{nei}")
                 self.__client.send(nei, msg, create_connection=create_connection)
+                trace(self.__self_addr, f"sent_model>{nei}")
             # progress => go again at once; no progress => wait (interruptibly) for the period
             if repr(status_fn()) != before:
                 continue

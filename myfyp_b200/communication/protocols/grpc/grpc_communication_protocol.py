@@ -72,16 +72,17 @@ class GrpcCommunicationProtocol(CommunicationProtocol):
         self._client.broadcast(msg, node_list)
 
     @running
-    def broadcast_async(self, msg: Any, coalesce: bool = False) -> None:
+    def broadcast_async(self, msg: Any, coalesce: bool = False, linger: float = 0.0) -> None:
         """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers).
-        ``coalesce``: a queued, not yet sent message of the same command and round is superseded by this one."""
+        ``coalesce``: a queued, not yet sent message of the same command and round is superseded by this one;
+        ``linger``: hold a coalescable message back this long so that a burst of them collapses into one."""
         if isinstance(msg, dict) and "hash" in msg:
             self._gossiper.check_and_set_processed(msg["hash"])
         nodes = list(self._neighbors.get_all(only_direct=True))
         if isinstance(msg, dict) and "hash" in msg:
             msg["seen"] = [self.addr, *nodes]
         key = (msg.get("cmd"), msg.get("round")) if coalesce and isinstance(msg, dict) else None
-        self._gossiper.add_message(msg, nodes, coalesce_key=key)
+        self._gossiper.add_message(msg, nodes, coalesce_key=key, linger=linger)
 
     @running
     def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]:

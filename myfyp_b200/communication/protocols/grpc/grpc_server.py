@@ -117,6 +117,8 @@ class GrpcServer:
         if not is_weights and not self._gossiper.check_and_set_processed(msg["hash"]):
             return None
         cmd = msg["cmd"]
+        if cmd != "beat":
+            logger.log_bytes("msgs/" + cmd, 1)  # control-plane message census (benchmarks report it per round)
         if not is_weights and cmd != "beat" and msg["source"] != self.addr:
             # any message proves its origin is alive: learn about it now rather than at its next heartbeat
             self._neighbors.refresh_or_add(msg["source"], time.time())

@@ -63,6 +63,8 @@ class InMemoryServer:
         if not self.__gossiper.check_and_set_processed(request["hash"]):
             return {}
         cmd = request["cmd"]
+        if cmd != "beat":
+            logger.log_bytes("msgs/" + cmd, 1)  # control-plane message census (benchmarks report it per round)
         if cmd != "beat" and request["source"] != self.addr:
             # any message proves its origin is alive: learn about it now rather than at its next heartbeat (a node that
             # just (re)joined would otherwise be missing from some nodes' vote bookkeeping -> diverging train sets)
@@ -93,6 +95,7 @@ class InMemoryServer:
         if not self.__started:
             return {"error": "server not running"}
         handler = self.__commands.get(request["cmd"])
+        logger.log_bytes("msgs/" + request["cmd"], 1)
         if handler is None:
             logger.error(self.addr, f"Unknown command: {request['cmd']} from {request['source']}")
             return {"error": f"Unknown command: {request['cmd']}"}

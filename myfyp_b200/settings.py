@@ -55,6 +55,13 @@ class Settings(metaclass=_SettingsMeta):
 
     # --- gossip (models) -----------------------------------------------------
     GOSSIP_MODELS_PERIOD: float = 1
+    # An intermediate "models_aggregated" announcement (the node holds some, not yet all, models of the round) is held back this
+    # long so that a burst of arrivals is announced once; the announcement of a COMPLETE set is never delayed.  (B200 addition.)
+    ANNOUNCE_LINGER: float = 0.005
+    # A node forwards models it did not train itself to a peer only after holding them this long: in a dense topology the origin
+    # delivers its own model to that peer directly within milliseconds, and an early forward is a duplicate the peer must
+    # refuse.  Own models are always offered at once.  (B200 addition; the reference forwards immediately, every second.)
+    FORWARD_GRACE: float = 0.02
     GOSSIP_MODELS_PER_ROUND: int = 2
     GOSSIP_EXIT_ON_X_EQUAL_ROUNDS: int = 10
 

@@ -19,6 +19,7 @@ from myfyp_b200.communication.commands.message.models_ready_command import Model
 from myfyp_b200.communication.commands.weights.partial_model_command import PartialModelCommand
 from myfyp_b200.learning.aggregators.aggregator import NoModelsToAggregateError
 from myfyp_b200.management.logger import logger
+from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
 from myfyp_b200.stages.base_node.start_learning_stage import _transport
 from myfyp_b200.stages.stage import EarlyStopException, Stage, check_early_stop
@@ -39,6 +40,7 @@ class TrainStage(Stage):
         def lap(name: str) -> None:  # wall-time split of the stage, read by benchmarks (logger.get_device_times())
             t.append(time.perf_counter())
             logger.log_device_time(f"train_stage/{name}", 1e3 * (t[-1] - t[-2]))
+            trace(state.addr, f"lap {name} r{state.round}")
 
         try:
             check_early_stop(state)
@@ -99,9 +101,17 @@ class TrainStage(Stage):
         offered: dict = {}
         reoffer_after = max(1.0, 20 * Settings.GOSSIP_MODELS_PERIOD)
 
+        arrival: dict = {}  # contributor -> when this loop first saw it in our held set
+
         def model_fn(node: str) -> Any:
             if not fresh_offer(node):  # nothing new for this peer: do not even run the partial-aggregation kernel
                 return None
+            offer = aggregator.peek_offer(aggregated_by(node))
+            now = time.monotonic()
+            for c in offer:
+                arrival.setdefault(c, now)
+            if state.addr not in offer and any(now - arrival[c] < Settings.FORWARD_GRACE for c in offer):
+                return None  # pure forwarding: give the origins a moment to deliver directly (the loop wakes up again)
             try:
                 model = aggregator.get_model(aggregated_by(node))
             except NoModelsToAggregateError:
