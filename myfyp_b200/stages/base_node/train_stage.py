@@ -82,8 +82,20 @@ class TrainStage(Stage):
         def remaining(node: str) -> Set[str]:
             return set(state.train_set) - set(aggregated_by(node))
 
+        def excluded_for(node: str) -> List[str]:
+            """Contributors that must not be in an offer to ``node``.  A peer that still lacks OUR OWN model gets exactly that
+            model, alone: a single fresh model can never overlap what the peer holds, whereas a partial aggregate built from a
+            stale view of the peer (own + others it has meanwhile received directly) is refused as a whole - and our own model
+            with it.  (The reference always offers the widest aggregate and relies on its once-per-second retries.)"""
+            have = aggregated_by(node)
+            if state.addr not in have:
+                others = [n for n in state.train_set if n != state.addr]
+                if aggregator.peek_offer(others):  # we do hold our own model as a single (we always do after fit)
+                    return others
+            return have
+
         def fresh_offer(node: str) -> bool:
-            key = (node, frozenset(aggregator.peek_offer(aggregated_by(node))))
+            key = (node, frozenset(aggregator.peek_offer(excluded_for(node))))
             return bool(key[1]) and time.monotonic() - offered.get(key, -1e9) >= reoffer_after
 
         def get_candidates_fn() -> List[str]:
@@ -106,14 +118,15 @@ class TrainStage(Stage):
         def model_fn(node: str) -> Any:
             if not fresh_offer(node):  # nothing new for this peer: do not even run the partial-aggregation kernel
                 return None
-            offer = aggregator.peek_offer(aggregated_by(node))
+            excluded = excluded_for(node)
+            offer = aggregator.peek_offer(excluded)
             now = time.monotonic()
             for c in offer:
                 arrival.setdefault(c, now)
             if state.addr not in offer and any(now - arrival[c] < Settings.FORWARD_GRACE for c in offer):
                 return None  # pure forwarding: give the origins a moment to deliver directly (the loop wakes up again)
             try:
-                model = aggregator.get_model(aggregated_by(node))
+                model = aggregator.get_model(excluded)
             except NoModelsToAggregateError:
                 logger.debug(state.addr, f"❔ No models to aggregate from {node}.")
                 return None
