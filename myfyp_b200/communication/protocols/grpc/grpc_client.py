@@ -56,7 +56,10 @@ class GrpcClient(Client):
 
                 payload = dict(msg)
                 payload["weights"] = encode_descriptor(msg["weights"])
-            err = stub.send(payload, Settings.GRPC_TIMEOUT)
+            if not raise_error and "weight" not in msg and hasattr(stub, "send_oneway"):
+                err = stub.send_oneway(payload)  # the caller does not want the peer's verdict: do not wait for it
+            else:
+                err = stub.send(payload, Settings.GRPC_TIMEOUT)
             if err:
                 raise CommunicationError(f"Error while sending a message: {msg['cmd']!r}: {err!r}")
         except Exception as e:  # noqa: BLE001

@@ -2,7 +2,8 @@
 
 Same commands, flood, heartbeats and neighbour semantics as the other two transports (it reuses the gRPC protocol's
 client / neighbour / servicer logic); only the pipe differs: length-prefixed pickled frames over ``AF_UNIX`` stream
-sockets (``multiprocessing.connection``), one persistent connection per neighbour, request -> response.  A Python gRPC
+sockets (``multiprocessing.connection``), one persistent connection per neighbour; weights and handshakes are
+request -> response, control messages are one-way frames.  A Python gRPC
 unary call costs 0.3-1 ms of interpreter time on each side; a frame on a unix socket costs tens of microseconds, which
 is what a federation needs when every round is a few hundred small control messages and the model bytes travel over
 NVLink anyway (weights messages carry slab descriptors, see :mod:`myfyp_b200.parallel.ipc`).
@@ -62,6 +63,15 @@ class UdsStub:
     def send(self, msg: Any, timeout: float) -> Optional[str]:
         return self._call("s", msg, timeout)
 
+    def send_oneway(self, msg: Any) -> None:
+        """Control messages (votes, announcements, metrics, beats) whose sender ignores the peer's verdict travel as one-way
+        frames: waiting for the (error-text-only) answer made every flood fan-out cost one round trip per neighbour.  Frames
+        of one connection are handled in order, so later request/response calls still pair up; a dead peer shows up as a
+        socket error here or through its missing heartbeats."""
+        with self._lock:
+            self._conn.send(("a", msg))
+        return None
+
     def close(self) -> None:
         try:
             self._conn.close()
@@ -111,6 +121,14 @@ class UdsServer(GrpcServer):
                     kind, payload = conn.recv()
                 except (EOFError, OSError):
                     return
+                if kind == "a":  # one-way control frame: no answer is written
+                    try:
+                        err = self.send(payload)
+                        if err:
+                            logger.debug(self.addr, f"one-way frame refused: {err}")
+                    except Exception as e:  # noqa: BLE001
+                        logger.debug(self.addr, f"one-way frame failed: {e}")
+                    continue
                 try:
                     if kind == "s":
                         res = self.send(payload)

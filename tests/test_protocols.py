@@ -91,6 +91,9 @@ def test_errors_and_command_dispatch(proto):
         assert (src, rnd, args) == (p1.get_address(), 7, ()) and bytes(kw["weights"]) == b"\x00payload\xff"
         assert list(kw["contributors"]) == ["c1", "c2"] and kw["num_samples"] == 42
         p2.broadcast(p2.build_msg("mock", ["x"]))
+        deadline = time.time() + 2  # a broadcast does not wait for the peers' verdicts (one-way frames on the socket protocol)
+        while time.time() < deadline and not (cmd1.calls and cmd1.calls[-1][2] == ("x",)):
+            time.sleep(0.005)
         assert cmd1.calls[-1][2] == ("x",)
     finally:
         p1.stop()
