@@ -17,6 +17,7 @@ Deliberate differences:
 from __future__ import annotations
 
 import collections
+from concurrent.futures import ThreadPoolExecutor
 import random
 import threading
 import time
@@ -40,6 +41,7 @@ class Gossiper(threading.Thread):
         self.__pending: Deque[Tuple[Any, List[str], float]] = collections.deque()  # (message, recipients, not before [monotonic])
         self.__cv = threading.Condition()
         self.__terminate = threading.Event()
+        self.__pool: Optional[ThreadPoolExecutor] = None
 
     # ------------------------------------------------------------------ thread control
     def start(self) -> None:
@@ -51,6 +53,8 @@ class Gossiper(threading.Thread):
         self.__terminate.set()
         with self.__cv:
             self.__cv.notify_all()
+        if self.__pool is not None:
+            self.__pool.shutdown(wait=False)
 
     # ------------------------------------------------------------------ flood
     def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None, linger: float = 0.0) -> None:
@@ -160,14 +164,28 @@ class Gossiper(threading.Thread):
             if len(last_status) == x and all(s == before for s in last_status):
                 logger.info(self.__self_addr, f"⏹️  Gossiping exited for {x} equal rounds.")
                 return
+            outbox = []
             for nei in random.sample(neis, min(Settings.GOSSIP_MODELS_PER_ROUND, len(neis))):
                 msg = model_fn(nei)
-                if msg is None:
-                    continue
+                if msg is not None:
+                    outbox.append((nei, msg))
+
+            def deliver(item) -> None:
+                nei, msg = item
                 logger.debug(self.__self_addr, f"🗣️ Gossiping model to {nei}.")
                 trace(self.__self_addr, f"send_model>{nei}")
                 self.__client.send(nei, msg, create_connection=create_connection)
                 trace(self.__self_addr, f"sent_model>{nei}")
+
+            if len(outbox) > 1 and Settings.GOSSIP_SEND_WORKERS > 1:
+                # each send is a blocking request -> response (the peer pulls and files the model before it answers):
+                # to several peers they overlap instead of adding up (the reference sends one after the other)
+                if self.__pool is None:
+                    self.__pool = ThreadPoolExecutor(max_workers=Settings.GOSSIP_SEND_WORKERS, thread_name_prefix=f"gossip-send-{self.__self_addr}")
+                list(self.__pool.map(deliver, outbox))
+            else:
+                for item in outbox:
+                    deliver(item)
             # progress => go again at once; no progress => wait (interruptibly) for the period
             if repr(status_fn()) != before:
                 continue

@@ -58,6 +58,8 @@ class Settings(metaclass=_SettingsMeta):
     # An intermediate "models_aggregated" announcement (the node holds some, not yet all, models of the round) is held back this
     # long so that a burst of arrivals is announced once; the announcement of a COMPLETE set is never delayed.  (B200 addition.)
     ANNOUNCE_LINGER: float = 0.005
+    # Model offers of one gossip tick are delivered by this many threads at once (1 = one after the other, like the reference).
+    GOSSIP_SEND_WORKERS: int = 8
     # A node forwards models it did not train itself to a peer only after holding them this long: in a dense topology the origin
     # delivers its own model to that peer directly within milliseconds, and an early forward is a duplicate the peer must
     # refuse.  Own models are always offered at once.  (B200 addition; the reference forwards immediately, every second.)
