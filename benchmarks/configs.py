@@ -78,8 +78,9 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
     fi = FaultInjector()
     late = []
     if faults:
-        for idx, rnd in faults.get("drop", []):
-            fi.drop_at(nodes[idx], round=rnd, stage="TrainStage")
+        for j, (idx, rnd) in enumerate(faults.get("drop", [])):
+            # the first victim dies wherever it is in that round, the others only if they are training at that moment
+            fi.drop_at(nodes[idx], round=rnd, stage=None if j == 0 else "TrainStage")
         for idx, at_round in faults.get("rejoin", []):
             def make(idx=idx):
                 n = Node(mk(device=f"cuda:{idx % gpus}" if gpus else "cpu", seed=1000 + idx), parts[idx], address=f"{name}-re-{idx}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs)

@@ -19,14 +19,21 @@ class VoteTrainSetCommand(Command):
         if st.round is None:
             logger.debug(st.addr, f"Vote received from {source} while not learning. Ignored.")
             return
-        # votes may arrive one round early (the sender finished its round first)
+        # Votes may arrive one round early (the sender finished its round first).  They are kept apart from the current round's
+        # ballots: a node still waiting in THIS round's vote (e.g. for the ballot of a peer that just died) would otherwise see a
+        # fast peer's next-round ballot overwrite its current one, tally different ballots than everybody else and end up with
+        # a different train set - after which every round waits for time-outs.  (The reference keeps one dict,
+        # vote_train_set_command.py:60-71, and has this failure mode.)
         if round in (st.round, st.round + 1):
             votes = list(args)
             tmp = {}
             for i in range(0, len(votes) - 1, 2):
                 tmp[votes[i]] = int(votes[i + 1])
             with st.train_set_votes_lock:
-                st.train_set_votes[source] = tmp
+                if round == st.round:
+                    st.train_set_votes[source] = tmp
+                else:
+                    st.train_set_votes_next[source] = tmp
             with contextlib.suppress(Exception):
                 st.wait_votes_ready_lock.release()
             st.notify()

@@ -26,6 +26,15 @@ class PartialModelCommand(Command):
     def get_name() -> str:
         return "partial_model"
 
+    def absorb_early(self) -> None:
+        """Called by TrainStage once the round's train set is installed: file the offers that arrived one round early."""
+        st = self.state
+        with st.train_set_votes_lock:
+            mine = [e for e in st.early_models if e[0] == st.round]
+            st.early_models = [e for e in st.early_models if st.round is not None and e[0] > st.round]
+        for _, source, weights, contributors, num_samples in mine:
+            self.absorb(source, weights, contributors, num_samples)
+
     def execute(self, source: str, round: int, weights=None, contributors: Optional[List[str]] = None, num_samples: Optional[int] = None, **kwargs) -> None:
         if weights is None or contributors is None or num_samples is None:
             raise ValueError("Weights, contributors and weight are required")
@@ -33,12 +42,25 @@ class PartialModelCommand(Command):
         if st.round is None:
             logger.debug(st.addr, "Tried to add a model while learning is not running")
             return
+        if round == st.round + 1 or (round == st.round and not self.aggregator.is_collecting() and st.addr not in self.aggregator.get_aggregated_models()):
+            # The sender is ahead of us: a round ahead, or already training while we still tally this round's votes (we are still finishing the previous round, e.g. waiting for the ballot of a peer
+            # that died).  Its published snapshot is immutable for the round, so the offer is kept and filed when we get
+            # there; dropping it (reference: partial_model_command.py:66-70) makes the sender retry for a few ticks, give up
+            # and leave the round - after which this node waits for a model that never comes until AGGREGATION_TIMEOUT.
+            with st.train_set_votes_lock:
+                st.early_models = [e for e in st.early_models if e[0] >= st.round][-64:] + [(round, source, weights, list(contributors), num_samples)]
+            return
         if round != st.round:
             logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
             return
         if len(st.train_set) == 0:
             logger.error(st.addr, "Model Reception when there is no trainset")
             return
+        self.absorb(source, weights, contributors, num_samples)
+
+    def absorb(self, source: str, weights, contributors: List[str], num_samples: int) -> None:
+        """File one offered model with the aggregator and announce what we hold now."""
+        st = self.state
         trace(st.addr, f"recv_model<{source} {len(contributors)}")
         try:
             model = self.learner.get_model().build_copy(params=weights, num_samples=num_samples, contributors=list(contributors))

@@ -49,6 +49,10 @@ class Aggregator:
         self.__train_set = list(nodes_to_aggregate)
         self._finish_aggregation_event.clear()
 
+    def is_collecting(self) -> bool:
+        """True between :meth:`set_nodes_to_aggregate` and the moment the last model of the train set is filed."""
+        return not self._finish_aggregation_event.is_set()
+
     def clear(self) -> None:
         with self.__agg_lock:
             self.__train_set = []

@@ -92,6 +92,8 @@ class Node:
         self._learning_args: Optional[tuple] = None
 
         p = self._communication_protocol
+        partial_model = PartialModelCommand(self.state, self.stop, self.aggregator, p, self.learner)
+        self.state.absorb_early_models = partial_model.absorb_early
         p.add_command(
             [
                 StartLearningCommand(self.__start_learning_thread),
@@ -102,7 +104,7 @@ class Node:
                 ModelsReadyCommand(self.state),
                 MetricsCommand(self.state),
                 InitModelCommand(self.state, self.stop, self.aggregator, self.learner, p),
-                PartialModelCommand(self.state, self.stop, self.aggregator, p, self.learner),
+                partial_model,
                 FullModelCommand(self.state, self.stop, self.aggregator, self.learner, p),
             ]
         )

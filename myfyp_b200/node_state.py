@@ -32,6 +32,10 @@ class NodeState:
         self.nei_status: Dict[str, int] = {}
         self.train_set: List[str] = []
         self.train_set_votes: Dict[str, Dict[str, int]] = {}
+        self.train_set_votes_next: Dict[str, Dict[str, int]] = {}  # ballots of peers that are already one round ahead
+        self.early_models: List[tuple] = []  # model offers that arrived before this node started collecting for that round
+        if not hasattr(self, "absorb_early_models"):
+            self.absorb_early_models = None  # set by Node: files the stashed offers (PartialModelCommand.absorb_early)
 
         # locks / events (same names as the reference)
         self.train_set_votes_lock = threading.Lock()
@@ -89,6 +93,8 @@ class NodeState:
             raise ValueError("Experiment not initialized")
         self.experiment.increase_round()
         self.models_aggregated, self.models_aggregated_next = self.models_aggregated_next, {}
+        with self.train_set_votes_lock:
+            self.train_set_votes, self.train_set_votes_next = self.train_set_votes_next, {}
         self.notify()
 
     def clear(self) -> None:

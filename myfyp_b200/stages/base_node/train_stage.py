@@ -45,6 +45,15 @@ class TrainStage(Stage):
         try:
             check_early_stop(state)
             aggregator.set_nodes_to_aggregate(state.train_set)
+            # a member evicted by the failure detector between the vote's validation and this point was reported to an
+            # aggregator that did not know the train set yet: check once more, or the round waits for a dead node's model
+            alive = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
+            for dead in [n for n in state.train_set if n not in alive]:
+                if aggregator.drop_node(dead):
+                    state.train_set = [n for n in state.train_set if n != dead]
+                    logger.info(state.addr, f"☠️ {dead} left before training started: aggregating without it.")
+            if getattr(state, "absorb_early_models", None) is not None:
+                state.absorb_early_models()  # offers from peers that started this round before we did
             check_early_stop(state)
             evaluate_and_broadcast(state, learner, communication_protocol)
             check_early_stop(state)

@@ -65,9 +65,12 @@ class VoteTrainSetStage(Stage):
             check_early_stop(state)
             neis = set(communication_protocol.get_neighbors(only_direct=False))
             needed = neis | {state.addr}
+            # Every ballot received for this round counts, also the ballot of a node that has left the neighbour table since it
+            # voted: whether a dead node's ballot is in the tally must not depend on WHEN a node noticed the death, or the
+            # survivors elect different train sets.  (The reference filters by the current neighbours, :137-141.)
             with state.train_set_votes_lock:
-                votes = {k: v for k, v in state.train_set_votes.items() if k in needed}
-            ready = needed == set(votes.keys())
+                votes = dict(state.train_set_votes)
+            ready = needed <= set(votes.keys())
             timeout = time.monotonic() > deadline
             if ready or timeout:
                 if timeout and not ready:

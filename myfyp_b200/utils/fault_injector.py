@@ -58,12 +58,13 @@ class FaultInjector:
         self._threads: List[threading.Thread] = []
         self.events: List[tuple] = []
 
-    def drop_at(self, node, round: int, stage: str = "TrainStage", poll: float = 0.005) -> None:
+    def drop_at(self, node, round: int, stage: Optional[str] = "TrainStage", poll: float = 0.005) -> None:
+        """Stop ``node`` as soon as it is in ``stage`` of ``round`` (``stage=None``: anywhere in that round)."""
         def watch():
             while True:
                 if node.learning_workflow.finished and node.state.round is None and len(node.learning_workflow.history) > 1:
                     return
-                if node.state.round == round and node.learning_workflow.history and node.learning_workflow.history[-1] == stage:
+                if node.state.round == round and node.learning_workflow.history and (stage is None or node.learning_workflow.history[-1] == stage):
                     self.events.append(("drop", node.addr, round, stage, time.time()))
                     node.stop()
                     return

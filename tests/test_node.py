@@ -144,6 +144,48 @@ def test_node_down_on_learning():
         _stop(nodes)
 
 
+def test_train_set_member_dying_mid_round_costs_no_timeouts():
+    """A sparse 16-node federation (train set 6) loses a train-set member in TrainStage of round 1.  The survivors must keep
+    electing the SAME train sets and finish without sitting out VOTE_TIMEOUT / AGGREGATION_TIMEOUT: ballots are kept per round
+    and counted whoever cast them, offers that arrive early are kept, a dead member is dropped from the aggregation.  (In the
+    reference every later round of such a run waits for time-outs: vote_train_set_command.py:60-71, partial_model_command.py:66-70.)"""
+    import threading
+
+    Settings.HEARTBEAT_PERIOD, Settings.HEARTBEAT_TIMEOUT = 0.3, 2
+    Settings.VOTE_TIMEOUT, Settings.AGGREGATION_TIMEOUT = 20, 40
+    Settings.TRAIN_SET_SIZE = 6
+    Settings.TTL = 16
+    n = 16
+    nodes = _nodes(n, samples=64)
+    killed = []
+    try:
+        TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.RANDOM, n, p=0.2, seed=3), nodes)
+        wait_convergence(nodes, n - 1, only_direct=False, wait=20)
+
+        def watch():  # kill the first node (other than the initiator) that enters TrainStage of round 1
+            while not killed:
+                for nd in nodes[1:]:
+                    if nd.state.round == 1 and nd.learning_workflow.history and nd.learning_workflow.history[-1] == "TrainStage":
+                        killed.append(nd)
+                        nd.stop()
+                        return
+                time.sleep(0.002)
+
+        threading.Thread(target=watch, daemon=True).start()
+        t0 = time.time()
+        nodes[0].set_start_learning(rounds=4, epochs=1)
+        alive = lambda: [nd for nd in nodes if nd not in killed]  # noqa: E731
+        while not all(nd.learning_workflow.finished for nd in alive()):
+            assert time.time() - t0 < 19, "the survivors are sitting out a time-out"
+            time.sleep(0.05)
+        assert killed
+        for nd in alive():
+            assert nd.learning_workflow.history.count("RoundFinishedStage") == 4
+        check_equal_models(alive())
+    finally:
+        _stop(nodes)
+
+
 def test_interrupt_train():
     nodes = _nodes(2, samples=2000)
     try:
