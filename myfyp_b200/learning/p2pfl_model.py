@@ -256,6 +256,9 @@ class TorchP2PFLModel(P2PFLModel):
             snap = Fabric.get().snapshot(self.slab)
             self._ref = SlabRef(snap.tensor, self.layout.total, self.layout.hash, str(self.slab.device), {}, snap.rank, snap.offset, snap.generation)
             return dataclasses.replace(self._ref, additional_info=dict(self.additional_info))
+        if not getattr(self, "_visible", False):
+            Fabric.make_visible(self.slab)  # e.g. an aggregation result still being written on this GPU's stream
+            self._visible = True
         return SlabRef(self.slab, self.layout.total, self.layout.hash, str(self.slab.device), dict(self.additional_info))
 
     def encode_for_transport(self, device_ok: bool) -> Union[bytes, SlabRef]:

@@ -90,7 +90,18 @@ class Fabric:
             return self._arena.publish(slab)
         if slab.is_cuda:
             self.enable_peer_access()
-        return Snapshot(slab.clone())
+        snap = slab.clone()
+        self.make_visible(snap)
+        return Snapshot(snap)
+
+    @staticmethod
+    def make_visible(t: torch.Tensor) -> None:
+        """Call before a descriptor of ``t`` leaves the thread that produced it.  Consumers on the SAME GPU run on that GPU's
+        default stream, i.e. behind the kernel that wrote ``t``; a consumer on ANOTHER GPU (peer access) is ordered against
+        nothing and would read the allocation's previous contents - typically last round's snapshot.  With more than one GPU
+        in the process the producing stream is therefore drained first (the wait releases the interpreter lock)."""
+        if t.is_cuda and torch.cuda.device_count() > 1:
+            torch.cuda.current_stream(t.device).synchronize()
 
     def has_arena(self) -> bool:
         return self._arena is not None

@@ -836,3 +836,43 @@ def test_native_resnet18_learns_and_evaluates(dev):
     with torch.no_grad():
         acc_ref = (module(x).argmax(1) == y).float().mean().item()
     assert abs(acc_ref - after["test_metric"]) < 0.05
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_in_process_federation_across_two_gpus_learns(dev):
+    """Nodes of ONE process placed on two GPUs exchange descriptors of slabs that peers read over NVLink.  A snapshot or an
+    aggregation result must be complete on its GPU before a descriptor leaves the producing thread (Fabric.make_visible):
+    a consumer on the other GPU is ordered against nothing, and reading the allocation's old contents (last round's
+    snapshot) silently stops the federation from learning while all nodes still agree on the same model."""
+    import time
+
+    from myfyp_b200.communication.protocols.memory.memory_communication_protocol import InMemoryCommunicationProtocol
+    from myfyp_b200.learning.aggregators import FedAvg
+    from myfyp_b200.learning.dataset import P2PFLDataset, RandomIIDPartitionStrategy
+    from myfyp_b200.models import cnn_model
+    from myfyp_b200.node import Node
+    from myfyp_b200.parallel.fabric import Fabric
+    from myfyp_b200.utils.topologies import TopologyFactory
+    from myfyp_b200.utils.utils import set_fast_settings
+
+    set_fast_settings(train_set_size=3)
+    Fabric.get().enable_peer_access()
+    n = 6
+    data = P2PFLDataset.synthetic((3, 32, 32), 10, 256 * n, 64 * n, seed=0)
+    parts = data.generate_partitions(n, RandomIIDPartitionStrategy, seed=0)
+    nodes = [Node(cnn_model(device=f"cuda:{i % 2}", seed=i), parts[i], address=f"mg-{i}", aggregator=FedAvg(), protocol=InMemoryCommunicationProtocol, batch_size=64) for i in range(n)]
+    try:
+        for nd in nodes:
+            nd.start()
+        TopologyFactory.connect_nodes(TopologyFactory.generate_matrix("full", n), nodes)
+        time.sleep(0.5)
+        nodes[0].set_start_learning(rounds=8, epochs=1)
+        deadline = time.time() + 120
+        while not all(nd.learning_workflow.finished for nd in nodes):
+            assert time.time() < deadline
+            time.sleep(0.05)
+        accs = [nd.learner.evaluate()["test_metric"] for nd in nodes]
+        assert min(accs) > 0.8, accs
+    finally:
+        for nd in nodes:
+            nd.stop()
