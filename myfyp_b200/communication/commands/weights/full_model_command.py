@@ -41,6 +41,7 @@ class FullModelCommand(Command):
                     return
                 logger.info(st.addr, "📦 Aggregated model received.")
                 self.learner.set_model(weights)
+                self.aggregator.observe_global(self.learner.get_model())  # server-side state that travels with the model (Scaffold's c)
                 st.rejoining = False
                 st.aggregated_model_event.set()
             st.notify()

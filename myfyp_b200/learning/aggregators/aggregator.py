@@ -49,6 +49,10 @@ class Aggregator:
         self.__train_set = list(nodes_to_aggregate)
         self._finish_aggregation_event.clear()
 
+    def observe_global(self, model: P2PFLModel) -> None:
+        """The node adopted an aggregate it did not compute itself (it was not in the round's train set).  Aggregators with
+        server-side state that must stay equal on all nodes (Scaffold's control variate) refresh it from the model's info."""
+
     def is_collecting(self) -> bool:
         """True between :meth:`set_nodes_to_aggregate` and the moment the last model of the train set is filed."""
         return not self._finish_aggregation_event.is_set()

@@ -26,15 +26,26 @@ from myfyp_b200.learning.p2pfl_model import P2PFLModel
 class Scaffold(Aggregator):
     REQUIRED_INFO_KEYS = ["delta_y_i", "delta_c_i"]
 
-    def __init__(self, node_name: str = "unknown", global_lr: float = 0.1) -> None:
+    def __init__(self, node_name: str = "unknown", global_lr: float = 0.1, rebase: bool = True) -> None:
         super().__init__(node_name)
         self.global_lr = global_lr
+        self.rebase = rebase  # slab path: recover the round's starting point from the clients' models (see _aggregate_slab)
         self.c: Any = []  # list of arrays (generic path) or flat tensor (slab path)
         self.global_model_params: Any = []
         self.partial_aggregation = False
 
     def get_required_callbacks(self) -> List[str]:
         return ["scaffold"]
+
+    def observe_global(self, model: P2PFLModel) -> None:
+        try:
+            g = model.get_info("scaffold").get("global_c")
+        except Exception:  # noqa: BLE001
+            return
+        if isinstance(g, torch.Tensor):
+            self.c = g.detach().clone()
+        elif g is not None and hasattr(model, "layout"):
+            self.c = _as_flat(g, model)
 
     def _get_and_validate_model_info(self, model: P2PFLModel) -> Dict[str, Any]:
         info = model.get_info("scaffold")
@@ -87,9 +98,13 @@ class Scaffold(Aggregator):
         dev = first.slab.device
         dys = [_as_flat(info["delta_y_i"], first) for info in infos]
         dcs = [_as_flat(info["delta_c_i"], first) for info in infos]
-        if not isinstance(self.global_model_params, torch.Tensor):
+        if self.rebase:
+            # x = the model every client started this round from = y_k - delta_y_k (any k).  A copy kept from "our" last
+            # aggregation is stale on a node that was outside the train set for a few rounds (train set < network).
+            self.global_model_params = first.slab.to(dev, copy=True) - dys[0].to(dev)
+        elif not isinstance(self.global_model_params, torch.Tensor):
             self.global_model_params = first.slab.to(dev, copy=True)
-        if not isinstance(self.c, torch.Tensor):
+        if not isinstance(self.c, torch.Tensor) or self.c.numel() != self.global_model_params.numel():
             self.c = torch.zeros_like(self.global_model_params)
         wy = [self.global_lr * m.get_num_samples() / total for m in models]
         ops.scaffold_server_update(self.global_model_params, self.c, dys, dcs, wy, 1.0 / len(models))

@@ -46,10 +46,12 @@ class SCAFFOLDCallback(P2PFLCallback):
         g = self.additional_info.get("global_c") if isinstance(self.additional_info, dict) else None
         if g is not None:
             self.c.copy_(_flat_prefix(g, model, n))
-        if self.x_start is None or self.x_start.numel() != n or self.x_start.device != slab.device:
-            self.x_start = slab[:n].clone()
+        # x_start covers the whole slab: the non-trainable tail (BatchNorm running statistics) is part of delta_y too,
+        # otherwise the aggregated model keeps the buffers it was initialised with
+        if self.x_start is None or self.x_start.numel() != slab.numel() or self.x_start.device != slab.device:
+            self.x_start = slab.clone()
         else:
-            self.x_start.copy_(slab[:n])
+            self.x_start.copy_(slab)
 
     def optimizer_terms(self, learner) -> Dict[str, Any]:
         if self.variant == "reference":
@@ -64,7 +66,9 @@ class SCAFFOLDCallback(P2PFLCallback):
         total = model.layout.total
         dy = torch.zeros(total, dtype=torch.float32, device=model.slab.device)
         dc = torch.zeros(total, dtype=torch.float32, device=model.slab.device)
-        ops.scaffold_finalize(self.c_i, dy[:n], dc[:n], self.x_start, model.slab[:n], max(steps, 1) * lr)
+        ops.scaffold_finalize(self.c_i, dy[:n], dc[:n], self.x_start[:n], model.slab[:n], max(steps, 1) * lr)
+        if total > n:
+            torch.sub(model.slab[n:], self.x_start[n:], out=dy[n:])
         # flat device slabs on the fabric; `encode_parameters` turns them into NumPy for the wire
         self.additional_info = {"delta_y_i": dy, "delta_c_i": dc}
 

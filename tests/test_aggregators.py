@@ -165,13 +165,33 @@ def test_scaffold_slab_path_matches_generic():
     ns = [5, 10, 20]
     slab_models = [base.build_copy(params=ref, num_samples=n, contributors=[str(i)], additional_info={"scaffold": info}) for i, (info, n) in enumerate(zip(infos, ns))]
     gen_models = [ListModel(params=ref, num_samples=n, contributors=[str(i)], additional_info={"scaffold": info}) for i, (info, n) in enumerate(zip(infos, ns))]
-    a, b = Scaffold(global_lr=0.5).aggregate(slab_models), Scaffold(global_lr=0.5).aggregate(gen_models)
+    # rebase=False: the reference's math verbatim (x starts as models[0]'s parameters and persists in the aggregator)
+    a, b = Scaffold(global_lr=0.5, rebase=False).aggregate(slab_models), Scaffold(global_lr=0.5).aggregate(gen_models)
     for x, y in zip(a.get_parameters(), b.get_parameters()):
         np.testing.assert_allclose(x, y, atol=1e-5)
     ca = a.get_info("scaffold")["global_c"]
     lay = base.layout
     for e, y in zip(lay.in_order(), b.get_info("scaffold")["global_c"]):
         np.testing.assert_allclose(ca[e.offset : e.offset + e.numel].view(e.shape).numpy(), y, atol=1e-5)
+
+
+def test_scaffold_rebases_on_the_round_start_recovered_from_the_clients():
+    """Default slab path: x = y_k - delta_y_k, so an aggregator that sat out rounds (node outside the train set) does not apply
+    this round's deltas to a stale copy of the global model."""
+    base = mlp_model(seed=0)
+    x = [p.copy() for p in base.get_parameters()]
+    rng = np.random.default_rng(2)
+    dys = [[0.01 * rng.standard_normal(p.shape).astype(np.float32) for p in x] for _ in range(2)]
+    ns = [10, 30]
+    models = [
+        base.build_copy(params=[p + d for p, d in zip(x, dy)], num_samples=n, contributors=[str(i)], additional_info={"scaffold": {"delta_y_i": dy, "delta_c_i": [np.zeros_like(p) for p in x]}})
+        for i, (dy, n) in enumerate(zip(dys, ns))
+    ]
+    agg = Scaffold(global_lr=1.0)
+    agg.global_model_params = torch.full((base.layout.total,), 123.0)  # a stale leftover from some earlier round
+    out = agg.aggregate(models)
+    for got, p, d0, d1 in zip(out.get_parameters(), x, dys[0], dys[1]):
+        np.testing.assert_allclose(got, p + 0.25 * d0 + 0.75 * d1, atol=1e-5)
 
 
 def test_scaffold_errors():
