@@ -41,7 +41,10 @@ class FullModelCommand(Command):
                     return
                 logger.info(st.addr, "📦 Aggregated model received.")
                 self.learner.set_model(weights)
-                self.aggregator.observe_global(self.learner.get_model())  # server-side state that travels with the model (Scaffold's c)
+                try:  # server-side state that travels with the model (Scaffold's c); never a reason to reject the model
+                    self.aggregator.observe_global(self.learner.get_model())
+                except Exception as e:  # noqa: BLE001
+                    logger.debug(st.addr, f"observe_global failed: {e}")
                 st.rejoining = False
                 st.aggregated_model_event.set()
             st.notify()

@@ -49,6 +49,17 @@ class Aggregator:
         self.__train_set = list(nodes_to_aggregate)
         self._finish_aggregation_event.clear()
 
+    def local_device(self, models: List[P2PFLModel]):
+        """Where this node's aggregation should run: the GPU of the model this node contributed (its own snapshot), so that
+        the result is born where the learner will adopt it; else the first model's device."""
+        for m in models:
+            try:
+                if self.node_name in m.get_contributors() and hasattr(m, "slab"):
+                    return m.slab.device
+            except Exception:  # noqa: BLE001
+                pass
+        return getattr(getattr(models[0], "slab", None), "device", None) if models else None
+
     def observe_global(self, model: P2PFLModel) -> None:
         """The node adopted an aggregate it did not compute itself (it was not in the round's train set).  Aggregators with
         server-side state that must stay equal on all nodes (Scaffold's control variate) refresh it from the model's info."""

@@ -27,11 +27,11 @@ class FedAvg(Aggregator):
         contributors: List[str] = []
         for m in models:
             contributors += m.get_contributors()
-        return weighted_average(models, [m.get_num_samples() / total for m in models], total, contributors)
+        return weighted_average(models, [m.get_num_samples() / total for m in models], total, contributors, device=self.local_device(models))
 
 
-def weighted_average(models: List[P2PFLModel], weights: List[float], num_samples: int, contributors: List[str]) -> P2PFLModel:
-    """``sum_k w_k theta_k`` as a held model; device kernel for slab models, NumPy otherwise."""
+def weighted_average(models: List[P2PFLModel], weights: List[float], num_samples: int, contributors: List[str], device=None) -> P2PFLModel:
+    """``sum_k w_k theta_k`` as a held model; device kernel for slab models (on ``device``, default: the first model's), NumPy otherwise."""
     from myfyp_b200 import ops
     from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
 
@@ -40,8 +40,10 @@ def weighted_average(models: List[P2PFLModel], weights: List[float], num_samples
         if len(models) == 1 and abs(weights[0] - 1.0) < 1e-12:
             # one model, weight 1: hand out the same immutable slab (with its arena coordinates, if any) - no kernel, no copy
             return first.build_copy(params=first.as_ref() if first.model is None else first.publish(), num_samples=num_samples, contributors=contributors)
-        out = ops.fedavg([m.slab for m in models], weights, device=ops.pick_device([m.slab for m in models], prefer=first.slab.device))  # type: ignore[attr-defined]
-        return first.build_copy(params=out, num_samples=num_samples, contributors=contributors)
+        dev = ops.pick_device([m.slab for m in models], prefer=device if device is not None else first.slab.device)  # type: ignore[attr-defined]
+        out = ops.fedavg([m.slab for m in models], weights, device=dev)  # type: ignore[attr-defined]
+        like = next((m for m in models if m.slab.device == dev), first)  # type: ignore[attr-defined]
+        return like.build_copy(params=out, num_samples=num_samples, contributors=contributors)
     # generic (non-torch) models: per-layer NumPy, like the reference
     import numpy as np
 

@@ -42,7 +42,7 @@ class FedMedian(Aggregator):
         if all(isinstance(m, TorchP2PFLModel) for m in models):
             first: TorchP2PFLModel = models[0]  # type: ignore[assignment]
             slabs = [m.slab for m in models]  # type: ignore[attr-defined]
-            out = ops.median(slabs, trim=trim, device=ops.pick_device(slabs, prefer=first.slab.device))
+            out = ops.median(slabs, trim=trim, device=ops.pick_device(slabs, prefer=self.local_device(models)))
             return first.build_copy(params=out, num_samples=total, contributors=contributors)
         import numpy as np
 

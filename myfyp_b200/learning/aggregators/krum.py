@@ -39,7 +39,7 @@ class Krum(Aggregator):
         m = max(1, min(self.m, k))
         if all(isinstance(x, TorchP2PFLModel) for x in models):
             slabs = [x.slab for x in models]  # type: ignore[attr-defined]
-            dist = ops.pairwise_sqdist(slabs, device=ops.pick_device(slabs, prefer=slabs[0].device))
+            dist = ops.pairwise_sqdist(slabs, device=ops.pick_device(slabs, prefer=self.local_device(models)))
             scores, selected = ops.krum_select(dist, self.f, m)
         else:
             import numpy as np
@@ -56,7 +56,7 @@ class Krum(Aggregator):
         for x in models:
             contributors += x.get_contributors()
         all_samples = sum(x.get_num_samples() for x in models)
-        return weighted_average(chosen, [x.get_num_samples() / total for x in chosen], all_samples, contributors)
+        return weighted_average(chosen, [x.get_num_samples() / total for x in chosen], all_samples, contributors, device=self.local_device(models))
 
 
 def krum_select_reference(dist, f: int, m: int):

@@ -95,9 +95,10 @@ class Scaffold(Aggregator):
         from myfyp_b200 import ops
 
         first = models[0]
-        dev = first.slab.device
+        dev = self.local_device(models)
         dys = [_as_flat(info["delta_y_i"], first) for info in infos]
         dcs = [_as_flat(info["delta_c_i"], first) for info in infos]
+        ops.order_after_producers([first.slab, *dys, *dcs], dev)  # clients' tensors may live on other GPUs of this process
         if self.rebase:
             # x = the model every client started this round from = y_k - delta_y_k (any k).  A copy kept from "our" last
             # aggregation is stale on a node that was outside the train set for a few rounds (train set < network).
@@ -106,6 +107,8 @@ class Scaffold(Aggregator):
             self.global_model_params = first.slab.to(dev, copy=True)
         if not isinstance(self.c, torch.Tensor) or self.c.numel() != self.global_model_params.numel():
             self.c = torch.zeros_like(self.global_model_params)
+        elif self.c.device != dev:
+            self.c = self.c.to(dev)
         wy = [self.global_lr * m.get_num_samples() / total for m in models]
         ops.scaffold_server_update(self.global_model_params, self.c, dys, dcs, wy, 1.0 / len(models))
         out = first.build_copy(params=self.global_model_params.clone(), num_samples=total, contributors=contributors)

@@ -31,9 +31,26 @@ def pick_device(slabs: Sequence[torch.Tensor], prefer: Optional[torch.device] = 
     return slabs[0].device
 
 
+def order_after_producers(slabs: Sequence[torch.Tensor], device: torch.device) -> None:
+    """A kernel on ``device`` is about to read slabs that live on OTHER GPUs of this process (peer access).  Streams of
+    different devices are ordered against nothing, so the consumer's stream is made to wait for everything queued so far on
+    each producer GPU's current (default) stream - the stream all aggregation / snapshot / adoption work of a process runs on.
+    One event record + one cross-device stream wait per foreign GPU, no host synchronisation."""
+    if device.type != "cuda":
+        return
+    seen = set()
+    for s in slabs:
+        if s.is_cuda and s.device != device and s.device not in seen:
+            seen.add(s.device)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(s.device))
+            torch.cuda.current_stream(device).wait_event(ev)
+
+
 def _same_place(slabs: Sequence[torch.Tensor], device: torch.device) -> List[torch.Tensor]:
     """CPU inputs of a CUDA reduction are staged; CUDA inputs (any GPU) are read in place over NVLink."""
     if device.type == "cuda":
+        order_after_producers(slabs, device)
         return [s if s.is_cuda else s.to(device, non_blocking=True) for s in slabs]
     return [s.cpu() if s.is_cuda else s for s in slabs]
 
@@ -45,6 +62,7 @@ def pull_copy(dst: torch.Tensor, src: torch.Tensor) -> None:
         return
     n = dst.numel()
     if dst.is_cuda and src.is_cuda and src.dtype == torch.float32 and src.is_contiguous():
+        order_after_producers([src], dst.device)
         lib = native.load()
         with native.device_guard(dst.device):
             native.check(lib.b2_pull_copy(native.ptr(dst), native.ptr(src), ctypes.c_int64(n), native.stream_ptr(dst.device)), "b2_pull_copy")
