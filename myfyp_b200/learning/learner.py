@@ -83,9 +83,6 @@ class LearnerFactory:
 
     @staticmethod
     def create_learner(model: P2PFLModel):
-        fw = model.get_framework()
-        if fw == "pytorch":
-            from myfyp_b200.learning.torch_learner import TorchLearner
+        from myfyp_b200.learning.frameworks import learner_for
 
-            return TorchLearner
-        raise ValueError(f"Framework {fw} is not supported (TensorFlow/Flax bindings of the reference are not built).")
+        return learner_for(model.get_framework())
