@@ -175,7 +175,7 @@ def test_small_seams():
 
     assert learner_for(Framework.PYTORCH.value).__name__ == "TorchLearner"
     try:
-        learner_for("flax")
+        learner_for("no-such-framework")
         raise AssertionError("expected ValueError")
     except ValueError as e:
         assert "register_learner" in str(e)
