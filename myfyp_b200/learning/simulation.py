@@ -90,3 +90,6 @@ def try_init_learner_with_simulation(learner: Learner, slots_per_device: Optiona
     if slots_per_device is not None:
         FitPool.configure(slots_per_device)
     return VirtualNodeLearner(learner)
+
+
+try_init_learner_with_ray = try_init_learner_with_simulation  # the reference's name

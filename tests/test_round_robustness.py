@@ -187,6 +187,28 @@ def test_small_seams():
 
     assert One() is One()
 
+    from myfyp_b200.learning.simulation import try_init_learner_with_ray, try_init_learner_with_simulation
+    from myfyp_b200.management.decorators import AsyncLogger, FileLogger, LoggerDecorator, RayP2PFLogger, WebP2PFLogger  # noqa: F401
+    from myfyp_b200.utils.check_ray import ray_installed
+
+    assert try_init_learner_with_ray is try_init_learner_with_simulation and ray_installed() is False
+
+    class _L:
+        calls = []
+
+        def enable_async(self):
+            self.calls.append("async")
+
+        def enable_file_logging(self, d=None):
+            self.calls.append(("file", d))
+
+        def info(self, node, msg):
+            self.calls.append((node, msg))
+
+    stacked = FileLogger(AsyncLogger(_L()), "/tmp/x")
+    stacked.info("n", "hello")
+    assert _L.calls == ["async", ("file", "/tmp/x"), ("n", "hello")]
+
     ops.order_after_producers([torch.zeros(3)], torch.device("cpu"))  # CPU: nothing to order, must not touch CUDA
     was = tr.ENABLED
     try:
