@@ -23,7 +23,7 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--rounds", type=int, default=2)
     ap.add_argument("--epochs", type=int, default=1)
     ap.add_argument("--protocol", default="memory", choices=["memory", "grpc", "unix"])
-    ap.add_argument("--framework", default="pytorch", choices=["pytorch"], help="only the PyTorch binding exists here")
+    ap.add_argument("--framework", default="pytorch", choices=["pytorch", "tensorflow", "flax"], help="tensorflow / flax: host-side bindings, need those frameworks installed (MLP only)")
     ap.add_argument("--aggregator", default="fedavg", choices=["fedavg", "fedmedian", "trimmedmean", "krum", "multikrum", "scaffold", "fedprox"])
     ap.add_argument("--topology", default="line", choices=["star", "full", "line", "ring", "random"])
     ap.add_argument("--model", default="mlp", choices=["mlp", "cnn", "resnet18"])
@@ -39,7 +39,34 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--show_metrics", action="store_true", help="print the metric stores and write them to --out")
     ap.add_argument("--out", default="mnist_metrics.json")
     ap.add_argument("--log-level", default="INFO")
+    ap.add_argument("--profiling", action="store_true", help="cProfile the run and print the top functions (the reference uses yappi)")
+    ap.add_argument("--plot", default=None, help="write the global metrics as a PNG (matplotlib Agg backend; never opens a window)")
     return ap.parse_args()
+
+
+def _plot(global_logs, path: str) -> None:
+    """Global metrics per node as a PNG - headless (Agg); skipped with a message when matplotlib is missing."""
+    try:
+        import matplotlib
+
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+    except ImportError:
+        print("matplotlib is not installed: no plot written")
+        return
+    for exp, per_node in global_logs.items():
+        names = sorted({k for m in per_node.values() for k in m})
+        fig, axes = plt.subplots(1, max(len(names), 1), figsize=(5 * max(len(names), 1), 4), squeeze=False)
+        for ax, name in zip(axes[0], names):
+            for node, metrics in per_node.items():
+                if name in metrics:
+                    ax.plot([r for r, _ in metrics[name]], [v for _, v in metrics[name]], label=node)
+            ax.set_title(f"{exp}: {name}")
+            ax.set_xlabel("round")
+        fig.savefig(path)
+        plt.close(fig)
+        print(f"plot written to {path}")
+        return
 
 
 def main() -> None:
@@ -70,6 +97,21 @@ def main() -> None:
     strat = {"iid": RandomIIDPartitionStrategy, "dirichlet": DirichletPartitionStrategy, "label-skew": LabelSkewedPartitionStrategy}[a.partition]
     parts = data.generate_partitions(a.nodes, strat, seed=a.seed)
     mk_model = {"mlp": mlp_model, "cnn": cnn_model, "resnet18": resnet18_model}[a.model]
+    if a.framework == "tensorflow":
+        from myfyp_b200.learning.frameworks.tensorflow.keras_model import MLP as KerasMLP
+        from myfyp_b200.learning.frameworks.tensorflow.keras_model import KerasModel
+
+        mk_model = lambda seed=None: KerasModel(KerasMLP())  # noqa: E731
+    elif a.framework == "flax":
+        import jax
+        import numpy as np
+
+        from myfyp_b200.learning.frameworks.flax.flax_model import MLP as FlaxMLP
+        from myfyp_b200.learning.frameworks.flax.flax_model import FlaxModel
+
+        def mk_model(seed=0):
+            module = FlaxMLP()
+            return FlaxModel(module, init_params=module.init(jax.random.PRNGKey(seed or 0), np.zeros((1, 28, 28), np.float32))["params"])
     mk_agg = {
         "fedavg": FedAvg, "fedmedian": FedMedian, "trimmedmean": lambda: TrimmedMean(trim=max(1, a.byzantine)), "krum": lambda: Krum(f=a.byzantine),
         "multikrum": lambda: Krum(f=a.byzantine, m=max(1, a.train_set_size - a.byzantine)), "scaffold": lambda: Scaffold(global_lr=1.0), "fedprox": lambda: FedProx(mu=0.01),
@@ -90,11 +132,24 @@ def main() -> None:
     if a.drop_node_at_round >= 0:
         fi.drop_at(nodes[-1], a.drop_node_at_round)
 
+    prof = None
+    if a.profiling:
+        import cProfile
+
+        prof = cProfile.Profile()
+        prof.enable()
     t0 = time.time()
     nodes[0].set_start_learning(rounds=a.rounds, epochs=a.epochs)
     alive = nodes[:-1] if a.drop_node_at_round >= 0 else nodes
     wait_to_finish(alive, timeout=3600)
     dt = time.time() - t0
+    if prof is not None:
+        import pstats
+
+        prof.disable()
+        pstats.Stats(prof).sort_stats("cumulative").print_stats(25)
+    if a.plot:
+        _plot(logger.get_global_logs(), a.plot)
     if a.measure_time:
         print(f"--- {dt:.2f} seconds --- ({a.rounds / dt:.2f} rounds/s)")
     if a.show_metrics:
