@@ -102,3 +102,6 @@ class Settings(metaclass=_SettingsMeta):
     GRPC_LOCAL_SHORTCUT: bool = True
     # Default experiment name (reference hard-codes "experiment").
     EXPERIMENT_NAME: str = "experiment"
+    # Directory for per-round checkpoints (wire-layout blob + JSON side-car per node); None = off.  (B200 addition; the
+    # reference has no disk checkpoints.)
+    CHECKPOINT_DIR: str | None = None

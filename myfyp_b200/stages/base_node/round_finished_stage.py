@@ -5,6 +5,7 @@ from __future__ import annotations
 from typing import Type, Union
 
 from myfyp_b200.management.logger import logger
+from myfyp_b200.settings import Settings
 from myfyp_b200.stages.base_node.train_stage import evaluate_and_broadcast
 from myfyp_b200.stages.stage import Stage
 from myfyp_b200.stages.stage_factory import StageFactory
@@ -25,6 +26,15 @@ class RoundFinishedStage(Stage):
         state.increase_round()
         logger.round_finished(state.addr)
         logger.info(state.addr, f"🎉 Round {state.round} of {state.total_rounds} finished.")
+        if Settings.CHECKPOINT_DIR:
+            # the model every node holds after the round, in the wire layout, plus the experiment position (resume: utils/checkpoint.py)
+            try:
+                from myfyp_b200.utils.checkpoint import save_checkpoint
+
+                name = state.addr.replace(":", "_").replace("/", "_")
+                save_checkpoint(f"{Settings.CHECKPOINT_DIR}/{name}.ckpt", learner.get_model(), state.round, state.total_rounds, state.exp_name)
+            except Exception as e:  # noqa: BLE001 - a full disk must not stop the federation
+                logger.error(state.addr, f"checkpoint failed: {e}")
         if state.round is None or state.total_rounds is None:
             raise ValueError("Round or total rounds not set.")
         if state.round < state.total_rounds:

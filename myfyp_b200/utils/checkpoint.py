@@ -48,3 +48,14 @@ def save_node(node, directory: str) -> str:
     path = os.path.join(directory, f"{node.addr.replace(':', '_').replace('/', '_')}.ckpt")
     save_checkpoint(path, node.get_model(), st.round, st.total_rounds, st.exp_name)
     return path
+
+
+def resume_node(node, path: str) -> int:
+    """Load a checkpoint into ``node``'s model and return the number of rounds that were still to run when it was written
+    (``node.set_start_learning(rounds=resume_node(node, path), epochs=...)`` on the initiator continues the experiment; the other
+    nodes receive the restored parameters through the usual ``init_model`` diffusion)."""
+    meta = load_checkpoint(path, node.get_model())
+    if node.learner is not None:
+        node.learner.set_model(node.get_model())
+    total, done = meta.get("total_rounds"), meta.get("round")
+    return max(int(total) - int(done), 0) if total is not None and done is not None else 0

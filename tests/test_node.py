@@ -248,3 +248,73 @@ def test_node_api_guards():
     n.stop()
     with pytest.raises(NodeRunningException):
         n.assert_running(True)
+
+
+def test_per_round_checkpoints_and_resume(tmp_path):
+    """`Settings.CHECKPOINT_DIR`: every node writes the wire-layout blob + its experiment position after each round;
+    `resume_node` restores a fresh node from it and says how many rounds were left (the reference has neither)."""
+    import os
+
+    from myfyp_b200.utils.checkpoint import resume_node
+
+    Settings.CHECKPOINT_DIR = str(tmp_path)
+    nodes = _nodes(2)
+    try:
+        nodes[0].connect(nodes[1].addr)
+        wait_convergence(nodes, 1, only_direct=True, wait=10)
+        nodes[0].set_start_learning(rounds=2, epochs=1)
+        wait_to_finish(nodes, timeout=60)
+        files = sorted(f for f in os.listdir(tmp_path) if f.endswith(".ckpt"))
+        assert len(files) == 2
+        fresh = _nodes(1)[0]
+        try:
+            left = resume_node(fresh, os.path.join(tmp_path, files[0]))
+            assert left == 0  # written after the last round: 2 of 2 done
+            for a, b in zip(fresh.get_model().get_parameters(), nodes[0].get_model().get_parameters()):
+                np.testing.assert_allclose(a, b, atol=1e-6)
+        finally:
+            fresh.stop()
+    finally:
+        Settings.CHECKPOINT_DIR = None
+        _stop(nodes)
+
+
+def test_randomised_message_delays_do_not_break_a_run():
+    """Stress: every delivery of the in-memory protocol is delayed by a random 0-15 ms, so ballots, announcements
+    and model offers overtake each other and nodes drift a stage or a round apart; the federation must still finish every
+    round with equal models and without sitting out a time-out."""
+    import random as _random
+
+    from myfyp_b200.communication.protocols.memory.memory_server import InMemoryServer
+
+    Settings.VOTE_TIMEOUT = 30
+    Settings.AGGREGATION_TIMEOUT = 30
+    Settings.TRAIN_SET_SIZE = 4
+    rng = _random.Random(7)
+    orig_msg, orig_w = InMemoryServer.send_message, InMemoryServer.send_weights
+
+    def slow_msg(self, request):
+        if request.get("cmd") != "beat":
+            time.sleep(rng.random() * 0.015)
+        return orig_msg(self, request)
+
+    def slow_w(self, request):
+        time.sleep(rng.random() * 0.015)
+        return orig_w(self, request)
+
+    InMemoryServer.send_message, InMemoryServer.send_weights = slow_msg, slow_w
+    n = 6
+    nodes = _nodes(n, samples=64)
+    try:
+        TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.RING, n), nodes)
+        wait_convergence(nodes, n - 1, only_direct=False, wait=20)
+        t0 = time.time()
+        nodes[0].set_start_learning(rounds=5, epochs=1)
+        wait_to_finish(nodes, timeout=25)
+        assert time.time() - t0 < 25
+        for nd in nodes:
+            _check_history(nd, 5)
+        check_equal_models(nodes)
+    finally:
+        InMemoryServer.send_message, InMemoryServer.send_weights = orig_msg, orig_w
+        _stop(nodes)
