@@ -19,6 +19,7 @@ from myfyp_b200.communication.commands.message.models_ready_command import Model
 from myfyp_b200.communication.commands.weights.partial_model_command import PartialModelCommand
 from myfyp_b200.learning.aggregators.aggregator import NoModelsToAggregateError
 from myfyp_b200.management.logger import logger
+from myfyp_b200.management.nvtx import nvtx_range
 from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
 from myfyp_b200.stages.base_node.start_learning_stage import _transport
@@ -60,7 +61,8 @@ class TrainStage(Stage):
             lap("evaluate")
 
             logger.info(state.addr, "🏋️‍♀️ Training...")
-            learner.fit()
+            with nvtx_range(f"{state.addr}/fit"):
+                learner.fit()
             check_early_stop(state)
             lap("fit")
 
@@ -71,7 +73,8 @@ class TrainStage(Stage):
             check_early_stop(state)
             lap("gossip")
 
-            agg_model = aggregator.wait_and_get_aggregation()
+            with nvtx_range(f"{state.addr}/aggregate"):
+                agg_model = aggregator.wait_and_get_aggregation()
             lap("aggregate")
             learner.set_model(agg_model)
             communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))

@@ -13,6 +13,9 @@ from myfyp_b200.stages.stage import Stage
 from myfyp_b200.stages.stage_factory import StageFactory
 
 
+from myfyp_b200.management.nvtx import nvtx_range
+
+
 class StageWorkflow:
     def __init__(self, first_stage: Type[Stage]) -> None:
         self.current_stage = first_stage
@@ -26,7 +29,9 @@ class StageWorkflow:
             name = self.current_stage.name()
             self.history.append(name)
             t0 = time.perf_counter()
-            next_stage = self.current_stage.execute(**kwargs)
+            st = kwargs.get("state")
+            with nvtx_range(f"{getattr(st, 'addr', '?')}/{name}"):
+                next_stage = self.current_stage.execute(**kwargs)
             self.timings.append((name, time.perf_counter() - t0))
             if next_stage is None:  # every stage turns an early stop into None itself
                 self.finished = True
