@@ -1,7 +1,7 @@
 """``init_model`` (reference: commands/weights/init_model_command.py:31-97)."""
 
 import threading
-from typing import Callable, Optional
+from typing import Callable
 
 from myfyp_b200.communication.commands.command import Command
 from myfyp_b200.communication.commands.weights._common import handle_bad_model

@@ -17,7 +17,7 @@ unknown field and simply floods as before, so mixed deployments still work.
 
 from __future__ import annotations
 
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Dict, Optional, Tuple
 
 _MASK64 = (1 << 64) - 1
 

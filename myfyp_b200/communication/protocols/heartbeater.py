@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import threading
 import time
-from typing import Optional
+
 
 from myfyp_b200.communication.protocols.client import Client
 from myfyp_b200.communication.protocols.neighbors import Neighbors

@@ -14,7 +14,7 @@ fused K-way kernel (A8) over both sets of slabs.  ``partial_aggregation=False``.
 
 from __future__ import annotations
 
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict, List
 
 import numpy as np
 import torch

@@ -9,7 +9,7 @@ aggregated one (rebuilding optimizer state around a deep copy); here the aggrega
 from __future__ import annotations
 
 import abc
-from typing import Dict, List, Optional, Union
+from typing import Dict, List, Union
 
 import numpy as np
 

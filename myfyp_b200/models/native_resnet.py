@@ -16,7 +16,7 @@ configs 3-4 name it).
 
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 

@@ -18,7 +18,7 @@ from __future__ import annotations
 
 import dataclasses
 import threading
-from typing import Dict, List, Optional
+from typing import Optional
 
 import torch
 

@@ -16,7 +16,7 @@ from __future__ import annotations
 import ctypes
 import pickle
 import threading
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict, List
 
 import torch
 

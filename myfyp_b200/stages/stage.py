@@ -3,7 +3,7 @@
 from __future__ import annotations
 
 import abc
-from typing import Optional, Type, Union
+from typing import Type, Union
 
 
 class EarlyStopException(Exception):

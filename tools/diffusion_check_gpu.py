@@ -7,7 +7,6 @@ from myfyp_b200.learning.dataset import P2PFLDataset, RandomIIDPartitionStrategy
 from myfyp_b200.management.logger import logger
 from myfyp_b200.models import resnet18_model
 from myfyp_b200.node import Node
-from myfyp_b200.settings import Settings
 from myfyp_b200.utils.utils import set_fast_settings
 from myfyp_b200.utils.topologies import TopologyFactory
 set_fast_settings(train_set_size=3)

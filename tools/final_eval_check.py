@@ -1,5 +1,5 @@
 """After a short ResNet-18 federation on the GPU: logged per-round accuracy vs learner.evaluate() vs a plain torch eval-mode forward."""
-import os, sys, time, json
+import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from myfyp_b200.communication.protocols.memory.memory_communication_protocol import InMemoryCommunicationProtocol
