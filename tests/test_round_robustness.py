@@ -238,3 +238,48 @@ def test_aggregates_are_computed_where_the_node_lives():
     out = agg.aggregate(ms)
     np.testing.assert_allclose(out.get_parameters()[0], ref[0] + 0.5, atol=1e-6)
     assert FedAvg("nobody").local_device(ms) == ms[0].slab.device
+
+
+def test_a_peer_that_lacks_our_model_is_offered_exactly_that_model():
+    """TrainStage's offer policy: own model alone first (it can never overlap what the peer holds), other nodes' models only to
+    peers that already have ours and only after `FORWARD_GRACE` (the origin usually delivers directly meanwhile)."""
+    from myfyp_b200.settings import Settings
+    from myfyp_b200.stages.base_node.train_stage import TrainStage
+
+    keep = Settings.FORWARD_GRACE
+    Settings.FORWARD_GRACE = 0.05
+    st = _state(1)
+    st.train_set = ["me", "a", "b"]
+    base = mlp_model(seed=0)
+    ref = base.get_parameters()
+    agg = FedAvg("me")
+    agg.set_nodes_to_aggregate(st.train_set)
+    agg.add_model(base.build_copy(params=ref, num_samples=10, contributors=["me"]))
+    agg.add_model(base.build_copy(params=[p + 1 for p in ref], num_samples=10, contributors=["a"]))
+    captured = {}
+
+    class _P(_Proto):
+        def gossip_weights(self, early_stopping_fn, get_candidates_fn, status_fn, model_fn, **kw):
+            captured.update(candidates=get_candidates_fn, model=model_fn)
+
+        def build_weights(self, cmd, round, model, contributors=None, weight=1):
+            return {"cmd": cmd, "round": round, "contributors": list(contributors), "weight": weight}
+
+        def fabric_reachable(self, nei):
+            return False
+
+    try:
+        TrainStage._TrainStage__gossip_model_aggregation(st, _P(["a", "b"]), agg)
+        assert sorted(captured["candidates"]()) == ["a", "b"]
+        first = captured["model"]("b")  # b has announced nothing: it gets our own model, not the {me, a} aggregate
+        assert first["contributors"] == ["me"] and first["cmd"] == "partial_model"
+        assert captured["model"]("b") is None  # the same offer is not repeated right away
+        st.models_aggregated["b"] = ["me"]  # b has ours now and still lacks a's
+        assert captured["model"]("b") is None  # pure forwarding waits for the grace period
+        time.sleep(0.08)
+        fwd = captured["model"]("b")
+        assert fwd is not None and fwd["contributors"] == ["a"]
+        st.models_aggregated["b"] = ["me", "a"]
+        assert "b" not in captured["candidates"]() or captured["model"]("b") is None
+    finally:
+        Settings.FORWARD_GRACE = keep
