@@ -152,7 +152,7 @@ def test_train_set_member_dying_mid_round_costs_no_timeouts():
     import threading
 
     Settings.HEARTBEAT_PERIOD, Settings.HEARTBEAT_TIMEOUT = 0.3, 2
-    Settings.VOTE_TIMEOUT, Settings.AGGREGATION_TIMEOUT = 20, 40
+    Settings.VOTE_TIMEOUT, Settings.AGGREGATION_TIMEOUT = 45, 60
     Settings.TRAIN_SET_SIZE = 6
     Settings.TTL = 16
     n = 16
@@ -176,7 +176,7 @@ def test_train_set_member_dying_mid_round_costs_no_timeouts():
         nodes[0].set_start_learning(rounds=4, epochs=1)
         alive = lambda: [nd for nd in nodes if nd not in killed]  # noqa: E731
         while not all(nd.learning_workflow.finished for nd in alive()):
-            assert time.time() - t0 < 19, "the survivors are sitting out a time-out"
+            assert time.time() - t0 < 40, "the survivors are sitting out a time-out"  # typically 9-11 s: 4 rounds + failure detection
             time.sleep(0.05)
         assert killed
         for nd in alive():
@@ -211,7 +211,7 @@ def test_rejoin_running_experiment():
     try:
         TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.FULL, 3), nodes)
         wait_convergence(nodes, 2, only_direct=True, wait=10)
-        nodes[0].set_start_learning(rounds=6, epochs=1)
+        nodes[0].set_start_learning(rounds=15, epochs=1)  # long enough for the newcomer to be invited while it still runs
         while nodes[0].state.round is None or nodes[0].state.round < 1:
             time.sleep(0.01)
         late.start()
@@ -287,8 +287,8 @@ def test_randomised_message_delays_do_not_break_a_run():
 
     from myfyp_b200.communication.protocols.memory.memory_server import InMemoryServer
 
-    Settings.VOTE_TIMEOUT = 30
-    Settings.AGGREGATION_TIMEOUT = 30
+    Settings.VOTE_TIMEOUT = 60
+    Settings.AGGREGATION_TIMEOUT = 60
     Settings.TRAIN_SET_SIZE = 4
     rng = _random.Random(7)
     orig_msg, orig_w = InMemoryServer.send_message, InMemoryServer.send_weights
@@ -310,8 +310,8 @@ def test_randomised_message_delays_do_not_break_a_run():
         wait_convergence(nodes, n - 1, only_direct=False, wait=20)
         t0 = time.time()
         nodes[0].set_start_learning(rounds=5, epochs=1)
-        wait_to_finish(nodes, timeout=25)
-        assert time.time() - t0 < 25
+        wait_to_finish(nodes, timeout=50)
+        assert time.time() - t0 < 50  # typically 5-8 s; any time-out sat out would push it past 60
         for nd in nodes:
             _check_history(nd, 5)
         check_equal_models(nodes)
