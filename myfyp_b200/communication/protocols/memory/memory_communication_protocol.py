@@ -1,119 +1,25 @@
-"""In-memory protocol = neighbours + client + gossiper + server + heartbeater.
-
-Reference: communication/protocols/memory/memory_communication_protocol.py:64-268.
-"""
+"""In-memory transport: every node of the process registers its server in ``ServerRegistry`` and a "send" is a method call
+on the peer's server object - nothing is serialised, weights travel as device descriptors.
+(Reference: communication/protocols/memory/memory_communication_protocol.py:64-268; the facade itself is ``ComposedProtocol``.)"""
 
 from __future__ import annotations
 
 import random
-from typing import Any, Callable, Dict, List, Optional, Union
+from typing import List, Optional
 
 from myfyp_b200.communication.commands.command import Command
-from myfyp_b200.communication.commands.message.heartbeat_command import HeartbeatCommand
-from myfyp_b200.communication.protocols.communication_protocol import CommunicationProtocol, running
-from myfyp_b200.communication.protocols.gossiper import Gossiper
-from myfyp_b200.communication.protocols.heartbeater import Heartbeater
+from myfyp_b200.communication.protocols.composed_protocol import ComposedProtocol
 from myfyp_b200.communication.protocols.memory.memory_client import InMemoryClient
 from myfyp_b200.communication.protocols.memory.memory_neighbors import InMemoryNeighbors
 from myfyp_b200.communication.protocols.memory.memory_server import InMemoryServer
 from myfyp_b200.communication.protocols.memory.registry import ServerRegistry
-from myfyp_b200.settings import Settings
 
 
-class InMemoryCommunicationProtocol(CommunicationProtocol):
+class InMemoryCommunicationProtocol(ComposedProtocol):
     def __init__(self, addr: Optional[str] = None, commands: Optional[List[Command]] = None) -> None:
         # Node() passes its default "127.0.0.1": for an in-process protocol that means "pick a name"
-        self.addr = addr if addr and addr != "127.0.0.1" else f"node-{random.randint(0, 99999999)}"
-        self._neighbors = InMemoryNeighbors(self.addr)
-        self._client = InMemoryClient(self.addr, self._neighbors)
-        self._gossiper = Gossiper(self.addr, self._client)
-        self._server = InMemoryServer(self.addr, self._gossiper, self._neighbors, commands)
-        self._heartbeater = Heartbeater(self.addr, self._neighbors, self._client)
-        self._server.add_command(HeartbeatCommand(self._heartbeater))
-        if commands:
-            self._server.add_command(commands)
-
-    def get_address(self) -> str:
-        return self.addr
-
-    def start(self) -> None:
-        self._server.start()
-        self._heartbeater.start()
-        self._gossiper.start()
-
-    @running
-    def stop(self) -> None:
-        self._heartbeater.stop()
-        self._gossiper.stop()
-        self._neighbors.clear_neighbors()
-        self._server.stop()
-
-    def add_command(self, cmds: Union[Command, List[Command]]) -> None:
-        self._server.add_command(cmds)
-
-    @running
-    def connect(self, addr: str, non_direct: bool = False) -> bool:
-        return self._neighbors.add(addr, non_direct=non_direct)
-
-    @running
-    def disconnect(self, nei: str, disconnect_msg: bool = True) -> None:
-        self._neighbors.remove(nei, disconnect_msg=disconnect_msg)
-
-    def build_msg(self, cmd: str, args: Optional[List[str]] = None, round: Optional[int] = None) -> Any:
-        return self._client.build_message(cmd, args, round)
-
-    def build_weights(self, cmd: str, round: int, serialized_model: Any, contributors: Optional[List[str]] = None, weight: int = 1) -> Any:
-        return self._client.build_weights(cmd, round, serialized_model, contributors, weight)
-
-    @running
-    def send(self, nei: str, msg: Any, raise_error: bool = False, remove_on_error: bool = True) -> None:
-        self._client.send(nei, msg, raise_error=raise_error, remove_on_error=remove_on_error)
-
-    @running
-    def broadcast(self, msg: Any, node_list: Optional[List[str]] = None) -> None:
-        # the originator marks its own hash as seen so the flood never comes back to it
-        if isinstance(msg, dict) and "hash" in msg:
-            self._gossiper.check_and_set_processed(msg["hash"])
-        self._client.broadcast(msg, node_list)
-
-    @running
-    def broadcast_async(self, msg: Any, coalesce: bool = False, linger: float = 0.0) -> None:
-        """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers).
-        ``coalesce``: a queued, not yet sent message of the same command and round is superseded by this one;
-        ``linger``: hold a coalescable message back this long so that a burst of them collapses into one."""
-        if isinstance(msg, dict) and "hash" in msg:
-            self._gossiper.check_and_set_processed(msg["hash"])
-        nodes = list(self._neighbors.get_all(only_direct=True))
-        if isinstance(msg, dict) and "hash" in msg:
-            msg["seen"] = [self.addr, *nodes]
-        key = (msg.get("cmd"), msg.get("round")) if coalesce and isinstance(msg, dict) else None
-        self._gossiper.add_message(msg, nodes, coalesce_key=key, linger=linger)
-
-    @running
-    def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]:
-        return self._neighbors.get_all(only_direct)
-
-    @running
-    def wait_for_termination(self) -> None:
-        self._server.wait_for_termination()
-
-    @running
-    def gossip_weights(
-        self,
-        early_stopping_fn: Callable[[], bool],
-        get_candidates_fn: Callable[[], List[str]],
-        status_fn: Callable[[], Any],
-        model_fn: Callable[[str], Any],
-        period: Optional[float] = None,
-        create_connection: bool = False,
-        wait_fn: Optional[Callable[[float], None]] = None,
-    ) -> None:
-        if period is None:
-            period = Settings.GOSSIP_MODELS_PERIOD
-        self._gossiper.gossip_weights(early_stopping_fn, get_candidates_fn, status_fn, model_fn, period, create_connection, wait_fn)
-
-    def on_neighbors_changed(self, fn: Callable[[], None]) -> None:
-        self._neighbors.on_change(fn)
+        name = addr if addr and addr != "127.0.0.1" else f"node-{random.randint(0, 99999999)}"
+        self._assemble(name, InMemoryNeighbors(name), InMemoryClient, InMemoryServer, commands)
 
     def fabric_reachable(self, nei: str) -> bool:
         """Same process => the peer's slab is dereferenceable (same GPU or via P2P)."""

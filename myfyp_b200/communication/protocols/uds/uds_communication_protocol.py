@@ -21,13 +21,10 @@ from multiprocessing.connection import Listener
 from typing import Any, List, Optional, Tuple
 
 from myfyp_b200.communication.commands.command import Command
-from myfyp_b200.communication.commands.message.heartbeat_command import HeartbeatCommand
-from myfyp_b200.communication.protocols.gossiper import Gossiper
 from myfyp_b200.communication.protocols.grpc.grpc_client import GrpcClient
 from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
 from myfyp_b200.communication.protocols.grpc.grpc_neighbors import GrpcNeighbors, LocalStub
 from myfyp_b200.communication.protocols.grpc.grpc_server import GrpcServer, _local_lock, _local_servers, local_server
-from myfyp_b200.communication.protocols.heartbeater import Heartbeater
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
 
@@ -168,17 +165,11 @@ class UdsServer(GrpcServer):
 
 
 class UdsCommunicationProtocol(GrpcCommunicationProtocol):
+    """Same servicer / client / neighbour logic as the gRPC transport, over a unix-socket pipe (and the same fabric test)."""
+
     def __init__(self, addr: Optional[str] = None, commands: Optional[List[Command]] = None) -> None:
         if not addr or addr == "127.0.0.1":
             addr = f"{SCHEME}/tmp/myfyp-b200-{os.getpid()}-{random.randint(0, 1 << 30)}.sock"
         elif not addr.startswith(SCHEME):
             addr = SCHEME + addr
-        self.addr = addr
-        self._neighbors = UdsNeighbors(self.addr)
-        self._client = GrpcClient(self.addr, self._neighbors)
-        self._gossiper = Gossiper(self.addr, self._client)
-        self._server = UdsServer(self.addr, self._gossiper, self._neighbors, commands)
-        self._heartbeater = Heartbeater(self.addr, self._neighbors, self._client)
-        self._server.add_command(HeartbeatCommand(self._heartbeater))
-        if commands:
-            self._server.add_command(commands)
+        self._assemble(addr, UdsNeighbors(addr), GrpcClient, UdsServer, commands)

@@ -1,21 +1,29 @@
 """StartLearningStage (reference: stages/base_node/start_learning_stage.py:44-112).
 
-Set the experiment, wait until this node's model is initialised (the initiator owns the weights, everyone
-else blocks until an ``init_model`` arrives), announce it, gossip the initial weights to direct neighbours
-that have not announced theirs, let heartbeats converge, then vote.
+Install the experiment, wait until this node holds the initial model (the initiator owns it, everybody else blocks until an
+``init_model`` arrives - interruptibly, unlike the reference's bare ``lock.acquire()``), announce that, hand the model on to
+direct neighbours that have not announced theirs, give fresh heartbeats time to flood, then vote.
 """
 
 from __future__ import annotations
 
 import time
-from typing import Any, List, Optional, Type, Union
+from typing import Optional, Type, Union
 
 from myfyp_b200.communication.commands.message.model_initialized_command import ModelInitializedCommand
 from myfyp_b200.communication.commands.weights.init_model_command import InitModelCommand
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
+from myfyp_b200.stages.diffusion import Diffusion
 from myfyp_b200.stages.stage import Stage
 from myfyp_b200.stages.stage_factory import StageFactory
+
+def _holds_initial_model(state) -> bool:
+    """Block (in slices, so a stop is noticed) until the model-initialised lock can be taken; False when the experiment stopped."""
+    while not state.model_initialized_lock.acquire(timeout=0.25):
+        if state.round is None:
+            return False
+    return True
 
 
 class StartLearningStage(Stage):
@@ -25,53 +33,25 @@ class StartLearningStage(Stage):
 
     @staticmethod
     def execute(rounds: Optional[int] = None, epochs: Optional[int] = None, state=None, learner=None, communication_protocol=None, aggregator=None, start_round: int = 0, **kwargs) -> Union[Type[Stage], None]:
-        if rounds is None or epochs is None or state is None or learner is None or communication_protocol is None or aggregator is None:
+        if None in (rounds, epochs, state, learner, communication_protocol, aggregator):
             raise Exception("Invalid parameters on StartLearningStage.")
-        with state.start_thread_lock:
+        t_start = time.monotonic()
+        with state.start_thread_lock:  # one learning thread per node
             state.set_experiment(Settings.EXPERIMENT_NAME, rounds, round=start_round)
             learner.set_epochs(epochs)
             logger.experiment_started(state.addr, state.experiment)
-        begin = time.monotonic()
 
-        logger.info(state.addr, "⏳ Waiting initialization.")
-        # interruptible version of the reference's blocking lock.acquire()
-        while not state.model_initialized_lock.acquire(timeout=0.25):
-            if state.round is None:
-                return None
+        logger.info(state.addr, "⏳ Waiting for the initial model.")
+        if not _holds_initial_model(state):
+            return None
         communication_protocol.broadcast(communication_protocol.build_msg(ModelInitializedCommand.get_name()))
 
-        logger.info(state.addr, "🗣️ Gossiping model initialization.")
-        StartLearningStage.__gossip_model(state, communication_protocol, learner)
+        logger.info(state.addr, "🗣️ Passing the initial model on.")
+        uninitialised = lambda: [n for n in communication_protocol.get_neighbors(only_direct=True) if n not in state.nei_status]  # noqa: E731
+        Diffusion(state, communication_protocol, InitModelCommand.get_name(), uninitialised, learner.get_model).run()
 
         # heartbeats of freshly connected nodes must have flooded before the vote counts candidates
-        left = Settings.WAIT_HEARTBEATS_CONVERGENCE - (time.monotonic() - begin)
-        if left > 0:
-            time.sleep(left)
+        settle = Settings.WAIT_HEARTBEATS_CONVERGENCE - (time.monotonic() - t_start)
+        if settle > 0:
+            time.sleep(settle)
         return StageFactory.get_stage("VoteTrainSetStage")
-
-    @staticmethod
-    def __gossip_model(state, communication_protocol, learner) -> None:
-        def early_stopping_fn() -> bool:
-            return state.round is None
-
-        def get_candidates_fn() -> List[str]:
-            return [n for n in communication_protocol.get_neighbors(only_direct=True) if n not in state.nei_status]
-
-        def model_fn(nei: str) -> Any:
-            if state.round is None:
-                raise Exception("Round not initialized.")
-            model = learner.get_model()
-            payload = _transport(model, communication_protocol, nei)
-            return communication_protocol.build_weights(InitModelCommand.get_name(), state.round, payload)
-
-        communication_protocol.gossip_weights(
-            early_stopping_fn, get_candidates_fn, get_candidates_fn, model_fn, wait_fn=state.wait_change
-        )
-
-
-def _transport(model, communication_protocol, nei: str):
-    """Device descriptor when ``nei`` can dereference it, the reference pickle otherwise."""
-    enc = getattr(model, "encode_for_transport", None)
-    if enc is None:
-        return model.encode_parameters()
-    return enc(communication_protocol.fabric_reachable(nei))

@@ -22,7 +22,7 @@ from myfyp_b200.management.logger import logger
 from myfyp_b200.management.nvtx import nvtx_range
 from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
-from myfyp_b200.stages.base_node.start_learning_stage import _transport
+from myfyp_b200.stages.diffusion import transport_payload as _transport
 from myfyp_b200.stages.stage import EarlyStopException, Stage, check_early_stop
 from myfyp_b200.stages.stage_factory import StageFactory
 

@@ -1,12 +1,14 @@
 """VoteTrainSetStage (reference: stages/base_node/vote_train_set_stage.py:43-184).
 
-Vote: sample ``min(TRAIN_SET_SIZE, n)`` candidates among all known nodes + self with weights
-``floor(randint(0,1000)/(i+1))``, broadcast.  Tally when every live neighbour has voted or at
-``VOTE_TIMEOUT``: sum weights, order by address descending then (stable) by votes descending, keep the top
-``TRAIN_SET_SIZE`` (SURVEY Q18 - every node must reach the same set), drop nodes that vanished.
+Election of the round's train set, in three steps every node performs on its own:
 
-Event-driven: instead of re-polling every 2 s the stage sleeps on the node state's condition variable, which
-vote arrivals and neighbour-table changes notify.
+1. ``cast_ballot``   pick ``min(TRAIN_SET_SIZE, n)`` candidates among all known nodes + self, weight the i-th pick
+                     ``floor(randint(0, 1000) / (i + 1))``, flood the ballot;
+2. ``collect``       sleep on the node's condition variable until a ballot of every live neighbour is in (ballot arrivals and
+                     neighbour-table changes wake it) or ``VOTE_TIMEOUT`` passes;
+3. ``elect``         add up ALL ballots received for this round - also those of nodes that have left the neighbour table since
+                     (otherwise survivors of a node death elect different sets) - rank by votes, ties by address (descending,
+                     SURVEY Q18), keep the first ``TRAIN_SET_SIZE`` that are still alive.
 """
 
 from __future__ import annotations
@@ -22,6 +24,51 @@ from myfyp_b200.settings import Settings
 from myfyp_b200.stages.stage import EarlyStopException, Stage, check_early_stop
 from myfyp_b200.stages.stage_factory import StageFactory
 
+Ballot = Dict[str, int]
+
+
+def cast_ballot(state, communication_protocol) -> Ballot:
+    known = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
+    picks = random.sample(sorted(known), min(Settings.TRAIN_SET_SIZE, len(known)))
+    ballot: Ballot = {node: math.floor(random.randint(0, 1000) / (rank + 1)) for rank, node in enumerate(picks)}
+    with state.train_set_votes_lock:
+        state.train_set_votes[state.addr] = dict(ballot)
+    logger.info(state.addr, "🗳️ Ballot cast.")
+    wire = [str(x) for pair in ballot.items() for x in pair]
+    communication_protocol.broadcast(communication_protocol.build_msg(VoteTrainSetCommand.get_name(), wire, round=state.round))
+    return ballot
+
+
+def collect(state, communication_protocol) -> Dict[str, Ballot]:
+    """Every ballot of the round once all live neighbours have voted (or at VOTE_TIMEOUT); clears the ballot box."""
+    deadline = time.monotonic() + Settings.VOTE_TIMEOUT
+    while True:
+        check_early_stop(state)
+        electorate = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
+        with state.train_set_votes_lock:
+            box = dict(state.train_set_votes)
+        missing = electorate - set(box)
+        timed_out = time.monotonic() > deadline
+        if not missing or timed_out:
+            if missing:
+                logger.info(state.addr, f"Vote time-out: no ballot from {sorted(missing)}")
+            with state.train_set_votes_lock:
+                state.train_set_votes = {}
+            return box
+        seen = len(box)
+        # woken by a ballot, a neighbour change or a stop; the short time-out only bounds a lost wake-up
+        state.wait_for(lambda: state.round is None or len(state.train_set_votes) != seen, timeout=min(0.5, max(deadline - time.monotonic(), 0.01)))
+
+
+def elect(box: Dict[str, Ballot], alive: set, size: int) -> List[str]:
+    totals: Dict[str, int] = {}
+    for ballot in box.values():
+        for node, weight in ballot.items():
+            totals[node] = totals.get(node, 0) + weight
+    # most votes first; equal votes: larger address first - every node must order ties the same way
+    ranking = sorted(sorted(totals, reverse=True), key=lambda n: totals[n], reverse=True)
+    return [n for n in ranking[:size] if n in alive]
+
 
 class VoteTrainSetStage(Stage):
     @staticmethod
@@ -34,63 +81,11 @@ class VoteTrainSetStage(Stage):
             raise Exception("Invalid parameters on VoteTrainSetStage.")
         logger.round_started(state.addr, state.experiment)
         try:
-            VoteTrainSetStage.__vote(state, communication_protocol)
-            state.train_set = VoteTrainSetStage.__validate_train_set(VoteTrainSetStage.__aggregate_votes(state, communication_protocol), state, communication_protocol)
-            logger.info(state.addr, f"🚂 Train set of {len(state.train_set)} nodes: {state.train_set}")
-            if state.addr in state.train_set:
-                return StageFactory.get_stage("TrainStage")
-            return StageFactory.get_stage("WaitAggregatedModelsStage")
+            cast_ballot(state, communication_protocol)
+            box = collect(state, communication_protocol)
+            alive = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
+            state.train_set = elect(box, alive, Settings.TRAIN_SET_SIZE)
+            logger.info(state.addr, f"🚂 {len(box)} ballots -> train set of {len(state.train_set)}: {state.train_set}")
         except EarlyStopException:
             return None
-
-    @staticmethod
-    def __vote(state, communication_protocol) -> None:
-        candidates = list(communication_protocol.get_neighbors(only_direct=False))
-        if state.addr not in candidates:
-            candidates.append(state.addr)
-        samples = min(Settings.TRAIN_SET_SIZE, len(candidates))
-        voted = random.sample(candidates, samples)
-        weights = [math.floor(random.randint(0, 1000) / (i + 1)) for i in range(samples)]
-        votes = list(zip(voted, weights))
-        with state.train_set_votes_lock:
-            state.train_set_votes[state.addr] = dict(votes)
-        logger.info(state.addr, "🗳️ Sending train set vote.")
-        flat = [str(x) for pair in votes for x in pair]
-        communication_protocol.broadcast(communication_protocol.build_msg(VoteTrainSetCommand.get_name(), flat, round=state.round))
-
-    @staticmethod
-    def __aggregate_votes(state, communication_protocol) -> List[str]:
-        deadline = time.monotonic() + Settings.VOTE_TIMEOUT
-        while True:
-            check_early_stop(state)
-            neis = set(communication_protocol.get_neighbors(only_direct=False))
-            needed = neis | {state.addr}
-            # Every ballot received for this round counts, also the ballot of a node that has left the neighbour table since it
-            # voted: whether a dead node's ballot is in the tally must not depend on WHEN a node noticed the death, or the
-            # survivors elect different train sets.  (The reference filters by the current neighbours, :137-141.)
-            with state.train_set_votes_lock:
-                votes = dict(state.train_set_votes)
-            ready = needed <= set(votes.keys())
-            timeout = time.monotonic() > deadline
-            if ready or timeout:
-                if timeout and not ready:
-                    logger.info(state.addr, f"Timeout for vote aggregation. Missing votes from {needed - set(votes.keys())}")
-                tally: Dict[str, int] = {}
-                for ballot in votes.values():
-                    for k, v in ballot.items():
-                        tally[k] = tally.get(k, 0) + v
-                ordered = sorted(tally.items(), key=lambda kv: kv[0], reverse=True)  # tie-break: address, descending
-                ordered = sorted(ordered, key=lambda kv: kv[1], reverse=True)  # stable
-                top = ordered[: min(len(ordered), Settings.TRAIN_SET_SIZE)]
-                with state.train_set_votes_lock:
-                    state.train_set_votes = {}
-                logger.info(state.addr, f"🔢 Computed {len(votes)} votes.")
-                return [k for k, _ in top]
-            # woken by a vote, a neighbour change or stop; the timeout only bounds a lost wake-up
-            n_votes = len(votes)
-            state.wait_for(lambda: state.round is None or len(state.train_set_votes) != n_votes, timeout=min(0.5, max(deadline - time.monotonic(), 0.01)))
-
-    @staticmethod
-    def __validate_train_set(train_set: List[str], state, communication_protocol) -> List[str]:
-        alive = set(communication_protocol.get_neighbors(only_direct=False))
-        return [n for n in train_set if n in alive or n == state.addr]
+        return StageFactory.get_stage("TrainStage" if state.addr in state.train_set else "WaitAggregatedModelsStage")

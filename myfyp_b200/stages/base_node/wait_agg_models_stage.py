@@ -1,5 +1,6 @@
-"""WaitAggregatedModelsStage (reference: stages/base_node/wait_agg_models_stage.py:40-67): nodes outside
-the train set wait (<= AGGREGATION_TIMEOUT) for the full aggregated model, then announce ``models_ready``."""
+"""WaitAggregatedModelsStage (reference: stages/base_node/wait_agg_models_stage.py:40-67): a node outside the round's train
+set waits - on the node's condition variable, at most AGGREGATION_TIMEOUT - until a ``FullModelCommand`` has delivered the
+aggregated model, then tells everybody that it is ready for the next round."""
 
 from __future__ import annotations
 
@@ -21,15 +22,14 @@ class WaitAggregatedModelsStage(Stage):
     def execute(state=None, communication_protocol=None, **kwargs) -> Union[Type[Stage], None]:
         if state is None or communication_protocol is None:
             raise Exception("Invalid parameters on WaitAggregatedModelsStage.")
-        state.aggregated_model_event.clear()
-        logger.info(state.addr, "⏳ Waiting aggregation.")
-        ok = state.wait_for(lambda: state.aggregated_model_event.is_set() or state.round is None, timeout=Settings.AGGREGATION_TIMEOUT)
-        if state.round is None:
+        arrived = state.aggregated_model_event
+        arrived.clear()
+        logger.info(state.addr, "⏳ Waiting for the aggregated model.")
+        in_time = state.wait_for(lambda: arrived.is_set() or state.round is None, timeout=Settings.AGGREGATION_TIMEOUT)
+        if state.round is None:  # stopped while waiting
             return None
-        if ok:
-            logger.info(state.addr, "✅ Aggregation event received.")
-        else:
-            logger.warning(state.addr, "⏰ Aggregation timeout occurred.")
-            state.aggregated_model_event.set()
+        if not in_time:
+            logger.warning(state.addr, f"⏰ No aggregated model within {Settings.AGGREGATION_TIMEOUT} s: going on with the local one.")
+            arrived.set()
         communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
         return StageFactory.get_stage("GossipModelStage")
