@@ -1,4 +1,8 @@
-"""Shared error handling for weights commands."""
+"""Shared error policy of the weights commands."""
+
+import contextlib
+
+from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
 
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
@@ -19,3 +23,17 @@ def handle_bad_model(state, stop_fn, source: str, what: str, protocol=None) -> N
             protocol.disconnect(source, disconnect_msg=False)
         except Exception:
             pass
+
+
+@contextlib.contextmanager
+def bad_model_guard(state, stop_fn, source: str, protocol=None):
+    """``with bad_model_guard(...)``: anything that goes wrong while a received model is decoded / adopted / filed is the
+    SENDER's fault as far as this node can tell - apply :func:`handle_bad_model` instead of letting the handler die."""
+    try:
+        yield
+    except DecodingParamsError:
+        handle_bad_model(state, stop_fn, source, "Error decoding parameters", protocol)
+    except ModelNotMatchingError:
+        handle_bad_model(state, stop_fn, source, "Models not matching", protocol)
+    except Exception as e:  # noqa: BLE001
+        handle_bad_model(state, stop_fn, source, f"Unknown error adding model: {e}", protocol)

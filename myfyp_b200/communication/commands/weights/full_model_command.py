@@ -4,8 +4,7 @@ import threading
 from typing import Callable
 
 from myfyp_b200.communication.commands.command import Command
-from myfyp_b200.communication.commands.weights._common import handle_bad_model
-from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
+from myfyp_b200.communication.commands.weights._common import bad_model_guard
 from myfyp_b200.management.logger import logger
 
 
@@ -34,7 +33,7 @@ class FullModelCommand(Command):
             else:
                 logger.debug(st.addr, f"Model reception in a late round ({round} != {st.round}).")
                 return
-        try:
+        with bad_model_guard(st, self.stop, source, self.protocol):
             with self._mutex:
                 if st.aggregated_model_event.is_set():
                     logger.debug(st.addr, "😲 Aggregated model not expected.")
@@ -48,9 +47,3 @@ class FullModelCommand(Command):
                 st.rejoining = False
                 st.aggregated_model_event.set()
             st.notify()
-        except DecodingParamsError:
-            handle_bad_model(st, self.stop, source, "❌ Error decoding parameters", self.protocol)
-        except ModelNotMatchingError:
-            handle_bad_model(st, self.stop, source, "❌ Models not matching", self.protocol)
-        except Exception as e:  # noqa: BLE001
-            handle_bad_model(st, self.stop, source, f"❌ Unknown error adding model: {e}", self.protocol)

@@ -10,8 +10,7 @@ from typing import Callable, List, Optional
 
 from myfyp_b200.communication.commands.command import Command
 from myfyp_b200.communication.commands.message.models_aggregated_command import ModelsAggregatedCommand
-from myfyp_b200.communication.commands.weights._common import handle_bad_model
-from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
+from myfyp_b200.communication.commands.weights._common import bad_model_guard
 from myfyp_b200.management.logger import logger
 from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
@@ -62,7 +61,7 @@ class PartialModelCommand(Command):
         """File one offered model with the aggregator and announce what we hold now."""
         st = self.state
         trace(st.addr, f"recv_model<{source} {len(contributors)}")
-        try:
+        with bad_model_guard(st, self.stop, source, self.communication_protocol):
             model = self.learner.get_model().build_copy(params=weights, num_samples=num_samples, contributors=list(contributors))
             models_added = self.aggregator.add_model(model)
             trace(st.addr, f"added<{source} held={len(models_added)}")
@@ -79,9 +78,3 @@ class PartialModelCommand(Command):
                     self.communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=st.round), coalesce=True,
                     linger=0.0 if complete else Settings.ANNOUNCE_LINGER,
                 )
-        except DecodingParamsError:
-            handle_bad_model(st, self.stop, source, "Error decoding parameters", self.communication_protocol)
-        except ModelNotMatchingError:
-            handle_bad_model(st, self.stop, source, "Models not matching", self.communication_protocol)
-        except Exception as e:  # noqa: BLE001
-            handle_bad_model(st, self.stop, source, f"Unknown error adding model: {e}", self.communication_protocol)
