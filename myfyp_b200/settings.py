@@ -105,3 +105,51 @@ class Settings(metaclass=_SettingsMeta):
     # Directory for per-round checkpoints (wire-layout blob + JSON side-car per node); None = off.  (B200 addition; the
     # reference has no disk checkpoints.)
     CHECKPOINT_DIR: str | None = None
+
+    # --- loading (the reference has no files, environment variables or validation) ------------------------
+    @classmethod
+    def names(cls) -> list:
+        """Every setting (upper-case attribute), in definition order."""
+        return [k for k in vars(cls) if k.isupper() and not k.startswith("_")] + ["WAIT_HEARTBEATS_CONVERGENCE"]
+
+    @classmethod
+    def update(cls, values: dict, strict: bool = True) -> None:
+        """Set several settings at once; a value is coerced to the type of the current one (``"0.5"`` -> 0.5, ``"false"`` ->
+        False).  Unknown names raise ``KeyError`` (``strict``) - a typo must not silently configure nothing."""
+        known = set(cls.names())
+        for key, value in values.items():
+            if key not in known:
+                if strict:
+                    raise KeyError(f"unknown setting {key!r}")
+                continue
+            cur = getattr(cls, key)
+            if isinstance(value, str) and cur is not None and not isinstance(cur, str):
+                if isinstance(cur, bool):
+                    value = value.strip().lower() in ("1", "true", "yes", "on")
+                else:
+                    value = type(cur)(float(value)) if isinstance(cur, int) else type(cur)(value)
+            setattr(cls, key, value)
+
+    @classmethod
+    def update_from_env(cls, prefix: str = "MYFYP_B200_") -> list:
+        """``MYFYP_B200_TRAIN_SET_SIZE=8`` etc.; returns the names that were set."""
+        found = {k[len(prefix):]: v for k, v in os.environ.items() if k.startswith(prefix)}
+        cls.update(found, strict=False)
+        return sorted(k for k in found if k in set(cls.names()))
+
+    @classmethod
+    def load_file(cls, path: str) -> None:
+        """A JSON or YAML mapping of setting names to values."""
+        with open(path) as f:
+            text = f.read()
+        if path.endswith((".yaml", ".yml")):
+            import yaml
+
+            data = yaml.safe_load(text)
+        else:
+            import json
+
+            data = json.loads(text)
+        if not isinstance(data, dict):
+            raise ValueError(f"{path}: expected a mapping of setting names to values")
+        cls.update(data)

@@ -150,3 +150,30 @@ def test_build_entry_point():
     import __graft_entry__ as g
 
     g.build()
+
+
+def test_settings_bulk_update_env_and_file(tmp_path, monkeypatch):
+    """`Settings.update / update_from_env / load_file` (the reference can only be configured by assigning class attributes)."""
+    import json
+
+    from myfyp_b200.settings import Settings
+
+    keep = {k: getattr(Settings, k) for k in ("TRAIN_SET_SIZE", "USE_SSL", "GOSSIP_PERIOD", "LOG_LEVEL")}
+    keep_wait = Settings.__dict__.get("_WAIT_HEARTBEATS_CONVERGENCE")
+    try:
+        Settings.update({"TRAIN_SET_SIZE": "8", "USE_SSL": "false", "GOSSIP_PERIOD": "0.25", "WAIT_HEARTBEATS_CONVERGENCE": 1.5})
+        assert (Settings.TRAIN_SET_SIZE, Settings.USE_SSL, Settings.GOSSIP_PERIOD, Settings.WAIT_HEARTBEATS_CONVERGENCE) == (8, False, 0.25, 1.5)
+        with pytest.raises(KeyError):
+            Settings.update({"TRAIN_SET_SIZ": 3})
+        monkeypatch.setenv("MYFYP_B200_TRAIN_SET_SIZE", "5")
+        monkeypatch.setenv("MYFYP_B200_NOT_A_SETTING", "1")
+        assert Settings.update_from_env() == ["TRAIN_SET_SIZE"] and Settings.TRAIN_SET_SIZE == 5
+        path = tmp_path / "s.json"
+        path.write_text(json.dumps({"LOG_LEVEL": "ERROR", "TRAIN_SET_SIZE": 2}))
+        Settings.load_file(str(path))
+        assert Settings.LOG_LEVEL == "ERROR" and Settings.TRAIN_SET_SIZE == 2
+        assert "HEARTBEAT_PERIOD" in Settings.names() and "update" not in Settings.names()
+    finally:
+        for k, v in keep.items():
+            setattr(Settings, k, v)
+        Settings._WAIT_HEARTBEATS_CONVERGENCE = keep_wait
