@@ -1,6 +1,10 @@
-"""``models_ready`` (reference: commands/message/models_ready_command.py:26-62).
+"""``models_ready``: "I hold the aggregated model of round r" (reference: commands/message/models_ready_command.py:26-62).
 
-Like the reference it stores the *receiver's* round.
+The reference stores the RECEIVER's round for a message of its current or previous round.  That is wrong by one
+exactly when it matters: a peer's announcement for round r that arrives after this node has moved on to r + 1 is filed as
+"has the model of r + 1", the peer is never offered that model in ``GossipModelStage``, and - when this node is its only route
+to the train set - it sits in ``WaitAggregatedModelsStage`` until ``AGGREGATION_TIMEOUT`` while everybody else waits for its
+ballot.  Here the announced round itself is stored (never moving backwards), so a peer that is behind stays visibly behind.
 """
 
 from myfyp_b200.communication.commands.command import Command
@@ -19,8 +23,9 @@ class ModelsReadyCommand(Command):
         st = self.state
         if st.round is None:
             return
-        if round in (st.round - 1, st.round):
-            st.nei_status[source] = st.round
+        if round < st.round - 1:
+            logger.debug(st.addr, f"models_ready from {source} for round {round}, long past ({st.round}). Ignored.")
+            return
+        if round > st.nei_status.get(source, -2):
+            st.nei_status[source] = round
             st.notify()
-        else:
-            logger.debug(st.addr, f"models_ready from {source} in a late round ({round} != {st.round}). Ignored.")

@@ -60,9 +60,11 @@ def test_round_bookkeeping_commands():
     assert st.nei_status["a"] == -1
     ready = ModelsReadyCommand(st)
     ready.execute("a", 2)
-    ready.execute("b", 1)  # one round behind is still accepted (reference models_ready_command.py:52-56)
-    ready.execute("c", 7)  # a stranger round is not
-    assert st.nei_status == {"a": 2, "b": 2}
+    ready.execute("b", 1)  # b announces the PREVIOUS round's model: it is filed as round 1, i.e. b still needs round 2's model
+    ready.execute("c", 0)  # long past: ignored
+    ready.execute("a", 1)  # an older announcement overtaken by a newer one does not move a backwards
+    ready.execute("d", 3)  # a peer that is ahead of us
+    assert st.nei_status == {"a": 2, "b": 1, "d": 3}
     agg = ModelsAggregatedCommand(st)
     agg.execute("a", 2, "x", "y")
     agg.execute("a", 2, "y", "z")  # merged, not overwritten: announcements can overtake each other
