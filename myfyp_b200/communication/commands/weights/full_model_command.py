@@ -17,12 +17,25 @@ class FullModelCommand(Command):
     def get_name() -> str:
         return "add_model"
 
+    def adopt_early(self) -> bool:
+        """Called by WaitAggregatedModelsStage once it waits: adopt an aggregate of this round that arrived before that."""
+        st = self.state
+        kept, st.early_full_model = st.early_full_model, None
+        if kept is None or st.round is None or kept[0] != st.round:
+            return False
+        self.execute(kept[1], kept[0], weights=kept[2])
+        return st.aggregated_model_event.is_set()
+
     def execute(self, source: str, round: int, weights=None, **kwargs) -> None:
         if weights is None:
             raise ValueError("Weights are required")
         st = self.state
         if st.round is None:
             logger.debug(st.addr, "❌ Tried to add a model while learning is not running")
+            return
+        if round == st.round + 1 and not st.rejoining:
+            # the sender has already finished the round we are still voting in: keep its aggregate for when we wait for it
+            st.early_full_model = (round, source, weights)
             return
         if round != st.round:
             if st.rejoining and round > st.round and st.experiment is not None:
@@ -36,7 +49,11 @@ class FullModelCommand(Command):
         with bad_model_guard(st, self.stop, source, self.protocol):
             with self._mutex:
                 if st.aggregated_model_event.is_set():
-                    logger.debug(st.addr, "😲 Aggregated model not expected.")
+                    # Not waiting for it (yet).  A node outside the train set that is still tallying this round's votes - e.g.
+                    # held up by the ballot of a peer that just died - will wait for exactly this model in a moment, and the
+                    # pusher gives up after a few unanswered offers (reference: full_model_command.py:71-74 drops it).
+                    st.early_full_model = (round, source, weights)
+                    logger.debug(st.addr, "😲 Aggregated model not expected yet: kept.")
                     return
                 logger.info(st.addr, "📦 Aggregated model received.")
                 self.learner.set_model(weights)

@@ -94,6 +94,8 @@ class Node:
         p = self._communication_protocol
         partial_model = PartialModelCommand(self.state, self.stop, self.aggregator, p, self.learner)
         self.state.absorb_early_models = partial_model.absorb_early
+        full_model = FullModelCommand(self.state, self.stop, self.aggregator, self.learner, p)
+        self.state.adopt_early_full_model = full_model.adopt_early
         p.add_command(
             [
                 StartLearningCommand(self.__start_learning_thread),
@@ -105,7 +107,7 @@ class Node:
                 MetricsCommand(self.state),
                 InitModelCommand(self.state, self.stop, self.aggregator, self.learner, p),
                 partial_model,
-                FullModelCommand(self.state, self.stop, self.aggregator, self.learner, p),
+                full_model,
             ]
         )
         # wake waiting stages when the neighbour table or the aggregator changes

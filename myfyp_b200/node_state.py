@@ -34,6 +34,9 @@ class NodeState:
         self.train_set_votes: Dict[str, Dict[str, int]] = {}
         self.train_set_votes_next: Dict[str, Dict[str, int]] = {}  # ballots of peers that are already one round ahead
         self.early_models: List[tuple] = []  # model offers that arrived before this node started collecting for that round
+        self.early_full_model: Optional[tuple] = None  # (round, source, weights): an aggregated model pushed before we waited for it
+        if not hasattr(self, "adopt_early_full_model"):
+            self.adopt_early_full_model = None  # set by Node (FullModelCommand.adopt_early)
         if not hasattr(self, "absorb_early_models"):
             self.absorb_early_models = None  # set by Node: files the stashed offers (PartialModelCommand.absorb_early)
 

@@ -25,6 +25,8 @@ class WaitAggregatedModelsStage(Stage):
         arrived = state.aggregated_model_event
         arrived.clear()
         logger.info(state.addr, "⏳ Waiting for the aggregated model.")
+        if getattr(state, "adopt_early_full_model", None) is not None:
+            state.adopt_early_full_model()  # a neighbour may have pushed it while this node was still tallying votes
         in_time = state.wait_for(lambda: arrived.is_set() or state.round is None, timeout=Settings.AGGREGATION_TIMEOUT)
         if state.round is None:  # stopped while waiting
             return None

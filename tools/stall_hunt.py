@@ -20,6 +20,7 @@ ap.add_argument("--nodes", type=int, default=6); ap.add_argument("--rounds", typ
 ap.add_argument("--topology", default="line"); ap.add_argument("--train-set", type=int, default=4)
 ap.add_argument("--aggregator", default="fedavg"); ap.add_argument("--iters", type=int, default=30)
 ap.add_argument("--stall", type=float, default=6.0); ap.add_argument("--fast", action="store_true")
+ap.add_argument("--kill", action="store_true", help="stop the first non-initiator node that enters TrainStage of round 1")
 a = ap.parse_args()
 if a.fast:
     from myfyp_b200.utils.utils import set_fast_settings
@@ -38,19 +39,35 @@ for it in range(a.iters):
         nd.start()
     TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(a.topology, n, seed=it), nodes)
     wait_convergence(nodes, n - 1, only_direct=False, wait=20)
+    killed = []
+    if a.kill:
+        import threading
+
+        def watch():
+            while not killed:
+                for x in nodes[1:]:
+                    if x.state.round == 1 and x.learning_workflow.history and x.learning_workflow.history[-1] == "TrainStage":
+                        killed.append(x)
+                        x.stop()
+                        return
+                time.sleep(0.002)
+
+        threading.Thread(target=watch, daemon=True).start()
     t0 = time.time()
     nodes[0].set_start_learning(rounds=a.rounds, epochs=1)
     last, t_change = None, time.time()
-    while not all(x.learning_workflow.finished for x in nodes):
-        snap = [(x.state.round, x.learning_workflow.history[-1] if x.learning_workflow.history else None) for x in nodes]
+    while not all(x.learning_workflow.finished for x in nodes if x not in killed):
+        snap = [(x.state.round, x.learning_workflow.history[-1] if x.learning_workflow.history else None) for x in nodes if x not in killed]
         if snap != last:
             last, t_change = snap, time.time()
         if time.time() - t_change > a.stall:
             stalls += 1
             ix = {x.addr: i for i, x in enumerate(nodes)}
             nm = lambda v: ix.get(v, v)  # noqa: E731
-            print(f"STALL in run {it} after {time.time() - t0:.1f} s")
+            print(f"STALL in run {it} after {time.time() - t0:.1f} s; killed {[ix[k.addr] for k in killed]}")
             for i, x in enumerate(nodes):
+                if x in killed:
+                    continue
                 st = x.state
                 print(f"  {i}: round {st.round} {x.learning_workflow.history[-2:]} train_set {[nm(v) for v in st.train_set]} "
                       f"announced {{{', '.join(f'{nm(k)}: {[nm(c) for c in v]}' for k, v in st.models_aggregated.items())}}} "
