@@ -147,3 +147,15 @@ def test_init_and_full_model_commands_adopt_once():
     with pytest.raises(ValueError):
         full.execute("a", 1)
     assert stopped == []
+    # an aggregate pushed before the node waits for it (still tallying votes, or a round behind) is kept and adopted on entry
+    st3 = _state(1)
+    learner3 = _Learner(mlp_model(seed=3))
+    early = FullModelCommand(st3, lambda: stopped.append(1), FedAvg("me"), learner3, None)
+    early.execute("a", 1, weights=blob)  # same round, not waiting yet
+    assert learner3.set_calls == 0 and st3.early_full_model[0] == 1
+    st3.aggregated_model_event.clear()  # WaitAggregatedModelsStage starts waiting ...
+    assert early.adopt_early() and learner3.set_calls == 1 and st3.early_full_model is None
+    early.execute("a", 2, weights=blob)  # the sender is a whole round ahead
+    assert st3.early_full_model[0] == 2 and learner3.set_calls == 1
+    assert early.adopt_early() is False  # ... not this round's model: dropped, nothing adopted
+    assert learner3.set_calls == 1
