@@ -20,6 +20,7 @@ ap.add_argument("--nodes", type=int, default=6); ap.add_argument("--rounds", typ
 ap.add_argument("--topology", default="line"); ap.add_argument("--train-set", type=int, default=4)
 ap.add_argument("--aggregator", default="fedavg"); ap.add_argument("--iters", type=int, default=30)
 ap.add_argument("--stall", type=float, default=6.0); ap.add_argument("--fast", action="store_true")
+ap.add_argument("--protocol", default="memory", choices=["memory", "grpc", "grpc-wire"], help="grpc-wire: real RPCs also between nodes of this process")
 ap.add_argument("--kill", action="store_true", help="stop the first non-initiator node that enters TrainStage of round 1")
 a = ap.parse_args()
 if a.fast:
@@ -28,13 +29,18 @@ if a.fast:
 else:
     set_test_settings()
 Settings.TRAIN_SET_SIZE = a.train_set
+Settings.USE_SSL = False
+if a.protocol == "grpc-wire":
+    Settings.GRPC_LOCAL_SHORTCUT = False
+from myfyp_b200.communication.protocols.grpc.grpc_communication_protocol import GrpcCommunicationProtocol
+proto = InMemoryCommunicationProtocol if a.protocol == "memory" else GrpcCommunicationProtocol
 Settings.TTL = max(Settings.TTL, a.nodes)
 logger.set_level("ERROR")
 agg = {"fedavg": FedAvg, "fedmedian": FedMedian, "krum": lambda: Krum(f=1), "scaffold": lambda: Scaffold(global_lr=1.0)}[a.aggregator]
 n, stalls = a.nodes, 0
 for it in range(a.iters):
     parts = P2PFLDataset.synthetic_mnist(96 * n, 32 * n, seed=it).generate_partitions(n, RandomIIDPartitionStrategy)
-    nodes = [Node(mlp_model(seed=i), parts[i], protocol=InMemoryCommunicationProtocol, aggregator=agg(), batch_size=32) for i in range(n)]
+    nodes = [Node(mlp_model(seed=i), parts[i], protocol=proto, aggregator=agg(), batch_size=32) for i in range(n)]
     for nd in nodes:
         nd.start()
     TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(a.topology, n, seed=it), nodes)
