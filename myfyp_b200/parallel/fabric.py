@@ -94,13 +94,19 @@ class Fabric:
         self.make_visible(snap)
         return Snapshot(snap)
 
+    _gpus_in_use: set = set()
+
     @staticmethod
     def make_visible(t: torch.Tensor) -> None:
         """Call before a descriptor of ``t`` leaves the thread that produced it.  Consumers on the SAME GPU run on that GPU's
         default stream, i.e. behind the kernel that wrote ``t``; a consumer on ANOTHER GPU (peer access) is ordered against
-        nothing and would read the allocation's previous contents - typically last round's snapshot.  With more than one GPU
-        in the process the producing stream is therefore drained first (the wait releases the interpreter lock)."""
-        if t.is_cuda and torch.cuda.device_count() > 1:
+        nothing and would read the allocation's previous contents - typically last round's snapshot.  Once models of this
+        process live on more than one GPU the producing stream is therefore drained first (the wait releases the interpreter
+        lock); with a single GPU in use nothing is waited for.  (``ops.order_after_producers`` is the consumer-side half.)"""
+        if not t.is_cuda:
+            return
+        Fabric._gpus_in_use.add(t.device.index)
+        if len(Fabric._gpus_in_use) > 1:
             torch.cuda.current_stream(t.device).synchronize()
 
     def has_arena(self) -> bool:
