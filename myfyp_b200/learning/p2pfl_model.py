@@ -174,6 +174,10 @@ class TorchP2PFLModel(P2PFLModel):
                 view.copy_(t.detach().to(torch.float32))
                 self._int_entries.append(e.name)
         self.slab, self.grad_slab = slab, grad
+        if slab.is_cuda:  # the fabric learns which GPUs of this process hold models (see Fabric.make_visible)
+            from myfyp_b200.parallel.fabric import Fabric
+
+            Fabric._gpus_in_use.add(slab.device.index)
 
     def sync_mirrors_to_slab(self) -> None:
         """Refresh the fp32 mirrors of non-fp32 buffers (e.g. BatchNorm num_batches_tracked)."""
