@@ -240,17 +240,27 @@ class Node:
 
     def __start_learning_thread(self, rounds: int, epochs: int, start_round: int = 0) -> None:
         with self.state.start_thread_lock:
-            if self._learning_thread is not None and self._learning_thread.is_alive():
-                return  # duplicated start (flood + direct invite)
+            old = self._learning_thread
+            winding_down = None
+            if old is not None and old.is_alive():
+                if not (getattr(old, "b2_experiment_set", False) and self.state.round is None):
+                    return  # duplicated start (flood + direct invite) of the experiment that thread is running
+                # that thread's experiment was stopped (its state is cleared) and it has not noticed yet - it is inside a
+                # wait or a fit.  Dropping this start would leave the node out of the new experiment while everybody waits
+                # VOTE_TIMEOUT for its ballot: the new learning thread starts as soon as the old one is gone.
+                winding_down = old
             self._learning_args = (rounds, epochs)
             self._invited: set = set()
-            t = threading.Thread(target=self.__start_learning, args=(rounds, epochs, start_round), name="learning_thread-" + self.addr, daemon=True)
+            t = threading.Thread(target=self.__start_learning, args=(rounds, epochs, start_round, winding_down), name="learning_thread-" + self.addr, daemon=True)
             self._learning_thread = t
         t.start()
 
-    def __start_learning(self, rounds: int, epochs: int, start_round: int = 0) -> None:
+    def __start_learning(self, rounds: int, epochs: int, start_round: int = 0, after: Optional[threading.Thread] = None) -> None:
         try:
+            if after is not None:
+                after.join(timeout=30)
             if start_round > 0:
+                threading.current_thread().b2_experiment_set = True  # type: ignore[attr-defined]
                 # rejoin: we enter a running experiment; the model comes with this round's add_model diffusion,
                 # so we behave like a node outside the train set for our first round
                 self.state.set_experiment(Settings.EXPERIMENT_NAME, rounds, round=start_round)

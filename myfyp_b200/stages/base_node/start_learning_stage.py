@@ -7,6 +7,7 @@ direct neighbours that have not announced theirs, give fresh heartbeats time to 
 
 from __future__ import annotations
 
+import threading
 import time
 from typing import Optional, Type, Union
 
@@ -40,6 +41,7 @@ class StartLearningStage(Stage):
             state.set_experiment(Settings.EXPERIMENT_NAME, rounds, round=start_round)
             learner.set_epochs(epochs)
             logger.experiment_started(state.addr, state.experiment)
+            threading.current_thread().b2_experiment_set = True  # type: ignore[attr-defined]  (Node tells a stopped thread from a duplicate start by it)
 
         logger.info(state.addr, "⏳ Waiting for the initial model.")
         if not _holds_initial_model(state):

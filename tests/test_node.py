@@ -318,3 +318,33 @@ def test_randomised_message_delays_do_not_break_a_run():
     finally:
         InMemoryServer.send_message, InMemoryServer.send_weights = orig_msg, orig_w
         _stop(nodes)
+
+
+def test_start_right_after_stop_is_not_dropped():
+    """`set_stop_learning` clears the state at once, but a node's learning thread only notices at its next check.  A new
+    `start_learning` that arrives in between used to be taken for a duplicate of the running experiment and dropped - the
+    node then stayed out of the new experiment and everybody waited VOTE_TIMEOUT for its ballot."""
+    Settings.VOTE_TIMEOUT = 30
+    Settings.TRAIN_SET_SIZE = 3
+    n = 5
+    nodes = _nodes(n, samples=96)
+    try:
+        TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.RING, n), nodes)
+        wait_convergence(nodes, n - 1, only_direct=False, wait=20)
+        for it in range(4):
+            nodes[it % n].set_start_learning(rounds=40, epochs=1)
+            time.sleep(0.15 + 0.1 * it)
+            nodes[(it + 2) % n].set_stop_learning()
+            deadline = time.time() + 10
+            while any(nd.state.round is not None for nd in nodes):
+                assert time.time() < deadline, "the stop did not reach every node"
+                time.sleep(0.01)
+            before = [len(nd.learning_workflow.history) for nd in nodes]  # the history accumulates over experiments
+            nodes[(it + 1) % n].set_start_learning(rounds=2, epochs=1)  # at once: old learning threads may still be winding down
+            t0 = time.time()
+            while not all(nd.learning_workflow.finished and len(nd.learning_workflow.history) >= b + 9 for nd, b in zip(nodes, before)):
+                assert time.time() - t0 < 20, [(nd.state.round, nd.learning_workflow.history[-2:]) for nd in nodes]
+                time.sleep(0.02)
+            time.sleep(0.2)
+    finally:
+        _stop(nodes)
