@@ -53,9 +53,63 @@ def remote() -> None:
 
 
 @app.command()
-def launch() -> None:
-    """Launch a node."""
-    _not_yet()
+def launch(
+    address: str = typer.Option("127.0.0.1", help="ip[:port], [v6]:port, unix:///path (gRPC) or uds:///path.sock"),
+    connect: Optional[List[str]] = typer.Option(None, help="address of a node to connect to (repeatable)"),
+    model: str = typer.Option("mlp", help="mlp | cnn | resnet18"),
+    aggregator: str = typer.Option("fedavg", help="fedavg | fedmedian | krum | scaffold | fedprox"),
+    samples: int = typer.Option(600, help="synthetic training samples of this node (real data: use the Python API)"),
+    seed: int = 0,
+    rounds: int = typer.Option(0, help="> 0: start learning (this node initiates) once connected, and exit when it finishes"),
+    epochs: int = 1,
+    ssl: bool = False,
+    settings: Optional[str] = typer.Option(None, help="JSON / YAML file of Settings values"),
+) -> None:
+    """Launch one node of a federation in this process and keep it running (the reference leaves this command unimplemented,
+    cli.py:87-95).  Without --rounds it serves until interrupted; other nodes connect to it and one of them starts the learning."""
+    import time
+
+    from myfyp_b200.learning.aggregators import FedAvg, FedMedian, FedProx, Krum, Scaffold
+    from myfyp_b200.learning.dataset import P2PFLDataset
+    from myfyp_b200.models import cnn_model, mlp_model, resnet18_model
+    from myfyp_b200.node import Node
+    from myfyp_b200.settings import Settings
+    from myfyp_b200.utils.utils import wait_to_finish
+
+    Settings.update_from_env()
+    if settings:
+        Settings.load_file(settings)
+    Settings.USE_SSL = ssl
+    mk = {"mlp": mlp_model, "cnn": cnn_model, "resnet18": resnet18_model}[model]
+    agg = {"fedavg": FedAvg, "fedmedian": FedMedian, "krum": lambda: Krum(f=1), "scaffold": lambda: Scaffold(global_lr=1.0), "fedprox": lambda: FedProx(mu=0.01)}[aggregator]()
+    shape = (28, 28) if model == "mlp" else (3, 32, 32)
+    data = P2PFLDataset.synthetic(shape, 10, samples, max(64, samples // 5), seed=seed)
+    protocol = None
+    if address.startswith("uds://"):
+        from myfyp_b200.communication.protocols.uds.uds_communication_protocol import UdsCommunicationProtocol as protocol  # noqa: N813
+    node = Node(mk(seed=seed), data, address=address, aggregator=agg, protocol=protocol)
+    node.start()
+    console.print(f":satellite: node up at [green]{node.addr}[/green]")
+    try:
+        for peer in connect or []:
+            deadline = time.time() + 60
+            while not node.connect(peer):
+                if time.time() > deadline:
+                    raise typer.Exit(code=1)
+                time.sleep(0.5)
+            console.print(f":link: connected to {peer}")
+        if rounds > 0:
+            time.sleep(2 * Settings.HEARTBEAT_PERIOD)  # let the heartbeats flood before candidates are counted
+            node.set_start_learning(rounds=rounds, epochs=epochs)
+            wait_to_finish([node], timeout=24 * 3600)
+            console.print(":checkered_flag: learning finished")
+        else:
+            while True:
+                time.sleep(1.0)
+    except KeyboardInterrupt:
+        pass
+    finally:
+        node.stop()
 
 
 @app.command()

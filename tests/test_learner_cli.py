@@ -177,3 +177,28 @@ def test_settings_bulk_update_env_and_file(tmp_path, monkeypatch):
         for k, v in keep.items():
             setattr(Settings, k, v)
         Settings._WAIT_HEARTBEATS_CONVERGENCE = keep_wait
+
+
+def test_cli_launch_two_nodes_over_grpc(tmp_path):
+    """`python -m myfyp_b200 launch`: one process serves, a second connects, initiates two rounds and exits."""
+    import os
+    import time
+
+    env = dict(os.environ, MYFYP_B200_LOG_LEVEL="ERROR", MYFYP_B200_HEARTBEAT_PERIOD="0.5")
+    a, b = f"unix://{tmp_path}/a.sock", f"unix://{tmp_path}/b.sock"
+    server = subprocess.Popen([sys.executable, "-m", "myfyp_b200", "launch", "--address", a, "--samples", "128"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        deadline = time.time() + 90
+        while not os.path.exists(f"{tmp_path}/a.sock"):
+            assert time.time() < deadline and server.poll() is None, "the serving node did not come up"
+            time.sleep(0.2)
+        out = subprocess.run([sys.executable, "-m", "myfyp_b200", "launch", "--address", b, "--connect", a, "--samples", "128", "--rounds", "2", "--seed", "1"],
+                             env=env, capture_output=True, text=True, timeout=240)
+        assert out.returncode == 0, out.stdout + out.stderr
+        assert "learning finished" in out.stdout
+    finally:
+        server.terminate()
+        try:
+            server.wait(timeout=20)
+        except subprocess.TimeoutExpired:
+            server.kill()
