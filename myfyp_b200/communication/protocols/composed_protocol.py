@@ -105,7 +105,7 @@ class ComposedProtocol(CommunicationProtocol):
         if _is_flood(msg):
             self._gossiper.check_and_set_processed(msg["hash"])
             msg["seen"] = [self.addr, *nodes]
-        key = (msg.get("cmd"), msg.get("round")) if coalesce and isinstance(msg, dict) else None
+        key = (self.addr, msg.get("cmd"), msg.get("round")) if coalesce and isinstance(msg, dict) else None  # own messages only
         self._gossiper.add_message(msg, nodes, coalesce_key=key, linger=linger)
 
     @running

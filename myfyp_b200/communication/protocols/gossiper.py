@@ -125,6 +125,10 @@ class Gossiper(threading.Thread):
                 self.__pending = kept
             t0 = time.monotonic()
             for msg, neis in batch:
+                if isinstance(msg, dict) and "_ckey" in msg:
+                    # the coalescing tag is queue-local: on the wire it would make the RECEIVER's gossiper take this (forwarded)
+                    # message for one of its own and replace it with its own next announcement
+                    msg = {k: v for k, v in msg.items() if k != "_ckey"}
                 for nei in neis:
                     if self.__terminate.is_set():
                         return

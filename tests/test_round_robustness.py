@@ -283,3 +283,30 @@ def test_a_peer_that_lacks_our_model_is_offered_exactly_that_model():
         assert "b" not in captured["candidates"]() or captured["model"]("b") is None
     finally:
         Settings.FORWARD_GRACE = keep
+
+
+def test_coalescing_never_replaces_a_forwarded_message_of_another_node():
+    """The coalescing tag stays inside the sender's queue.  It used to travel with the message: a forwarder's own next
+    announcement then replaced the foreign announcement still queued for forwarding, and in multi-hop topologies nodes
+    waited for announcements that had been overwritten on the way (found with tools/stall_hunt.py on a 12-node ring)."""
+    client = _RecordingClient()
+    sent_msgs = []
+    orig = client.send
+
+    def send(nei, msg, **kw):
+        sent_msgs.append((nei, dict(msg)))
+        return orig(nei, msg, **kw)
+
+    client.send = send
+    g = Gossiper("me", client, period=0.0, messages_per_period=1000)
+    # a foreign announcement queued for forwarding, as it arrives off the wire (no tag), then our own coalescable one
+    g.add_message({"cmd": "models_aggregated", "args": ["theirs"], "round": 1, "source": "other"}, ["b"])
+    g.add_message({"cmd": "models_aggregated", "args": ["ours-1"], "round": 1, "source": "me"}, ["b"], coalesce_key=("me", "models_aggregated", 1), linger=0.05)
+    g.add_message({"cmd": "models_aggregated", "args": ["ours-2"], "round": 1, "source": "me"}, ["b"], coalesce_key=("me", "models_aggregated", 1), linger=0.05)
+    g.start()
+    try:
+        time.sleep(0.3)
+        assert [m["args"] for _, m in sent_msgs] == [["theirs"], ["ours-2"]]
+        assert all("_ckey" not in m for _, m in sent_msgs)
+    finally:
+        g.stop()
