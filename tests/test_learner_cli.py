@@ -188,12 +188,12 @@ def test_cli_launch_two_nodes_over_grpc(tmp_path):
     a, b = f"unix://{tmp_path}/a.sock", f"unix://{tmp_path}/b.sock"
     server = subprocess.Popen([sys.executable, "-m", "myfyp_b200", "launch", "--address", a, "--samples", "128"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     try:
-        deadline = time.time() + 90
+        deadline = time.time() + 240  # a cold `import torch` can take a minute
         while not os.path.exists(f"{tmp_path}/a.sock"):
             assert time.time() < deadline and server.poll() is None, "the serving node did not come up"
             time.sleep(0.2)
         out = subprocess.run([sys.executable, "-m", "myfyp_b200", "launch", "--address", b, "--connect", a, "--samples", "128", "--rounds", "2", "--seed", "1"],
-                             env=env, capture_output=True, text=True, timeout=240)
+                             env=env, capture_output=True, text=True, timeout=420)
         assert out.returncode == 0, out.stdout + out.stderr
         assert "learning finished" in out.stdout
     finally:
