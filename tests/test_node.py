@@ -348,3 +348,28 @@ def test_start_right_after_stop_is_not_dropped():
             time.sleep(0.2)
     finally:
         _stop(nodes)
+
+
+def test_ring_where_everybody_trains_finishes_without_waiting_for_lost_announcements():
+    """Integration side of the coalescing-tag fix: on a 10-node ring with every node in the train set, announcements travel
+    up to five hops through nodes that are sending their own; if one is replaced on the way, nodes sit in TrainStage's gossip
+    loop until its 'X equal rounds' exit (10 s with this preset)."""
+    from myfyp_b200.utils.utils import set_fast_settings
+
+    set_fast_settings(train_set_size=10)
+    Settings.TTL = 12
+    logger.set_level("ERROR")
+    n = 10
+    nodes = _nodes(n, samples=64)
+    try:
+        TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.RING, n), nodes)
+        wait_convergence(nodes, n - 1, only_direct=False, wait=30)
+        t0 = time.time()
+        nodes[0].set_start_learning(rounds=3, epochs=1)
+        wait_to_finish(nodes, timeout=60)
+        took = time.time() - t0
+        assert took < 9, f"{took:.1f} s: a gossip loop ran into its stall exit"  # typically 1-2 s
+        check_equal_models(nodes)
+    finally:
+        _stop(nodes)
+        set_test_settings()
