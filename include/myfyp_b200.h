@@ -200,6 +200,57 @@ int b2_pool_im2col(const void* y_bf16, void* idx_u8, void* col_bf16, int ldc, in
 int b2_unpool_col2im(const void* dcol_bf16, int ldc, const void* idx_u8, const void* y_bf16, void* dz_bf16, float* bias_grad, int B, int PH, int PW, int C, int KH, int KW,
                      int stride, int pad, void* stream);
 
+/* ------------------------------------------------------------------------------------------------ node-batched TF32 training
+ * One training step of a conv3x3-ReLU-maxpool2 ... Flatten-Linear-ReLU-Linear network for G co-resident federated nodes per
+ * launch sequence (csrc/train_tf32.cu): fp32 storage, convolutions on tcgen05 kind::tf32 (torch's default precision for
+ * cuDNN convolutions), linear layers as 3xTF32 (fp32-class accuracy, torch's default for nn.Linear), loss / head in fp32.
+ * Every kernel takes the node ("slot") index from blockIdx.y; tensor maps, shapes and epilogue pointers of each slot sit in
+ * device memory (built once by b2_cnn_plan_create), per-node pointers in a bind table rewritten before a graph replay.
+ * Replaces the reference's one-actor-process-per-learner pool (p2pfl/learning/frameworks/simulation/actor_pool.py:101-128,
+ * virtual_learner.py:101-137) and its Lightning training loop (pytorch/lightning_learner.py:78-100). */
+#define B2_CNN_MAX_CONV 4
+typedef struct {
+  int groups;   /* G: slots (nodes trained together) */
+  int batch;    /* samples per step and node */
+  int image;    /* input height = width */
+  int in_ch;    /* 1 or 3 */
+  int n_conv;   /* 2..4 conv blocks */
+  int conv_ch[B2_CNN_MAX_CONV];
+  int hidden, classes;
+  int64_t off_conv_w[B2_CNN_MAX_CONV], off_conv_b[B2_CNN_MAX_CONV]; /* element offsets inside the parameter slab */
+  int64_t off_fc1_w, off_fc1_b, off_fc2_w, off_fc2_b;
+  int64_t slab_elems; /* trainable elements of the slab (multiple of 4) */
+} b2_cnn_desc;
+typedef struct {
+  float* slab;          /* the node's fp32 parameters */
+  float* m;             /* Adam moments */
+  float* v;
+  float* adam_state;    /* {steps done, ...} as b2_adam_step's dev_state */
+  const float* x;       /* [n, in_ch, image, image] fp32 */
+  const int64_t* y;     /* [n] */
+  const int64_t* perm;  /* [n] sample order, or NULL = identity */
+  float* losses;        /* training: [steps] mean loss per step (+=); evaluation: {sum nll, #correct} (+=) */
+  const float* prox_ref;   /* FedProx anchor or NULL */
+  const float* cv_global;  /* Scaffold c or NULL */
+  const float* cv_local;   /* Scaffold c_i */
+  float prox_mu, cv_scale, lr, weight_decay;
+  int n_samples;
+  int active;
+} b2_cnn_bind;
+int64_t b2_cnn_workspace_bytes(const b2_cnn_desc* d);
+/* `workspace` (device, 1024-byte aligned, b2_cnn_workspace_bytes) is carved into every slot's activations, weight mirrors and
+ * gradient mirror plus the problem / bind tables; the call encodes all tensor maps and uploads the tables on `stream`. */
+void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, void* stream);
+int b2_cnn_plan_destroy(void* plan);
+int b2_cnn_plan_bind(void* plan, const b2_cnn_bind* host_binds, void* stream);   /* G entries; async copy through pinned staging */
+int b2_cnn_plan_refresh(void* plan, void* stream);                                /* slab -> tf32 weight mirrors, clear gradient mirrors */
+int b2_cnn_plan_train_step(void* plan, int step, void* stream);                   /* all kernels of one step for all active slots; returns <0 on error else #launches */
+int b2_cnn_plan_eval_step(void* plan, int step, void* stream);                    /* forward + loss / accuracy accumulation */
+int b2_cnn_plan_advance(void* plan, int steps, void* stream);                     /* adam_state[0] += steps the slot really took (once per epoch) */
+/* test / debug: run one kernel of the step (`which` as enumerated in train_tf32.cu), look a slot buffer up */
+int b2_cnn_plan_run(void* plan, int which, int step, void* stream);
+int b2_cnn_plan_query(void* plan, int slot, int buf, void** ptr, int64_t* bytes);
+
 #ifdef __cplusplus
 }
 #endif

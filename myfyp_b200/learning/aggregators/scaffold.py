@@ -117,10 +117,10 @@ class Scaffold(Aggregator):
 
 
 def _as_flat(value: Any, like) -> torch.Tensor:
-    """delta in wire form (list of per-layer arrays) or fabric form (flat tensor) -> flat tensor."""
-    if isinstance(value, torch.Tensor):
+    """delta in wire form (list of per-layer arrays), flat form (1-D array of slab length) or fabric form (flat tensor) -> flat
+    tensor on the model's device; a shape that is none of these raises."""
+    from myfyp_b200.parallel.slab import flat_from_wire
+
+    if isinstance(value, torch.Tensor) and value.numel() == like.layout.total:
         return value
-    host = np.zeros(like.layout.total, dtype=np.float32)
-    for e, layer in zip(like.layout.in_order(), value):
-        host[e.offset : e.offset + e.numel] = np.asarray(layer, dtype=np.float32).reshape(-1)
-    return torch.from_numpy(host).to(like.slab.device)
+    return flat_from_wire(value, like.layout, like.slab.device)

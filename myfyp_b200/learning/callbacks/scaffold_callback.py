@@ -74,9 +74,6 @@ class SCAFFOLDCallback(P2PFLCallback):
 
 
 def _flat_prefix(value: Any, model, n: int) -> torch.Tensor:
-    if isinstance(value, torch.Tensor):
-        return value.to(model.slab.device)[:n].contiguous()
-    host = np.zeros(model.layout.total, dtype=np.float32)
-    for e, layer in zip(model.layout.in_order(), value):
-        host[e.offset : e.offset + e.numel] = np.asarray(layer, dtype=np.float32).reshape(-1)
-    return torch.from_numpy(host[:n].copy()).to(model.slab.device)
+    from myfyp_b200.parallel.slab import flat_from_wire
+
+    return flat_from_wire(value, model.layout, model.slab.device)[:n].contiguous()

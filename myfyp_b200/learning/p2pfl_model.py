@@ -113,6 +113,16 @@ def _info_to_numpy(info: Any) -> Any:
     return info
 
 
+def _slab_vectors_to_layers(info: Any, layout: SlabLayout) -> Any:
+    from myfyp_b200.parallel.slab import layers_from_flat
+
+    if isinstance(info, torch.Tensor) and info.dim() == 1 and info.numel() in (layout.total, layout.n_trainable) and info.numel() > 0:
+        return layers_from_flat(info, layout)
+    if isinstance(info, dict):
+        return {k: _slab_vectors_to_layers(v, layout) for k, v in info.items()}
+    return info
+
+
 class TorchP2PFLModel(P2PFLModel):
     """PyTorch model whose ``state_dict`` is backed by one flat fp32 slab.
 
@@ -272,6 +282,14 @@ class TorchP2PFLModel(P2PFLModel):
         if device_ok and Settings.DEVICE_WEIGHTS:
             return self.as_ref() if self.model is None else self.publish()
         return self.encode_parameters()
+
+    def encode_parameters(self, params: Optional[List[np.ndarray]] = None) -> bytes:
+        """The reference's pickle.  Slab-shaped device vectors inside ``additional_info`` (Scaffold's deltas and global c) leave
+        in the reference's form - one array per ``state_dict`` entry (pytorch/callbacks/scaffold_callback.py:131-135) - so a
+        reference node, and our own receiving side, read them layer by layer."""
+        if params is None:
+            params = self.get_parameters()
+        return pickle.dumps({"params": params, "additional_info": _info_to_numpy(_slab_vectors_to_layers(self.additional_info, self.layout))})
 
     # ------------------------------------------------------------------ parameter access
     def get_parameters(self) -> List[np.ndarray]:

@@ -22,6 +22,7 @@ Like the reference (a fresh Trainer => fresh optimizer per fit) the optimizer st
 from __future__ import annotations
 
 import threading
+import zlib
 from typing import Any, Dict, List, Optional
 
 import torch
@@ -77,7 +78,7 @@ class TorchLearner(Learner):
         self._stream: Optional[torch.cuda.Stream] = None
         self._global_step = 0
         self._rng = torch.Generator()
-        self._rng.manual_seed(torch.initial_seed() ^ (hash(self_addr) & 0xFFFFFFF))
+        self._rng.manual_seed(torch.initial_seed() ^ (zlib.crc32(self_addr.encode()) & 0xFFFFFFF))
 
     def get_framework(self) -> str:
         return "pytorch"
@@ -224,7 +225,10 @@ class TorchLearner(Learner):
             trace(self._self_addr, "fit:alloc")
             steps = 0
             graph_ok = cuda and self.use_cuda_graph
-            if graph_ok:
+            grouped = self._cohort(module) if graph_ok and self.optimizer == "adam" else None
+            if grouped is not None:
+                steps, vals_grouped = self._fit_grouped(grouped, x, y, n, st, terms, steps_per_epoch)
+            elif graph_ok:
                 pkey = ("perm", n)
                 if pkey not in self._static:
                     self._static[pkey] = (torch.arange(n, device=dev), torch.zeros(steps_per_epoch, device=dev))
@@ -251,7 +255,10 @@ class TorchLearner(Learner):
                     steps += self._epoch_body(x, y, perm, all_losses[e * steps_per_epoch :], steps_per_epoch, st, terms)
             for cb in self.callbacks:
                 cb.on_fit_end(self, steps, self.lr)
-            vals = self._read_back(all_losses[:steps]) if steps else []  # one D2H copy per fit (synchronises the learner's stream)
+            if grouped is not None:
+                vals = vals_grouped
+            else:
+                vals = self._read_back(all_losses[:steps]) if steps else []  # one D2H copy per fit (synchronises the learner's stream)
         if cuda:
             self._stream.synchronize()
         if steps:
@@ -281,6 +288,41 @@ class TorchLearner(Learner):
         buf[:n].copy_(t.reshape(-1), non_blocking=True)
         torch.cuda.current_stream(t.device).synchronize()
         return buf[:n].tolist()
+
+    # ------------------------------------------------------------------ node-batched TF32 path (models/grouped_cnn.py)
+    def _cohort(self, module):
+        spec = getattr(module, "grouped_spec", None)
+        if spec is None:
+            return None
+        from myfyp_b200.models.grouped_cnn import CohortTrainer
+
+        model: TorchP2PFLModel = self.model  # type: ignore[assignment]
+        tr = CohortTrainer.get(spec, model.layout, model.device, self.batch_size)
+        tr.register(self)
+        return tr
+
+    def _fit_grouped(self, trainer, x, y, n: int, st, terms, steps_per_epoch: int):
+        """Hand this node's epoch(s) to the GPU's cohort trainer: it runs together with the other nodes that ask within the
+        window, one graph replay per epoch for all of them.  Returns (steps done, per-step losses)."""
+        model: TorchP2PFLModel = self.model  # type: ignore[assignment]
+        dev = model.device
+        pkey = ("gperm", n)
+        if pkey not in self._static:
+            self._static[pkey] = (torch.arange(n, device=dev), torch.zeros(max(steps_per_epoch, 2), device=dev), torch.empty(n, dtype=torch.int64).pin_memory())
+        perm, losses, host_perm = self._static[pkey]
+
+        def make_perm():
+            torch.randperm(n, generator=self._rng, out=host_perm)
+            return host_perm
+
+        ev = torch.cuda.Event()
+        ev.record(self._stream)
+        args = dict(
+            slab=model.slab, m=st["m"], v=st["v"], adam_state=st["dev_state"], x=x, y=y, perm=perm if self.shuffle else None, losses=losses, n_samples=n,
+            lr=self.lr, weight_decay=self.weight_decay, epochs=self.epochs, max_steps=self.max_steps_per_epoch, shuffle=self.shuffle, make_perm=make_perm, ready=ev, **terms,
+        )
+        res = trainer.submit("fit", self, args)
+        return res["steps"], res["losses"]
 
     def interrupt_fit(self) -> None:
         self._interrupt = True
@@ -334,7 +376,13 @@ class TorchLearner(Learner):
                 if "conf" not in self._static:
                     self._static["conf"] = torch.zeros(ncls, ncls, device=dev)
                 conf = self._static["conf"]
-            if cuda and self.use_cuda_graph:
+            grouped = self._cohort(module) if cuda and self.use_cuda_graph and conf is None else None
+            if grouped is not None:
+                acc.zero_()
+                ev = torch.cuda.Event()
+                ev.record(self._stream)
+                tot = grouped.submit("eval", self, {"slab": model.slab, "x": x, "y": y, "perm": None, "losses": acc, "n_samples": x.shape[0], "ready": ev})
+            elif cuda and self.use_cuda_graph:
                 self._state(model.layout.n_trainable, dev)
                 g = self._graph_for(("eval", x.shape[0], x.data_ptr(), conf is not None), lambda: self._eval_body(x, y, acc, conf))
                 g.replay()
@@ -342,7 +390,8 @@ class TorchLearner(Learner):
             else:
                 self._eval_body(x, y, acc, conf)
             module.train()
-            tot = self._read_back(acc)
+            if grouped is None:
+                tot = self._read_back(acc)
         self.d2h_bytes += 8
         results = {"test_loss": tot[0] / x.shape[0], "test_metric": tot[1] / x.shape[0]}
         if conf is not None:

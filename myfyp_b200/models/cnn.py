@@ -26,9 +26,13 @@ class CNN(nn.Module):
         return self.classifier(self.features(x.float()))
 
 
-def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, native: Optional[bool] = None, **kwargs):
-    """``TorchP2PFLModel`` around a fresh CNN; ``native`` (default: on CUDA) attaches the hand-written training step
-    (patch gather + tcgen05 GEMMs, :mod:`myfyp_b200.models.native_cnn`) which the learner prefers over autograd / cuDNN."""
+def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, native: Optional[bool] = None, precision: str = "tf32", **kwargs):
+    """``TorchP2PFLModel`` around a fresh CNN; ``native`` (default: on CUDA) attaches a hand-written training step which the
+    learner prefers over autograd / cuDNN:
+
+    * ``precision="tf32"`` (default): fp32 storage, TF32 tensor-core convolutions, fp32-class linear layers - torch's own
+      defaults for this module - trained node-batched (:mod:`myfyp_b200.models.grouped_cnn`, ``csrc/train_tf32.cu``);
+    * ``precision="bf16"``: bf16 operands / fp32 accumulation, one graph per node (:mod:`myfyp_b200.models.native_cnn`)."""
     from myfyp_b200.learning.p2pfl_model import TorchP2PFLModel
 
     if seed is not None:
@@ -40,7 +44,16 @@ def cnn_model(device: Optional[str] = None, seed: Optional[int] = None, native: 
         module.wants_native = True
         native = model.device.type == "cuda"
     if native:
-        from myfyp_b200.models.native_cnn import attach_native_cnn
+        spec = None
+        if precision == "tf32":
+            from myfyp_b200.models.grouped_cnn import attach_grouped_cnn
 
-        attach_native_cnn(model, module.image_size)
+            spec = attach_grouped_cnn(model, module.image_size)
+        elif precision != "bf16":
+            raise ValueError("precision must be 'tf32' or 'bf16'")
+        if spec is None:  # bf16 asked for, or an architecture outside the node-batched plan
+            from myfyp_b200.models.native_cnn import attach_native_cnn
+
+            attach_native_cnn(model, module.image_size)
+        module.precision = "tf32" if spec is not None else "bf16"
     return model

@@ -92,3 +92,53 @@ class SlabRef:
 
     def nbytes(self) -> int:
         return 4 * self.numel
+
+
+# ---------------------------------------------------------------------------------------------- slab-shaped side information
+def layers_from_flat(flat: Any, layout: SlabLayout) -> List[Any]:
+    """A slab-shaped flat vector (Scaffold's delta_y_i / delta_c_i / global_c) as the reference's wire form: one NumPy array
+    per ``state_dict`` entry, in ``state_dict`` order, padding dropped (reference: pytorch/callbacks/scaffold_callback.py:131-135).
+    A vector that only covers the trainable prefix yields zeros for the buffers behind it."""
+    import numpy as np
+
+    host = flat.detach().cpu().numpy() if isinstance(flat, torch.Tensor) else np.asarray(flat)
+    host = host.reshape(-1)
+    out = []
+    for e in layout.in_order():
+        if e.offset + e.numel <= host.size:
+            out.append(host[e.offset : e.offset + e.numel].reshape(e.shape).astype(np.float32, copy=True))
+        else:
+            out.append(np.zeros(e.shape, dtype=np.float32))
+    return out
+
+
+def flat_from_wire(value: Any, layout: SlabLayout, device: Any) -> torch.Tensor:
+    """The inverse: a flat fp32 tensor of ``layout.total`` elements on ``device`` from whatever form the value travelled in -
+    a tensor (fabric form), a 1-D array of slab length (flat form), or the reference's list of per-layer arrays.
+    Anything else is a malformed message and raises instead of being broadcast over whole layers."""
+    import numpy as np
+
+    if isinstance(value, torch.Tensor):
+        t = value.reshape(-1)
+        if t.numel() not in (layout.total, layout.n_trainable):
+            raise ValueError(f"flat side information has {t.numel()} elements, the slab has {layout.total}")
+        if t.numel() < layout.total:
+            full = torch.zeros(layout.total, dtype=torch.float32, device=t.device)
+            full[: t.numel()] = t
+            t = full
+        return t if str(t.device) == str(torch.device(device)) else t.to(device)
+    if isinstance(value, np.ndarray) and value.ndim == 1 and value.size in (layout.total, layout.n_trainable) and value.dtype != object:
+        host = np.zeros(layout.total, dtype=np.float32)
+        host[: value.size] = value
+        return torch.from_numpy(host).to(device)
+    entries = layout.in_order()
+    if not isinstance(value, (list, tuple)) or len(value) != len(entries):
+        got = f"{len(value)} items" if isinstance(value, (list, tuple)) else f"{type(value).__name__} of shape {getattr(value, 'shape', '?')}"
+        raise ValueError(f"side information must be a slab-length vector or a list of {len(entries)} per-layer arrays (got {got})")
+    host = np.zeros(layout.total, dtype=np.float32)
+    for e, layer in zip(entries, value):
+        a = np.asarray(layer, dtype=np.float32).reshape(-1)
+        if a.size != e.numel:
+            raise ValueError(f"layer {e.name}: expected {e.numel} values, got {a.size}")
+        host[e.offset : e.offset + e.numel] = a
+    return torch.from_numpy(host).to(device)

@@ -194,6 +194,50 @@ def test_scaffold_rebases_on_the_round_start_recovered_from_the_clients():
         np.testing.assert_allclose(got, p + 0.25 * d0 + 0.75 * d1, atol=1e-5)
 
 
+def test_scaffold_survives_every_transport_form():
+    """Deltas that travelled as bytes (per-layer lists, the reference's wire form), as a flat array (descriptor side channel)
+    or stayed tensors must aggregate to the same model; a malformed shape raises instead of being broadcast over layers."""
+    import pickle
+
+    from myfyp_b200.learning.aggregators.scaffold import _as_flat
+    from myfyp_b200.models import mlp_model
+
+    torch.manual_seed(0)
+    base = mlp_model(seed=0)
+    clients = []
+    for k in range(3):
+        m = base.build_copy(params=base.slab.clone() + 0.01 * (k + 1), num_samples=10 * (k + 1), contributors=[f"n{k}"])
+        m.add_info("scaffold", {"delta_y_i": torch.arange(m.layout.total, dtype=torch.float32) * 1e-4 * (k + 1), "delta_c_i": torch.full((m.layout.total,), 0.5 * (k + 1))})
+        clients.append(m)
+    want = Scaffold(global_lr=0.5).aggregate(clients)
+    # (a) bytes round trip: encode -> build_copy(bytes) on the receiving side
+    received = [base.build_copy(params=m.encode_parameters(), num_samples=m.get_num_samples(), contributors=m.get_contributors()) for m in clients]
+    wire = pickle.loads(clients[0].encode_parameters())["additional_info"]["scaffold"]["delta_y_i"]
+    assert isinstance(wire, list) and len(wire) == len(base.layout.order)
+    got = Scaffold(global_lr=0.5).aggregate(received)
+
+    def same(a, b):  # compare the state_dict entries (slab padding is not part of the model and does not travel)
+        for x, y in zip(a, b):
+            np.testing.assert_allclose(x, y, rtol=1e-6, atol=1e-6)
+
+    from myfyp_b200.parallel.slab import layers_from_flat
+
+    same(got.get_parameters(), want.get_parameters())
+    same(layers_from_flat(_as_flat(got.get_info("scaffold")["global_c"], base), base.layout), layers_from_flat(want.get_info("scaffold")["global_c"], base.layout))
+    # (b) flat array form
+    flat = [base.build_copy(params=m.slab.clone(), num_samples=m.get_num_samples(), contributors=m.get_contributors()) for m in clients]
+    for f, m in zip(flat, clients):
+        f.add_info("scaffold", {k: v.numpy() for k, v in m.get_info("scaffold").items()})
+    same(Scaffold(global_lr=0.5).aggregate(flat).get_parameters(), want.get_parameters())
+    rt = _as_flat(np.arange(base.layout.total, dtype=np.float32), base)
+    torch.testing.assert_close(rt, torch.arange(base.layout.total, dtype=torch.float32))
+    # (c) malformed
+    with pytest.raises(ValueError):
+        _as_flat(np.zeros(7, dtype=np.float32), base)
+    with pytest.raises(ValueError):
+        _as_flat([np.zeros(3)], base)
+
+
 def test_scaffold_errors():
     with pytest.raises(NoModelsToAggregateError):
         Scaffold().aggregate([])

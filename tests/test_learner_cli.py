@@ -95,7 +95,8 @@ def test_scaffold_callback_produces_the_deltas_the_aggregator_needs():
     import pickle
 
     blob = pickle.loads(model.encode_parameters())
-    assert isinstance(blob["additional_info"]["scaffold"]["delta_y_i"], np.ndarray)
+    wire = blob["additional_info"]["scaffold"]["delta_y_i"]  # the reference's form: one array per state_dict entry
+    assert isinstance(wire, list) and [a.shape for a in wire] == [tuple(e.shape) for e in model.layout.in_order()]
     # a global_c coming back from the aggregator is picked up at the next fit
     model.add_info("scaffold", {"global_c": torch.ones_like(model.slab)})
     learner.update_callbacks_with_model_info()
