@@ -44,8 +44,28 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="cnn", choices=["cnn", "mlp", "resnet18"])
     ap.add_argument("--nodes", type=int, default=TOTAL_NODES)
+    ap.add_argument("--nodes-per-gpu", type=int, default=0, help="weak scaling: this many nodes on every GPU (overrides --nodes)")
+    ap.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"], help="tf32 = the reference's precision (fp32 storage, TF32 convolutions, fp32-class linear layers)")
+    ap.add_argument("--topology", default="line", choices=["line", "full"], help="line = what the reference arm can run (its own test topology); full = BASELINE config 2 as worded")
+    ap.add_argument("--also-full", action="store_true", help="after the timed line-topology rounds, complete the mesh and time the same number of rounds again (reported under 'full_mesh')")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.nodes_per_gpu > 0:
+        a.nodes = a.nodes_per_gpu * max(1, int(os.environ.get("WORLD_SIZE", a.gpus)))
+    return a
+
+
+DTYPE_NAMES = {"tf32": "fp32 (tf32 conv, fp32 linear)", "bf16": "bf16"}
+MODEL_NAMES = {"cnn": "CNN (3 conv + 2 fc, 0.55M params) on CIFAR-10-shaped data", "mlp": "MLP 784-256-128-10 on MNIST-shaped data", "resnet18": "ResNet-18 CIFAR"}
+
+
+def common_config(args, n_nodes: int) -> dict:
+    """Config keys both arms print with identical values when the runs are the same experiment."""
+    return {
+        "model": MODEL_NAMES[args.model], "nodes": n_nodes, "train_set_size": n_nodes, "topology": args.topology, "aggregator": "FedAvg",
+        "samples_per_node": SAMPLES_PER_NODE, "global_batch": BATCH * n_nodes, "batch_per_node": BATCH, "local_epochs": 1, "seq_len": None,
+        "optimizer": "Adam lr 1e-3, fresh per fit", "step": "one federated round of all nodes",
+    }
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -90,10 +110,12 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ our arm
-def make_model(name: str, device, seed: int):
+def make_model(name: str, device, seed: int, dtype: str = "tf32"):
     from myfyp_b200.models import cnn_model, mlp_model, resnet18_model
 
-    return {"cnn": cnn_model, "mlp": mlp_model, "resnet18": resnet18_model}[name](device=device, seed=seed)
+    if name == "cnn":
+        return cnn_model(device=device, seed=seed, precision=dtype)
+    return {"mlp": mlp_model, "resnet18": resnet18_model}[name](device=device, seed=seed)
 
 
 def make_data(name: str, n_nodes: int):
@@ -172,7 +194,7 @@ def run_ours(args) -> None:
         addrs = [f"node-{i}" for i in range(n_nodes)]
         proto = InMemoryCommunicationProtocol
 
-    models = {i: make_model(args.model, dev, seed=i) for i in mine}
+    models = {i: make_model(args.model, dev, seed=i, dtype=args.dtype) for i in mine}
     if multi:
         from myfyp_b200.parallel.ipc import ArenaPool, register_addresses
 
@@ -187,16 +209,22 @@ def run_ours(args) -> None:
         n.start()
     if multi:
         dist.barrier()
-    for i in mine:  # fully connected: i -> j for i < j (the handshake makes it symmetric)
-        for j in range(i + 1, n_nodes):
-            nodes[i].connect(addrs[j])
-    deadline = time.time() + 60
-    while any(len(n.get_neighbors(only_direct=True)) < n_nodes - 1 for n in nodes.values()):
-        if time.time() > deadline:
-            raise RuntimeError("topology did not converge")
-        time.sleep(0.02)
-    if multi:
-        dist.barrier()
+    def wire(topology: str) -> None:
+        """line: i - i+1 (the reference's own test topology, test/node_test.py:92-96); full: i -> j for i < j.  The handshake makes
+        every link symmetric; the heartbeat flood then tells everybody about everybody (non-direct neighbours)."""
+        for i in mine:
+            for j in (range(i + 1, n_nodes) if topology == "full" else range(i + 1, min(i + 2, n_nodes))):
+                nodes[i].connect(addrs[j])
+        deadline = time.time() + 60
+        want_direct = (lambda i: n_nodes - 1) if topology == "full" else (lambda i: 1 if i in (0, n_nodes - 1) else 2)
+        while any(len(n.get_neighbors(only_direct=True)) < min(want_direct(i), n_nodes - 1) or len(n.get_neighbors(only_direct=False)) < n_nodes - 1 for i, n in nodes.items()):
+            if time.time() > deadline:
+                raise RuntimeError("topology did not converge")
+            time.sleep(0.02)
+        if multi:
+            dist.barrier()
+
+    wire(args.topology)
 
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
@@ -300,6 +328,32 @@ def run_ours(args) -> None:
         e2e = {"value": args.steps / wall, "unit": "rounds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * wall / args.steps}
         set_host_mode(False)
 
+    # ---- optional second measurement: the same federation as a full mesh (BASELINE config 2 as worded)
+    full_mesh = None
+    if args.also_full and args.topology != "full":
+        try:
+            wire("full")
+            barrier()
+            run_rounds(max(2, args.warmup))
+            barrier()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(torch.cuda.current_stream(dev))
+            run_rounds(args.steps)
+            f1.record(torch.cuda.current_stream(dev))
+            barrier()
+            fms = allmax(f0.elapsed_time(f1))
+            full_mesh = {"value": args.steps / (fms / 1e3), "unit": "rounds/s", "ms_per_step": fms / args.steps, "topology": "full"}
+        except Exception as e:  # noqa: BLE001 - the headline line must still be printed
+            full_mesh = {"error": f"{type(e).__name__}: {e}"[:200]}
+
+    cohort = None
+    if args.model == "cnn" and args.dtype == "tf32":
+        from myfyp_b200.models.grouped_cnn import CohortTrainer
+
+        trs = list(CohortTrainer._instances.values())
+        if trs:
+            cohort = {"requests": sum(t.batched for t in trs), "launches": sum(t.batches for t in trs)}
+
     for n in nodes.values():
         n.stop()
     if multi:
@@ -314,17 +368,21 @@ def run_ours(args) -> None:
             pass
         out = {
             "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": (value / base) if base else None, "dtype": "bf16" if args.model in ("mlp", "cnn") else "fp32+tf32",
+            "higher_is_better": True, "scaling": "weak" if args.nodes_per_gpu > 0 else "strong", "vs_baseline": (value / base) if base else None,
+            "dtype": DTYPE_NAMES[args.dtype] if args.model == "cnn" else ("bf16" if args.model == "mlp" else "bf16 operands, fp32 accumulate"),
             "data": "synthetic", "impl": "ours",
             "config": {
-                "model": {"cnn": "CNN (3 conv + 2 fc, 0.55M params) on CIFAR-10-shaped data", "mlp": "MLP 784-256-128-10 on MNIST-shaped data", "resnet18": "ResNet-18 CIFAR"}[args.model],
-                "nodes": n_nodes, "nodes_per_gpu": n_nodes / world, "train_set_size": n_nodes, "topology": "full", "aggregator": "FedAvg",
-                "samples_per_node": SAMPLES_PER_NODE, "global_batch": BATCH * n_nodes, "batch_per_node": BATCH, "local_epochs": 1, "seq_len": None,
-                "protocol": (os.environ.get("B2_BENCH_PROTOCOL", "uds") + "+cuda-ipc") if multi else "in-memory", "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
-                "step": "one federated round of all nodes",
+                **common_config(args, n_nodes),
+                "precision": "fp32 storage; convolutions on tcgen05 kind::tf32 (operands rounded to tf32); linear layers 3xTF32 (fp32-class); loss / optimizer fp32" if args.dtype == "tf32" and args.model == "cnn" else "bf16 operands, fp32 accumulation, fp32 master weights",
+                "nodes_per_gpu": n_nodes / world, "protocol": (os.environ.get("B2_BENCH_PROTOCOL", "uds") + "+cuda-ipc") if multi else "in-memory",
+                "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
             },
             "clocks": clocks, "gpu_launches": launches, "stage_ms_per_round_rank0": stage_ms,
         }
+        if full_mesh is not None:
+            out["full_mesh"] = full_mesh
+        if cohort is not None:
+            out["cohort_rank0"] = cohort
         if e2e is not None:
             out["e2e"] = e2e
         print(json.dumps(out), flush=True)

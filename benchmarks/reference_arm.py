@@ -72,7 +72,7 @@ def _run_rank0(args, n_gpus: int, torch) -> None:
     from p2pfl.settings import Settings
 
     sys.path.insert(0, ROOT)
-    from bench import BATCH, METRIC, SAMPLES_PER_NODE, TEST_PER_NODE, ClockSampler
+    from bench import BATCH, DTYPE_NAMES, METRIC, SAMPLES_PER_NODE, TEST_PER_NODE, ClockSampler, common_config
 
     n_nodes = args.nodes
     has_cuda = torch.cuda.is_available()  # CPU fallback only for debugging the arm on a box without a GPU
@@ -322,11 +322,16 @@ def _run_rank0(args, n_gpus: int, torch) -> None:
     value = args.steps / (ms / 1e3)
     out = {
         "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32 (torch default)", "data": "synthetic", "impl": "reference",
+        "higher_is_better": True, "scaling": "weak" if getattr(args, "nodes_per_gpu", 0) > 0 else "strong", "vs_baseline": None,
+        # torch's defaults, read back from the process that trained: fp32 storage, cuDNN convolutions may use TF32 tensor cores
+        # (torch.backends.cudnn.allow_tf32 = True), nn.Linear in plain fp32 (torch.backends.cuda.matmul.allow_tf32 = False)
+        "dtype": DTYPE_NAMES["tf32"] if (args.model == "cnn" and torch.backends.cudnn.allow_tf32 and not torch.backends.cuda.matmul.allow_tf32) else "fp32 (torch default)",
+        "data": "synthetic", "impl": "reference",
         "config": {
-            "model": "CNN (3 conv + 2 fc) on CIFAR-10-shaped data" if args.model == "cnn" else "MLP 784-256-128-10 on MNIST-shaped data", "nodes": n_nodes, "train_set_size": n_nodes,
-            "topology": "line (a full mesh trips a reference race, see benchmarks/reference_arm.py); partial-model gossip all-to-all", "aggregator": "FedAvg (reference NumPy)", "samples_per_node": SAMPLES_PER_NODE, "global_batch": BATCH * n_nodes, "batch_per_node": BATCH, "local_epochs": 1,
-            "protocol": "in-memory (reference)", "learner": "plain-torch shim (lightning is not installable here)", "parallelism": f"8 in-process nodes over {n_gpus} gpu(s)",
+            **common_config(args, n_nodes), "topology": "line",
+            "precision": f"torch defaults: fp32 storage, cudnn.allow_tf32={torch.backends.cudnn.allow_tf32}, cuda.matmul.allow_tf32={torch.backends.cuda.matmul.allow_tf32}",
+            "topology_note": "a full mesh trips a reference race (benchmarks/reference_arm.py); partial-model gossip is all-to-all either way", "aggregator_impl": "reference NumPy FedAvg",
+            "protocol": "in-memory", "learner": "plain-torch shim (lightning is not installable here)", "parallelism": f"{n_nodes} in-process nodes over {n_gpus} gpu(s)",
         },
         "clocks": clocks, "gpu_launches": 0,
     }

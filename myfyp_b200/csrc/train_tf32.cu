@@ -26,7 +26,8 @@
 //   conv0_wgrad    producer-built operands again (patches of x, un-pooled dz), one TMEM accumulator across all tiles of a CTA
 //   adam           fused Adam (+FedProx / Scaffold terms) over the slab; reads the gradient mirror through the layer's index
 //                  permutation, clears it, and writes the next step's tf32 / hi-lo weight mirrors - no separate repack / cast
-// Shared-memory operand layout everywhere: canonical SWIZZLE_128B (one 128-byte row = 32 fp32), K-major or MN-major.
+// Shared-memory operand layouts: K-major = canonical SWIZZLE_128B (one 128-byte row = 32 fp32, 16-byte chunks XOR row & 7);
+// MN-major = the 32-byte-atom variant of it (32-byte chunks XOR row & 3), the only one the tensor core accepts for 32-bit types.
 // TMA loads here read this GPU's memory only and none uses cluster multicast.
 #include <cuda.h>
 
@@ -71,11 +72,14 @@ __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__flo
 __device__ __forceinline__ bool slot_live(const b2_cnn_bind& bd, int step, int batch) { return bd.active != 0 && (long long)step * batch < (long long)bd.n_samples; }
 
 __device__ __forceinline__ uint64_t desc_k(uint32_t addr) { return tc::smem_desc_sw128(addr); }
-// MN-major canonical SWIZZLE_128B: a row = one K index, 32 fp32 of the MN extent; 8-row groups 1024 B apart (SBO); the next 32 MN
-// elements `lbo` bytes further (LBO)
+// MN-major operands of 32-bit types have ONE legal shared-memory layout: 128-byte rows (a row = one K index, 32 fp32 of the MN
+// extent) swizzled in 32-byte chunks with a period of 4 rows (layout type 1, "128B swizzle with 32B atoms"; TMA writes it with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B).  4-row groups are 512 B apart (SBO); the next 32 MN elements `lbo` bytes further (LBO).
 __device__ __forceinline__ uint64_t desc_mn(uint32_t addr, uint32_t lbo) {
-  return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+  return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | (32ull << 32) | (1ull << 46) | (1ull << 61);
 }
+// byte offset of (row, 16-byte chunk) in that layout
+__device__ __forceinline__ uint32_t sw32_offset(uint32_t row, uint32_t chunk16) { return row * 128u + ((((chunk16 >> 1) ^ (row & 3u)) << 5) | ((chunk16 & 1u) << 4)); }
 
 __device__ __forceinline__ void pixel_tile(const Problem& P, int pt, int& n, int& h0) {
   if (P.hw_tiles > 0) {
@@ -480,7 +484,7 @@ __device__ __forceinline__ void c0_stage_input(float* sin, const b2_cnn_bind& bd
 }
 
 // one pixel's 3x3xCIN patch in (tap, channel) order, zero padded to 32, tf32-rounded, into row r of a SWIZZLE_128B tile
-template <int CIN>
+template <int CIN, bool MN>
 __device__ __forceinline__ void c0_build_patch_row(uint8_t* tile, const float* sin, int r) {
   int hh, w;
   c0_row_pixel(r, hh, w);
@@ -494,7 +498,8 @@ __device__ __forceinline__ void c0_build_patch_row(uint8_t* tile, const float* s
 #pragma unroll
       for (int c = 0; c < CIN; ++c) pv[(kh * 3 + kw) * CIN + c] = tf32_rna(sin[c * C0_SIN + (hh + kh) * 34 + w + kw]);
 #pragma unroll
-  for (int ch = 0; ch < 8; ++ch) *reinterpret_cast<float4*>(tile + tc::sw128_offset((uint32_t)r, (uint32_t)ch)) = make_float4(pv[4 * ch], pv[4 * ch + 1], pv[4 * ch + 2], pv[4 * ch + 3]);
+  for (int ch = 0; ch < 8; ++ch)
+    *reinterpret_cast<float4*>(tile + (MN ? sw32_offset((uint32_t)r, (uint32_t)ch) : tc::sw128_offset((uint32_t)r, (uint32_t)ch))) = make_float4(pv[4 * ch], pv[4 * ch + 1], pv[4 * ch + 2], pv[4 * ch + 3]);
 }
 
 template <int CIN>
@@ -544,7 +549,7 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
       float* sn = sin + s * (CIN * C0_SIN);
       c0_stage_input<CIN>(sn, bd, step, P.batch, H, t / tiles_per_img, (t % tiles_per_img) * 4, tid);
       named_bar_sync(1, 128);
-      c0_build_patch_row<CIN>(a_tiles + s * A_BYTES, sn, tid);
+      c0_build_patch_row<CIN, false>(a_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
       tc::mbar_arrive(&full_bar[s]);
     }
@@ -654,7 +659,7 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
     tc::mbar_init(&done_bar, 1);
     tc::mbar_fence_init();
   }
-  if (warp == 4) tc::tmem_alloc<32>(&tmem_base_s);
+  if (warp == 4) tc::tmem_alloc<128>(&tmem_base_s);
   for (int i = tid; i < 2 * C0W_A_STAGE / 16; i += C0_THREADS) reinterpret_cast<float4*>(a_tiles)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   tc::fence_proxy_async();
   tc::fence_before_sync();
@@ -689,11 +694,11 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
           o.y = (((code[ch] >> 8) & 3u) == (uint32_t)pos) ? d.y : 0.f;
           o.z = (((code[ch] >> 16) & 3u) == (uint32_t)pos) ? d.z : 0.f;
           o.w = (((code[ch] >> 24) & 3u) == (uint32_t)pos) ? d.w : 0.f;
-          *reinterpret_cast<float4*>(arow + cb * A_BYTES + tc::sw128_offset((uint32_t)tid, (uint32_t)ch)) = o;
+          *reinterpret_cast<float4*>(arow + cb * A_BYTES + sw32_offset((uint32_t)tid, (uint32_t)ch)) = o;
         }
       }
       named_bar_sync(1, 128);
-      c0_build_patch_row<CIN>(b_tiles + s * A_BYTES, sn, tid);
+      c0_build_patch_row<CIN, true>(b_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
       tc::mbar_arrive(&full_bar[s]);
     }
@@ -706,8 +711,10 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
         tc::mbar_wait(&full_bar[s], (it >> 1) & 1u);
         tc::fence_after_sync();
         const uint32_t a_addr = tc::smem_u32(a_tiles + s * C0W_A_STAGE), b_addr = tc::smem_u32(b_tiles + s * A_BYTES);
+        // the tiles rotate over 4 accumulators (summed in the epilogue): 4x shorter fp32 accumulation chains in the tensor core
+        const uint32_t d_tmem = tmem_base + (it & 3u) * 32u;
 #pragma unroll
-        for (int ks = 0; ks < 16; ++ks) tc::mma_tf32(tmem_base, desc_mn(a_addr + ks * 1024, A_BYTES), desc_mn(b_addr + ks * 1024, A_BYTES), idesc, (it | ks) != 0 ? 1u : 0u);
+        for (int ks = 0; ks < 16; ++ks) tc::mma_tf32(d_tmem, desc_mn(a_addr + ks * 1024, A_BYTES), desc_mn(b_addr + ks * 1024, A_BYTES), idesc, (it >= 4u || ks != 0) ? 1u : 0u);
         tc::mma_commit(&empty_bar[s]);
       }
       tc::mma_commit(&done_bar);
@@ -717,8 +724,15 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
     if (q < cout / 32) {
       tc::mbar_wait(&done_bar, 0);
       tc::fence_after_sync();
+      const int my_tiles = (P.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
       float v[32];
       tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
+      for (int a = 1; a < 4 && a < my_tiles; ++a) {
+        float t[32];
+        tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * 32), t);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] += t[e];
+      }
       float* g = P.gw + (int64_t)(q * 32 + lane) * KD;
 #pragma unroll
       for (int k = 0; k < KD; ++k)
@@ -728,7 +742,7 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 4) tc::tmem_dealloc<32>(tmem_base);
+  if (warp == 4) tc::tmem_dealloc<128>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ head: fc2 + loss + their gradients, fp32
@@ -984,7 +998,7 @@ static EncodeTiledFn encode_fn() {
 }
 
 // fp32 [rows, ld] row-major; box = 32 (inner, one swizzle row) x box_rows
-static int tmap2d(CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows) {
+static int tmap2d(CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows, bool mn = false) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -998,8 +1012,8 @@ static int tmap2d(CUtensorMap* tm, const void* base, int rows, int cols, int ld,
   cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
   cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  mn ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled (fp32 2-D) failed with CUresult %d (rows=%d cols=%d ld=%d box_rows=%d)", (int)r, rows, cols, ld, box_rows);
     return 1;
@@ -1008,7 +1022,7 @@ static int tmap2d(CUtensorMap* tm, const void* base, int rows, int cols, int ld,
 }
 
 // fp32 NHWC activation as {C, W, H, N}; box = {32, W, tile_h, tile_n}
-static int tmap_nhwc(CUtensorMap* tm, const void* base, int n_img, int h, int w, int c, int tile_h, int tile_n) {
+static int tmap_nhwc(CUtensorMap* tm, const void* base, int n_img, int h, int w, int c, int tile_h, int tile_n, bool mn = false) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -1022,8 +1036,8 @@ static int tmap_nhwc(CUtensorMap* tm, const void* base, int n_img, int h, int w,
   cuuint64_t strides[3] = {(cuuint64_t)c * 4, (cuuint64_t)w * c * 4, (cuuint64_t)h * w * c * 4};
   cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)w, (cuuint32_t)tile_h, (cuuint32_t)tile_n};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  mn ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled (fp32 4-D) failed with CUresult %d (n=%d h=%d w=%d c=%d tile %dx%d)", (int)r, n_img, h, w, c, tile_h, tile_n);
     return 1;
@@ -1343,8 +1357,8 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
         P.splits = (total_k + P.kb_per_split - 1) / P.kb_per_split;
         P.cblocks = cin / 32; P.kw = 3; P.off = -1; P.sign = 1; P.ncols = cin;
         bad |= tile_shape(h, h, BK, &P.tile_h, &P.tile_n, &P.hw_tiles) != 0;
-        bad |= tmap2d(&P.ta, dz, pixels, cout, cout, BK) != 0;
-        bad |= tmap_nhwc(&P.tb, x_in, B, h, h, cin, P.tile_h, P.tile_n) != 0;
+        bad |= tmap2d(&P.ta, dz, pixels, cout, cout, BK, true) != 0;
+        bad |= tmap_nhwc(&P.tb, x_in, B, h, h, cin, P.tile_h, P.tile_n, true) != 0;
         P.out = gm + d->off_conv_w[l];
         P.bias_off = -1; P.ldo = kdim;
       }
@@ -1356,7 +1370,7 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
         P.cblocks = cout / 32; P.kw = 3; P.off = 1; P.sign = -1; P.ncols = cin;
         bad |= tile_shape(h, h, BM, &P.tile_h, &P.tile_n, &P.hw_tiles) != 0;
         bad |= tmap_nhwc(&P.ta, dz, B, h, h, cout, P.tile_h, P.tile_n) != 0;
-        bad |= tmap2d(&P.tb, w_m, cout, kdim, kdim, BK) != 0;
+        bad |= tmap2d(&P.tb, w_m, cout, kdim, kdim, BK, true) != 0;
         P.idx = p->slot_ptr(g, L.idx[l - 1]);
         P.colsum = gm + d->off_conv_b[l - 1];
         P.bias_off = -1; P.chans = cin;
@@ -1390,10 +1404,10 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
       Problem& P = p->h_prob[(size_t)p->p_fc1_wgrad() * G + g];
       P.M = hid; P.N = feat; P.K = B; P.batch = B;
       P.tiles_m = (hid + BM - 1) / BM; P.tiles_n = feat / 64; P.splits = 1; P.kb_per_split = (B + BK - 1) / BK;
-      bad |= tmap2d(&P.ta, F(L.dh_hi), B, hid, hid, BK) != 0;
-      bad |= tmap2d(&P.ta_lo, F(L.dh_lo), B, hid, hid, BK) != 0;
-      bad |= tmap2d(&P.tb, F(L.a_hi), B, feat, feat, BK) != 0;
-      bad |= tmap2d(&P.tb_lo, F(L.a_lo), B, feat, feat, BK) != 0;
+      bad |= tmap2d(&P.ta, F(L.dh_hi), B, hid, hid, BK, true) != 0;
+      bad |= tmap2d(&P.ta_lo, F(L.dh_lo), B, hid, hid, BK, true) != 0;
+      bad |= tmap2d(&P.tb, F(L.a_hi), B, feat, feat, BK, true) != 0;
+      bad |= tmap2d(&P.tb_lo, F(L.a_lo), B, feat, feat, BK, true) != 0;
       P.out = gm + d->off_fc1_w; P.ldo = feat; P.bias_off = -1;
     }
     {  // ---- fc1 input gradient: da[B, feat] = dh W1, un-pooled into dz of the last conv layer
@@ -1402,8 +1416,8 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
       P.tiles_m = (B + BM - 1) / BM; P.tiles_n = feat / 64; P.splits = 1; P.kb_per_split = hid / BK;
       bad |= tmap2d(&P.ta, F(L.dh_hi), B, hid, hid, BM) != 0;
       bad |= tmap2d(&P.ta_lo, F(L.dh_lo), B, hid, hid, BM) != 0;
-      bad |= tmap2d(&P.tb, w1, hid, feat, feat, BK) != 0;
-      bad |= tmap2d(&P.tb_lo, wlo, hid, feat, feat, BK) != 0;
+      bad |= tmap2d(&P.tb, w1, hid, feat, feat, BK, true) != 0;
+      bad |= tmap2d(&P.tb_lo, wlo, hid, feat, feat, BK, true) != 0;
       P.out = F(L.dz[nl - 1]);
       P.idx = p->slot_ptr(g, L.idx[nl - 1]);
       P.colsum = gm + d->off_conv_b[nl - 1];
