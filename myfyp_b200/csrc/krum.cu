@@ -201,9 +201,12 @@ __global__ void __launch_bounds__(64) krum_select_kernel(const float* __restrict
   if (i < K) {
     float d[B2_MAX_K];
     int m = 0;
+    int finite = 0;
     for (int j = 0; j < K; ++j) {
       if (j == i) continue;
       float x = dist[i * K + j];
+      if (isnan(x)) x = INFINITY;  // a model with non-finite parameters is infinitely far from everybody: ranks stay a total order
+      finite += isinf(x) ? 0 : 1;
       int p = m++;
       while (p > 0 && d[p - 1] > x) { d[p] = d[p - 1]; --p; }  // insertion sort (K <= 64)
       d[p] = x;
@@ -211,6 +214,10 @@ __global__ void __launch_bounds__(64) krum_select_kernel(const float* __restrict
     int closest = K - f - 2;
     if (closest < 1) closest = 1;
     if (closest > m) closest = m;
+    // fewer finite neighbours than the rule asks for (more broken models than f allows): score over those there are, so that
+    // healthy models still rank ahead of broken ones; a model without any finite neighbour scores +inf
+    if (closest > finite) closest = finite;
+    if (finite == 0 && K > 1) closest = 1;
     float sc = 0.f;
     for (int j = 0; j < closest; ++j) sc += d[j];
     s_score[i] = sc;

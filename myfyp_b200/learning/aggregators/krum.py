@@ -64,11 +64,14 @@ def krum_select_reference(dist, f: int, m: int):
     import numpy as np
 
     dist = np.asarray(dist, dtype=np.float64)
+    dist = np.where(np.isnan(dist), np.inf, dist)  # a broken model is infinitely far away
     k = dist.shape[0]
     closest = max(1, k - f - 2)
     scores = []
     for i in range(k):
         others = np.sort(np.delete(dist[i], i))
-        scores.append(float(others[: min(closest, k - 1)].sum()) if k > 1 else 0.0)
+        finite = int(np.isfinite(others).sum())
+        take = min(closest, k - 1, finite) if finite else min(1, k - 1)
+        scores.append(float(others[:take].sum()) if k > 1 else 0.0)
     order = sorted(range(k), key=lambda i: (scores[i], i))
     return scores, order[:m]

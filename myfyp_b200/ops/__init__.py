@@ -141,9 +141,42 @@ def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Op
 
 # ====================================================================== A6/A7: Krum
 def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None, passes: int = 3) -> torch.Tensor:
-    """K x K matrix of squared L2 distances.  CUDA: centred Gram matrix on tcgen05 (A6) + d = Gii+Gjj-2Gij."""
+    """K x K matrix of squared L2 distances.  CUDA: centred Gram matrix on tcgen05 (A6) + d = Gii+Gjj-2Gij.
+
+    A Byzantine update may contain NaN / Inf / values whose square overflows.  Such a model is put at distance +inf from every
+    other one (never NaN): the Gram matrix is centred on one of the models, so if THAT one is broken every entry is non-finite
+    and the product is redone around the next candidate; otherwise only the broken models' rows and columns are."""
     device = device or pick_device(slabs)
     slabs = _same_place(slabs, device)
+    k = len(slabs)
+    bad: List[int] = []
+    for ref in range(k):
+        order = [ref] + [i for i in range(k) if i != ref]
+        g = _centred_gram([slabs[i] for i in order], device, passes)
+        # a broken centre (NaN / Inf, or so large that every difference overflows) shows as a non-finite own entry or as a
+        # majority of the other models looking broken
+        if bool(torch.isfinite(g[0, 0])) and (k <= 2 or int((~torch.isfinite(torch.diagonal(g)[1:])).sum()) * 2 <= k - 1):
+            break
+        bad.append(ref)
+    else:
+        return torch.full((k, k), float("inf"), device=device).fill_diagonal_(0.0)
+    d = torch.diagonal(g)
+    dist = (d[:, None] + d[None, :] - 2 * g).clamp_min(0)
+    broken = ~torch.isfinite(d)
+    dist[broken, :] = float("inf")
+    dist[:, broken] = float("inf")
+    dist = torch.nan_to_num(dist, nan=float("inf"), posinf=float("inf"))
+    inv = torch.empty(k, dtype=torch.long, device=dist.device)
+    inv[torch.tensor(order, device=dist.device)] = torch.arange(k, device=dist.device)
+    dist = dist[inv][:, inv]  # back to the caller's model order
+    for b in bad:
+        dist[b, :] = float("inf")
+        dist[:, b] = float("inf")
+    return dist.fill_diagonal_(0.0).float()
+
+
+def _centred_gram(slabs: Sequence[torch.Tensor], device: torch.device, passes: int) -> torch.Tensor:
+    """fp64 view of G[i][j] = <slab_i - slab_0, slab_j - slab_0>."""
     k, n = len(slabs), slabs[0].numel()
     if device.type == "cuda":
         if k > MAX_K:
@@ -154,14 +187,10 @@ def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device
         with native.device_guard(device):
             native.check(lib.b2_krum_gram(native.ptr(gram), native.ptr_array(slabs), k, ctypes.c_int64(n), native.ptr(ws), ctypes.c_int(passes), native.stream_ptr(device)), "b2_krum_gram")
         native.count_launch()
-        g = gram.view(MAX_K, MAX_K)[:k, :k].double()
-        d = torch.diagonal(g)
-        return (d[:, None] + d[None, :] - 2 * g).clamp_min(0).float()
+        return gram.view(MAX_K, MAX_K)[:k, :k].double()
     m = torch.stack([s.double() for s in slabs])
     m = m - m[0:1]
-    g = m @ m.T
-    d = torch.diagonal(g)
-    return (d[:, None] + d[None, :] - 2 * g).clamp_min(0).float()
+    return (m @ m.T).float().double()  # through fp32 like the kernel's result: values whose square overflows fp32 count as broken
 
 
 _krum_ws = {}
@@ -183,7 +212,7 @@ def krum_select(dist: torch.Tensor, f: int, m: int) -> Tuple[List[float], List[i
     if dist.is_cuda:
         lib = native.load()
         scores = torch.empty(k, dtype=torch.float32, device=dist.device)
-        sel = torch.empty(k, dtype=torch.int32, device=dist.device)
+        sel = torch.zeros(k, dtype=torch.int32, device=dist.device)
         d = dist.contiguous()
         with native.device_guard(dist.device):
             native.check(lib.b2_krum_select(native.ptr(d), k, f, native.ptr(scores), native.ptr(sel), native.stream_ptr(dist.device)), "b2_krum_select")

@@ -132,6 +132,34 @@ def test_krum_picks_the_cluster_and_ignores_byzantine():
     assert kg.last_selected == k.last_selected
 
 
+@pytest.mark.parametrize("poison", ["nan", "inf", "huge"])
+@pytest.mark.parametrize("where", [0, 3])
+def test_krum_survives_non_finite_models(poison, where):
+    """The simplest Byzantine update: a model full of NaN / Inf / 1e30.  It must rank last wherever it sits in the list (index 0
+    is the model the Gram matrix is centred on), the honest ranking must match the NumPy oracle, and nothing may be NaN."""
+    from myfyp_b200 import ops
+    from myfyp_b200.learning.aggregators.krum import krum_select_reference
+
+    torch.manual_seed(1)
+    base = torch.randn(4096)
+    slabs = [base + 0.01 * torch.randn(4096) for _ in range(6)]
+    slabs[where] = torch.full((4096,), {"nan": float("nan"), "inf": float("inf"), "huge": 1e30}[poison])
+    dist = ops.pairwise_sqdist(slabs)
+    assert not torch.isnan(dist).any()
+    others = [i for i in range(6) if i != where]
+    assert torch.isinf(dist[where, others]).all() and torch.isinf(dist[others, where]).all()
+    assert torch.isfinite(dist[others][:, others]).all()
+    want = torch.cdist(torch.stack([slabs[i] for i in others]).double(), torch.stack([slabs[i] for i in others]).double()) ** 2
+    torch.testing.assert_close(dist[others][:, others].double(), want, rtol=1e-3, atol=1e-6)
+    scores, sel = ops.krum_select(dist, 1, 5)
+    assert where not in sel and sorted(sel) == others
+    assert (scores, sel) == krum_select_reference(dist.numpy(), 1, 5)
+    # more broken models than f allows for: the honest ones still rank first
+    slabs[(where + 1) % 6] = torch.full((4096,), float("nan"))
+    _, sel2 = ops.krum_select(ops.pairwise_sqdist(slabs), 0, 4)
+    assert where not in sel2 and (where + 1) % 6 not in sel2
+
+
 def _scaffold_inputs():
     # the reference's own fixture values (test/learning/scaffold_test.py:80-141)
     p = [np.array([1.0, 2.0]), np.array([3.0])]

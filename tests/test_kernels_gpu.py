@@ -76,6 +76,30 @@ def test_trimmed_mean(dev, k, trim):
 
 
 @pytest.mark.parametrize("k,n,passes", [(2, 4096, 3), (5, 235264, 3), (16, 1 << 20, 3), (64, 131072, 3), (33, 70000, 3), (8, 1 << 20, 1)])
+def test_krum_gpu_path_survives_non_finite_models(dev):
+    """NaN / 1e30 model at index 0 (the centre of the Gram matrix) and at index > 0: distances to it are +inf, never NaN, the
+    selection equals the NumPy oracle's and `sel` holds valid indices only."""
+    import numpy as np
+
+    from myfyp_b200 import ops
+    from myfyp_b200.learning.aggregators.krum import krum_select_reference
+
+    torch.manual_seed(2)
+    base = torch.randn(1 << 16, device=dev)
+    for where in (0, 4):
+        for poison in (float("nan"), 1e30):
+            slabs = [base + 0.01 * torch.randn_like(base) for _ in range(7)]
+            slabs[where] = torch.full_like(base, poison)
+            dist = ops.pairwise_sqdist(slabs)
+            assert not torch.isnan(dist).any()
+            others = [i for i in range(7) if i != where]
+            assert torch.isinf(dist[where, others]).all()
+            scores, sel = ops.krum_select(dist, 1, 6)
+            ref_scores, ref_sel = krum_select_reference(dist.cpu().numpy(), 1, 6)
+            assert sel == ref_sel and where not in sel
+            np.testing.assert_allclose(scores, ref_scores, rtol=1e-5)
+
+
 def test_krum_gram_tcgen05(dev, k, n, passes):
     """Pairwise distances from the tcgen05 Gram kernel vs fp64 direct distances; models close to each other (late-round regime)."""
     from myfyp_b200 import ops
