@@ -46,7 +46,10 @@ class Neighbors:
             logger.info(self.self_addr, "❌ Cannot add itself")
             return False
         with self.neis_lock:
-            if addr in self.neis:
+            cur = self.neis.get(addr)
+            # a node only known through the heartbeat flood (non-direct) may be upgraded to a direct neighbour by an explicit
+            # connect; the reference refuses that as a duplicate (neighbors.py:85-88), which makes a topology impossible to densify
+            if cur is not None and (cur[1] or kwargs.get("non_direct")):
                 logger.debug(self.self_addr, f"❌ Cannot add duplicates. {addr} already exists.")
                 return False
         # connect outside the lock: the handshake calls back into the peer, which may

@@ -111,22 +111,24 @@ __device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane) {
   return w[0];
 }
 
-template <bool X3, int BN>
+template <bool X3, int BN, bool LEAN = false>
 struct Cfg {
   static constexpr int B_BYTES = BN * 128;
   static constexpr int OPS = X3 ? 2 : 1;
   static constexpr int STAGE_BYTES = OPS * (A_BYTES + B_BYTES);
-  static constexpr int STAGES = 4;
+  // LEAN (kernels with a light epilogue): 3 stages, 3 CTAs per SM - these kernels are bound by the latency of their small TMA
+  // boxes, not by bandwidth, so more resident CTAs is what buys throughput
+  static constexpr int STAGES = LEAN ? 3 : 4;
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
-  static constexpr int CTAS_PER_SM = X3 ? 1 : 2;
+  static constexpr int CTAS_PER_SM = X3 ? 1 : (LEAN ? 3 : 2);
   static constexpr uint32_t TMEM_COLS = (uint32_t)(ACC_STAGES * BN) < 32u ? 32u : (uint32_t)(ACC_STAGES * BN);
 };
 
 // ------------------------------------------------------------------------------------------------ grouped tf32 GEMM / implicit conv
 // CONV 0: plain GEMM   1: A = 4-D activation boxes (fwd, or dgrad with B_MN)   2: wgrad (A = dz MN-major, B = activation boxes MN-major)
 template <int CONV, bool A_MN, bool B_MN, bool X3, int EPI, int BN>
-__global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN>::CTAS_PER_SM) ggemm_kernel(const Problem* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
-  using C = Cfg<X3, BN>;
+__global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CTAS_PER_SM) ggemm_kernel(const Problem* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
+  using C = Cfg<X3, BN, EPI == EPI_ATOMIC>;
   const Problem& P = probs[blockIdx.y];
   const b2_cnn_bind& bd = binds[blockIdx.y];
   if (!slot_live(bd, step, P.batch)) return;  // whole CTA leaves before any barrier / TMEM allocation
@@ -466,6 +468,15 @@ __device__ __forceinline__ void c0_row_pixel(int r, int& hh, int& w) {
   w = ((q & 1) << 4) | (l & 15);
 }
 
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, bool valid) {
+  const uint32_t sz = valid ? 4u : 0u;  // src-size 0: the destination is zero-filled, nothing is read
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Asynchronous copy (cp.async) of the tile's input rows h0-1 .. h0+4 of every channel into the staging buffer (interior columns
+// 1..32; the border columns stay zero from the prologue).  The batch row -> data-set sample lookup goes through the permutation.
 template <int CIN>
 __device__ __forceinline__ void c0_stage_input(float* sin, const b2_cnn_bind& bd, int step, int batch, int H, int b, int h0, int ptid) {
   long long posn = (long long)step * batch + b;
@@ -475,11 +486,16 @@ __device__ __forceinline__ void c0_stage_input(float* sin, const b2_cnn_bind& bd
   for (int i = ptid; i < CIN * 6 * 32; i += 128) {
     const int c = i / 192, rr = (i % 192) >> 5, w = i & 31;
     const int h = h0 - 1 + rr;
-    sin[c * C0_SIN + rr * 34 + w + 1] = (h >= 0 && h < H) ? __ldg(xs + ((long long)c * H + h) * C0_W + w) : 0.f;
+    const bool ok = h >= 0 && h < H;
+    cp_async4(sin + c * C0_SIN + rr * 34 + w + 1, ok ? xs + ((long long)c * H + h) * C0_W + w : xs, ok);
   }
-  if (ptid < CIN * 12) {
-    const int c = ptid / 12, rr = (ptid % 12) >> 1, side = ptid & 1;
-    sin[c * C0_SIN + rr * 34 + (side ? 33 : 0)] = 0.f;
+  cp_async_commit();
+}
+__device__ __forceinline__ void c0_zero_borders(float* sin2, int cin, int tid, int nthreads) {
+  for (int i = tid; i < 2 * cin * 12; i += nthreads) {
+    const int st = i / (cin * 12), j = i % (cin * 12);
+    const int c = j / 12, rr = (j % 12) >> 1, side = j & 1;
+    sin2[st * (cin * C0_SIN) + c * C0_SIN + rr * 34 + (side ? 33 : 0)] = 0.f;
   }
 }
 
@@ -528,6 +544,7 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
     tc::mbar_fence_init();
   }
   if (warp == 4) tc::tmem_alloc<128>(&tmem_base_s);
+  c0_zero_borders(sin, CIN, tid, C0_THREADS);
   // weights [cout, KD] -> K-major swizzled rows padded to 32
   for (int i = tid; i < cout * 32; i += C0_THREADS) {
     const int rowi = i >> 5, k = i & 31;
@@ -542,13 +559,17 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
 
   if (warp < 4) {
     // ================================ producers: gather the batch rows by permutation index, build patch rows
+    // the input rows of tile i+1 are in flight (cp.async) while the patch rows of tile i are built
     uint32_t it = 0;
+    if ((int)blockIdx.x < P.tiles) c0_stage_input<CIN>(sin, bd, step, P.batch, H, blockIdx.x / tiles_per_img, (blockIdx.x % tiles_per_img) * 4, tid);
     for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
       const int s = it & 1;
-      tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
       float* sn = sin + s * (CIN * C0_SIN);
-      c0_stage_input<CIN>(sn, bd, step, P.batch, H, t / tiles_per_img, (t % tiles_per_img) * 4, tid);
-      named_bar_sync(1, 128);
+      cp_async_wait_all();
+      named_bar_sync(1, 128);  // everybody's copies have landed, and everybody is done reading the other staging buffer
+      const int tn = t + gridDim.x;
+      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), bd, step, P.batch, H, tn / tiles_per_img, (tn % tiles_per_img) * 4, tid);
+      tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
       c0_build_patch_row<CIN, false>(a_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
       tc::mbar_arrive(&full_bar[s]);
@@ -633,10 +654,15 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
   if (warp == 4) tc::tmem_dealloc<128>(tmem_base);
 }
 
-// dW0[co, k] = sum_pixels dz[pixel, co] * patch[pixel, k]:  M = co (MN-major A, blocks beyond cout / 32 stay zero), N = 32 (k), K = pixels.
-constexpr int C0W_A_STAGE = 4 * A_BYTES;  // 4 MN blocks x 128 pixel rows x 128 B
-template <int CIN>
-__global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0Prob* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
+// dW0[co, k] = sum_pixels dz[pixel, co] * patch[pixel, k]:  M = 64 (co; MN-major A, the block beyond cout stays zero), N = 32 (k),
+// K = pixels.  With M = 64 the accumulator row m sits in TMEM lane 32 * (m / 16) + m % 16: epilogue warp q reads rows 16q .. 16q+15.
+constexpr int C0W_A_STAGE = 2 * A_BYTES;  // 2 MN blocks x 128 pixel rows x 128 B
+struct C0wPre {  // next tile's pooled gradients + winner codes of this thread's pixel, fetched one tile ahead
+  float4 d[8];
+  uint4 i0, i1;
+};
+template <int CIN, int CB>
+__global__ void __launch_bounds__(C0_THREADS, 2) conv0_wgrad_kernel(const Conv0Prob* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
   const Conv0Prob& P = probs[blockIdx.y];
   const b2_cnn_bind& bd = binds[blockIdx.y];
   if (!slot_live(bd, step, P.batch)) return;
@@ -644,11 +670,12 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
   __shared__ __align__(8) uint64_t full_bar[2], empty_bar[2], done_bar;
   __shared__ uint32_t tmem_base_s;
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_tiles = base;                          // 2 x 64 KB
+  uint8_t* a_tiles = base;                          // 2 x 32 KB
   uint8_t* b_tiles = base + 2 * C0W_A_STAGE;        // 2 x 16 KB
   float* sin = reinterpret_cast<float*>(base + 2 * C0W_A_STAGE + 2 * A_BYTES);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int cout = P.cout, H = P.H, tiles_per_img = H / 4;
+  const int H = P.H, tiles_per_img = H / 4;
+  constexpr int cout = 32 * CB;
   constexpr int KD = 9 * CIN;
 
   if (tid == 0) {
@@ -661,6 +688,7 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
   }
   if (warp == 4) tc::tmem_alloc<128>(&tmem_base_s);
   for (int i = tid; i < 2 * C0W_A_STAGE / 16; i += C0_THREADS) reinterpret_cast<float4*>(a_tiles)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  c0_zero_borders(sin, CIN, tid, C0_THREADS);
   tc::fence_proxy_async();
   tc::fence_before_sync();
   __syncthreads();
@@ -668,27 +696,44 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
   const uint32_t tmem_base = tmem_base_s;
 
   if (warp < 4) {
-    uint32_t it = 0;
-    for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
-      const int s = it & 1;
-      tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
-      float* sn = sin + s * (CIN * C0_SIN);
+    int hh, w;
+    c0_row_pixel(tid, hh, w);
+    const int pos = ((hh & 1) << 1) | (w & 1);
+    auto fetch = [&](int t, C0wPre (&pre)[CB]) {
       const int b = t / tiles_per_img, h0 = (t % tiles_per_img) * 4;
-      c0_stage_input<CIN>(sn, bd, step, P.batch, H, b, h0, tid);
-      // this pixel's dz row: the pooled gradient goes to the window's winner only
-      int hh, w;
-      c0_row_pixel(tid, hh, w);
-      const int pos = ((hh & 1) << 1) | (w & 1);
       const int64_t pp = ((int64_t)b * (H >> 1) + ((h0 + hh) >> 1)) * (C0_W >> 1) + (w >> 1);
-      uint8_t* arow = a_tiles + s * C0W_A_STAGE;
-      for (int cb = 0; cb < cout / 32; ++cb) {
+#pragma unroll
+      for (int cb = 0; cb < CB; ++cb) {
         const float4* dp = reinterpret_cast<const float4*>(P.dpm + pp * cout + cb * 32);
         const uint4* ip = reinterpret_cast<const uint4*>(P.idx + pp * cout + cb * 32);
-        const uint4 i0 = ip[0], i1 = ip[1];
-        const uint32_t code[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) pre[cb].d[ch] = __ldg(dp + ch);
+        pre[cb].i0 = __ldg(ip);
+        pre[cb].i1 = __ldg(ip + 1);
+      }
+    };
+    C0wPre cur[CB];
+    uint32_t it = 0;
+    if ((int)blockIdx.x < P.tiles) {
+      c0_stage_input<CIN>(sin, bd, step, P.batch, H, blockIdx.x / tiles_per_img, (blockIdx.x % tiles_per_img) * 4, tid);
+      fetch(blockIdx.x, cur);
+    }
+    for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
+      const int s = it & 1;
+      float* sn = sin + s * (CIN * C0_SIN);
+      cp_async_wait_all();
+      named_bar_sync(1, 128);
+      const int tn = t + gridDim.x;
+      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), bd, step, P.batch, H, tn / tiles_per_img, (tn % tiles_per_img) * 4, tid);
+      tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
+      // this pixel's dz row: the (already ReLU-masked) pooled gradient goes to the window's winner only
+      uint8_t* arow = a_tiles + s * C0W_A_STAGE;
+#pragma unroll
+      for (int cb = 0; cb < CB; ++cb) {
+        const uint32_t code[8] = {cur[cb].i0.x, cur[cb].i0.y, cur[cb].i0.z, cur[cb].i0.w, cur[cb].i1.x, cur[cb].i1.y, cur[cb].i1.z, cur[cb].i1.w};
 #pragma unroll
         for (int ch = 0; ch < 8; ++ch) {
-          const float4 d = dp[ch];
+          const float4 d = cur[cb].d[ch];
           float4 o;
           o.x = (((code[ch] >> 0) & 3u) == (uint32_t)pos) ? d.x : 0.f;
           o.y = (((code[ch] >> 8) & 3u) == (uint32_t)pos) ? d.y : 0.f;
@@ -697,14 +742,14 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
           *reinterpret_cast<float4*>(arow + cb * A_BYTES + sw32_offset((uint32_t)tid, (uint32_t)ch)) = o;
         }
       }
-      named_bar_sync(1, 128);
+      if (tn < P.tiles) fetch(tn, cur);  // in flight while the patch row is built and the next input rows arrive
       c0_build_patch_row<CIN, true>(b_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
       tc::mbar_arrive(&full_bar[s]);
     }
   } else if (warp == 4) {
     if (tc::elect_one()) {
-      const uint32_t idesc = tc::make_idesc(tc::FMT_TF32, BM, 32) | (1u << 15) | (1u << 16);
+      const uint32_t idesc = tc::make_idesc(tc::FMT_TF32, 64, 32) | (1u << 15) | (1u << 16);
       uint32_t it = 0;
       for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
         const int s = it & 1;
@@ -721,7 +766,7 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
     }
   } else {
     const int q = warp & 3;
-    if (q < cout / 32) {
+    if (16 * q < cout) {  // warp-uniform; lanes 16-31 of the quarter hold nothing for M = 64
       tc::mbar_wait(&done_bar, 0);
       tc::fence_after_sync();
       const int my_tiles = (P.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
@@ -733,10 +778,12 @@ __global__ void __launch_bounds__(C0_THREADS, 1) conv0_wgrad_kernel(const Conv0P
 #pragma unroll
         for (int e = 0; e < 32; ++e) v[e] += t[e];
       }
-      float* g = P.gw + (int64_t)(q * 32 + lane) * KD;
+      if (lane < 16) {
+        float* g = P.gw + (int64_t)(q * 16 + lane) * KD;
 #pragma unroll
-      for (int k = 0; k < KD; ++k)
-        if (v[k] != 0.f) atomicAdd(g + k, v[k]);
+        for (int k = 0; k < KD; ++k)
+          if (v[k] != 0.f) atomicAdd(g + k, v[k]);
+      }
       tc::fence_before_sync();
     }
   }
@@ -865,16 +912,24 @@ __global__ void __launch_bounds__(HD_THREADS) head_kernel(const HeadProb* __rest
 }
 
 // ------------------------------------------------------------------------------------------------ Adam + mirror maintenance
+// The slab keeps PyTorch's layouts ([co][ci][tap]); the GEMMs read / write mirrors in [co][tap][ci] order.  Adam walks the slab
+// row by row (one output channel / unit = one row): the row's gradients come in mirror order with coalesced loads, are turned
+// through shared memory, p / m / v are updated in slab order with coalesced accesses, and the new parameters go back through
+// shared memory into the mirror (tf32-rounded, or split hi / lo for the 3xTF32 layers).  Everything else (biases, last layer,
+// padding) is processed in 1024-element chunks.
 struct TensorEnt {
-  long long begin, end;  // element range inside the slab
-  long long lo_off;      // kind 2: offset of this tensor inside the lo mirror
-  int kind;              // 0 plain, 1 permuted [co][ci][tap] -> [co][tap][ci] + tf32 mirror, 2 permuted + hi / lo mirror
-  int cin, taps, pad0;
+  long long begin;   // first element inside the slab
+  long long lo_off;  // kind 2: offset of this tensor inside the lo mirror
+  int rows, ct;      // rows of ct elements (kind 0: chunks of ADAM_CHUNK elements, the last one may be short)
+  int kind;          // 0 plain, 1 permuted + tf32 mirror, 2 permuted + hi / lo mirror
+  int cin, taps;
+  int len;           // kind 0: elements in the region
 };
+constexpr int ADAM_CHUNK = 1024;
+constexpr int ADAM_MAX_ENT = 12;
 struct AdamTab {
-  int n;
-  int pad0;
-  TensorEnt e[12];
+  int n, total_rows, max_ct, pad0;
+  TensorEnt e[ADAM_MAX_ENT];
 };
 struct SlotBufs {
   float* wm;
@@ -882,98 +937,117 @@ struct SlotBufs {
   float* gm;
 };
 
-__global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __restrict__ bufs, const b2_cnn_bind* __restrict__ binds, const __grid_constant__ AdamTab tab, int64_t n4, int step, int batch,
+__device__ __forceinline__ int pad32(int x) { return x + (x >> 5); }
+
+struct AdamCoef {
+  float lr, wd, b1, b2, eps, inv_bc1, inv_sqrt_bc2;
+};
+__device__ __forceinline__ float adam_one(const b2_cnn_bind& bd, const AdamCoef& c, int64_t i, float g, float p, float* m, float* v) {
+  if (c.wd != 0.f) g = fmaf(c.wd, p, g);
+  if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - bd.prox_ref[i], g);
+  if (bd.cv_global != nullptr && bd.cv_local != nullptr) g = fmaf(bd.cv_scale, bd.cv_global[i] - bd.cv_local[i], g);
+  const float mn = fmaf(c.b1, m[i], (1.f - c.b1) * g);
+  const float vn = fmaf(c.b2, v[i], (1.f - c.b2) * g * g);
+  m[i] = mn;
+  v[i] = vn;
+  return p - c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
+}
+
+__global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __restrict__ bufs, const b2_cnn_bind* __restrict__ binds, const __grid_constant__ AdamTab tab, int step, int batch,
                                                            float b1, float b2, float eps, int refresh_only) {
   const b2_cnn_bind& bd = binds[blockIdx.y];
   if (refresh_only ? bd.active == 0 : !slot_live(bd, step, batch)) return;
+  extern __shared__ float asm_[];
+  float* sg = asm_;
+  float* sp = asm_ + pad32(tab.max_ct) + 1;
   const SlotBufs sb = bufs[blockIdx.y];
-  float inv_bc1 = 1.f, inv_sqrt_bc2 = 1.f;
+  AdamCoef c{bd.lr, bd.weight_decay, b1, b2, eps, 1.f, 1.f};
   if (!refresh_only) {
     const float st = bd.adam_state[0] + (float)(step + 1);
-    inv_bc1 = 1.f / (1.f - powf(b1, st));
-    inv_sqrt_bc2 = rsqrtf(1.f - powf(b2, st));
+    c.inv_bc1 = 1.f / (1.f - powf(b1, st));
+    c.inv_sqrt_bc2 = rsqrtf(1.f - powf(b2, st));
   }
-  const float lr = bd.lr, wd = bd.weight_decay;
-  float4* p4 = reinterpret_cast<float4*>(bd.slab);
-  float4* m4 = reinterpret_cast<float4*>(bd.m);
-  float4* v4 = reinterpret_cast<float4*>(bd.v);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += stride) {
-    const int64_t i = 4 * i4;
-    int kind = 0, cin = 1, taps = 1;
-    long long begin = 0, lo_off = 0;
-    for (int t = 0; t < tab.n; ++t)
-      if (i >= tab.e[t].begin && i < tab.e[t].end) {
-        kind = tab.e[t].kind; cin = tab.e[t].cin; taps = tab.e[t].taps; begin = tab.e[t].begin; lo_off = tab.e[t].lo_off;
-      }
-    int64_t j[4];
-    if (kind == 0) {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) j[e] = i + e;
-    } else {
-      const int ct = cin * taps;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int64_t local = i + e - begin;
-        const int64_t co = local / ct;
-        const int r = (int)(local - co * ct);
-        const int ci = r / taps, tap = r - ci * taps;
-        j[e] = begin + co * ct + tap * cin + ci;
-      }
+  const int tid = threadIdx.x;
+  for (int row = blockIdx.x; row < tab.total_rows; row += gridDim.x) {
+    int t = 0, r = row;
+    while (t + 1 < tab.n && r >= tab.e[t].rows) {
+      r -= tab.e[t].rows;
+      ++t;
     }
-    float4 pv = p4[i4];
-    float* pp = &pv.x;
+    const TensorEnt& en = tab.e[t];
+    if (en.kind == 0) {
+      const int64_t i0 = en.begin + (int64_t)r * ADAM_CHUNK;
+      int cnt = en.len - r * ADAM_CHUNK;
+      cnt = cnt > ADAM_CHUNK ? ADAM_CHUNK : cnt;
+      for (int l = tid; l < cnt; l += 256) {
+        const int64_t i = i0 + l;
+        if (!refresh_only) {
+          const float g = sb.gm[i];
+          bd.slab[i] = adam_one(bd, c, i, g, bd.slab[i], bd.m, bd.v);
+        }
+        sb.gm[i] = 0.f;
+      }
+      continue;
+    }
+    const int ct = en.ct;
+    const int64_t base = en.begin + (int64_t)r * ct;
     if (!refresh_only) {
-      float g[4];
+      for (int l = tid; l < ct; l += 256) sg[pad32(l)] = sb.gm[base + l];
+    }
+    for (int l = tid; l < ct; l += 256) sb.gm[base + l] = 0.f;
+    __syncthreads();
+    // four rows of 256 threads per trip, every global load issued before the first use (p, m, v and the optional terms)
+    for (int l0 = 0; l0 < ct; l0 += 4 * 256) {
+      float pv[4], mv[4], vv[4], q[4], cg[4], cl[4];
+      int jm[4];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        g[e] = sb.gm[j[e]];
-        sb.gm[j[e]] = 0.f;
+      for (int u = 0; u < 4; ++u) {
+        const int l = l0 + u * 256 + tid;
+        const bool ok = l < ct;
+        const int64_t i = base + (ok ? l : 0);
+        pv[u] = bd.slab[i];
+        if (!refresh_only) {
+          mv[u] = bd.m[i];
+          vv[u] = bd.v[i];
+          q[u] = bd.prox_ref != nullptr ? bd.prox_ref[i] : 0.f;
+          cg[u] = bd.cv_global != nullptr && bd.cv_local != nullptr ? bd.cv_global[i] : 0.f;
+          cl[u] = bd.cv_global != nullptr && bd.cv_local != nullptr ? bd.cv_local[i] : 0.f;
+        }
+        const int ci = l / en.taps, tap = l - ci * en.taps;
+        jm[u] = pad32(tap * en.cin + ci);
       }
-      if (wd != 0.f) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) g[e] = fmaf(wd, pp[e], g[e]);
+      for (int u = 0; u < 4; ++u) {
+        const int l = l0 + u * 256 + tid;
+        if (l >= ct) continue;
+        float p = pv[u];
+        if (!refresh_only) {
+          float g = sg[jm[u]];
+          if (c.wd != 0.f) g = fmaf(c.wd, p, g);
+          if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - q[u], g);
+          g = fmaf(bd.cv_scale, cg[u] - cl[u], g);
+          const float mn = fmaf(c.b1, mv[u], (1.f - c.b1) * g);
+          const float vn = fmaf(c.b2, vv[u], (1.f - c.b2) * g * g);
+          p -= c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
+          bd.m[base + l] = mn;
+          bd.v[base + l] = vn;
+          bd.slab[base + l] = p;
+        }
+        sp[jm[u]] = p;
       }
-      if (bd.prox_ref != nullptr) {
-        const float4 qv = reinterpret_cast<const float4*>(bd.prox_ref)[i4];
-        const float* qq = &qv.x;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) g[e] = fmaf(bd.prox_mu, pp[e] - qq[e], g[e]);
-      }
-      if (bd.cv_global != nullptr && bd.cv_local != nullptr) {
-        const float4 cg = reinterpret_cast<const float4*>(bd.cv_global)[i4], cl = reinterpret_cast<const float4*>(bd.cv_local)[i4];
-        const float* cgp = &cg.x;
-        const float* clp = &cl.x;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) g[e] = fmaf(bd.cv_scale, cgp[e] - clp[e], g[e]);
-      }
-      float4 mv = m4[i4], vv = v4[i4];
-      float* mp = &mv.x;
-      float* vp = &vv.x;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        mp[e] = fmaf(b1, mp[e], (1.f - b1) * g[e]);
-        vp[e] = fmaf(b2, vp[e], (1.f - b2) * g[e] * g[e]);
-        pp[e] -= lr * (mp[e] * inv_bc1) / (sqrtf(vp[e]) * inv_sqrt_bc2 + eps);
-      }
-      p4[i4] = pv;
-      m4[i4] = mv;
-      v4[i4] = vv;
+    }
+    __syncthreads();
+    if (en.kind == 1) {
+      for (int l = tid; l < ct; l += 256) sb.wm[base + l] = tf32_rna(sp[pad32(l)]);
     } else {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) sb.gm[j[e]] = 0.f;
-    }
-    if (kind == 1) {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) sb.wm[j[e]] = tf32_rna(pp[e]);
-    } else if (kind == 2) {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float hi = tf32_hi(pp[e]);
-        sb.wm[j[e]] = hi;
-        sb.wlo[j[e] - begin + lo_off] = tf32_rna(pp[e] - hi);
+      float* lo = sb.wlo + en.lo_off + (int64_t)r * ct;
+      for (int l = tid; l < ct; l += 256) {
+        const float p = sp[pad32(l)], hi = tf32_hi(p);
+        sb.wm[base + l] = hi;
+        lo[l] = tf32_rna(p - hi);
       }
     }
+    __syncthreads();
   }
 }
 
@@ -1174,7 +1248,7 @@ static int64_t tables_bytes(const Plan& p) {
 
 template <int CONV, bool A_MN, bool B_MN, bool X3, int EPI, int BN>
 static int launch_gg(const Plan& p, int pi, int step, cudaStream_t st) {
-  using C = Cfg<X3, BN>;
+  using C = Cfg<X3, BN, EPI == EPI_ATOMIC>;
   auto kern = ggemm_kernel<CONV, A_MN, B_MN, X3, EPI, BN>;
   static bool attr_set[64] = {false};
   static std::mutex mu;
@@ -1197,6 +1271,11 @@ static int launch_gg(const Plan& p, int pi, int step, cudaStream_t st) {
   return 0;
 }
 
+template <int CIN, int CB>
+static void launch_conv0_wgrad_t(const Plan& p, int gx, int smem, int step, cudaStream_t st) {
+  conv0_wgrad_kernel<CIN, CB><<<dim3(gx, p.G), C0_THREADS, smem, st>>>(p.d_c0, p.d_bind, step);
+}
+
 static int launch_conv0(const Plan& p, bool wgrad, int step, cudaStream_t st) {
   static bool attr_set[64] = {false};
   static std::mutex mu;
@@ -1210,18 +1289,23 @@ static int launch_conv0(const Plan& p, bool wgrad, int step, cudaStream_t st) {
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
       B2_CUDA(cudaFuncSetAttribute(conv0_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
       B2_CUDA(cudaFuncSetAttribute(conv0_fwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_f));
-      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
-      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+      B2_CUDA(cudaFuncSetAttribute(conv0_wgrad_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
       attr_set[dev] = true;
     }
   }
   const int tiles = p.d.batch * p.H[0] / 4;
-  int per_slot = (p.sms * (wgrad ? 1 : 2) + p.G - 1) / p.G;
+  int per_slot = (p.sms * 2 + p.G - 1) / p.G;
   if (per_slot < 8) per_slot = 8;
   const int gx = tiles < per_slot ? tiles : per_slot;
   if (wgrad) {
-    if (p.d.in_ch == 3) conv0_wgrad_kernel<3><<<dim3(gx, p.G), C0_THREADS, smem_w, st>>>(p.d_c0, p.d_bind, step);
-    else conv0_wgrad_kernel<1><<<dim3(gx, p.G), C0_THREADS, smem_w, st>>>(p.d_c0, p.d_bind, step);
+    const int cb = p.Cout[0] / 32;
+    if (p.d.in_ch == 3 && cb == 1) launch_conv0_wgrad_t<3, 1>(p, gx, smem_w, step, st);
+    else if (p.d.in_ch == 3) launch_conv0_wgrad_t<3, 2>(p, gx, smem_w, step, st);
+    else if (cb == 1) launch_conv0_wgrad_t<1, 1>(p, gx, smem_w, step, st);
+    else launch_conv0_wgrad_t<1, 2>(p, gx, smem_w, step, st);
   } else {
     if (p.d.in_ch == 3) conv0_fwd_kernel<3><<<dim3(gx, p.G), C0_THREADS, smem_f, st>>>(p.d_c0, p.d_bind, step);
     else conv0_fwd_kernel<1><<<dim3(gx, p.G), C0_THREADS, smem_f, st>>>(p.d_c0, p.d_bind, step);
@@ -1249,12 +1333,23 @@ static int launch_head(const Plan& p, int step, int train, cudaStream_t st) {
 }
 
 static int launch_adam(const Plan& p, int step, int refresh_only, cudaStream_t st) {
-  const int64_t n4 = p.d.slab_elems / 4;
-  int gx = (int)((n4 + 255) / 256);
-  int cap = (p.sms * 8 + p.G - 1) / p.G;
+  const int smem = (2 * (p.tab.max_ct + p.tab.max_ct / 32 + 2)) * 4;
+  static bool attr_set[64] = {false};
+  static std::mutex mu;
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      B2_CUDA(cudaFuncSetAttribute(adam_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+      attr_set[dev] = true;
+    }
+  }
+  int gx = p.tab.total_rows;
+  int cap = (p.sms * 6 + p.G - 1) / p.G;
   if (cap < 16) cap = 16;
   if (gx > cap) gx = cap;
-  adam_grouped_kernel<<<dim3(gx, p.G), 256, 0, st>>>(p.d_bufs, p.d_bind, p.tab, n4, step, p.d.batch, 0.9f, 0.999f, 1e-8f, refresh_only);
+  adam_grouped_kernel<<<dim3(gx, p.G), 256, smem, st>>>(p.d_bufs, p.d_bind, p.tab, step, p.d.batch, 0.9f, 0.999f, 1e-8f, refresh_only);
   B2_LAUNCH_CHECK("adam_grouped_kernel");
   return 0;
 }
@@ -1428,20 +1523,38 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
     delete p;
     return nullptr;
   }
-  // Adam / mirror table
+  // Adam / mirror table: the permuted tensors row by row, everything between them in chunks
   AdamTab& tab = p->tab;
-  tab.n = 0;
-  for (int l = 0; l < nl; ++l) {
+  tab = AdamTab{};
+  struct Perm { int64_t begin, numel; int rows, ct, kind, cin, taps; };
+  std::vector<Perm> perms;
+  for (int l = 0; l < nl; ++l) perms.push_back(Perm{d->off_conv_w[l], (int64_t)p->Cout[l] * p->Cin[l] * 9, p->Cout[l], p->Cin[l] * 9, 1, p->Cin[l], 9});
+  perms.push_back(Perm{d->off_fc1_w, (int64_t)d->hidden * p->feat, d->hidden, p->feat, 2, p->Cout[nl - 1], p->fh * p->fh});
+  for (size_t a = 0; a < perms.size(); ++a)  // slab order
+    for (size_t b = a + 1; b < perms.size(); ++b)
+      if (perms[b].begin < perms[a].begin) std::swap(perms[a], perms[b]);
+  int64_t cursor = 0;
+  auto plain = [&](int64_t from, int64_t to) {
+    if (to <= from || tab.n >= ADAM_MAX_ENT) return;
     TensorEnt& e = tab.e[tab.n++];
-    e.begin = d->off_conv_w[l];
-    e.end = e.begin + (int64_t)p->Cout[l] * p->Cin[l] * 9;
-    e.kind = 1; e.cin = p->Cin[l]; e.taps = 9; e.lo_off = 0;
+    e = TensorEnt{};
+    e.begin = from; e.kind = 0; e.len = (int)(to - from); e.rows = (e.len + ADAM_CHUNK - 1) / ADAM_CHUNK; e.ct = ADAM_CHUNK;
+  };
+  for (const Perm& q : perms) {
+    plain(cursor, q.begin);
+    if (tab.n >= ADAM_MAX_ENT) break;
+    TensorEnt& e = tab.e[tab.n++];
+    e = TensorEnt{};
+    e.begin = q.begin; e.rows = q.rows; e.ct = q.ct; e.kind = q.kind; e.cin = q.cin; e.taps = q.taps; e.lo_off = 0;
+    if (q.ct > tab.max_ct) tab.max_ct = q.ct;
+    cursor = q.begin + q.numel;
   }
-  {
-    TensorEnt& e = tab.e[tab.n++];
-    e.begin = d->off_fc1_w;
-    e.end = e.begin + (int64_t)d->hidden * p->feat;
-    e.kind = 2; e.cin = p->Cout[nl - 1]; e.taps = p->fh * p->fh; e.lo_off = 0;
+  plain(cursor, d->slab_elems);
+  for (int i = 0; i < tab.n; ++i) tab.total_rows += tab.e[i].rows;
+  if (tab.max_ct > 15000 || (perms.size() * 2 + 1 > (size_t)ADAM_MAX_ENT)) {
+    set_error("cnn plan: layer rows of %d elements exceed the optimizer kernel's shared memory", tab.max_ct);
+    delete p;
+    return nullptr;
   }
   bool fail = false;
   fail |= cudaMemcpyAsync(p->d_prob, p->h_prob.data(), p->h_prob.size() * sizeof(Problem), cudaMemcpyHostToDevice, st) != cudaSuccess;
