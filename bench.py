@@ -346,6 +346,7 @@ def run_ours(args) -> None:
         except Exception as e:  # noqa: BLE001 - the headline line must still be printed
             full_mesh = {"error": f"{type(e).__name__}: {e}"[:200]}
 
+    stale = int(allsum(arena.stale_refused)) if multi else 0
     cohort = None
     if args.model == "cnn" and args.dtype == "tf32":
         from myfyp_b200.models.grouped_cnn import CohortTrainer
@@ -383,6 +384,8 @@ def run_ours(args) -> None:
             out["full_mesh"] = full_mesh
         if cohort is not None:
             out["cohort_rank0"] = cohort
+        if multi:
+            out["stale_descriptors_refused"] = stale
         if e2e is not None:
             out["e2e"] = e2e
         print(json.dumps(out), flush=True)

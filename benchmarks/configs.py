@@ -25,7 +25,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples, train_set, device_mode, byzantine=0, faults=None, seed=0, batch=64, graphs=None):
+def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples, train_set, device_mode, byzantine=0, faults=None, seed=0, batch=64, graphs=None, max_gpus=None, learner_kw=None):
     import numpy as np
     import torch
 
@@ -56,6 +56,8 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
     parts = data.generate_partitions(n_nodes, RandomIIDPartitionStrategy, seed=seed)
     mk = {"mlp": mlp_model, "cnn": cnn_model, "resnet18": resnet18_model}[model_name]
     gpus = torch.cuda.device_count() if device_mode == "cuda" else 0
+    if max_gpus:
+        gpus = min(gpus, max_gpus)
     if graphs is None:  # all three models train through their hand-written steps: one CUDA graph per local epoch
         graphs = True
     Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS = 60
@@ -64,7 +66,7 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
     nodes = []
     for i in range(n_nodes):
         dev = f"cuda:{i % gpus}" if gpus else "cpu"
-        nodes.append(Node(mk(device=dev, seed=seed + i), parts[i], address=f"{name}-{i}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs))
+        nodes.append(Node(mk(device=dev, seed=seed + i), parts[i], address=f"{name}-{i}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs, **(learner_kw or {})))
     for n in nodes:
         n.start()
     for n in nodes[n_nodes - byzantine :]:
@@ -83,7 +85,7 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
             fi.drop_at(nodes[idx], round=rnd, stage=None if j == 0 else "TrainStage")
         for idx, at_round in faults.get("rejoin", []):
             def make(idx=idx):
-                n = Node(mk(device=f"cuda:{idx % gpus}" if gpus else "cpu", seed=1000 + idx), parts[idx], address=f"{name}-re-{idx}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs)
+                n = Node(mk(device=f"cuda:{idx % gpus}" if gpus else "cpu", seed=1000 + idx), parts[idx], address=f"{name}-re-{idx}", aggregator=aggregator_factory(), protocol=InMemoryCommunicationProtocol, batch_size=batch, use_cuda_graph=graphs, **(learner_kw or {}))
                 late.append(n)
                 return n
             targets = [nodes[j].addr for j in range(min(4, n_nodes)) if j != idx]
@@ -165,8 +167,10 @@ def main() -> None:
     else:
         n = a.nodes or 64
         faults = {"drop": [(n - 1, 1), (n - 2, 1)], "rejoin": [(n - 1, 3)]}  # two nodes die in round 1, one comes back in round 3
-        for nm, agg in (("c4-scaffold", lambda: Scaffold(global_lr=1.0)), ("c4-fedprox", lambda: FedProx(mu=0.01))):
-            res.append(run(nm, n, a.model or "resnet18", agg, "random", a.rounds, a.samples_per_node or 256, min(8, n), mode, faults=faults))
+        # Scaffold's control variates estimate gradients from (x - y) / (K lr): that is SGD arithmetic (Karimireddy et al., Alg. 1), so
+        # its clients run SGD; FedProx keeps the reference's Adam
+        for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0), {"optimizer": "sgd", "lr": 0.05}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
+            res.append(run(nm, n, a.model or "resnet18", agg, "random", a.rounds, a.samples_per_node or 256, min(8, n), mode, faults=faults, learner_kw=kw))
     if a.out:
         os.makedirs(os.path.dirname(os.path.abspath(a.out)) or ".", exist_ok=True)
         with open(a.out, "w") as f:

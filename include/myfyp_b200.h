@@ -27,6 +27,17 @@ int b2_arena_free(void* p);
 int b2_ipc_export(void* base, char* out_handle64);
 void* b2_ipc_open(const char* handle64);
 int b2_ipc_close(void* p);
+/* Interprocess events (cudaEventInterprocess): recorded by the publisher after the copy into an arena slot, waited for by the
+ * consumer's stream before the slot is read - the cross-process edge that replaces a host synchronisation.  No reference
+ * counterpart (the reference ships pickled bytes, gossiper.py:229-235). */
+void* b2_ipc_event_create(void);
+int b2_ipc_event_export(void* ev, char* out_handle64);
+void* b2_ipc_event_open(const char* handle64);
+int b2_event_record(void* ev, void* stream);
+int b2_stream_wait_event(void* stream, void* ev);
+int b2_event_destroy(void* ev);
+/* 1 / 0: launch the training-step kernels of the bf16 path with / without programmatic dependent launch (default off; B2_PDL=1). */
+void b2_set_pdl(int on);
 
 /* ------------------------------------------------------------------------------------------------ aggregation */
 /* A1 FedAvg K-way pull-reduce: out = (accumulate ? out : 0) + sum_k weights[k] * srcs[k].  `srcs`/`weights` are HOST
@@ -236,6 +247,8 @@ typedef struct {
   float prox_mu, cv_scale, lr, weight_decay;
   int n_samples;
   int active;
+  int sgd;          /* 0: Adam (m, v);  1: SGD with momentum (buffer in m, v unused) */
+  float momentum;
 } b2_cnn_bind;
 int64_t b2_cnn_workspace_bytes(const b2_cnn_desc* d);
 /* `workspace` (device, 1024-byte aligned, b2_cnn_workspace_bytes) is carved into every slot's activations, weight mirrors and

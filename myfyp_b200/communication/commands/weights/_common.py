@@ -2,7 +2,7 @@
 
 import contextlib
 
-from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError
+from myfyp_b200.learning.exceptions import DecodingParamsError, ModelNotMatchingError, StaleDescriptorError
 
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
@@ -31,6 +31,10 @@ def bad_model_guard(state, stop_fn, source: str, protocol=None):
     SENDER's fault as far as this node can tell - apply :func:`handle_bad_model` instead of letting the handler die."""
     try:
         yield
+    except StaleDescriptorError as e:
+        # nobody's fault: the owner has reused the slot since it sent the descriptor (we were slow, or the message was kept for a
+        # later stage).  The model is refused; the sender still sees us lacking it and offers its current snapshot again.
+        logger.warning(state.addr, f"Refused a model from {source}: {e}")
     except DecodingParamsError:
         handle_bad_model(state, stop_fn, source, "Error decoding parameters", protocol)
     except ModelNotMatchingError:

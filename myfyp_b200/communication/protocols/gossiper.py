@@ -151,8 +151,15 @@ class Gossiper(threading.Thread):
         create_connection: bool,
         wait_fn: Optional[Callable[[float], None]] = None,
     ) -> None:
-        x = Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS
-        last_status: Deque[str] = collections.deque(maxlen=max(1, x))
+        # "X equal rounds" is a statement about TIME in the reference (its rounds are one period apart, gossiper.py:205-222).  The
+        # loop here is also woken by state changes that have nothing to do with the status (ballots for the next round, other
+        # nodes' announcements): such wake-ups re-evaluate the candidates but must not count, or ten of them within milliseconds
+        # end the gossip while a peer still lacks models.  A tick is counted once per period without a status change.
+        x = max(1, Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS)
+        tick = period if period > 0 else 0.02
+        last_seen: Optional[str] = None
+        equal_ticks = 0
+        tick_at = time.monotonic()
         while True:
             t0 = time.monotonic()
             if early_stopping_fn():
@@ -164,8 +171,12 @@ class Gossiper(threading.Thread):
                 return
             logger.debug(self.__self_addr, f"👥 Gossip remaining nodes: {neis}")
             before = repr(status_fn())
-            last_status.append(before)
-            if len(last_status) == x and all(s == before for s in last_status):
+            if before != last_seen:
+                last_seen, equal_ticks, tick_at = before, 0, t0
+            elif t0 - tick_at >= tick:
+                equal_ticks += 1
+                tick_at = t0
+            if equal_ticks >= x:
                 logger.info(self.__self_addr, f"⏹️  Gossiping exited for {x} equal rounds.")
                 return
             outbox = []

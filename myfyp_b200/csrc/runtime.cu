@@ -123,4 +123,51 @@ int b2_ipc_close(void* p) {
   return 0;
 }
 
+/* Interprocess events: the publisher records one after the copy into an arena slot, a consumer in another process makes its
+ * stream wait for it before it dereferences the slot - cross-process ordering without a host synchronisation on either side. */
+void* b2_ipc_event_create(void) {
+  cudaEvent_t ev = nullptr;
+  cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming | cudaEventInterprocess);
+  if (e != cudaSuccess) {
+    b2::cuda_fail(e, "cudaEventCreateWithFlags(interprocess)");
+    return nullptr;
+  }
+  return ev;
+}
+
+int b2_ipc_event_export(void* ev, char* out_handle64) {
+  cudaIpcEventHandle_t h;
+  B2_CUDA(cudaIpcGetEventHandle(&h, static_cast<cudaEvent_t>(ev)));
+  static_assert(sizeof(h) == 64, "cudaIpcEventHandle_t is 64 bytes");
+  memcpy(out_handle64, &h, sizeof(h));
+  return 0;
+}
+
+void* b2_ipc_event_open(const char* handle64) {
+  cudaIpcEventHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  cudaEvent_t ev = nullptr;
+  cudaError_t e = cudaIpcOpenEventHandle(&ev, h);
+  if (e != cudaSuccess) {
+    b2::cuda_fail(e, "cudaIpcOpenEventHandle");
+    return nullptr;
+  }
+  return ev;
+}
+
+int b2_event_record(void* ev, void* stream) {
+  B2_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(ev), static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+int b2_stream_wait_event(void* stream, void* ev) {
+  B2_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), static_cast<cudaEvent_t>(ev), 0));
+  return 0;
+}
+
+int b2_event_destroy(void* ev) {
+  B2_CUDA(cudaEventDestroy(static_cast<cudaEvent_t>(ev)));
+  return 0;
+}
+
 }  // extern "C"

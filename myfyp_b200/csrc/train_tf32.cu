@@ -946,6 +946,11 @@ __device__ __forceinline__ float adam_one(const b2_cnn_bind& bd, const AdamCoef&
   if (c.wd != 0.f) g = fmaf(c.wd, p, g);
   if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - bd.prox_ref[i], g);
   if (bd.cv_global != nullptr && bd.cv_local != nullptr) g = fmaf(bd.cv_scale, bd.cv_global[i] - bd.cv_local[i], g);
+  if (bd.sgd) {
+    const float mn = bd.momentum != 0.f ? fmaf(bd.momentum, m[i], g) : g;
+    if (bd.momentum != 0.f) m[i] = mn;
+    return p - c.lr * mn;
+  }
   const float mn = fmaf(c.b1, m[i], (1.f - c.b1) * g);
   const float vn = fmaf(c.b2, v[i], (1.f - c.b2) * g * g);
   m[i] = mn;
@@ -1026,11 +1031,17 @@ __global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __res
           if (c.wd != 0.f) g = fmaf(c.wd, p, g);
           if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - q[u], g);
           g = fmaf(bd.cv_scale, cg[u] - cl[u], g);
-          const float mn = fmaf(c.b1, mv[u], (1.f - c.b1) * g);
-          const float vn = fmaf(c.b2, vv[u], (1.f - c.b2) * g * g);
-          p -= c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
-          bd.m[base + l] = mn;
-          bd.v[base + l] = vn;
+          if (bd.sgd) {
+            const float mn = bd.momentum != 0.f ? fmaf(bd.momentum, mv[u], g) : g;
+            p -= c.lr * mn;
+            if (bd.momentum != 0.f) bd.m[base + l] = mn;
+          } else {
+            const float mn = fmaf(c.b1, mv[u], (1.f - c.b1) * g);
+            const float vn = fmaf(c.b2, vv[u], (1.f - c.b2) * g * g);
+            p -= c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
+            bd.m[base + l] = mn;
+            bd.v[base + l] = vn;
+          }
           bd.slab[base + l] = p;
         }
         sp[jm[u]] = p;

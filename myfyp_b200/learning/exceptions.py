@@ -7,3 +7,7 @@ class DecodingParamsError(Exception):
 
 class ModelNotMatchingError(Exception):
     """Received parameters do not fit this model's architecture."""
+
+
+class StaleDescriptorError(Exception):
+    """A slab descriptor names an arena slot that its owner has published something newer into since."""

@@ -225,7 +225,7 @@ class TorchLearner(Learner):
             trace(self._self_addr, "fit:alloc")
             steps = 0
             graph_ok = cuda and self.use_cuda_graph
-            grouped = self._cohort(module) if graph_ok and self.optimizer == "adam" else None
+            grouped = self._cohort(module) if graph_ok and self.optimizer in ("adam", "sgd") else None
             if grouped is not None:
                 steps, vals_grouped = self._fit_grouped(grouped, x, y, n, st, terms, steps_per_epoch)
             elif graph_ok:
@@ -319,7 +319,8 @@ class TorchLearner(Learner):
         ev.record(self._stream)
         args = dict(
             slab=model.slab, m=st["m"], v=st["v"], adam_state=st["dev_state"], x=x, y=y, perm=perm if self.shuffle else None, losses=losses, n_samples=n,
-            lr=self.lr, weight_decay=self.weight_decay, epochs=self.epochs, max_steps=self.max_steps_per_epoch, shuffle=self.shuffle, make_perm=make_perm, ready=ev, **terms,
+            lr=self.lr, weight_decay=self.weight_decay, optimizer=self.optimizer, momentum=self.momentum, epochs=self.epochs, max_steps=self.max_steps_per_epoch,
+            shuffle=self.shuffle, make_perm=make_perm, ready=ev, **terms,
         )
         res = trainer.submit("fit", self, args)
         return res["steps"], res["losses"]

@@ -55,7 +55,7 @@ class _Bind(ctypes.Structure):
         ("x", ctypes.c_void_p), ("y", ctypes.c_void_p), ("perm", ctypes.c_void_p), ("losses", ctypes.c_void_p),
         ("prox_ref", ctypes.c_void_p), ("cv_global", ctypes.c_void_p), ("cv_local", ctypes.c_void_p),
         ("prox_mu", ctypes.c_float), ("cv_scale", ctypes.c_float), ("lr", ctypes.c_float), ("weight_decay", ctypes.c_float),
-        ("n_samples", ctypes.c_int), ("active", ctypes.c_int),
+        ("n_samples", ctypes.c_int), ("active", ctypes.c_int), ("sgd", ctypes.c_int), ("momentum", ctypes.c_float),
     ]
 
 
@@ -177,6 +177,7 @@ class CnnPlan:
             b.prox_mu, b.cv_scale = float(s.get("prox_mu", 0.0)) if s.get("prox_ref") is not None else 0.0, float(s.get("cv_scale", 1.0))
             b.lr, b.weight_decay = float(s.get("lr", 1e-3)), float(s.get("weight_decay", 0.0))
             b.n_samples, b.active = int(s["n_samples"]), 1
+            b.sgd, b.momentum = (1 if s.get("optimizer", "adam") == "sgd" else 0), float(s.get("momentum", 0.0))
         with native.device_guard(self.device):
             native.check(_lib().b2_cnn_plan_bind(self._h, ctypes.byref(self._binds), native.stream_ptr(self.device)), "b2_cnn_plan_bind")
 

@@ -121,4 +121,4 @@ class Fabric:
             return ref.tensor
         if self._arena is None:
             raise RuntimeError("descriptor from another process but no IPC arena is attached (Fabric.attach_arena)")
-        return self._arena.view(ref.rank, ref.offset, ref.numel)
+        return self._arena.view(ref.rank, ref.offset, ref.numel, ref.generation)

@@ -14,6 +14,7 @@ descriptors only while it is itself in round r, and no node runs more than one r
 from __future__ import annotations
 
 import ctypes
+import os
 import pickle
 import threading
 from typing import Any, Dict, List
@@ -90,6 +91,22 @@ class ArenaPool:
         self._local = _wrap(self._base, self.slot_elems * slots, device)
         self._peers: Dict[int, torch.Tensor] = {rank: self._local}
         self._peer_bases: Dict[int, int] = {}
+        # one interprocess event per slot: recorded after the publishing copy, waited for by the consumer's stream
+        self._lib.b2_ipc_event_create.restype = ctypes.c_void_p
+        self._lib.b2_ipc_event_open.restype = ctypes.c_void_p
+        with torch.cuda.device(device):
+            self._events = [self._lib.b2_ipc_event_create() for _ in range(slots)]
+        if not all(self._events):
+            native.check(1, "b2_ipc_event_create")
+        self._peer_event_handles: Dict[int, List[bytes]] = {}
+        self._peer_events: Dict[tuple, int] = {}
+        # generation of every slot, in host shared memory every rank of the job maps: a descriptor is only as good as the
+        # generation it was issued for (slots rotate)
+        self._job = os.environ.get("MASTER_PORT", "0") + "-" + os.environ.get("TORCHELASTIC_RUN_ID", "0")
+        self._gen_table = _GenTable(self._job, rank, slots, create=True)
+        self._peer_gen: Dict[int, "_GenTable"] = {rank: self._gen_table}
+        self._peer_slot_elems: Dict[int, int] = {rank: self.slot_elems}
+        self.stale_refused = 0
 
     def export_handle(self) -> bytes:
         buf = ctypes.create_string_buffer(self.HANDLE_BYTES)
@@ -98,10 +115,23 @@ class ArenaPool:
         native.check(self._lib.b2_ipc_export(ctypes.c_void_p(self._base), buf), "b2_ipc_export")
         return bytes(buf.raw)
 
-    def import_handles(self, handles: List[bytes], slot_elems: List[int], slots: List[int]) -> None:
+    def export_event_handles(self) -> List[bytes]:
+        from myfyp_b200.ops import native
+
+        out = []
+        for ev in self._events:
+            buf = ctypes.create_string_buffer(self.HANDLE_BYTES)
+            native.check(self._lib.b2_ipc_event_export(ctypes.c_void_p(ev), buf), "b2_ipc_event_export")
+            out.append(bytes(buf.raw))
+        return out
+
+    def import_handles(self, handles: List[bytes], slot_elems: List[int], slots: List[int], event_handles: Optional[List[List[bytes]]] = None) -> None:
         from myfyp_b200.ops import native
 
         for r, h in enumerate(handles):
+            self._peer_slot_elems[r] = slot_elems[r]
+            if event_handles is not None and r != self.rank:
+                self._peer_event_handles[r] = event_handles[r]
             if r == self.rank:
                 continue
             with torch.cuda.device(self.device):
@@ -115,13 +145,18 @@ class ArenaPool:
         """All-gather the IPC handles over ``torch.distributed`` (object collective: plumbing, not the hot path)."""
         import torch.distributed as dist
 
-        mine = (self.export_handle(), self.slot_elems, self.slots)
+        mine = (self.export_handle(), self.slot_elems, self.slots, self.export_event_handles())
         gathered: List[Any] = [None] * self.world
         dist.all_gather_object(gathered, mine)
-        self.import_handles([g[0] for g in gathered], [g[1] for g in gathered], [g[2] for g in gathered])
+        self.import_handles([g[0] for g in gathered], [g[1] for g in gathered], [g[2] for g in gathered], [g[3] for g in gathered])
 
     def publish(self, slab: torch.Tensor):
+        """Copy ``slab`` into the next slot of the ring and return its coordinates.  No host synchronisation: the slot's
+        interprocess event is recorded behind the copy, and whoever dereferences the descriptor makes its stream wait for
+        that event first (:meth:`view`).  The slot's generation is bumped in the shared table BEFORE the copy is queued, so a
+        descriptor of the slot's previous content is refused from this moment on."""
         from myfyp_b200 import ops
+        from myfyp_b200.ops import native
         from myfyp_b200.parallel.fabric import Snapshot
 
         n = slab.numel()
@@ -132,20 +167,88 @@ class ArenaPool:
             self._next = (self._next + 1) % self.slots
             self._gen += 1
             gen = self._gen
+            self._gen_table.set(slot, gen)
         off = slot * self.slot_elems
         view = self._local[off : off + n]
         ops.pull_copy(view, slab)
-        # the descriptor is sent by the host right after: make the copy visible before any peer can dereference it
-        torch.cuda.current_stream(self.device).synchronize()
+        with torch.cuda.device(self.device):
+            native.check(self._lib.b2_event_record(ctypes.c_void_p(self._events[slot]), native.stream_ptr(self.device)), "b2_event_record")
         return Snapshot(view, self.rank, off, gen)
 
-    def view(self, rank: int, offset: int, numel: int) -> torch.Tensor:
+    def view(self, rank: int, offset: int, numel: int, generation: int = 0) -> torch.Tensor:
+        """Tensor view of ``(rank, offset)``.  With a ``generation`` the descriptor is validated against the owner's table
+        (:class:`StaleDescriptorError` if the slot has been reused) and the current stream of this GPU is made to wait for the
+        slot's publication event, so kernels queued afterwards see the published bytes."""
+        from myfyp_b200.learning.exceptions import StaleDescriptorError
+        from myfyp_b200.ops import native
+
+        if generation:
+            slot = offset // self._peer_slot_elems.get(rank, self.slot_elems)
+            tab = self._peer_gen.get(rank)
+            if tab is None:
+                tab = self._peer_gen[rank] = _GenTable(self._job, rank, 0, create=False)
+            now = tab.get(slot)
+            if now != generation:
+                self.stale_refused += 1
+                raise StaleDescriptorError(f"slot {slot} of rank {rank} holds generation {now}, the descriptor was issued for {generation}")
+            if rank != self.rank:
+                key = (rank, slot)
+                ev = self._peer_events.get(key)
+                if ev is None and rank in self._peer_event_handles:
+                    with torch.cuda.device(self.device):
+                        ev = self._lib.b2_ipc_event_open(ctypes.c_char_p(self._peer_event_handles[rank][slot]))
+                    if not ev:
+                        native.check(1, f"b2_ipc_event_open(rank {rank}, slot {slot})")
+                    self._peer_events[key] = ev
+                if ev:
+                    with torch.cuda.device(self.device):
+                        native.check(self._lib.b2_stream_wait_event(native.stream_ptr(self.device), ctypes.c_void_p(ev)), "b2_stream_wait_event")
         return self._peers[rank][offset : offset + numel]
+
+    def still_valid(self, rank: int, offset: int, generation: int) -> bool:
+        """Host-side re-check for a consumer that kept a descriptor (or a view) around: has the slot been reused since?"""
+        tab = self._peer_gen.get(rank)
+        return tab is None or tab.get(offset // self._peer_slot_elems.get(rank, self.slot_elems)) == generation
 
     def close(self) -> None:
         for r, p in self._peer_bases.items():
             self._lib.b2_ipc_close(ctypes.c_void_p(p))
         self._peer_bases.clear()
+        for tab in self._peer_gen.values():
+            tab.close()
+
+
+class _GenTable:
+    """``int64[slots]`` in ``/dev/shm`` (one file per rank and job): the generation currently held by every arena slot.
+    Written by the owner, mapped read-only by the peers; an aligned 8-byte store / load is atomic on every platform we run on."""
+
+    def __init__(self, job: str, rank: int, slots: int, create: bool) -> None:
+        import mmap
+
+        self.path = f"/dev/shm/b2-arena-{job}-{rank}.gen"
+        self.owner = create
+        if create:
+            with open(self.path, "wb") as f:
+                f.write(b"\0" * (8 * max(slots, 1)))
+        self._f = open(self.path, "r+b" if create else "rb")
+        self._mm = mmap.mmap(self._f.fileno(), 0, access=mmap.ACCESS_WRITE if create else mmap.ACCESS_READ)
+        self._view = memoryview(self._mm).cast("q")
+
+    def set(self, slot: int, gen: int) -> None:
+        self._view[slot] = gen
+
+    def get(self, slot: int) -> int:
+        return self._view[slot]
+
+    def close(self) -> None:
+        try:
+            self._view.release()
+            self._mm.close()
+            self._f.close()
+            if self.owner:
+                os.unlink(self.path)
+        except Exception:  # noqa: BLE001
+            pass
 
 
 class _Holder:

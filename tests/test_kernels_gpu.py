@@ -582,7 +582,7 @@ def test_native_cnn_step_matches_reference(dev, batch):
 
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    model = cnn_model(device="cuda:0", seed=2, native=True)
+    model = cnn_model(device="cuda:0", seed=2, native=True, precision="bf16")
     module = model.get_model()
     x = torch.randn(batch, 3, 32, 32, device=dev)
     y = torch.randint(0, 10, (batch,), device=dev)
@@ -615,7 +615,7 @@ def test_native_cnn_learns(dev):
     from myfyp_b200.models import cnn_model
 
     data = P2PFLDataset.synthetic_cifar10(2048, 512, seed=4)
-    model = cnn_model(device="cuda:0", seed=1, native=True)
+    model = cnn_model(device="cuda:0", seed=1, native=True, precision="bf16")
     assert getattr(model.get_model(), "native_train_step", None) is not None
     learner = TorchLearner(model, data, "n0", batch_size=64)
     learner.set_epochs(2)

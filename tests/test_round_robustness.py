@@ -310,3 +310,31 @@ def test_coalescing_never_replaces_a_forwarded_message_of_another_node():
         assert all("_ckey" not in m for _, m in sent_msgs)
     finally:
         g.stop()
+
+
+def test_model_gossip_stall_exit_counts_periods_not_wake_ups():
+    """GOSSIP_EXIT_ON_X_EQUAL_ROUNDS is about time (the reference's rounds are one period apart): a storm of unrelated state
+    notifications must not end the model gossip early, but x periods without progress must."""
+    from myfyp_b200.settings import Settings
+
+    class _Client:
+        def send(self, nei, msg, create_connection=False):
+            pass
+
+    old = Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS
+    Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS = 4
+    try:
+        g = Gossiper("me", _Client(), period=0.0, messages_per_period=1000)
+        wakes = []
+
+        def wait_fn(left):  # every wait is cut short at once, as a busy NodeState.notify() does
+            wakes.append(time.monotonic())
+            time.sleep(0.002)
+
+        t0 = time.monotonic()
+        g.gossip_weights(lambda: False, lambda: ["peer"], lambda: "no progress", lambda nei: None, period=0.1, create_connection=False, wait_fn=wait_fn)
+        took = time.monotonic() - t0
+        assert len(wakes) > 40, "the loop was woken many times"
+        assert 0.38 <= took < 1.5, f"exit after 4 periods of 0.1 s without progress, not after 4 wake-ups (took {took:.3f} s)"
+    finally:
+        Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS = old
