@@ -38,13 +38,16 @@ def main() -> None:
     ap.add_argument("--sizes-mb", type=float, nargs="*", default=[1, 4, 16, 64, 256, 1024])
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--no-nvls", action="store_true")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
     from myfyp_b200 import ops
-    from myfyp_b200.parallel.collective import TwoShotFedAvg
+    from myfyp_b200.parallel.collective import NvlsFedAvg, TwoShotFedAvg, nvls_available
+
+    use_nvls = world > 1 and nvls_available() and not a.no_nvls
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     samples = [float(10 + 3 * r) for r in range(world)]
@@ -96,6 +99,23 @@ def main() -> None:
             dist.all_reduce(yy)
 
         t_nccl = timed(nccl, iters)
+        t_nvls, err1v = None, None
+        if use_nvls:
+            # in-switch reduction: pre-weight into the bound buffer (the same elementwise pass the NCCL arm pays), one kernel
+            nv = NvlsFedAvg(n, rank, world, dev)
+
+            def nvls():
+                torch.mul(x, weights[rank], out=nv.src)
+                nv()
+
+            nvls()
+            torch.cuda.synchronize(dev)
+            if nv.timed_out():
+                raise RuntimeError("NVLS all-reduce timed out")
+            err1v = float((out1 - nv.out).abs().max())
+            t_nvls = timed(nvls, iters)
+            nv.close()
+            del nv
         row = {
             "gpus": world, "model_MB": mb,
             "oneshot_ms": round(t_one, 4), "twoshot_ms": round(t_two, 4), "nccl_ms": round(t_nccl, 4),
@@ -103,8 +123,13 @@ def main() -> None:
             "oneshot_input_GBs": round(world * size / t_one / 1e6, 1), "twoshot_input_GBs": round(world * size / t_two / 1e6, 1),
             "oneshot_roofline_frac": round(((world - 1) * size / (NVLINK_GBS * 1e6)) / t_one, 3),
             "twoshot_roofline_frac": round((2 * (world - 1) / world * size / (NVLINK_GBS * 1e6)) / t_two, 3),
-            "speedup_vs_nccl": round(t_nccl / min(t_one, t_two), 2), "max_abs_diff_one_vs_two": err12, "max_abs_diff_one_vs_nccl": err1n,
+            "speedup_vs_nccl": round(t_nccl / min(t for t in (t_one, t_two, t_nvls) if t), 2), "max_abs_diff_one_vs_two": err12, "max_abs_diff_one_vs_nccl": err1n,
         }
+        if t_nvls:
+            # NVLink bytes per GPU with the reduction in the switch: S/G read-reduced + S/G multicast-stored on the sending side,
+            # and (G-1)/G * S arriving - the receive direction is the bound
+            row.update(nvls_ms=round(t_nvls, 4), nvls_algbw_GBs=round(size / t_nvls / 1e6, 1), nvls_roofline_frac=round(((world - 1) / world * size / (NVLINK_GBS * 1e6)) / t_nvls, 3),
+                       nvls_vs_nccl=round(t_nccl / t_nvls, 2), max_abs_diff_one_vs_nvls=err1v)
         if rank == 0 and mb <= 256:
             import numpy as np
 

@@ -36,6 +36,10 @@ void* b2_ipc_event_open(const char* handle64);
 int b2_event_record(void* ev, void* stream);
 int b2_stream_wait_event(void* stream, void* ev);
 int b2_event_destroy(void* ev);
+/* NVLS probe: per device CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED and, where at least two devices report it, whether a multicast
+ * object over them can actually be created (the prerequisite of multimem.ld_reduce / multimem.st aggregation).  Human-readable
+ * report in `out`; returns 1 = usable, 0 = not exposed to this process, < 0 = driver error.  No reference counterpart. */
+int b2_multicast_probe(char* out, int cap);
 /* 1 / 0: launch the training-step kernels of the bf16 path with / without programmatic dependent launch (default off; B2_PDL=1). */
 void b2_set_pdl(int on);
 
@@ -75,6 +79,23 @@ int64_t b2_twoshot_flag_bytes(void);
 /* `weights` is a HOST array of `world` floats (n_g / sum n); `epoch` must be 1, 2, 3... on successive calls (same on every rank). */
 int b2_fedavg_twoshot(const b2_twoshot_args* dev_args, int ranks_in_launch, int64_t n, const float* weights, int world, unsigned int epoch, int max_ctas,
                       void* stream);
+
+/* A2, NVLS variant: the same average through NVSwitch multicast (csrc/nvls.cu): rank r reduces coordinate shard r with
+ * multimem.ld_reduce (the switch adds the ranks' values) and multimem.st broadcasts it; barriers are multimem.red on a multicast
+ * flag.  Set-up: the root creates the multicast object (b2_nvls_root_create -> POSIX fd, handed to the other ranks), every rank
+ * joins (imports + adds its device), and - after ALL ranks have joined - binds its buffer.  Region layout: [flags | in | out],
+ * offsets in bytes.  Inputs must be pre-weighted; `scale` multiplies the sum.  Waits are bounded (~2 s); b2_nvls_last_timeout
+ * reports a call that gave up.  Availability: b2_multicast_probe.  No reference counterpart (fedavg.py:61-69 runs on the host). */
+int64_t b2_nvls_granularity(int world);
+int b2_nvls_root_create(int world, int64_t bytes, int* out_fd);
+void* b2_nvls_join(int fd, int world, int rank, int64_t bytes);
+int b2_nvls_bind(void* comm);
+void* b2_nvls_local_ptr(void* comm);
+void* b2_nvls_mc_ptr(void* comm);
+int64_t b2_nvls_flag_bytes(void);
+int b2_nvls_allreduce(void* comm, int64_t off_in, int64_t off_out, int64_t n, unsigned int epoch, float scale, int max_ctas, void* stream);
+int b2_nvls_last_timeout(void* comm, unsigned int* epoch_out);
+int b2_nvls_destroy(void* comm);
 
 /* A6 Krum Gram matrix on tcgen05: gram[i*ld+j] = <src_i - src_0, src_j - src_0>, i,j < K <= 64, ld = 64, fp32 via
  * 3xTF32 split.  Split-K over coordinate chunks: every CTA keeps its partial Gram in TMEM, spills it to

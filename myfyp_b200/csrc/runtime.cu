@@ -3,6 +3,8 @@
 #include <cstdlib>
 #include <mutex>
 
+#include <cuda.h>
+
 #include "../../include/myfyp_b200.h"
 #include "common.cuh"
 
@@ -168,6 +170,79 @@ int b2_stream_wait_event(void* stream, void* ev) {
 int b2_event_destroy(void* ev) {
   B2_CUDA(cudaEventDestroy(static_cast<cudaEvent_t>(ev)));
   return 0;
+}
+
+/* NVLS probe: does this box expose NVSwitch multicast objects (the basis of multimem.ld_reduce / multimem.st) to this process?
+ * Reports, per device, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED and, when at least two devices say yes, the outcome of actually
+ * creating a multicast object over all of them (cuMulticastGetGranularity + cuMulticastCreate + cuMulticastAddDevice); the object
+ * is released again.  Text goes to `out`; returns 1 when a multicast object could be created, 0 when not, < 0 on a driver error. */
+int b2_multicast_probe(char* out, int cap) {
+  auto put = [&](const char* fmt, auto... a) {
+    const int used = (int)strlen(out);
+    if (used < cap - 1) snprintf(out + used, cap - used, fmt, a...);
+  };
+  if (cap > 0) out[0] = 0;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    put("no CUDA device\n");
+    return -1;
+  }
+  auto entry = [&](const char* name) -> void* {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return nullptr;
+    return p;
+  };
+  typedef CUresult (*GetAttrFn)(int*, CUdevice_attribute, CUdevice);
+  typedef CUresult (*McGranFn)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  typedef CUresult (*McCreateFn)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+  typedef CUresult (*McAddFn)(CUmemGenericAllocationHandle, CUdevice);
+  typedef CUresult (*ReleaseFn)(CUmemGenericAllocationHandle);
+  GetAttrFn get_attr = (GetAttrFn)entry("cuDeviceGetAttribute");
+  McGranFn mc_gran = (McGranFn)entry("cuMulticastGetGranularity");
+  McCreateFn mc_create = (McCreateFn)entry("cuMulticastCreate");
+  McAddFn mc_add = (McAddFn)entry("cuMulticastAddDevice");
+  ReleaseFn release = (ReleaseFn)entry("cuMemRelease");
+  if (get_attr == nullptr) {
+    put("cuDeviceGetAttribute not resolvable\n");
+    return -1;
+  }
+  int yes = 0;
+  for (int d = 0; d < n; ++d) {
+    int v = 0, fab = 0;
+    cudaSetDevice(d);
+    cudaFree(0);
+    const CUresult r = get_attr(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d);
+    get_attr(&fab, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_FABRIC_SUPPORTED, d);
+    put("device %d: MULTICAST_SUPPORTED=%d (CUresult %d), HANDLE_TYPE_FABRIC_SUPPORTED=%d\n", d, v, (int)r, fab);
+    yes += v ? 1 : 0;
+  }
+  cudaSetDevice(0);
+  if (yes < 2 || mc_gran == nullptr || mc_create == nullptr || mc_add == nullptr || release == nullptr) {
+    put("multicast object: not attempted (%d device(s) report support; entry points %s)\n", yes, mc_create ? "present" : "missing");
+    return 0;
+  }
+  CUmulticastObjectProp prop;
+  memset(&prop, 0, sizeof(prop));
+  prop.numDevices = (unsigned)yes;
+  prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t gran = 0;
+  CUresult r = mc_gran(&gran, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED);
+  put("cuMulticastGetGranularity: CUresult %d, recommended granularity %zu bytes\n", (int)r, gran);
+  if (r != CUDA_SUCCESS) return 0;
+  prop.size = gran;
+  CUmemGenericAllocationHandle h = 0;
+  r = mc_create(&h, &prop);
+  put("cuMulticastCreate(%u devices, %zu bytes): CUresult %d\n", prop.numDevices, prop.size, (int)r);
+  if (r != CUDA_SUCCESS) return 0;
+  int added = 0;
+  for (int d = 0; d < n && added < yes; ++d) {
+    r = mc_add(h, d);
+    put("cuMulticastAddDevice(%d): CUresult %d\n", d, (int)r);
+    added += r == CUDA_SUCCESS ? 1 : 0;
+  }
+  release(h);
+  return added == yes ? 1 : 0;
 }
 
 }  // extern "C"

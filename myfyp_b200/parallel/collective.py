@@ -145,3 +145,151 @@ def nccl_fedavg(x: torch.Tensor, n_k: float, total: float) -> torch.Tensor:
     y = x * (n_k / total)
     dist.all_reduce(y)
     return y
+
+
+# ====================================================================================================== NVLS (in-switch reduction)
+def nvls_available() -> bool:
+    """True when at least two visible GPUs report multicast support AND a multicast object over them can be created."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2 or not native.available():
+        return False
+    buf = ctypes.create_string_buffer(4096)
+    return native.load().b2_multicast_probe(buf, 4096) == 1
+
+
+class NvlsFedAvg:
+    """Sum (then scale) of one slab per rank through NVSwitch multicast: ``multimem.ld_reduce`` lets the switch add the ranks'
+    values of an address in one load, ``multimem.st`` writes the result into every rank's output (kernel in ``csrc/nvls.cu``).
+    Callers put their PRE-WEIGHTED model (``n_g / N * theta_g``, or a rank-local weighted partial average) into ``src``.
+
+    * ``NvlsFedAvg(n, rank, world, device)`` under ``torchrun``: rank 0 creates the multicast object and hands its file
+      descriptor to the other ranks over a unix socket (``SCM_RIGHTS``); every rank adds its device, then binds its buffer;
+    * ``NvlsFedAvg.in_process(n, devices)``: one communicator per GPU of a single process (tests, the one-process deployment).
+
+    No reference counterpart (p2pfl averages NumPy arrays on the host, fedavg.py:61-69); NCCL's own NVLS algorithm is the competitor.
+    """
+
+    def __init__(self, n: int, rank: int, world: int, device: torch.device, _fd: Optional[int] = None, _defer_bind: bool = False) -> None:
+        if n % 4:
+            raise ValueError("n must be a multiple of 4")
+        self.n, self.rank, self.world, self.device = n, rank, world, device
+        lib = self.lib = native.load()
+        lib.b2_nvls_granularity.restype = ctypes.c_int64
+        lib.b2_nvls_join.restype = ctypes.c_void_p
+        lib.b2_nvls_join.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int64]
+        lib.b2_nvls_local_ptr.restype = ctypes.c_void_p
+        lib.b2_nvls_local_ptr.argtypes = [ctypes.c_void_p]
+        lib.b2_nvls_flag_bytes.restype = ctypes.c_int64
+        for f in (lib.b2_nvls_bind, lib.b2_nvls_destroy):
+            f.argtypes = [ctypes.c_void_p]
+        lib.b2_nvls_allreduce.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_uint, ctypes.c_float, ctypes.c_int, ctypes.c_void_p]
+        lib.b2_nvls_last_timeout.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        gran = int(lib.b2_nvls_granularity(world))
+        if gran <= 0:
+            native.check(1, "b2_nvls_granularity")
+        flag = int(lib.b2_nvls_flag_bytes())
+        self.off_in, self.off_out = flag, flag + 4 * n
+        self.bytes = (flag + 8 * n + gran - 1) // gran * gran
+        self.epoch = 0
+        fd = _fd
+        if fd is None:
+            fd = self._exchange_fd()
+        with torch.cuda.device(device):
+            self._h = lib.b2_nvls_join(fd, world, rank, ctypes.c_int64(self.bytes))
+        if not self._h:
+            native.check(1, "b2_nvls_join")
+        if _fd is None:
+            import os as _os
+
+            _os.close(fd)
+        if not _defer_bind:
+            if _fd is None:
+                import torch.distributed as dist
+
+                dist.barrier()  # every device is in the team before anyone binds
+            self._bind()
+
+    def _bind(self) -> None:
+        with torch.cuda.device(self.device):
+            native.check(self.lib.b2_nvls_bind(self._h), "b2_nvls_bind")
+        base = int(self.lib.b2_nvls_local_ptr(self._h))
+        self.src = _wrap(base + self.off_in, self.n, self.device)
+        self.out = _wrap(base + self.off_out, self.n, self.device)
+
+    def _exchange_fd(self) -> int:
+        """Rank 0 creates the multicast object; its descriptor travels to the other ranks as ancillary data of a unix socket."""
+        import os
+        import socket
+
+        import torch.distributed as dist
+
+        path = f"/tmp/b2-nvls-{os.environ.get('MASTER_PORT', '0')}-{os.getpid() if self.world == 1 else 'job'}.sock"
+        if self.rank == 0:
+            fd = ctypes.c_int(-1)
+            with torch.cuda.device(self.device):
+                native.check(self.lib.b2_nvls_root_create(self.world, ctypes.c_int64(self.bytes), ctypes.byref(fd)), "b2_nvls_root_create")
+            try:
+                os.unlink(path)
+            except OSError:
+                pass
+            srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            srv.bind(path)
+            srv.listen(self.world)
+            dist.barrier()
+            for _ in range(self.world - 1):
+                conn, _ = srv.accept()
+                socket.send_fds(conn, [b"mc"], [fd.value])
+                conn.close()
+            srv.close()
+            os.unlink(path)
+            return fd.value
+        dist.barrier()
+        cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        cli.connect(path)
+        _, fds, _, _ = socket.recv_fds(cli, 16, 1)
+        cli.close()
+        return fds[0]
+
+    @classmethod
+    def in_process(cls, n: int, devices: Sequence[torch.device]) -> List["NvlsFedAvg"]:
+        import os
+
+        lib = native.load()
+        lib.b2_nvls_granularity.restype = ctypes.c_int64
+        lib.b2_nvls_flag_bytes.restype = ctypes.c_int64
+        world = len(devices)
+        gran = int(lib.b2_nvls_granularity(world))
+        if gran <= 0:
+            native.check(1, "b2_nvls_granularity")
+        nbytes = (int(lib.b2_nvls_flag_bytes()) + 8 * n + gran - 1) // gran * gran
+        fd = ctypes.c_int(-1)
+        with torch.cuda.device(devices[0]):
+            native.check(lib.b2_nvls_root_create(world, ctypes.c_int64(nbytes), ctypes.byref(fd)), "b2_nvls_root_create")
+        comms = [cls(n, r, world, d, _fd=fd.value, _defer_bind=True) for r, d in enumerate(devices)]
+        os.close(fd.value)
+        for c in comms:
+            c._bind()
+        return comms
+
+    def __call__(self, scale: float = 1.0, max_ctas: int = 0) -> torch.Tensor:
+        """Launch on the current stream of this rank's device.  Every rank must call with the same sequence of calls."""
+        self.epoch += 1
+        with native.device_guard(self.device):
+            native.check(
+                self.lib.b2_nvls_allreduce(self._h, self.off_in, self.off_out, self.n, self.epoch, ctypes.c_float(scale), max_ctas, native.stream_ptr(self.device)),
+                "b2_nvls_allreduce",
+            )
+        native.count_launch()
+        return self.out
+
+    def timed_out(self) -> bool:
+        """After the stream has been synchronised: did the last call give up waiting for a rank?"""
+        e = ctypes.c_uint(0)
+        with native.device_guard(self.device):
+            native.check(self.lib.b2_nvls_last_timeout(self._h, ctypes.byref(e)), "b2_nvls_last_timeout")
+        return e.value == self.epoch and self.epoch > 0
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.src = self.out = None
+            self.lib.b2_nvls_destroy(self._h)
+            self._h = None

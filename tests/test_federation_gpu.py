@@ -76,3 +76,37 @@ def test_arena_refuses_a_descriptor_whose_slot_was_reused():
         assert pool.stale_refused == 1
     finally:
         pool.close()
+
+
+@pytest.mark.skipif(N_GPUS < 2, reason="NVLS needs at least two GPUs")
+def test_nvls_in_switch_fedavg_matches_fp64():
+    """multimem.ld_reduce / multimem.st all-reduce over every visible GPU (one process, one communicator per GPU) against an fp64
+    weighted average; two calls in a row (epoch handling), odd sizes."""
+    from myfyp_b200.parallel.collective import NvlsFedAvg, nvls_available
+
+    if not nvls_available():
+        pytest.skip("the box does not expose NVSwitch multicast to this process")
+    devs = [torch.device("cuda", i) for i in range(N_GPUS)]
+    for n in (1 << 20, 4 * 12345):
+        comms = NvlsFedAvg.in_process(n, devs)
+        try:
+            for trial in range(2):
+                g = torch.Generator().manual_seed(n + trial)
+                xs = [torch.randn(n, generator=g) for _ in devs]
+                ws = torch.rand(len(devs), generator=g)
+                ws = (ws / ws.sum()).tolist()
+                for c, x, w in zip(comms, xs, ws):
+                    with torch.cuda.device(c.device):
+                        c.src.copy_((x * w).to(c.device))
+                for c in comms:
+                    with torch.cuda.device(c.device):
+                        c()
+                for c in comms:
+                    torch.cuda.synchronize(c.device)
+                    assert not c.timed_out()
+                want = sum(x.double() * w for x, w in zip(xs, ws)).float()
+                for c in comms:
+                    torch.testing.assert_close(c.out.cpu(), want, rtol=1e-5, atol=1e-6)
+        finally:
+            for c in comms:
+                c.close()
