@@ -40,6 +40,7 @@ int b2_event_destroy(void* ev);
  * object over them can actually be created (the prerequisite of multimem.ld_reduce / multimem.st aggregation).  Human-readable
  * report in `out`; returns 1 = usable, 0 = not exposed to this process, < 0 = driver error.  No reference counterpart. */
 int b2_multicast_probe(char* out, int cap);
+int b2_multicast_supported(void); /* attribute of the current device only; creates no context elsewhere */
 /* 1 / 0: launch the training-step kernels of the bf16 path with / without programmatic dependent launch (default off; B2_PDL=1). */
 void b2_set_pdl(int on);
 

@@ -172,6 +172,18 @@ int b2_event_destroy(void* ev) {
   return 0;
 }
 
+/* 1 when the CURRENT device reports CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED (no context is created on any other GPU). */
+int b2_multicast_supported(void) {
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return 0;
+  typedef CUresult (*GetAttrFn)(int*, CUdevice_attribute, CUdevice);
+  if (((GetAttrFn)p)(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS) return 0;
+  return v ? 1 : 0;
+}
+
 /* NVLS probe: does this box expose NVSwitch multicast objects (the basis of multimem.ld_reduce / multimem.st) to this process?
  * Reports, per device, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED and, when at least two devices say yes, the outcome of actually
  * creating a multicast object over all of them (cuMulticastGetGranularity + cuMulticastCreate + cuMulticastAddDevice); the object
@@ -207,17 +219,16 @@ int b2_multicast_probe(char* out, int cap) {
     put("cuDeviceGetAttribute not resolvable\n");
     return -1;
   }
-  int yes = 0;
+  int yes = 0, cur = 0;
+  cudaGetDevice(&cur);
   for (int d = 0; d < n; ++d) {
     int v = 0, fab = 0;
-    cudaSetDevice(d);
-    cudaFree(0);
     const CUresult r = get_attr(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d);
     get_attr(&fab, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_FABRIC_SUPPORTED, d);
     put("device %d: MULTICAST_SUPPORTED=%d (CUresult %d), HANDLE_TYPE_FABRIC_SUPPORTED=%d\n", d, v, (int)r, fab);
     yes += v ? 1 : 0;
   }
-  cudaSetDevice(0);
+  cudaSetDevice(cur);
   if (yes < 2 || mc_gran == nullptr || mc_create == nullptr || mc_add == nullptr || release == nullptr) {
     put("multicast object: not attempted (%d device(s) report support; entry points %s)\n", yes, mc_create ? "present" : "missing");
     return 0;

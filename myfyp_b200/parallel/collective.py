@@ -149,11 +149,11 @@ def nccl_fedavg(x: torch.Tensor, n_k: float, total: float) -> torch.Tensor:
 
 # ====================================================================================================== NVLS (in-switch reduction)
 def nvls_available() -> bool:
-    """True when at least two visible GPUs report multicast support AND a multicast object over them can be created."""
-    if not torch.cuda.is_available() or torch.cuda.device_count() < 2 or not native.available():
+    """True when the current GPU reports NVSwitch multicast support (``tools/nvls_probe.py`` goes further and creates an object).
+    Touches no other GPU: a rank must not grow contexts on its peers' devices just to ask."""
+    if not torch.cuda.is_available() or not native.available():
         return False
-    buf = ctypes.create_string_buffer(4096)
-    return native.load().b2_multicast_probe(buf, 4096) == 1
+    return native.load().b2_multicast_supported() == 1
 
 
 class NvlsFedAvg:
