@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"], help="tf32 = the reference's precision (fp32 storage, TF32 convolutions, fp32-class linear layers)")
     ap.add_argument("--topology", default="line", choices=["line", "full"], help="line = what the reference arm can run (its own test topology); full = BASELINE config 2 as worded")
     ap.add_argument("--also-full", action="store_true", help="after the timed line-topology rounds, complete the mesh and time the same number of rounds again (reported under 'full_mesh')")
+    ap.add_argument("--no-coop", action="store_true", help="keep the reference's pairwise partial-model gossip even when the whole federation trains (default: one fused collective per round)")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
     if a.nodes_per_gpu > 0:
@@ -377,6 +378,7 @@ def run_ours(args) -> None:
                 "precision": "fp32 storage; convolutions on tcgen05 kind::tf32 (operands rounded to tf32); linear layers 3xTF32 (fp32-class); loss / optimizer fp32" if args.dtype == "tf32" and args.model == "cnn" else "bf16 operands, fp32 accumulation, fp32 master weights",
                 "nodes_per_gpu": n_nodes / world, "protocol": (os.environ.get("B2_BENCH_PROTOCOL", "uds") + "+cuda-ipc") if multi else "in-memory",
                 "parallelism": f"fed-dp{n_nodes}x{world}gpu", "l2": "flushed (256 MiB write) once per round per GPU",
+                "aggregation": ("cooperative: one K-way kernel per GPU" + (" + in-switch (NVLS multimem) sum over the GPUs" if multi and hub is not None and hub.comm is not None else "")) if hub is not None and hub.src is not None else "pairwise partial-model gossip + per-node K-way pull kernel",
             },
             "clocks": clocks, "gpu_launches": launches, "stage_ms_per_round_rank0": stage_ms,
         }
@@ -386,6 +388,8 @@ def run_ours(args) -> None:
             out["cohort_rank0"] = cohort
         if multi:
             out["stale_descriptors_refused"] = stale
+        if hub is not None:
+            out["coop_rank0"] = {"rounds_cooperative": hub.successes, "fallbacks": hub.fallbacks}
         if e2e is not None:
             out["e2e"] = e2e
         print(json.dumps(out), flush=True)

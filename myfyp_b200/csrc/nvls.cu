@@ -96,8 +96,9 @@ struct Comm {
   unsigned int epoch;
 };
 
-__device__ __forceinline__ void mm_red_add(unsigned int* mc_addr, unsigned int v) {
-  asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
+// one store that lands in every GPU's copy of the flag word
+__device__ __forceinline__ void mm_st_flag(unsigned int* mc_addr, unsigned int v) {
+  asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   unsigned int v;
@@ -118,38 +119,39 @@ __device__ __forceinline__ unsigned long long globaltimer() {
   return t;
 }
 
-// all CTAs: wait until the local copy of `flag` reaches `target`; false after ~2 s (some rank never arrived)
-__device__ __forceinline__ bool wait_flag(const unsigned int* flag, unsigned int target, int* s_ok) {
-  if (threadIdx.x == 0) {
+// all CTAs: wait until every rank's slot flags[0..world) has reached `epoch` (slots only grow; an epoch that some rank skipped
+// leaves nothing behind that a later epoch could trip over); false after ~2 s (some rank never arrived)
+__device__ __forceinline__ bool wait_all(const unsigned int* flags, int world, unsigned int epoch, int* s_ok) {
+  if (threadIdx.x == 0) *s_ok = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < world) {
     const unsigned long long t0 = globaltimer();
-    bool ok = true;
-    while ((int)(ld_acquire_sys(flag) - target) < 0) {
+    while ((int)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
       __nanosleep(100);
       if (globaltimer() - t0 > (1ull << TIMEOUT_NS_SHIFT)) {
-        ok = false;
+        *s_ok = 0;
         break;
       }
     }
-    *s_ok = ok ? 1 : 0;
   }
   __syncthreads();
   return *s_ok != 0;
 }
 
-// flags (unsigned, local copy at uc, multicast alias at mc): [0] arrivals before the reduce, [1] arrivals after, [8] CTA counter, [16] error
+// flags (unsigned; local copy at uc, multicast alias at mc): [0..31] "input of rank g is complete", [32..63] "shard of rank g is
+// everywhere", [64] CTA counter, [72] epoch of the last call that gave up waiting
 __global__ void __launch_bounds__(512) nvls_allreduce_kernel(unsigned char* uc, unsigned char* mc, int64_t off_in, int64_t off_out, int64_t n4, int world, int rank, unsigned int epoch,
                                                               float scale) {
   unsigned int* lflags = reinterpret_cast<unsigned int*>(uc);
   unsigned int* mflags = reinterpret_cast<unsigned int*>(mc);
   __shared__ int s_ok, s_last;
-  const unsigned int target = epoch * (unsigned)world;
   // ---- barrier A: every rank's input is complete (this kernel is stream-ordered behind its producer)
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     __threadfence_system();
-    mm_red_add(mflags + 0, 1u);
+    mm_st_flag(mflags + rank, epoch);
   }
-  if (!wait_flag(lflags + 0, target, &s_ok)) {
-    if (threadIdx.x == 0) lflags[16] = epoch;
+  if (!wait_all(lflags, world, epoch, &s_ok)) {
+    if (threadIdx.x == 0) lflags[72] = epoch;
     return;
   }
   // ---- reduce my shard in the switch, broadcast it to everybody
@@ -177,15 +179,15 @@ __global__ void __launch_bounds__(512) nvls_allreduce_kernel(unsigned char* uc, 
   // ---- barrier B: the last CTA of this rank announces "my shard is everywhere"
   __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(lflags + 8, 1u) == gridDim.x - 1);
+  if (threadIdx.x == 0) s_last = (atomicAdd(lflags + 64, 1u) == gridDim.x - 1);
   __syncthreads();
   if (s_last && threadIdx.x == 0) {
-    lflags[8] = 0u;
+    lflags[64] = 0u;
     __threadfence_system();
-    mm_red_add(mflags + 1, 1u);
+    mm_st_flag(mflags + 32 + rank, epoch);
   }
-  if (!wait_flag(lflags + 1, target, &s_ok)) {
-    if (threadIdx.x == 0) lflags[16] = epoch;
+  if (!wait_all(lflags + 32, world, epoch, &s_ok)) {
+    if (threadIdx.x == 0) lflags[72] = epoch;
   }
 }
 
@@ -313,6 +315,10 @@ int b2_nvls_allreduce(void* comm, int64_t off_in, int64_t off_out, int64_t n, un
     set_error("nvls: communicator is not bound");
     return 1;
   }
+  if (c->world > 32) {
+    set_error("nvls: at most 32 ranks");
+    return 1;
+  }
   if (n <= 0 || (n & 3) || (off_in & 15) || (off_out & 15) || off_in < FLAG_BYTES || off_out < FLAG_BYTES || (size_t)(off_in + 4 * n) > c->bytes || (size_t)(off_out + 4 * n) > c->bytes) {
     set_error("nvls: bad buffer geometry (n=%lld off_in=%lld off_out=%lld region=%zu)", (long long)n, (long long)off_in, (long long)off_out, c->bytes);
     return 1;
@@ -330,7 +336,7 @@ int b2_nvls_allreduce(void* comm, int64_t off_in, int64_t off_out, int64_t n, un
 /* After the stream has been synchronised: the epoch of the last call whose wait timed out on this rank (0 = none). */
 int b2_nvls_last_timeout(void* comm, unsigned int* epoch_out) {
   Comm* c = static_cast<Comm*>(comm);
-  B2_CUDA(cudaMemcpy(epoch_out, reinterpret_cast<unsigned int*>(c->uc_va) + 16, sizeof(unsigned int), cudaMemcpyDeviceToHost));
+  B2_CUDA(cudaMemcpy(epoch_out, reinterpret_cast<unsigned int*>(c->uc_va) + 72, sizeof(unsigned int), cudaMemcpyDeviceToHost));
   return 0;
 }
 

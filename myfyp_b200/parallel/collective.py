@@ -270,9 +270,10 @@ class NvlsFedAvg:
             c._bind()
         return comms
 
-    def __call__(self, scale: float = 1.0, max_ctas: int = 0) -> torch.Tensor:
-        """Launch on the current stream of this rank's device.  Every rank must call with the same sequence of calls."""
-        self.epoch += 1
+    def __call__(self, scale: float = 1.0, max_ctas: int = 0, epoch: Optional[int] = None) -> torch.Tensor:
+        """Launch on the current stream of this rank's device.  Every rank calls with the same, growing ``epoch`` (default: a
+        call counter); an epoch that some rank never joins times out on the others (:meth:`timed_out`) and harms no later one."""
+        self.epoch = self.epoch + 1 if epoch is None else int(epoch)
         with native.device_guard(self.device):
             native.check(
                 self.lib.b2_nvls_allreduce(self._h, self.off_in, self.off_out, self.n, self.epoch, ctypes.c_float(scale), max_ctas, native.stream_ptr(self.device)),

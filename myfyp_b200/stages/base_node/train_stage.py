@@ -66,6 +66,9 @@ class TrainStage(Stage):
             check_early_stop(state)
             lap("fit")
 
+            if TrainStage.__cooperative_round(state, communication_protocol, learner, aggregator, lap):
+                return StageFactory.get_stage("GossipModelStage")
+
             models_added = aggregator.add_model(learner.get_model().snapshot_model())
             communication_protocol.broadcast(communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), models_added, round=state.round))
             lap("publish")
@@ -82,6 +85,37 @@ class TrainStage(Stage):
             return StageFactory.get_stage("GossipModelStage")
         except EarlyStopException:
             return None
+
+    @staticmethod
+    def __cooperative_round(state, communication_protocol, learner, aggregator, lap) -> bool:
+        """Whole federation in the train set, everybody on the fabric: the resident nodes of this GPU aggregate once, together, and
+        the GPUs sum their partials in one fused collective (parallel/coop.py) instead of n (n-1) pairwise model offers
+        (reference: train_stage.py:120-176 + fedavg.py:61-69).  False = not applicable / did not complete: gossip as usual."""
+        from myfyp_b200.parallel.coop import CoopHub
+
+        hub = CoopHub.get()
+        if hub is None or not hub.eligible(state.addr, state.train_set, aggregator):
+            return False
+        if state.round == 0:
+            hub.experiment_started(state.addr)
+        model = learner.get_model()
+        res = hub.aggregate(state.addr, state.round, model.slab, model.get_num_samples())
+        if res is None:
+            logger.info(state.addr, "Cooperative aggregation did not complete: gossiping this round.")
+            return False
+        average, total = res
+        check_early_stop(state)
+        everybody = list(state.train_set)
+        state.models_aggregated[state.addr] = everybody
+        communication_protocol.broadcast(communication_protocol.build_msg(ModelsAggregatedCommand.get_name(), everybody, round=state.round))
+        lap("publish")
+        lap("gossip")
+        agg_model = model.build_copy(params=average, num_samples=total, contributors=everybody)
+        lap("aggregate")
+        learner.set_model(agg_model)
+        communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
+        lap("adopt")
+        return True
 
     @staticmethod
     def __gossip_model_aggregation(state, communication_protocol, aggregator) -> None:

@@ -373,3 +373,40 @@ def test_ring_where_everybody_trains_finishes_without_waiting_for_lost_announcem
     finally:
         _stop(nodes)
         set_test_settings()
+
+
+def test_cooperative_round_equals_gossip_round():
+    import torch
+
+    """Whole federation in the train set: the resident nodes aggregate once through the CoopHub instead of offering each other
+    partial models - same averaged model as the gossip path, and no `partial_model` message at all."""
+    from myfyp_b200.parallel.coop import CoopHub
+
+    def run(coop: bool):
+        logger.reset_metrics()
+        Settings.TRAIN_SET_SIZE = 4
+        nodes = _nodes(4)
+        try:
+            if coop:
+                CoopHub.configure(0, 1, "cpu", nodes[0].learner.get_model().layout.total, [n.addr for n in nodes], [n.addr for n in nodes])
+            TopologyFactory.connect_nodes(TopologyFactory.generate_matrix(TopologyType.FULL, 4), nodes)
+            wait_convergence(nodes, 3, only_direct=True, wait=10)
+            for n in nodes:
+                n.learner.shuffle = False  # identical batches in both runs
+            nodes[0].set_start_learning(rounds=2, epochs=1)
+            wait_to_finish(nodes, timeout=120)
+            check_equal_models(nodes)
+            msgs = {k: v for k, v in logger.get_bytes().items() if k.startswith("msgs/")}
+            hub = CoopHub.get()
+            return nodes[0].learner.get_model().slab.clone(), msgs, (hub.successes, hub.fallbacks) if hub else None
+        finally:
+            _stop(nodes)
+            CoopHub.reset()
+
+    torch.manual_seed(0)
+    want, msgs_gossip, _ = run(False)
+    torch.manual_seed(0)
+    got, msgs_coop, stats = run(True)
+    assert stats == (2, 0), stats
+    assert msgs_gossip.get("msgs/partial_model", 0) > 0 and msgs_coop.get("msgs/partial_model", 0) == 0, (msgs_gossip, msgs_coop)
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
