@@ -40,6 +40,12 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--out", default="mnist_metrics.json")
     ap.add_argument("--log-level", default="INFO")
     ap.add_argument("--profiling", action="store_true", help="cProfile the run and print the top functions (the reference uses yappi)")
+    # flags of the reference's example (p2pfl/examples/mnist.py:80-87)
+    ap.add_argument("--token", default="", help="API token of the P2PFL web services: stream logs and metrics there (needs --web-url)")
+    ap.add_argument("--web-url", default="", help="base URL of the P2PFL web services")
+    ap.add_argument("--reduced_dataset", action="store_true", help="tiny partitions (50 samples per node), just for testing")
+    ap.add_argument("--use_scaffold", action="store_true", help="same as --aggregator scaffold")
+    ap.add_argument("--disable_ray", action="store_true", help="reference flag: run the learners on per-node graphs instead of the per-GPU cohort trainer (the role Ray's actor pool plays there)")
     ap.add_argument("--plot", default=None, help="write the global metrics as a PNG (matplotlib Agg backend; never opens a window)")
     return ap.parse_args()
 
@@ -85,6 +91,14 @@ def main() -> None:
     from myfyp_b200.utils.utils import set_standalone_settings, wait_convergence, wait_to_finish
 
     set_standalone_settings()
+    if a.use_scaffold:
+        a.aggregator = "scaffold"
+    if a.reduced_dataset:
+        a.samples_per_node = 50
+    if a.disable_ray:
+        Settings.DISABLE_RAY = True  # the cohort trainer is this framework's actor pool (learning/simulation.py)
+    if a.token and a.web_url:
+        logger.connect_web(a.web_url, a.token)
     Settings.TRAIN_SET_SIZE = a.train_set_size
     Settings.USE_SSL = False
     logger.set_level(a.log_level)

@@ -291,8 +291,10 @@ class TorchLearner(Learner):
 
     # ------------------------------------------------------------------ node-batched TF32 path (models/grouped_cnn.py)
     def _cohort(self, module):
+        from myfyp_b200.settings import Settings
+
         spec = getattr(module, "grouped_spec", None)
-        if spec is None:
+        if spec is None or getattr(Settings, "DISABLE_RAY", False):  # the reference's switch for its actor pool turns ours off too
             return None
         from myfyp_b200.models.grouped_cnn import CohortTrainer
 

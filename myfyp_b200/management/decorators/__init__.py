@@ -46,6 +46,51 @@ class WebP2PFLogger(LoggerDecorator):
         self._p2pflogger.connect_web(url, key)
 
 
+def _merge_logs(dst: dict, src: dict) -> dict:
+    """Union of two metric-store dumps (nested dicts whose leaves are lists of (step | round, value) pairs)."""
+    for k, v in src.items():
+        if isinstance(v, dict):
+            _merge_logs(dst.setdefault(k, {}), v)
+        else:
+            have = dst.setdefault(k, [])
+            have.extend(x for x in v if x not in have)
+    return dst
+
+
 class RayP2PFLogger(LoggerDecorator):
-    """The reference wraps its logger in a Ray actor so that simulated nodes in other processes share it.  Nodes of a process
-    share the logger object here (``FitPool`` runs learners in-process), so this is a plain pass-through kept for the name."""
+    """One logger view across processes.  The reference makes its logger a detached Ray actor so that learners running in other
+    processes log into the same stores (decorators/ray_logger.py:32-250).  Here the processes are the ``torchrun`` ranks (one per
+    GPU), each with its own in-process logger; this wrapper gives any rank the federation-wide view by merging the ranks' stores
+    over ``torch.distributed`` (an object all-gather on the host - observability plumbing, not a hot path):
+
+    ``get_local_logs()`` / ``get_global_logs()`` return the union over all ranks when a process group exists (every rank must
+    call, like any collective), and the plain local stores otherwise; ``all_ranks=False`` never communicates."""
+
+    def _gather(self, mine: dict) -> dict:
+        try:
+            import torch.distributed as dist
+        except ImportError:  # pragma: no cover
+            return mine
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return mine
+        parts = [None] * dist.get_world_size()
+        dist.all_gather_object(parts, mine)
+        out: dict = {}
+        for p in parts:
+            _merge_logs(out, p or {})
+        return out
+
+    def get_local_logs(self, all_ranks: bool = True):
+        mine = self._p2pflogger.get_local_logs()
+        return self._gather(mine) if all_ranks else mine
+
+    def get_global_logs(self, all_ranks: bool = True):
+        mine = self._p2pflogger.get_global_logs()
+        return self._gather(mine) if all_ranks else mine
+
+    def get_nodes(self, all_ranks: bool = True):
+        mine = {k: {"rank": None} for k in getattr(self._p2pflogger, "_nodes", {})}
+        return self._gather(mine) if all_ranks else mine
+
+
+DistributedP2PFLogger = RayP2PFLogger  # what it is, next to the reference's name

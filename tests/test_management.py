@@ -124,3 +124,48 @@ def test_web_services_client_against_a_local_stub():
         assert "n" not in web.node_id
     finally:
         srv.shutdown()
+
+
+def _rank_logs(rank, port, q):
+    import os
+
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE="2")
+    dist.init_process_group("gloo", rank=rank, world_size=2)
+    from myfyp_b200.management.decorators import RayP2PFLogger
+    from myfyp_b200.management.logger import logger
+
+    addr = f"node-of-rank-{rank}"
+    logger.register_node(addr)
+    logger.experiment_started(addr, __import__("myfyp_b200.experiment", fromlist=["Experiment"]).Experiment("experiment", 3))
+    logger.log_metric(addr, "test_metric", 0.5 + rank)             # global store
+    logger.log_metric(addr, "train_loss", 1.0 - 0.1 * rank, step=7)  # local store
+    view = RayP2PFLogger(logger)
+    g, l = view.get_global_logs(), view.get_local_logs()
+    q.put((rank, sorted(g["experiment"].keys()), sorted(l["experiment"][0].keys()), sorted(view.get_global_logs(all_ranks=False)["experiment"].keys())))
+    dist.destroy_process_group()
+
+
+def test_cross_rank_logger_view_merges_the_ranks_metric_stores():
+    """The role of the reference's Ray logger actor (ray_logger.py:32-250): every process sees the metrics of all nodes."""
+    import multiprocessing as mp
+    import socket
+
+    from myfyp_b200.management.decorators import _merge_logs
+
+    assert _merge_logs({"e": {"a": {"m": [(0, 1.0)]}}}, {"e": {"a": {"m": [(0, 1.0), (1, 2.0)]}, "b": {"m": [(0, 3.0)]}}}) == {"e": {"a": {"m": [(0, 1.0), (1, 2.0)]}, "b": {"m": [(0, 3.0)]}}}
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_rank_logs, args=(r, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    got = sorted(q.get(timeout=120) for _ in range(2))
+    [p.join(30) for p in ps]
+    both = ["node-of-rank-0", "node-of-rank-1"]
+    for rank, glob, loc, mine in got:
+        assert glob == both and loc == both, got   # every rank sees both nodes
+        assert mine == [f"node-of-rank-{rank}"]    # the un-gathered view is the local one
