@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"], help="tf32 = the reference's precision (fp32 storage, TF32 convolutions, fp32-class linear layers)")
     ap.add_argument("--topology", default="line", choices=["line", "full"], help="line = what the reference arm can run (its own test topology); full = BASELINE config 2 as worded")
     ap.add_argument("--also-full", action="store_true", help="after the timed line-topology rounds, complete the mesh and time the same number of rounds again (reported under 'full_mesh')")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4], help="BASELINE.json config: 2 = CNN / FedAvg / 8 nodes (the headline), 3 = ResNet-18 / 32 nodes / random topology / FedMedian + Krum under attack, 4 = ResNet-18 / Scaffold + FedProx / 64 nodes with drop + rejoin")
     ap.add_argument("--no-coop", action="store_true", help="keep the reference's pairwise partial-model gossip even when the whole federation trains (default: one fused collective per round)")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -397,8 +398,57 @@ def run_ours(args) -> None:
         dist.destroy_process_group()
 
 
+def run_scenarios(args) -> None:
+    """Configs 3 and 4: one process drives every GPU of the job (in-memory control plane, peer access between the GPUs), the
+    other ranks of a torchrun launch only keep the barrier.  A step = one federated round; `steps` rounds are timed after the
+    first one (which holds the graph captures), `value` = the slowest scenario of the config."""
+    import torch
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("gloo")
+    try:
+        if rank == 0:
+            from benchmarks.configs import run
+            from myfyp_b200.learning.aggregators import FedMedian, FedProx, Krum, Scaffold
+
+            rounds = args.steps + 1
+            n = args.nodes if args.nodes != TOTAL_NODES else (32 if args.config == 3 else 64)
+            sampler = ClockSampler()
+            sampler.start()
+            res = []
+            if args.config == 3:
+                ts, byz = min(8, n), max(1, n // 8)
+                for nm, agg in (("c3-fedmedian", FedMedian), ("c3-krum", lambda: Krum(f=2, m=ts - 4))):
+                    res.append(run(nm, n, "resnet18", agg, "random", rounds, 256, ts, "cuda", byzantine=byz, max_gpus=args.gpus))
+            else:
+                faults = {"drop": [(n - 1, 1), (n - 2, 1)], "rejoin": [(n - 1, 3)]}
+                for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0), {"optimizer": "sgd", "lr": 0.05}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
+                    res.append(run(nm, n, "resnet18", agg, "random", max(rounds, 6), 256, min(8, n), "cuda", faults=faults, max_gpus=args.gpus, learner_kw=kw))
+            clocks = sampler.stop(args.gpus)
+            value = min(r["rounds_per_s"] for r in res)
+            print(json.dumps({
+                "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": 1, "ms_per_step": 1e3 / value, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "bf16 operands, fp32 accumulate (ResNet-18 native step)", "data": "synthetic", "impl": "ours",
+                "config": {"baseline_config": args.config, "model": MODEL_NAMES["resnet18"], "nodes": n, "topology": "random", "train_set_size": min(8, n), "protocol": "in-memory, one process, all GPUs",
+                           "timing": "wall clock from the end of round 1 to the end of the last round (many streams on many GPUs)"},
+                "clocks": clocks, "gpu_launches": sum(r["kernel_launches"] for r in res), "scenarios": res,
+            }), flush=True)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+            dist.destroy_process_group()
+
+
 def main() -> None:
     args = parse()
+    if args.config != 2 and args.impl == "ours":
+        run_scenarios(args)
+        return
     if args.impl == "reference":
         from benchmarks.reference_arm import run_reference
 
