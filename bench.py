@@ -211,6 +211,13 @@ def run_ours(args) -> None:
         n.start()
     if multi:
         dist.barrier()
+    hub = None
+    if not args.no_coop:
+        from myfyp_b200.parallel.coop import CoopHub
+
+        total_elems = next(iter(models.values())).layout.total if models else 64
+        hub = CoopHub.configure(rank, world, dev, total_elems, [addrs[i] for i in mine], addrs)
+
     def wire(topology: str) -> None:
         """line: i - i+1 (the reference's own test topology, test/node_test.py:92-96); full: i -> j for i < j.  The handshake makes
         every link symmetric; the heartbeat flood then tells everybody about everybody (non-direct neighbours)."""

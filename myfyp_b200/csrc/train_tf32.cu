@@ -31,6 +31,7 @@
 // TMA loads here read this GPU's memory only and none uses cluster multicast.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -442,6 +443,148 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ conv weight gradient, wide tiles
+// dW[co, (tap, ci)] = sum_pixels dz[pixel, co] * x[pixel + tap, ci], one CTA per (cout tile, group of 9 column blocks, K split).
+// The generic kernel above computes 64 output columns per pass over the pixels and therefore re-reads dz once per 64 columns
+// (4.5x for a 32-channel layer, 9x for a 64-channel one); its pipeline is bound by the bytes that cross from L2 into shared
+// memory.  Here a stage holds the dz tile ONCE plus nine activation boxes (= all nine taps of a 32-channel block: the boxes are
+// the same pixels shifted by one, L2 serves them), the accumulator is 288 TMEM columns wide, and three N = 96 MMAs per k-step
+// consume the stage.  Same operand layouts as CONV = 2 (both MN-major, 32-byte-atom swizzle).
+constexpr int WW_NB = 9;                          // 32-column blocks per CTA
+constexpr int WW_B_BYTES = WW_NB * BK * 128;      // 36 KB
+constexpr int WW_STAGE = A_BYTES + WW_B_BYTES;    // 52 KB
+constexpr int WW_STAGES = 4;
+constexpr int WW_SMEM = WW_STAGES * WW_STAGE + 1024;
+
+__global__ void __launch_bounds__(GG_THREADS, 1) wgrad_wide_kernel(const Problem* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
+  const Problem& P = probs[blockIdx.y];
+  const b2_cnn_bind& bd = binds[blockIdx.y];
+  if (!slot_live(bd, step, P.batch)) return;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[WW_STAGES], empty_bar[WW_STAGES], acc_full, acc_empty;
+  __shared__ uint32_t tmem_base_s;
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int M = P.M, N = P.N;
+  const int total_k = (P.K + BK - 1) / BK;
+  const int groups = (N + 32 * WW_NB - 1) / (32 * WW_NB);
+  const int splits = P.splits, kb_per_split = P.kb_per_split;
+  const int n_work = P.tiles_m * groups * splits;
+
+  if (tid == 0) {
+    tc::tma_prefetch_desc(&P.ta);
+    tc::tma_prefetch_desc(&P.tb);
+    for (int s = 0; s < WW_STAGES; ++s) {
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], 1);
+    }
+    tc::mbar_init(&acc_full, 1);
+    tc::mbar_init(&acc_empty, 4);
+    tc::mbar_fence_init();
+  }
+  if (warp == 1) tc::tmem_alloc<512>(&tmem_base_s);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = tmem_base_s;
+
+  auto work_coords = [&](int w, int& m0, int& n0, int& kb0, int& nk) {
+    const int z = w % splits;
+    const int t = w / splits;
+    m0 = (t / groups) * BM;
+    n0 = (t % groups) * (32 * WW_NB);
+    kb0 = z * kb_per_split;
+    nk = total_k - kb0;
+    nk = nk < 0 ? 0 : (nk < kb_per_split ? nk : kb_per_split);
+  };
+
+  if (warp == 0) {
+    if (tc::elect_one()) {
+      uint32_t it = 0;
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+        int m0, n0, kb0, nk;
+        work_coords(w, m0, n0, kb0, nk);
+        int nblk = 0;
+        for (int j = 0; j < WW_NB; ++j) nblk += (n0 + 32 * j < N) ? 1 : 0;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % WW_STAGES;
+          tc::mbar_wait(&empty_bar[s], ((it / WW_STAGES) & 1u) ^ 1u);
+          uint8_t* a_dst = tiles + s * WW_STAGE;
+          uint8_t* b_dst = a_dst + A_BYTES;
+          const int k0 = (kb0 + kb) * BK;
+          tc::mbar_arrive_expect_tx(&full_bar[s], A_BYTES + nblk * (BK * 128));
+#pragma unroll
+          for (int j = 0; j < 4; ++j) tc::tma_load_2d(a_dst + j * (BK * 128), &P.ta, &full_bar[s], m0 + 32 * j, k0);
+          int n_img, h0;
+          pixel_tile(P, kb0 + kb, n_img, h0);
+          for (int j = 0; j < nblk; ++j) {
+            const int col = n0 + 32 * j;
+            const int t = col / P.ncols, c0 = col % P.ncols;
+            tc::tma_load_4d(b_dst + j * (BK * 128), &P.tb, &full_bar[s], c0, P.off + P.sign * (t % P.kw), h0 + P.off + P.sign * (t / P.kw), n_img);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (tc::elect_one()) {
+      constexpr uint32_t idesc = tc::make_idesc(tc::FMT_TF32, BM, 96) | (1u << 15) | (1u << 16);
+      uint32_t it = 0, acc_it = 0;
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++acc_it) {
+        int m0, n0, kb0, nk;
+        work_coords(w, m0, n0, kb0, nk);
+        tc::mbar_wait(&acc_empty, (acc_it & 1u) ^ 1u);
+        tc::fence_after_sync();
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % WW_STAGES;
+          tc::mbar_wait(&full_bar[s], (it / WW_STAGES) & 1u);
+          tc::fence_after_sync();
+          const uint32_t a_addr = tc::smem_u32(tiles + s * WW_STAGE);
+          const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+          for (int ks = 0; ks < BK / 8; ++ks) {
+            const uint64_t da = desc_mn(a_addr + ks * 1024, BK * 128);
+#pragma unroll
+            for (int g3 = 0; g3 < 3; ++g3) tc::mma_tf32(tmem_base + g3 * 96, da, desc_mn(b_addr + g3 * 3 * (BK * 128) + ks * 1024, BK * 128), idesc, (kb | ks) != 0 ? 1u : 0u);
+          }
+          tc::mma_commit(&empty_bar[s]);
+        }
+        tc::mma_commit(&acc_full);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    uint32_t acc_it = 0;
+    for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++acc_it) {
+      int m0, n0, kb0, nk;
+      work_coords(w, m0, n0, kb0, nk);
+      const int row = m0 + q * 32 + lane;
+      tc::mbar_wait(&acc_full, acc_it & 1u);
+      tc::fence_after_sync();
+      if (nk > 0) {
+#pragma unroll 1
+        for (int cb = 0; cb < WW_NB; ++cb) {
+          const int nb = n0 + cb * 32;
+          if (nb >= N) break;
+          float v[32];
+          tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cb * 32), v);
+          if (row < M) {
+            float* o = P.out + (int64_t)row * P.ldo + nb;
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+          }
+        }
+      }
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<512>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ first conv layer (1-3 input channels)
@@ -1366,7 +1509,33 @@ static int launch_adam(const Plan& p, int step, int refresh_only, cudaStream_t s
 }
 
 static int run_conv_fwd(const Plan& p, int l, int step, cudaStream_t st) { return launch_gg<1, false, false, false, EPI_POOL, 64>(p, p.p_conv_fwd(l), step, st); }
-static int run_conv_wgrad(const Plan& p, int l, int step, cudaStream_t st) { return launch_gg<2, true, true, false, EPI_ATOMIC, 64>(p, p.p_conv_wgrad(l), step, st); }
+static int run_conv_wgrad(const Plan& p, int l, int step, cudaStream_t st) {
+  // Default: the generic kernel's 64-column tiles.  The wide kernel (B2_T32_WIDE_WGRAD=1) moves half the bytes but measured
+  // SLOWER on B200 (conv1 145 us vs 90 us, conv2 145 us vs 54 us for 8 nodes): thirteen small TMA boxes per stage and a single
+  // resident CTA per SM; kept for the comparison (profiles/t32_step.md).
+  static const bool wide = getenv("B2_T32_WIDE_WGRAD") != nullptr;
+  if (!wide) return launch_gg<2, true, true, false, EPI_ATOMIC, 64>(p, p.p_conv_wgrad(l), step, st);
+  static bool attr_set[64] = {false};
+  static std::mutex mu;
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      B2_CUDA(cudaFuncSetAttribute(wgrad_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WW_SMEM));
+      attr_set[dev] = true;
+    }
+  }
+  const Problem& hp = p.h_prob[(size_t)p.p_conv_wgrad(l) * p.G];
+  const int groups = (hp.N + 32 * WW_NB - 1) / (32 * WW_NB);
+  const int n_work = hp.tiles_m * groups * hp.splits;
+  int per_slot = (p.sms + p.G - 1) / p.G;
+  if (per_slot < 4) per_slot = 4;
+  const int gx = n_work < per_slot ? n_work : per_slot;
+  wgrad_wide_kernel<<<dim3(gx, p.G), GG_THREADS, WW_SMEM, st>>>(p.d_prob + (size_t)p.p_conv_wgrad(l) * p.G, p.d_bind, step);
+  B2_LAUNCH_CHECK("wgrad_wide_kernel");
+  return 0;
+}
 static int run_conv_dgrad(const Plan& p, int l, int step, cudaStream_t st) {
   if (l == 1) {
     if (p.Cout[0] == 32) return launch_gg<1, false, true, false, EPI_MASK, 32>(p, p.p_conv_dgrad(l), step, st);
@@ -1457,6 +1626,13 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
         P.tiles_m = (cout + BM - 1) / BM; P.tiles_n = (kdim + 63) / 64;
         const int total_k = pixels / BK;
         int splits = total_k / 32;
+        if (getenv("B2_T32_WIDE_WGRAD") != nullptr) {  // one CTA per (cout tile, 288-column group, K split)
+          const int wgroups = (kdim + 32 * WW_NB - 1) / (32 * WW_NB) * ((cout + BM - 1) / BM);
+          int want = (p->sms + G - 1) / G;
+          if (want < 8) want = 8;
+          splits = (want + wgroups - 1) / wgroups;
+          if (splits > total_k / 4) splits = total_k / 4;
+        }
         if (splits < 1) splits = 1;
         if (splits > 16) splits = 16;
         P.kb_per_split = (total_k + splits - 1) / splits;
