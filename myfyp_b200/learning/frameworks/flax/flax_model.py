@@ -36,6 +36,23 @@ class FlaxModel(P2PFLModel):
             raise ModelNotMatchingError("Not matching models")
         self.model_params = jax.tree_util.tree_unflatten(treedef, [jax.numpy.asarray(p, dtype=l.dtype) for p, l in zip(params, leaves)])
 
+    # wire format = the reference's: the pickled parameter dict (flax/flax_model.py:102-127), not the list form of the other bindings
+    def encode_parameters(self, params=None) -> bytes:
+        from myfyp_b200.learning.frameworks.flax import wire
+        from myfyp_b200.learning.p2pfl_model import _info_to_numpy
+
+        tree = self.model_params if params is None else wire.fill_tree(self.model_params, list(params))
+        return wire.encode(tree, _info_to_numpy(self.additional_info))
+
+    def decode_parameters(self, data: bytes):
+        from myfyp_b200.learning.exceptions import DecodingParamsError
+        from myfyp_b200.learning.frameworks.flax import wire
+
+        try:
+            return wire.decode(data)
+        except Exception as e:  # noqa: BLE001
+            raise DecodingParamsError("Error decoding parameters") from e
+
     def build_copy(self, **kwargs) -> "FlaxModel":
         return FlaxModel(self.model, init_params=copy.deepcopy(self.model_params), **kwargs)
 
