@@ -166,6 +166,8 @@ def run_ours(args) -> None:
     n_nodes = args.nodes
     set_fast_settings(train_set_size=n_nodes)
     Settings.USE_SSL = False
+    Settings.TTL = max(Settings.TTL, n_nodes + 2)  # a flood must cross the whole line (reference: examples/mnist.py:153-156)
+    Settings.AMOUNT_LAST_MESSAGES_SAVED = max(Settings.AMOUNT_LAST_MESSAGES_SAVED, 200 * n_nodes)
     if os.environ.get("B2_BENCH_DEBUG"):
         from myfyp_b200.management.logger import logger
 

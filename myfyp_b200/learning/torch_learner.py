@@ -263,8 +263,7 @@ class TorchLearner(Learner):
             self._stream.synchronize()
         if steps:
             self.d2h_bytes += 4 * steps
-            for i, v in enumerate(vals):
-                logger.log_metric(self._self_addr, "train_loss", v, step=self._global_step + i)
+            logger.log_metric_series(self._self_addr, "train_loss", vals, self._global_step)
             self._global_step += steps
         if getattr(module, "native", None) is not None:
             model.sync_mirrors_from_slab()  # e.g. BatchNorm's integer batch counter, advanced on the device in its fp32 slab slot

@@ -32,6 +32,12 @@ class LocalMetricStorage:
             series = self._logs.setdefault(exp_name, {}).setdefault(round, {}).setdefault(node, {}).setdefault(metric, [])
             series.append((step, val))
 
+    def add_series(self, exp_name: str, round: int, metric: str, node: str, values, first_step: int) -> None:
+        """``values[i]`` at step ``first_step + i`` - one lock round trip for a whole epoch of per-step values."""
+        with self._lock:
+            series = self._logs.setdefault(exp_name, {}).setdefault(round, {}).setdefault(node, {}).setdefault(metric, [])
+            series.extend((first_step + i, v) for i, v in enumerate(values))
+
     def get_all_logs(self) -> LocalLogsType:
         with self._lock:
             return copy.deepcopy(self._logs)
