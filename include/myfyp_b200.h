@@ -85,7 +85,7 @@ int b2_fedavg_twoshot(const b2_twoshot_args* dev_args, int ranks_in_launch, int6
  * multimem.ld_reduce (the switch adds the ranks' values) and multimem.st broadcasts it; barriers are multimem.red on a multicast
  * flag.  Set-up: the root creates the multicast object (b2_nvls_root_create -> POSIX fd, handed to the other ranks), every rank
  * joins (imports + adds its device), and - after ALL ranks have joined - binds its buffer.  Region layout: [flags | in | out],
- * offsets in bytes.  Inputs must be pre-weighted; `scale` multiplies the sum.  Waits are bounded (~2 s); b2_nvls_last_timeout
+ * offsets in bytes.  Inputs must be pre-weighted; `scale` multiplies the sum.  Waits are bounded (~8.6 s); b2_nvls_last_timeout
  * reports a call that gave up.  Availability: b2_multicast_probe.  No reference counterpart (fedavg.py:61-69 runs on the host). */
 int64_t b2_nvls_granularity(int world);
 int b2_nvls_root_create(int world, int64_t bytes, int* out_fd);

@@ -29,6 +29,19 @@ from myfyp_b200.management.trace import trace
 from myfyp_b200.settings import Settings
 
 
+_POOL: Optional[ThreadPoolExecutor] = None
+_POOL_LOCK = threading.Lock()
+
+
+def _send_pool() -> ThreadPoolExecutor:
+    global _POOL
+    if _POOL is None:
+        with _POOL_LOCK:
+            if _POOL is None:
+                _POOL = ThreadPoolExecutor(max_workers=max(4, 4 * Settings.GOSSIP_SEND_WORKERS), thread_name_prefix="gossip-send")
+    return _POOL
+
+
 class Gossiper(threading.Thread):
     def __init__(self, self_addr: str, client: Client, period: Optional[float] = None, messages_per_period: Optional[int] = None) -> None:
         super().__init__(daemon=True, name=f"gossiper-thread-{self_addr}")
@@ -53,7 +66,7 @@ class Gossiper(threading.Thread):
         self.__terminate.set()
         with self.__cv:
             self.__cv.notify_all()
-        if self.__pool is not None:
+        if self.__pool is not None:  # (kept for subclasses that install a private pool)
             self.__pool.shutdown(wait=False)
 
     # ------------------------------------------------------------------ flood
@@ -192,12 +205,13 @@ class Gossiper(threading.Thread):
                 self.__client.send(nei, msg, create_connection=create_connection)
                 trace(self.__self_addr, f"sent_model>{nei}")
 
-            if len(outbox) > 1 and Settings.GOSSIP_SEND_WORKERS > 1:
+            if len(outbox) > 1 and Settings.GOSSIP_SEND_WORKERS > 1 and not getattr(self.__client, "in_process", False):
                 # each send is a blocking request -> response (the peer pulls and files the model before it answers):
-                # to several peers they overlap instead of adding up (the reference sends one after the other)
-                if self.__pool is None:
-                    self.__pool = ThreadPoolExecutor(max_workers=Settings.GOSSIP_SEND_WORKERS, thread_name_prefix=f"gossip-send-{self.__self_addr}")
-                list(self.__pool.map(deliver, outbox))
+                # to several peers they overlap instead of adding up (the reference sends one after the other).
+                # ONE pool per process: a pool per node meant hundreds of mostly idle threads at 64 nodes, and every submit of
+                # every pool serialises on the executor module's global lock.  In-process transports run the handler on the
+                # caller's thread anyway (nothing blocks on I/O): they deliver inline.
+                list(_send_pool().map(deliver, outbox))
             else:
                 for item in outbox:
                     deliver(item)

@@ -18,6 +18,8 @@ from myfyp_b200.settings import Settings
 
 
 class InMemoryClient(Client):
+    in_process = True  # a send IS the receiver's handler, run on this thread: nothing to overlap with worker threads
+
     def __init__(self, self_addr: str, neighbors) -> None:
         self.__self_addr = self_addr
         self.__neighbors = neighbors

@@ -85,7 +85,7 @@ static int cu_fail(CUresult r, const char* what) {
   } while (0)
 
 constexpr int FLAG_BYTES = 4096;
-constexpr unsigned int TIMEOUT_NS_SHIFT = 31;  // ~2.1 s
+constexpr unsigned int TIMEOUT_NS_SHIFT = 33;  // ~8.6 s: a first call may find its peers still capturing graphs
 
 struct Comm {
   int world, rank, dev;
@@ -120,7 +120,7 @@ __device__ __forceinline__ unsigned long long globaltimer() {
 }
 
 // all CTAs: wait until every rank's slot flags[0..world) has reached `epoch` (slots only grow; an epoch that some rank skipped
-// leaves nothing behind that a later epoch could trip over); false after ~2 s (some rank never arrived)
+// leaves nothing behind that a later epoch could trip over); false after ~8.6 s (some rank never arrived)
 __device__ __forceinline__ bool wait_all(const unsigned int* flags, int world, unsigned int epoch, int* s_ok) {
   if (threadIdx.x == 0) *s_ok = 1;
   __syncthreads();

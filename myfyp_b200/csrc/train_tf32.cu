@@ -963,13 +963,42 @@ __global__ void __launch_bounds__(HD_THREADS) head_kernel(const HeadProb* __rest
   const float* W2 = bd.slab + P.off_fc2_w;
   const float* b2 = bd.slab + P.off_fc2_b;
   if (tid < 2) s_red[tid] = 0.f;
-  for (int i = tid; i < HD_ROWS * Hd; i += HD_THREADS) {
-    const int s = i / Hd, j = i - s * Hd;
-    float* zp = P.z1 + (int64_t)(s0 + s) * Hd + j;
-    h1[i] = fmaxf(*zp + __ldg(b1 + j), 0.f);
-    *zp = 0.f;
+  // all global loads of a trip are issued before the first use: a load -> store -> load chain (z1 is cleared in place) would
+  // cost one memory latency per element
+  {
+    float* zrow = P.z1 + (int64_t)s0 * Hd;  // the 16 rows of this CTA are contiguous
+    for (int i0 = 0; i0 < HD_ROWS * Hd; i0 += 8 * HD_THREADS) {
+      float zv[8], bv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * HD_THREADS + tid;
+        const bool ok = i < HD_ROWS * Hd;
+        zv[u] = ok ? zrow[i] : 0.f;
+        bv[u] = ok ? __ldg(b1 + i % Hd) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * HD_THREADS + tid;
+        if (i < HD_ROWS * Hd) {
+          h1[i] = fmaxf(zv[u] + bv[u], 0.f);
+          zrow[i] = 0.f;
+        }
+      }
+    }
+    for (int i0 = 0; i0 < Cn * Hd; i0 += 8 * HD_THREADS) {
+      float wv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * HD_THREADS + tid;
+        wv[u] = i < Cn * Hd ? __ldg(W2 + i) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * HD_THREADS + tid;
+        if (i < Cn * Hd) w2[(i / Hd) * (Hd + 1) + (i % Hd)] = wv[u];
+      }
+    }
   }
-  for (int i = tid; i < Cn * Hd; i += HD_THREADS) w2[(i / Hd) * (Hd + 1) + (i % Hd)] = __ldg(W2 + i);
   __syncthreads();
   // logits: thread -> (sample, class); 16-lane groups share a sample
   const int s = tid >> 4, c = tid & 15;
@@ -1453,6 +1482,7 @@ static int launch_conv0(const Plan& p, bool wgrad, int step, cudaStream_t st) {
   const int tiles = p.d.batch * p.H[0] / 4;
   int per_slot = (p.sms * 2 + p.G - 1) / p.G;
   if (per_slot < 8) per_slot = 8;
+  if (wgrad && per_slot > 96) per_slot = 96;  // every CTA ends in 27 x cout atomics on the same few hundred addresses
   const int gx = tiles < per_slot ? tiles : per_slot;
   if (wgrad) {
     const int cb = p.Cout[0] / 32;
@@ -1625,16 +1655,18 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
         P.M = cout; P.N = kdim; P.K = pixels; P.batch = B;
         P.tiles_m = (cout + BM - 1) / BM; P.tiles_n = (kdim + 63) / 64;
         const int total_k = pixels / BK;
-        int splits = total_k / 32;
+        // K splits: as many as fill this slot's share of the chip in ONE wave (3 resident CTAs per SM), at least 4 k-blocks each
+        const int out_tiles = ((cout + BM - 1) / BM) * ((kdim + 63) / 64);
+        int splits = (p->sms * 3 / G) / out_tiles;
         if (getenv("B2_T32_WIDE_WGRAD") != nullptr) {  // one CTA per (cout tile, 288-column group, K split)
           const int wgroups = (kdim + 32 * WW_NB - 1) / (32 * WW_NB) * ((cout + BM - 1) / BM);
           int want = (p->sms + G - 1) / G;
           if (want < 8) want = 8;
           splits = (want + wgroups - 1) / wgroups;
-          if (splits > total_k / 4) splits = total_k / 4;
         }
+        if (splits > total_k / 4) splits = total_k / 4;
         if (splits < 1) splits = 1;
-        if (splits > 16) splits = 16;
+        if (splits > 64) splits = 64;
         P.kb_per_split = (total_k + splits - 1) / splits;
         P.splits = (total_k + P.kb_per_split - 1) / P.kb_per_split;
         P.cblocks = cin / 32; P.kw = 3; P.off = -1; P.sign = 1; P.ncols = cin;

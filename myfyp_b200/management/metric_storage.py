@@ -69,8 +69,9 @@ class GlobalMetricStorage:
     def add_log(self, exp_name: str, round: int, metric: str, node: str, val: Union[int, float]) -> None:
         with self._lock:
             series = self._logs.setdefault(exp_name, {}).setdefault(node, {}).setdefault(metric, [])
-            # a round holds one value: keep the first one logged for it
-            if round not in [r for r, _ in series]:
+            # a round holds one value: keep the first one logged for it (rounds arrive in order: looking at the tail is enough
+            # in all but pathological cases, which still fall back to the full scan)
+            if not series or (series[-1][0] != round and (series[-1][0] < round or round not in [r for r, _ in series])):
                 series.append((round, val))
 
     def get_all_logs(self) -> GlobalLogsType:

@@ -207,6 +207,8 @@ class NvlsFedAvg:
 
                 dist.barrier()  # every device is in the team before anyone binds
             self._bind()
+            if _fd is None:
+                dist.barrier()  # ... and everybody has bound before anyone touches the multicast address (binding can take seconds)
 
     def _bind(self) -> None:
         with torch.cuda.device(self.device):

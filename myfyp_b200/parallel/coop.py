@@ -30,7 +30,7 @@ from myfyp_b200.management.logger import logger
 class CoopHub:
     _instance: Optional["CoopHub"] = None
 
-    def __init__(self, rank: int, world: int, device: torch.device, numel: int, resident: Sequence[str], all_nodes: Sequence[str], window: float = 2.0) -> None:
+    def __init__(self, rank: int, world: int, device: torch.device, numel: int, resident: Sequence[str], all_nodes: Sequence[str], window: float = 10.0) -> None:
         self.rank, self.world, self.device, self.numel = rank, world, device, numel
         self.resident, self.all_nodes = list(resident), list(all_nodes)
         self.window = window
@@ -56,7 +56,7 @@ class CoopHub:
 
     # ------------------------------------------------------------------ set-up
     @classmethod
-    def configure(cls, rank: int, world: int, device, numel: int, resident: Sequence[str], all_nodes: Sequence[str], window: float = 2.0) -> "CoopHub":
+    def configure(cls, rank: int, world: int, device, numel: int, resident: Sequence[str], all_nodes: Sequence[str], window: float = 10.0) -> "CoopHub":
         cls._instance = CoopHub(rank, world, torch.device(device), numel, resident, all_nodes, window)
         return cls._instance
 
