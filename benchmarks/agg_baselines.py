@@ -104,7 +104,10 @@ def main() -> None:
             def build_copy(self, **kw):
                 return NpModel(kw.get("params", self._p), kw.get("num_samples"), kw.get("contributors"))
 
-        ref_models = [NpModel(p, m.get_num_samples(), m.get_contributors(), {"scaffold": m.get_info("scaffold")}) for p, m in zip(np_models, models)]
+        # the reference's Scaffold accumulates in arrays of the parameters' own dtype and fails on integer state entries
+        # (BatchNorm's int64 batch counter: "Cannot cast ufunc 'add' output"); it is given float32 copies of those
+        as_f32 = lambda arrs: [np.asarray(a, dtype=np.float32) for a in arrs]  # noqa: E731
+        ref_models = [NpModel(as_f32(p), m.get_num_samples(), m.get_contributors(), {"scaffold": {k: as_f32(v) for k, v in m.get_info("scaffold").items()}}) for p, m in zip(np_models, models)]
         t_ref_avg = host_time(lambda: RefFedAvg().aggregate(ref_models))
         t_ref_scaf = host_time(lambda: RefScaffold().aggregate(ref_models))
     else:
