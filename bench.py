@@ -434,7 +434,7 @@ def run_scenarios(args) -> None:
                     res.append(run(nm, n, "resnet18", agg, "random", rounds, 256, ts, "cuda", byzantine=byz, max_gpus=args.gpus))
             else:
                 faults = {"drop": [(n - 1, 1), (n - 2, 1)], "rejoin": [(n - 1, 3)]}
-                for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0), {"optimizer": "sgd", "lr": 0.1}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
+                for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0, variate_scaling="paper"), {"optimizer": "sgd", "lr": 0.1}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
                     res.append(run(nm, n, "resnet18", agg, "random", max(rounds, 6), 256, min(8, n), "cuda", faults=faults, max_gpus=args.gpus, learner_kw=kw))
             clocks = sampler.stop(args.gpus)
             value = min(r["rounds_per_s"] for r in res)

@@ -169,7 +169,7 @@ def main() -> None:
         faults = {"drop": [(n - 1, 1), (n - 2, 1)], "rejoin": [(n - 1, 3)]}  # two nodes die in round 1, one comes back in round 3
         # Scaffold's control variates estimate gradients from (x - y) / (K lr): that is SGD arithmetic (Karimireddy et al., Alg. 1), so
         # its clients run SGD; FedProx keeps the reference's Adam
-        for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0), {"optimizer": "sgd", "lr": 0.1}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
+        for nm, agg, kw in (("c4-scaffold", lambda: Scaffold(global_lr=1.0, variate_scaling="paper"), {"optimizer": "sgd", "lr": 0.1}), ("c4-fedprox", lambda: FedProx(mu=0.01), None)):
             res.append(run(nm, n, a.model or "resnet18", agg, "random", a.rounds, a.samples_per_node or 256, min(8, n), mode, faults=faults, learner_kw=kw))
     if a.out:
         os.makedirs(os.path.dirname(os.path.abspath(a.out)) or ".", exist_ok=True)

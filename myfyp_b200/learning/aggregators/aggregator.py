@@ -27,6 +27,7 @@ class NoModelsToAggregateError(Exception):
 class Aggregator:
     def __init__(self, node_name: str = "unknown") -> None:
         self.node_name = node_name
+        self.federation_size: Optional[int] = None  # nodes this node knows of (itself included); the train stage refreshes it every round
         self.__train_set: List[str] = []
         self.__models: List[P2PFLModel] = []
         self.partial_aggregation = False

@@ -26,8 +26,19 @@ from myfyp_b200.learning.p2pfl_model import P2PFLModel
 class Scaffold(Aggregator):
     REQUIRED_INFO_KEYS = ["delta_y_i", "delta_c_i"]
 
-    def __init__(self, node_name: str = "unknown", global_lr: float = 0.1, rebase: bool = True) -> None:
+    def __init__(self, node_name: str = "unknown", global_lr: float = 0.1, rebase: bool = True, variate_scaling: str = "reference") -> None:
+        """``variate_scaling``: how the clients' ``delta_c`` enter the global control variate.
+
+        * ``"reference"`` (default): ``c += (1/K) sum_k delta_c_k`` over the K contributors of the round - the reference's formula
+          (scaffold.py:90-111, pinned by its test).  With every node in every train set this is the paper's; with a train set smaller
+          than the federation it adds the participants' mean at full weight every round, ``c`` stops being the average of the ``c_i``
+          and grows round after round (SURVEY Q9) - with 8 of 64 nodes per round training falls to chance within a few rounds;
+        * ``"paper"``: ``c += (1/N) sum_k delta_c_k`` with N = the size of the federation (Karimireddy et al., Alg. 1, line 17), which
+          keeps ``c = mean_i c_i``.  N is ``federation_size`` (set by the train stage from the neighbour table every round)."""
         super().__init__(node_name)
+        if variate_scaling not in ("reference", "paper"):
+            raise ValueError("variate_scaling must be 'reference' or 'paper'")
+        self.variate_scaling = variate_scaling
         self.global_lr = global_lr
         self.rebase = rebase  # slab path: recover the round's starting point from the clients' models (see _aggregate_slab)
         self.c: Any = []  # list of arrays (generic path) or flat tensor (slab path)
@@ -36,6 +47,11 @@ class Scaffold(Aggregator):
 
     def get_required_callbacks(self) -> List[str]:
         return ["scaffold"]
+
+    def _variate_weight(self, k: int) -> float:
+        if self.variate_scaling == "paper":
+            return 1.0 / max(int(getattr(self, "federation_size", None) or k), k)
+        return 1.0 / k
 
     def observe_global(self, model: P2PFLModel) -> None:
         try:
@@ -82,7 +98,7 @@ class Scaffold(Aggregator):
         for info in infos:
             for i, layer in enumerate(info["delta_c_i"]):
                 acc_c[i] += np.asarray(layer, dtype=np.float64)
-        acc_c = [l / len(models) for l in acc_c]
+        acc_c = [l * self._variate_weight(len(models)) for l in acc_c]
         if not isinstance(self.c, list) or not self.c:
             self.c = [np.zeros_like(l) for l in acc_c]
         self.c = [c + d for c, d in zip(self.c, acc_c)]
@@ -110,7 +126,7 @@ class Scaffold(Aggregator):
         elif self.c.device != dev:
             self.c = self.c.to(dev)
         wy = [self.global_lr * m.get_num_samples() / total for m in models]
-        ops.scaffold_server_update(self.global_model_params, self.c, dys, dcs, wy, 1.0 / len(models))
+        ops.scaffold_server_update(self.global_model_params, self.c, dys, dcs, wy, self._variate_weight(len(models)))
         out = first.build_copy(params=self.global_model_params.clone(), num_samples=total, contributors=contributors)
         out.add_info("scaffold", {"global_c": self.c.clone()})
         return out

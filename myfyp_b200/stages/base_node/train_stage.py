@@ -49,6 +49,7 @@ class TrainStage(Stage):
             # a member evicted by the failure detector between the vote's validation and this point was reported to an
             # aggregator that did not know the train set yet: check once more, or the round waits for a dead node's model
             alive = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
+            aggregator.federation_size = len(alive)
             for dead in [n for n in state.train_set if n not in alive]:
                 if aggregator.drop_node(dead):
                     state.train_set = [n for n in state.train_set if n != dead]

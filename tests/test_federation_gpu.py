@@ -24,7 +24,7 @@ def _agg(name):
 
     return {
         "fedmedian": FedMedian, "trimmedmean": lambda: TrimmedMean(trim=2), "krum": lambda: Krum(f=2, m=2),
-        "scaffold": lambda: Scaffold(global_lr=1.0), "fedprox": lambda: FedProx(mu=0.01),
+        "scaffold": lambda: Scaffold(global_lr=1.0, variate_scaling="paper"), "fedprox": lambda: FedProx(mu=0.01),
     }[name]
 
 
