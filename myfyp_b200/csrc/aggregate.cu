@@ -111,6 +111,69 @@ __device__ __forceinline__ void bitonic_sort(float (&v)[KPAD]) {
   }
 }
 
+// Batcher's odd-even merge sort: the same depth as the bitonic network with ~20 % fewer compare-exchanges at 32 / 64 inputs
+// (191 / 543 against 240 / 672); all indices are compile-time constants after unrolling.
+template <int KPAD>
+__device__ __forceinline__ void oddeven_merge_sort(float (&v)[KPAD]) {
+#pragma unroll
+  for (int p = 1; p < KPAD; p <<= 1) {
+#pragma unroll
+    for (int k = p; k >= 1; k >>= 1) {
+#pragma unroll
+      for (int j = k % p; j + k < KPAD; j += 2 * k) {
+#pragma unroll
+        for (int i = 0; i < k; ++i) {
+          if (i + j + k < KPAD && (i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+            const float lo = fminf(v[i + j], v[i + j + k]), hi = fmaxf(v[i + j], v[i + j + k]);
+            v[i + j] = lo;
+            v[i + j + k] = hi;
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int KPAD>
+__device__ __forceinline__ float pick_median(const float (&v)[KPAD], int K, int trim) {
+  float r = 0.f;
+  if (trim < 0) {
+    const int a = (K - 1) >> 1, b = K >> 1;
+#pragma unroll
+    for (int k = 0; k < KPAD; ++k) r += (k == a ? 0.5f * v[k] : 0.f) + (k == b ? 0.5f * v[k] : 0.f);
+  } else {
+    const int lo = trim, hi = K - trim;
+#pragma unroll
+    for (int k = 0; k < KPAD; ++k) r += (k >= lo && k < hi) ? v[k] : 0.f;
+    r /= (float)(hi - lo);
+  }
+  return r;
+}
+
+// Four coordinates per thread (KPAD <= 16): one 16-byte load per model instead of four 4-byte ones - 4x the bytes in flight per
+// thread - and four independent sorting networks for the scheduler to interleave.  Needs n % 4 == 0 and 16-byte aligned slabs.
+template <int KPAD>
+__global__ void __launch_bounds__(256) median4_kernel(float4* __restrict__ out, const __grid_constant__ PtrTable srcs, int K, int trim, int64_t n4) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float a[KPAD], b[KPAD], c[KPAD], d[KPAD];
+#pragma unroll
+    for (int k = 0; k < KPAD; ++k) {
+      if (k < K) {
+        const float4 t = ld_stream(reinterpret_cast<const float4*>(srcs.p[k]) + i);
+        a[k] = t.x; b[k] = t.y; c[k] = t.z; d[k] = t.w;
+      } else {
+        a[k] = b[k] = c[k] = d[k] = __int_as_float(0x7f800000);
+      }
+    }
+    bitonic_sort<KPAD>(a);
+    bitonic_sort<KPAD>(b);
+    bitonic_sort<KPAD>(c);
+    bitonic_sort<KPAD>(d);
+    out[i] = make_float4(pick_median<KPAD>(a, K, trim), pick_median<KPAD>(b, K, trim), pick_median<KPAD>(c, K, trim), pick_median<KPAD>(d, K, trim));
+  }
+}
+
 template <int KPAD>
 __global__ void __launch_bounds__(KPAD >= 64 ? 128 : 256) median_kernel(float* __restrict__ out, const __grid_constant__ PtrTable srcs, int K, int trim, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -118,19 +181,9 @@ __global__ void __launch_bounds__(KPAD >= 64 ? 128 : 256) median_kernel(float* _
     float v[KPAD];
 #pragma unroll
     for (int k = 0; k < KPAD; ++k) v[k] = (k < K) ? ld_stream1(srcs.p[k] + i) : __int_as_float(0x7f800000);
-    bitonic_sort<KPAD>(v);
-    float r = 0.f;
-    if (trim < 0) {
-      const int a = (K - 1) >> 1, b = K >> 1;
-#pragma unroll
-      for (int k = 0; k < KPAD; ++k) r += (k == a ? 0.5f * v[k] : 0.f) + (k == b ? 0.5f * v[k] : 0.f);
-    } else {
-      const int lo = trim, hi = K - trim;
-#pragma unroll
-      for (int k = 0; k < KPAD; ++k) r += (k >= lo && k < hi) ? v[k] : 0.f;
-      r /= (float)(hi - lo);
-    }
-    out[i] = r;
+    if constexpr (KPAD >= 32) oddeven_merge_sort<KPAD>(v);
+    else bitonic_sort<KPAD>(v);
+    out[i] = pick_median<KPAD>(v, K, trim);
   }
 }
 
@@ -255,6 +308,18 @@ int b2_median(float* out, const void* const* srcs, int K, int trim, int64_t n, v
   }
   if (n <= 0) return 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const bool vec4 = al && (n & 3) == 0 && aligned16(out);
+#define B2_MEDIAN4_CASE(KP)                                                                                                            \
+  if (vec4 && K <= KP) {                                                                                                               \
+    median4_kernel<KP><<<stream_grid(n / 4, 256, 8), 256, 0, s>>>(reinterpret_cast<float4*>(out), pt, K, trim, n / 4);                 \
+    B2_LAUNCH_CHECK("median4_kernel");                                                                                                 \
+    return 0;                                                                                                                          \
+  }
+  B2_MEDIAN4_CASE(2)
+  B2_MEDIAN4_CASE(4)
+  B2_MEDIAN4_CASE(8)
+  B2_MEDIAN4_CASE(16)
+#undef B2_MEDIAN4_CASE
 #define B2_MEDIAN_CASE(KP, TH)                                                             \
   if (K <= KP) {                                                                           \
     median_kernel<KP><<<stream_grid(n, TH, 8), TH, 0, s>>>(out, pt, K, trim, n);           \

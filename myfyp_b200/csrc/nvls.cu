@@ -323,8 +323,10 @@ int b2_nvls_allreduce(void* comm, int64_t off_in, int64_t off_out, int64_t n, un
     set_error("nvls: bad buffer geometry (n=%lld off_in=%lld off_out=%lld region=%zu)", (long long)n, (long long)off_in, (long long)off_out, c->bytes);
     return 1;
   }
-  int grid = sm_count();  // persistent: every CTA must be resident (they wait on other GPUs)
-  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  // persistent: every CTA must be resident (they wait on other GPUs).  One CTA per SM by default; a caller that owns the whole GPU
+  // for the duration of the call may ask for up to two (50 registers x 512 threads: two fit), which helps above ~64 MB
+  int grid = sm_count();
+  if (max_ctas > 0) grid = max_ctas < 2 * grid ? max_ctas : 2 * grid;
   const int64_t need = (n / 4 / c->world + 511) / 512;
   if (need < grid) grid = (int)(need < 1 ? 1 : need);
   nvls_allreduce_kernel<<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned char*>(c->uc_va), reinterpret_cast<unsigned char*>(c->mc_va), off_in, off_out, n / 4,
