@@ -21,6 +21,7 @@ int b2_version(void);
 int b2_device_count(void);
 /* cudaDeviceEnablePeerAccess for every ordered GPU pair of this process; returns the number of enabled pairs. */
 int b2_enable_peer_access_all(void);
+int b2_enable_peer_access(const int* devs, int n); /* peer access among the listed GPUs only; returns the number of enabled ordered pairs */
 /* Publish arena of one rank (cudaMalloc + zero fill) and its CUDA-IPC export / import. */
 void* b2_arena_alloc(int64_t bytes);
 int b2_arena_free(void* p);

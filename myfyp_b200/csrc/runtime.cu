@@ -84,6 +84,28 @@ int b2_enable_peer_access_all(void) {
   return ok;
 }
 
+// Peer access among the listed GPUs only (both directions).  Unlike b2_enable_peer_access_all this creates no context on a GPU
+// the process does not use.
+int b2_enable_peer_access(const int* devs, int n) {
+  int ok = 0, cur = 0;
+  if (n < 2 || devs == nullptr) return 0;
+  cudaGetDevice(&cur);
+  for (int a = 0; a < n; ++a) {
+    cudaSetDevice(devs[a]);
+    for (int b = 0; b < n; ++b) {
+      if (devs[a] == devs[b]) continue;
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, devs[a], devs[b]);
+      if (!can) continue;
+      cudaError_t e = cudaDeviceEnablePeerAccess(devs[b], 0);
+      if (e == cudaSuccess || e == cudaErrorPeerAccessAlreadyEnabled) ++ok;
+      cudaGetLastError();
+    }
+  }
+  cudaSetDevice(cur);
+  return ok;
+}
+
 void* b2_arena_alloc(int64_t bytes) {
   void* p = nullptr;
   cudaError_t e = cudaMalloc(&p, (size_t)bytes);

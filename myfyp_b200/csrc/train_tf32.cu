@@ -336,6 +336,32 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
           const int n_img = row / HW, rem = row - n_img * HW, h = rem / W, wq = rem - h * W;
           const int pos = ((h & 1) << 1) | (wq & 1);
           uint32_t pk[2] = {0u, 0u};
+          if (P.relu && P.out_lo == nullptr) {
+            // non-negative, stored tf32-rounded (13 low bits zero): value and position travel as ONE unsigned key, bits | (3 - pos);
+            // a 2x2 max with "lowest position wins a tie" is two shuffles and two integer maxima per column
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              uint32_t k = (__float_as_uint(tf32_rna(v[e])) & 0x7fffffffu) | (uint32_t)(3 - pos);
+              k = max(k, __shfl_xor_sync(0xffffffffu, k, 1));
+              k = max(k, __shfl_xor_sync(0xffffffffu, k, W));
+              v[e] = __uint_as_float(k & ~3u);
+              pk[e >> 4] |= (3u - (k & 3u)) << (2 * (e & 15));
+            }
+          } else if (P.relu) {
+            // non-negative, kept exact (the consumer splits hi / lo): unsigned order is float order; the winner is the lowest
+            // position that holds the maximum
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const uint32_t k = __float_as_uint(v[e]) & 0x7fffffffu;
+              uint32_t mx = max(k, __shfl_xor_sync(0xffffffffu, k, 1));
+              mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, W));
+              uint32_t cand = k == mx ? (uint32_t)pos : 4u;
+              cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, 1));
+              cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, W));
+              v[e] = __uint_as_float(mx);
+              pk[e >> 4] |= cand << (2 * (e & 15));
+            }
+          } else
 #pragma unroll
           for (int e = 0; e < 32; ++e) {
             float a = v[e];
@@ -600,7 +626,9 @@ struct Conv0Prob {
 
 constexpr int C0_THREADS = 288;  // warps 0-3 producers, warp 4 MMA, warps 5-8 epilogue
 constexpr int C0_W = 32;         // image width this kernel is laid out for (a tile = 4 image rows = 128 pixels)
-constexpr int C0_SIN = 6 * 34;   // staged input rows per channel: 4 + halo, 32 + halo columns
+constexpr int C0_ROW = 48;       // staged row stride (floats): columns 4..35 hold the image row (16-byte aligned), 3 and 36 the zero halo;
+                                 // 48 = 16 mod 32 keeps the two image rows a warp reads in disjoint banks
+constexpr int C0_SIN = 6 * C0_ROW;  // staged input rows per channel: 4 + halo
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 
@@ -611,26 +639,30 @@ __device__ __forceinline__ void c0_row_pixel(int r, int& hh, int& w) {
   w = ((q & 1) << 4) | (l & 15);
 }
 
-__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, bool valid) {
-  const uint32_t sz = valid ? 4u : 0u;  // src-size 0: the destination is zero-filled, nothing is read
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool valid) {
+  const uint32_t sz = valid ? 16u : 0u;  // src-size 0: the destination is zero-filled, nothing is read
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Asynchronous copy (cp.async) of the tile's input rows h0-1 .. h0+4 of every channel into the staging buffer (interior columns
-// 1..32; the border columns stay zero from the prologue).  The batch row -> data-set sample lookup goes through the permutation.
-template <int CIN>
-__device__ __forceinline__ void c0_stage_input(float* sin, const b2_cnn_bind& bd, int step, int batch, int H, int b, int h0, int ptid) {
+// 4..35; the border columns 3 and 36 stay zero from the prologue).  The batch row -> data-set sample lookup goes through the permutation.
+__device__ __forceinline__ long long c0_sample(const b2_cnn_bind& bd, int step, int batch, int b) {
   long long posn = (long long)step * batch + b;
   if (posn >= bd.n_samples) posn = bd.n_samples - 1;  // rows past the data set repeat the last sample; the head ignores them
-  const long long sample = bd.perm != nullptr ? bd.perm[posn] : posn;
-  const float* xs = bd.x + sample * (long long)(CIN * H * C0_W);
-  for (int i = ptid; i < CIN * 6 * 32; i += 128) {
-    const int c = i / 192, rr = (i % 192) >> 5, w = i & 31;
+  return bd.perm != nullptr ? __ldg(bd.perm + posn) : posn;
+}
+// `sample` comes from c0_sample(), which the callers issue one tile earlier than the copies: the permutation lookup is a dependent
+// global load in front of every address below
+template <int CIN>
+__device__ __forceinline__ void c0_stage_input(float* sin, const float* x, long long sample, int H, int h0, int ptid) {
+  const float* xs = x + sample * (long long)(CIN * H * C0_W);
+  for (int i = ptid; i < CIN * 6 * 8; i += 128) {  // 16 bytes per copy: 8 per image row
+    const int c = i / 48, rr = (i % 48) >> 3, w4 = (i & 7) << 2;
     const int h = h0 - 1 + rr;
     const bool ok = h >= 0 && h < H;
-    cp_async4(sin + c * C0_SIN + rr * 34 + w + 1, ok ? xs + ((long long)c * H + h) * C0_W + w : xs, ok);
+    cp_async16(sin + c * C0_SIN + rr * C0_ROW + 4 + w4, ok ? xs + ((long long)c * H + h) * C0_W + w4 : xs, ok);
   }
   cp_async_commit();
 }
@@ -638,7 +670,7 @@ __device__ __forceinline__ void c0_zero_borders(float* sin2, int cin, int tid, i
   for (int i = tid; i < 2 * cin * 12; i += nthreads) {
     const int st = i / (cin * 12), j = i % (cin * 12);
     const int c = j / 12, rr = (j % 12) >> 1, side = j & 1;
-    sin2[st * (cin * C0_SIN) + c * C0_SIN + rr * 34 + (side ? 33 : 0)] = 0.f;
+    sin2[st * (cin * C0_SIN) + c * C0_SIN + rr * C0_ROW + (side ? 36 : 3)] = 0.f;
   }
 }
 
@@ -655,7 +687,7 @@ __device__ __forceinline__ void c0_build_patch_row(uint8_t* tile, const float* s
 #pragma unroll
     for (int kw = 0; kw < 3; ++kw)
 #pragma unroll
-      for (int c = 0; c < CIN; ++c) pv[(kh * 3 + kw) * CIN + c] = tf32_rna(sin[c * C0_SIN + (hh + kh) * 34 + w + kw]);
+      for (int c = 0; c < CIN; ++c) pv[(kh * 3 + kw) * CIN + c] = tf32_rna(sin[c * C0_SIN + (hh + kh) * C0_ROW + w + kw + 3]);
 #pragma unroll
   for (int ch = 0; ch < 8; ++ch)
     *reinterpret_cast<float4*>(tile + (MN ? sw32_offset((uint32_t)r, (uint32_t)ch) : tc::sw128_offset((uint32_t)r, (uint32_t)ch))) = make_float4(pv[4 * ch], pv[4 * ch + 1], pv[4 * ch + 2], pv[4 * ch + 3]);
@@ -704,14 +736,20 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
     // ================================ producers: gather the batch rows by permutation index, build patch rows
     // the input rows of tile i+1 are in flight (cp.async) while the patch rows of tile i are built
     uint32_t it = 0;
-    if ((int)blockIdx.x < P.tiles) c0_stage_input<CIN>(sin, bd, step, P.batch, H, blockIdx.x / tiles_per_img, (blockIdx.x % tiles_per_img) * 4, tid);
+    const float* xin = bd.x;
+    long long smp_next = 0;
+    if ((int)blockIdx.x < P.tiles) {
+      c0_stage_input<CIN>(sin, xin, c0_sample(bd, step, P.batch, blockIdx.x / tiles_per_img), H, (blockIdx.x % tiles_per_img) * 4, tid);
+      if ((int)(blockIdx.x + gridDim.x) < P.tiles) smp_next = c0_sample(bd, step, P.batch, (blockIdx.x + gridDim.x) / tiles_per_img);
+    }
     for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
       const int s = it & 1;
       float* sn = sin + s * (CIN * C0_SIN);
       cp_async_wait_all();
       named_bar_sync(1, 128);  // everybody's copies have landed, and everybody is done reading the other staging buffer
-      const int tn = t + gridDim.x;
-      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), bd, step, P.batch, H, tn / tiles_per_img, (tn % tiles_per_img) * 4, tid);
+      const int tn = t + gridDim.x, tnn = tn + gridDim.x;
+      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), xin, smp_next, H, (tn % tiles_per_img) * 4, tid);
+      if (tnn < P.tiles) smp_next = c0_sample(bd, step, P.batch, tnn / tiles_per_img);
       tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
       c0_build_patch_row<CIN, false>(a_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
@@ -748,37 +786,33 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
       for (int cb = 0; cb < cout / 32; ++cb) {
         float v[32];
         tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + s * 64 + cb * 32, v);
-        uint32_t pk[2] = {0u, 0u};
+        // The stored activation is tf32-rounded (13 low bits zero) and non-negative after the ReLU, so value and window position
+        // travel as ONE unsigned key: bits | (3 - pos).  A 2x2 max with "lowest position wins a tie" is then two shuffles and two
+        // integer maxima per column.
+        uint32_t key[32];
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          float a = fmaxf(v[e] + __ldg(bias + cb * 32 + e), 0.f);
-          int pa = pos;
-          const float o1 = __shfl_xor_sync(0xffffffffu, a, 1);
-          bool take = (o1 > a) || (o1 == a && (pos ^ 1) < pa);
-          a = take ? o1 : a;
-          pa = take ? (pos ^ 1) : pa;
-          const float o2 = __shfl_xor_sync(0xffffffffu, a, 16);
-          const int p2 = __shfl_xor_sync(0xffffffffu, pa, 16);
-          take = (o2 > a) || (o2 == a && p2 < pa);
-          a = take ? o2 : a;
-          pa = take ? p2 : pa;
-          v[e] = a;
-          pk[e >> 4] |= (uint32_t)pa << (2 * (e & 15));
+          const float a = tf32_rna(fmaxf(v[e] + __ldg(bias + cb * 32 + e), 0.f));
+          uint32_t k = (__float_as_uint(a) & 0x7fffffffu) | (uint32_t)(3 - pos);
+          k = max(k, __shfl_xor_sync(0xffffffffu, k, 1));
+          k = max(k, __shfl_xor_sync(0xffffffffu, k, 16));
+          key[e] = k;
         }
         if (pos == 0) {
           const int ph = (h0 >> 1) + (q >> 1), pw = ((q & 1) << 3) + ((lane & 15) >> 1);
           const int64_t pp = ((int64_t)b * (H >> 1) + ph) * (C0_W >> 1) + pw;
           float* o = P.out + pp * cout + cb * 32;
 #pragma unroll
-          for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(tf32_rna(v[e]), tf32_rna(v[e + 1]), tf32_rna(v[e + 2]), tf32_rna(v[e + 3]));
+          for (int e = 0; e < 32; e += 4)
+            *reinterpret_cast<float4*>(o + e) = make_float4(__uint_as_float(key[e] & ~3u), __uint_as_float(key[e + 1] & ~3u), __uint_as_float(key[e + 2] & ~3u), __uint_as_float(key[e + 3] & ~3u));
           uint32_t bytes[8];
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
             uint32_t wv = 0;
 #pragma unroll
             for (int bb = 0; bb < 4; ++bb) {
-              const int e = 4 * g + bb;
-              wv |= ((((pk[e >> 4] >> (2 * (e & 15))) & 3u) | (v[e] > 0.f ? 4u : 0u))) << (8 * bb);
+              const uint32_t k = key[4 * g + bb];
+              wv |= ((3u - (k & 3u)) | (k > 3u ? 4u : 0u)) << (8 * bb);
             }
             bytes[g] = wv;
           }
@@ -857,8 +891,11 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_wgrad_kernel(const Conv0P
     };
     C0wPre cur[CB];
     uint32_t it = 0;
+    const float* xin = bd.x;
+    long long smp_next = 0;
     if ((int)blockIdx.x < P.tiles) {
-      c0_stage_input<CIN>(sin, bd, step, P.batch, H, blockIdx.x / tiles_per_img, (blockIdx.x % tiles_per_img) * 4, tid);
+      c0_stage_input<CIN>(sin, xin, c0_sample(bd, step, P.batch, blockIdx.x / tiles_per_img), H, (blockIdx.x % tiles_per_img) * 4, tid);
+      if ((int)(blockIdx.x + gridDim.x) < P.tiles) smp_next = c0_sample(bd, step, P.batch, (blockIdx.x + gridDim.x) / tiles_per_img);
       fetch(blockIdx.x, cur);
     }
     for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
@@ -866,8 +903,9 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_wgrad_kernel(const Conv0P
       float* sn = sin + s * (CIN * C0_SIN);
       cp_async_wait_all();
       named_bar_sync(1, 128);
-      const int tn = t + gridDim.x;
-      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), bd, step, P.batch, H, tn / tiles_per_img, (tn % tiles_per_img) * 4, tid);
+      const int tn = t + gridDim.x, tnn = tn + gridDim.x;
+      if (tn < P.tiles) c0_stage_input<CIN>(sin + (s ^ 1) * (CIN * C0_SIN), xin, smp_next, H, (tn % tiles_per_img) * 4, tid);
+      if (tnn < P.tiles) smp_next = c0_sample(bd, step, P.batch, tnn / tiles_per_img);
       tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
       // this pixel's dz row: the (already ReLU-masked) pooled gradient goes to the window's winner only
       uint8_t* arow = a_tiles + s * C0W_A_STAGE;
@@ -1113,22 +1151,39 @@ __device__ __forceinline__ int pad32(int x) { return x + (x >> 5); }
 
 struct AdamCoef {
   float lr, wd, b1, b2, eps, inv_bc1, inv_sqrt_bc2;
+  // the slot's pointers and scalars, read from the bind table once (the table lives in global memory)
+  float *slab, *m, *v;
+  const float *prox, *cvg, *cvl;
+  float mu, cvs, mom;
+  int sgd;
 };
-__device__ __forceinline__ float adam_one(const b2_cnn_bind& bd, const AdamCoef& c, int64_t i, float g, float p, float* m, float* v) {
+// one element of the optimiser: FedProx / Scaffold terms, then SGD (+ momentum) or Adam.  m and v are updated in place.
+__device__ __forceinline__ float adam_update(const AdamCoef& c, float p, float g, float& m, float& v, float q, float cg, float cl) {
   if (c.wd != 0.f) g = fmaf(c.wd, p, g);
-  if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - bd.prox_ref[i], g);
-  if (bd.cv_global != nullptr && bd.cv_local != nullptr) g = fmaf(bd.cv_scale, bd.cv_global[i] - bd.cv_local[i], g);
-  if (bd.sgd) {
-    const float mn = bd.momentum != 0.f ? fmaf(bd.momentum, m[i], g) : g;
-    if (bd.momentum != 0.f) m[i] = mn;
-    return p - c.lr * mn;
+  if (c.prox != nullptr) g = fmaf(c.mu, p - q, g);
+  if (c.cvg != nullptr) g = fmaf(c.cvs, cg - cl, g);
+  if (c.sgd) {
+    if (c.mom != 0.f) {
+      m = fmaf(c.mom, m, g);
+      g = m;
+    }
+    return p - c.lr * g;
   }
-  const float mn = fmaf(c.b1, m[i], (1.f - c.b1) * g);
-  const float vn = fmaf(c.b2, v[i], (1.f - c.b2) * g * g);
-  m[i] = mn;
-  v[i] = vn;
-  return p - c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
+  m = fmaf(c.b1, m, (1.f - c.b1) * g);
+  v = fmaf(c.b2, v, (1.f - c.b2) * g * g);
+  return p - c.lr * (m * c.inv_bc1) / (sqrtf(v) * c.inv_sqrt_bc2 + c.eps);
 }
+__device__ __forceinline__ float adam_scalar(const AdamCoef& c, int64_t i, float g) {
+  float m = (!c.sgd || c.mom != 0.f) ? c.m[i] : 0.f, v = c.sgd ? 0.f : c.v[i];
+  const float q = c.prox != nullptr ? c.prox[i] : 0.f, cg = c.cvg != nullptr ? c.cvg[i] : 0.f, cl = c.cvg != nullptr ? c.cvl[i] : 0.f;
+  const float p = adam_update(c, c.slab[i], g, m, v, q, cg, cl);
+  if (!c.sgd || c.mom != 0.f) c.m[i] = m;
+  if (!c.sgd) c.v[i] = v;
+  c.slab[i] = p;
+  return p;
+}
+__device__ __forceinline__ float4 ldg4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void stg4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 __global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __restrict__ bufs, const b2_cnn_bind* __restrict__ binds, const __grid_constant__ AdamTab tab, int step, int batch,
                                                            float b1, float b2, float eps, int refresh_only) {
@@ -1138,7 +1193,9 @@ __global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __res
   float* sg = asm_;
   float* sp = asm_ + pad32(tab.max_ct) + 1;
   const SlotBufs sb = bufs[blockIdx.y];
-  AdamCoef c{bd.lr, bd.weight_decay, b1, b2, eps, 1.f, 1.f};
+  const bool cv = bd.cv_global != nullptr && bd.cv_local != nullptr;
+  AdamCoef c{bd.lr, bd.weight_decay, b1, b2, eps, 1.f, 1.f, bd.slab, bd.m, bd.v, bd.prox_ref, cv ? bd.cv_global : nullptr, cv ? bd.cv_local : nullptr,
+             bd.prox_mu, bd.cv_scale, bd.momentum, bd.sgd};
   if (!refresh_only) {
     const float st = bd.adam_state[0] + (float)(step + 1);
     c.inv_bc1 = 1.f / (1.f - powf(b1, st));
@@ -1158,66 +1215,77 @@ __global__ void __launch_bounds__(256) adam_grouped_kernel(const SlotBufs* __res
       cnt = cnt > ADAM_CHUNK ? ADAM_CHUNK : cnt;
       for (int l = tid; l < cnt; l += 256) {
         const int64_t i = i0 + l;
-        if (!refresh_only) {
-          const float g = sb.gm[i];
-          bd.slab[i] = adam_one(bd, c, i, g, bd.slab[i], bd.m, bd.v);
-        }
+        if (!refresh_only) adam_scalar(c, i, sb.gm[i]);
         sb.gm[i] = 0.f;
       }
       continue;
     }
-    const int ct = en.ct;
+    const int ct = en.ct, taps = en.taps, cin = en.cin;
     const int64_t base = en.begin + (int64_t)r * ct;
+    if (((en.begin | en.lo_off | (long long)ct) & 3) == 0) {
+      // ---- 16-byte path: every thread owns 4 consecutive slab elements (one float4 of p / m / v and of the mirrors)
+      for (int l = 4 * tid; l < ct; l += 4 * 256) {
+        if (!refresh_only) {
+          const float4 g = ldg4(sb.gm + base + l);
+          float* d = sg + pad32(l);  // l .. l+3 share one 32-element block: contiguous after padding
+          d[0] = g.x, d[1] = g.y, d[2] = g.z, d[3] = g.w;
+        }
+        stg4(sb.gm + base + l, make_float4(0.f, 0.f, 0.f, 0.f));
+      }
+      __syncthreads();
+      for (int l = 4 * tid; l < ct; l += 4 * 256) {
+        const int64_t i = base + l;
+        float4 p4 = ldg4(c.slab + i), m4, v4, q4, cg4, cl4;
+        m4 = v4 = q4 = cg4 = cl4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!refresh_only) {
+          if (!c.sgd || c.mom != 0.f) m4 = ldg4(c.m + i);
+          if (!c.sgd) v4 = ldg4(c.v + i);
+          if (c.prox != nullptr) q4 = ldg4(c.prox + i);
+          if (c.cvg != nullptr) cg4 = ldg4(c.cvg + i), cl4 = ldg4(c.cvl + i);
+        }
+        int ci = l / taps, tap = l - ci * taps;
+        float* pp = &p4.x;
+        float *mp = &m4.x, *vp = &v4.x;
+        const float *qp = &q4.x, *cgp = &cg4.x, *clp = &cl4.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int j = pad32(tap * cin + ci);
+          if (!refresh_only) pp[e] = adam_update(c, pp[e], sg[j], mp[e], vp[e], qp[e], cgp[e], clp[e]);
+          sp[j] = pp[e];
+          if (++tap == taps) tap = 0, ++ci;
+        }
+        if (!refresh_only) {
+          if (!c.sgd || c.mom != 0.f) stg4(c.m + i, m4);
+          if (!c.sgd) stg4(c.v + i, v4);
+          stg4(c.slab + i, p4);
+        }
+      }
+      __syncthreads();
+      float* lo = sb.wlo + en.lo_off + (int64_t)r * ct;
+      for (int l = 4 * tid; l < ct; l += 4 * 256) {
+        const float* s4 = sp + pad32(l);
+        const float p0 = s4[0], p1 = s4[1], p2 = s4[2], p3 = s4[3];
+        if (en.kind == 1) {
+          stg4(sb.wm + base + l, make_float4(tf32_rna(p0), tf32_rna(p1), tf32_rna(p2), tf32_rna(p3)));
+        } else {
+          const float4 hi = make_float4(tf32_hi(p0), tf32_hi(p1), tf32_hi(p2), tf32_hi(p3));
+          stg4(sb.wm + base + l, hi);
+          stg4(lo + l, make_float4(tf32_rna(p0 - hi.x), tf32_rna(p1 - hi.y), tf32_rna(p2 - hi.z), tf32_rna(p3 - hi.w)));
+        }
+      }
+      __syncthreads();
+      continue;
+    }
+    // ---- element-wise path (rows whose length or offset is not a multiple of 4: the first convolution)
     if (!refresh_only) {
       for (int l = tid; l < ct; l += 256) sg[pad32(l)] = sb.gm[base + l];
     }
     for (int l = tid; l < ct; l += 256) sb.gm[base + l] = 0.f;
     __syncthreads();
-    // four rows of 256 threads per trip, every global load issued before the first use (p, m, v and the optional terms)
-    for (int l0 = 0; l0 < ct; l0 += 4 * 256) {
-      float pv[4], mv[4], vv[4], q[4], cg[4], cl[4];
-      int jm[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int l = l0 + u * 256 + tid;
-        const bool ok = l < ct;
-        const int64_t i = base + (ok ? l : 0);
-        pv[u] = bd.slab[i];
-        if (!refresh_only) {
-          mv[u] = bd.m[i];
-          vv[u] = bd.v[i];
-          q[u] = bd.prox_ref != nullptr ? bd.prox_ref[i] : 0.f;
-          cg[u] = bd.cv_global != nullptr && bd.cv_local != nullptr ? bd.cv_global[i] : 0.f;
-          cl[u] = bd.cv_global != nullptr && bd.cv_local != nullptr ? bd.cv_local[i] : 0.f;
-        }
-        const int ci = l / en.taps, tap = l - ci * en.taps;
-        jm[u] = pad32(tap * en.cin + ci);
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int l = l0 + u * 256 + tid;
-        if (l >= ct) continue;
-        float p = pv[u];
-        if (!refresh_only) {
-          float g = sg[jm[u]];
-          if (c.wd != 0.f) g = fmaf(c.wd, p, g);
-          if (bd.prox_ref != nullptr) g = fmaf(bd.prox_mu, p - q[u], g);
-          g = fmaf(bd.cv_scale, cg[u] - cl[u], g);
-          if (bd.sgd) {
-            const float mn = bd.momentum != 0.f ? fmaf(bd.momentum, mv[u], g) : g;
-            p -= c.lr * mn;
-            if (bd.momentum != 0.f) bd.m[base + l] = mn;
-          } else {
-            const float mn = fmaf(c.b1, mv[u], (1.f - c.b1) * g);
-            const float vn = fmaf(c.b2, vv[u], (1.f - c.b2) * g * g);
-            p -= c.lr * (mn * c.inv_bc1) / (sqrtf(vn) * c.inv_sqrt_bc2 + c.eps);
-            bd.m[base + l] = mn;
-            bd.v[base + l] = vn;
-          }
-          bd.slab[base + l] = p;
-        }
-        sp[jm[u]] = p;
-      }
+    for (int l = tid; l < ct; l += 256) {
+      const int ci = l / taps, tap = l - ci * taps;
+      const int j = pad32(tap * cin + ci);
+      sp[j] = refresh_only ? c.slab[base + l] : adam_scalar(c, base + l, sg[j]);
     }
     __syncthreads();
     if (en.kind == 1) {

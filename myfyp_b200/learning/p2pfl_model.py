@@ -187,7 +187,7 @@ class TorchP2PFLModel(P2PFLModel):
         if slab.is_cuda:  # the fabric learns which GPUs of this process hold models (see Fabric.make_visible)
             from myfyp_b200.parallel.fabric import Fabric
 
-            Fabric._gpus_in_use.add(slab.device.index)
+            Fabric.ensure_peers((slab.device.index,))  # peer access among the GPUs that hold models - and only those
 
     def sync_mirrors_to_slab(self) -> None:
         """Refresh the fp32 mirrors of non-fp32 buffers (e.g. BatchNorm num_batches_tracked)."""

@@ -39,6 +39,11 @@ def order_after_producers(slabs: Sequence[torch.Tensor], device: torch.device) -
     if device.type != "cuda":
         return
     seen = set()
+    foreign = {s.device.index for s in slabs if s.is_cuda and s.device != device}
+    if foreign:
+        from myfyp_b200.parallel.fabric import Fabric
+
+        Fabric.ensure_peers(foreign | {device.index if device.index is not None else torch.cuda.current_device()})
     for s in slabs:
         if s.is_cuda and s.device != device and s.device not in seen:
             seen.add(s.device)

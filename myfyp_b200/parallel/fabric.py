@@ -70,17 +70,28 @@ class Fabric:
 
     # ------------------------------------------------------------------ peer access (single process)
     def enable_peer_access(self) -> int:
-        """``cudaDeviceEnablePeerAccess`` for every ordered GPU pair; returns how many pairs can reach each other."""
-        if self._peer_enabled:
-            return 0
-        n = self.device_count()
-        ok = 0
-        if n > 1:
-            from myfyp_b200.ops import native
+        """``cudaDeviceEnablePeerAccess`` among the GPUs this process holds models on (both directions); returns how many ordered
+        pairs can reach each other.  GPUs the process does not use are left alone - no context is created on them."""
+        return Fabric.ensure_peers(())
 
-            lib = native.load()
-            ok = lib.b2_enable_peer_access_all()
-        self._peer_enabled = True
+    _peers_enabled_for: frozenset = frozenset()
+
+    @classmethod
+    def ensure_peers(cls, devices) -> int:
+        """Peer access among every GPU in use so far plus ``devices`` (indices).  Cheap when nothing is new."""
+        for d in devices:
+            cls._gpus_in_use.add(int(d))
+        want = frozenset(cls._gpus_in_use)
+        if len(want) < 2 or want <= cls._peers_enabled_for:
+            return 0
+        import ctypes
+
+        from myfyp_b200.ops import native
+
+        lib = native.load()
+        arr = (ctypes.c_int * len(want))(*sorted(want))
+        ok = int(lib.b2_enable_peer_access(arr, len(want)))
+        cls._peers_enabled_for = want
         return ok
 
     # ------------------------------------------------------------------ snapshots
