@@ -316,6 +316,8 @@ def run_ours(args) -> None:
                 acc_t[name] += dt
         stage_ms = {k: round(1e3 * v / len(nodes) / args.steps, 2) for k, v in acc_t.items()}
         stage_ms.update({k: round(sum(v) / max(len(v), 1), 2) for k, v in _lg.get_device_times().items()})
+        if os.environ.get("B2_BENCH_SERIES"):  # per-round series of one key, e.g. cohort/fit_graph_on_device
+            stage_ms["series"] = [round(v, 2) for v in _lg.get_device_times().get(os.environ["B2_BENCH_SERIES"], [])]
         # control-plane messages handled by this rank's nodes, per round (all nodes of the rank together)
         stage_ms.update({k: round(v / args.steps, 1) for k, v in _lg.get_bytes().items() if k.startswith("msgs/")})
     ms = allmax(e0.elapsed_time(e1))

@@ -48,6 +48,33 @@ constexpr int A_BYTES = BM * 128;   // 16 KB
 constexpr int GG_THREADS = 192;     // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
 constexpr int ACC_STAGES = 2;
 
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// A lane of an epilogue warp owns one output row and writes 32 consecutive floats of it.  With 16-byte stores every warp instruction
+// touches 32 half-filled 32-byte sectors; the 32-byte form (STG.256, sm_100) writes whole sectors with half the requests.
+__device__ __forceinline__ void stg256(void* p, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4, uint32_t a5, uint32_t a6, uint32_t a7) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7) : "memory");
+}
+__device__ __forceinline__ void store_row32(float* o, const float (&v)[32]) {
+  if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 8)
+      stg256(o + e, __float_as_uint(v[e]), __float_as_uint(v[e + 1]), __float_as_uint(v[e + 2]), __float_as_uint(v[e + 3]), __float_as_uint(v[e + 4]), __float_as_uint(v[e + 5]),
+             __float_as_uint(v[e + 6]), __float_as_uint(v[e + 7]));
+  } else {
+#pragma unroll
+    for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+  }
+}
+__device__ __forceinline__ void store_codes32(uint8_t* ip, const uint32_t (&b)[8]) {
+  if ((reinterpret_cast<uintptr_t>(ip) & 31) == 0) {
+    stg256(ip, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7]);
+  } else {
+    reinterpret_cast<uint4*>(ip)[0] = make_uint4(b[0], b[1], b[2], b[3]);
+    reinterpret_cast<uint4*>(ip)[1] = make_uint4(b[4], b[5], b[6], b[7]);
+  }
+}
 enum { EPI_STORE = 0, EPI_ATOMIC = 1, EPI_POOL = 2, EPI_UNPOOL = 3, EPI_MASK = 4 };
 
 struct alignas(128) Problem {
@@ -318,16 +345,22 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
         }
         if constexpr (EPI == EPI_STORE) {
           if (row_ok) {
-            float* o = P.out + (int64_t)row * P.ldo + nb;
-#pragma unroll
-            for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+            store_row32(P.out + (int64_t)row * P.ldo + nb, v);
           }
         } else if constexpr (EPI == EPI_ATOMIC) {
           if (row_ok) {
             float* o = P.out + (int64_t)row * P.ldo + nb;
+            // a lane owns a row, so every reduction of a warp instruction lands in a different 32-byte sector of L2: the 16-byte
+            // vector form sends a quarter of the sector operations (measured: the scalar form cost conv2's weight gradient 25 %)
+            if (nb + 32 <= N && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
 #pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+              for (int e = 0; e < 32; e += 4)
+                if (v[e] != 0.f || v[e + 1] != 0.f || v[e + 2] != 0.f || v[e + 3] != 0.f) red_add_v4(o + e, v[e], v[e + 1], v[e + 2], v[e + 3]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+            }
           }
         } else if constexpr (EPI == EPI_POOL) {
           // rows of a tile are pixels in (image, h, w) order and W divides 16: the 2x2 window of a pixel lives in this warp at
@@ -383,17 +416,19 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
             float* o = P.out + pp * P.ldo + nb;
             if (P.out_lo != nullptr) {  // consumer is a 3xTF32 GEMM: exact hi / lo split
               float* ol = P.out_lo + pp * P.ldo + nb;
+              float hi[32], lo[32];
 #pragma unroll
-              for (int e = 0; e < 32; e += 4) {
-                float4 hi4, lo4;
-                hi4.x = tf32_hi(v[e]); hi4.y = tf32_hi(v[e + 1]); hi4.z = tf32_hi(v[e + 2]); hi4.w = tf32_hi(v[e + 3]);
-                lo4.x = tf32_rna(v[e] - hi4.x); lo4.y = tf32_rna(v[e + 1] - hi4.y); lo4.z = tf32_rna(v[e + 2] - hi4.z); lo4.w = tf32_rna(v[e + 3] - hi4.w);
-                *reinterpret_cast<float4*>(o + e) = hi4;
-                *reinterpret_cast<float4*>(ol + e) = lo4;
+              for (int e = 0; e < 32; ++e) {
+                hi[e] = tf32_hi(v[e]);
+                lo[e] = tf32_rna(v[e] - hi[e]);
               }
+              store_row32(o, hi);
+              store_row32(ol, lo);
             } else {
+              float r[32];
 #pragma unroll
-              for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(tf32_rna(v[e]), tf32_rna(v[e + 1]), tf32_rna(v[e + 2]), tf32_rna(v[e + 3]));
+              for (int e = 0; e < 32; ++e) r[e] = tf32_rna(v[e]);
+              store_row32(o, r);
             }
             uint32_t bytes[8];
 #pragma unroll
@@ -407,9 +442,7 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
               }
               bytes[g] = wv;
             }
-            uint4* ip = reinterpret_cast<uint4*>(P.idx + pp * P.ldo + nb);
-            ip[0] = make_uint4(bytes[0], bytes[1], bytes[2], bytes[3]);
-            ip[1] = make_uint4(bytes[4], bytes[5], bytes[6], bytes[7]);
+            store_codes32(P.idx + pp * P.ldo + nb, bytes);
           }
         } else {
           // EPI_UNPOOL / EPI_MASK: this row's 32 values are gradients of pooled outputs (pooled pixel pr, channels cbase..+32)
@@ -437,25 +470,17 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
           }
           if (row_ok) {
             if constexpr (EPI == EPI_MASK) {
-              float* o = P.out + pr * Cn + cbase;
-#pragma unroll
-              for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+              store_row32(P.out + pr * Cn + cbase, v);
             } else {
               const int FW = P.img_w, FH = P.img_h, PW = FW >> 1, PHW = (FH >> 1) * PW;
               const int n_img = (int)(pr / PHW), rem = (int)(pr - (int64_t)n_img * PHW), ph = rem / PW, pw = rem - ph * PW;
               const int64_t fr = ((int64_t)n_img * FH + 2 * ph) * FW + 2 * pw;
 #pragma unroll
               for (int ps = 0; ps < 4; ++ps) {
-                float* o = P.out + (fr + (ps >> 1) * FW + (ps & 1)) * Cn + cbase;
+                float wv[32];
 #pragma unroll
-                for (int e = 0; e < 32; e += 4) {
-                  float4 wv;
-                  wv.x = (((code[e >> 2] >> 0) & 3u) == (uint32_t)ps) ? v[e] : 0.f;
-                  wv.y = (((code[e >> 2] >> 8) & 3u) == (uint32_t)ps) ? v[e + 1] : 0.f;
-                  wv.z = (((code[e >> 2] >> 16) & 3u) == (uint32_t)ps) ? v[e + 2] : 0.f;
-                  wv.w = (((code[e >> 2] >> 24) & 3u) == (uint32_t)ps) ? v[e + 3] : 0.f;
-                  *reinterpret_cast<float4*>(o + e) = wv;
-                }
+                for (int e = 0; e < 32; ++e) wv[e] = (((code[e >> 2] >> (8 * (e & 3))) & 3u) == (uint32_t)ps) ? v[e] : 0.f;
+                store_row32(P.out + (fr + (ps >> 1) * FW + (ps & 1)) * Cn + cbase, wv);
               }
             }
           }
@@ -801,10 +826,10 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
         if (pos == 0) {
           const int ph = (h0 >> 1) + (q >> 1), pw = ((q & 1) << 3) + ((lane & 15) >> 1);
           const int64_t pp = ((int64_t)b * (H >> 1) + ph) * (C0_W >> 1) + pw;
-          float* o = P.out + pp * cout + cb * 32;
+          float r[32];
 #pragma unroll
-          for (int e = 0; e < 32; e += 4)
-            *reinterpret_cast<float4*>(o + e) = make_float4(__uint_as_float(key[e] & ~3u), __uint_as_float(key[e + 1] & ~3u), __uint_as_float(key[e + 2] & ~3u), __uint_as_float(key[e + 3] & ~3u));
+          for (int e = 0; e < 32; ++e) r[e] = __uint_as_float(key[e] & ~3u);
+          store_row32(P.out + pp * cout + cb * 32, r);
           uint32_t bytes[8];
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
@@ -816,9 +841,7 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
             }
             bytes[g] = wv;
           }
-          uint4* ip = reinterpret_cast<uint4*>(P.idx + pp * cout + cb * 32);
-          ip[0] = make_uint4(bytes[0], bytes[1], bytes[2], bytes[3]);
-          ip[1] = make_uint4(bytes[4], bytes[5], bytes[6], bytes[7]);
+          store_codes32(P.idx + pp * cout + cb * 32, bytes);
         }
       }
       tc::fence_before_sync();

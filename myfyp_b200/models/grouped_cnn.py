@@ -19,6 +19,7 @@ same ``nn.Module`` (see the header of train_tf32.cu); the bf16 path of :mod:`nat
 from __future__ import annotations
 
 import ctypes
+import os
 import threading
 import time
 import weakref
@@ -221,12 +222,19 @@ class CnnPlan:
 
 
 # ====================================================================================================== cohort trainer
+def _logger():
+    from myfyp_b200.management.logger import logger
+
+    return logger
+
+
 class _Job:
-    __slots__ = ("kind", "learner", "args", "done", "result", "error")
+    __slots__ = ("kind", "learner", "args", "done", "result", "error", "t_in")
 
     def __init__(self, kind: str, learner, args: dict) -> None:
         self.kind, self.learner, self.args = kind, learner, args
         self.done, self.result, self.error = False, None, None
+        self.t_in = time.perf_counter()
 
 
 class CohortTrainer:
@@ -352,6 +360,29 @@ class CohortTrainer:
             self._host = buf
         return buf
 
+    def _profile_kernels(self, plan: CnnPlan, st) -> None:
+        """``B2_COHORT_PROFILE=1``: CUDA-event time of every kernel of the step on the slots bound right now (the live data of a
+        federation, not the synthetic tensors of tools/t32_step_profile.py).  10 launches each; logged as ``cohortk/<name>`` (us)."""
+        seq = [("conv0_fwd", RUN_CONV0_FWD), ("conv1_fwd", RUN_CONV_FWD + 1), ("conv2_fwd", RUN_CONV_FWD + 2), ("fc1_fwd", RUN_FC1_FWD), ("head", RUN_HEAD_TRAIN),
+               ("fc1_wgrad", RUN_FC1_WGRAD), ("fc1_dgrad", RUN_FC1_DGRAD), ("conv2_wgrad", RUN_CONV_WGRAD + 2), ("conv2_dgrad", RUN_CONV_DGRAD + 2),
+               ("conv1_wgrad", RUN_CONV_WGRAD + 1), ("conv1_dgrad", RUN_CONV_DGRAD + 1), ("conv0_wgrad", RUN_CONV0_WGRAD), ("adam", RUN_ADAM)]
+        for name, which in seq:
+            plan.run(which, 1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(10):
+                plan.run(which, 1)
+            e1.record(st)
+            st.synchronize()
+            _logger().log_device_time(f"cohortk/{name}", 100.0 * e0.elapsed_time(e1))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for s in range(10):
+            plan.train_step(s)
+        e1.record(st)
+        st.synchronize()
+        _logger().log_device_time("cohortk/step_eager", 100.0 * e0.elapsed_time(e1))
+
     # ------------------------------------------------------------------ one cohort
     def _execute(self, kind: str, batch: List[_Job]) -> None:
         dev = self.device
@@ -361,6 +392,14 @@ class CohortTrainer:
         plan = self.plan(len(batch))
         self.batches += 1
         self.batched += len(batch)
+        t0 = time.perf_counter()
+        marks = [t0]
+
+        def lap(name: str) -> None:  # wall-time split of a cohort, next to the stage laps (logger.get_device_times())
+            marks.append(time.perf_counter())
+            _logger().log_device_time(f"cohort/{kind}_{name}", 1e3 * (marks[-1] - marks[-2]))
+
+        _logger().log_device_time(f"cohort/{kind}_gather", 1e3 * (t0 - min(j.t_in for j in batch)))  # first request -> everybody here
         with torch.cuda.device(dev), torch.cuda.stream(st):
             for j in batch:  # inputs were produced on the learners' own streams
                 ev = j.args.get("ready")
@@ -392,29 +431,47 @@ class CohortTrainer:
                             a["perm"].copy_(a["make_perm"](), non_blocking=True)
                         if e:
                             a["losses"].zero_()
+                    if e == 0 and os.environ.get("B2_COHORT_PROFILE"):
+                        keep = [(a[k], a[k].clone()) for a in slots for k in ("slab", "m", "v", "adam_state")]
+                        self._profile_kernels(plan, st)  # debugging aid; the training state is put back afterwards
+                        for t, c in keep:
+                            t.copy_(c)
+                        plan.refresh()
+                    if e == 0:
+                        lap("setup")
+                        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        ev0.record(st)
                     graph.replay()
+                    if e == 0:
+                        ev1.record(st)
+                        lap("launch")
                     native.count_launch(graph.native_kernels)
                     for k, j in enumerate(batch):
                         if j in live:
                             host[k, e * steps : (e + 1) * steps].copy_(j.args["losses"][:steps], non_blocking=True)
                 st.synchronize()  # releases the interpreter lock while the device works
+                lap("device")
+                _logger().log_device_time("cohort/fit_graph_on_device", ev0.elapsed_time(ev1))  # CUDA-event time of the first epoch's graph
                 for k, j in enumerate(batch):
                     n_mine = min(steps, (int(j.args["n_samples"]) + B - 1) // B)
                     ep = int(j.args.get("epochs", 1))
                     vals = host[k, : ep * steps].view(ep, steps)[:, :n_mine].reshape(-1).tolist()
                     j.result = {"losses": vals, "steps": len(vals)}
+                lap("post")
             else:
                 for j in batch:
                     j.args["losses"].zero_()
                 graph = self._graph(plan, "eval", steps)
                 plan.bind([j.args for j in batch] + [None] * (plan.groups - len(batch)))
                 plan.refresh()
+                lap("setup")
                 graph.replay()
                 native.count_launch(graph.native_kernels)
                 host = self._pinned(len(batch), 2)
                 for k, j in enumerate(batch):
                     host[k, :2].copy_(j.args["losses"][:2], non_blocking=True)
                 st.synchronize()
+                lap("device")
                 for k, j in enumerate(batch):
                     j.result = host[k, :2].tolist()
 

@@ -90,6 +90,26 @@ def main() -> None:
         e1.record()
         st.synchronize()
     rows[f"step inside the {steps}-step epoch graph"] = 1e3 * e0.elapsed_time(e1) / 3 / steps
+    # the same graph after the GPU sat idle (what a federation's round looks like: votes and gossip between two fits)
+    import time
+
+    scratch = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    with torch.cuda.stream(st):
+        for idle_ms, warm in ((2, 0), (10, 0), (30, 0), (100, 0), (30, 1), (30, 5)):
+            ts = []
+            for _ in range(3):
+                st.synchronize()
+                time.sleep(idle_ms / 1e3)
+                t0 = time.perf_counter()
+                while warm and time.perf_counter() - t0 < warm / 1e3:  # keep the GPU busy for `warm` ms first
+                    scratch.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                g.replay()
+                e1.record()
+                st.synchronize()
+                ts.append(1e3 * e0.elapsed_time(e1) / steps)
+            rows[f"step in the epoch graph after {idle_ms} ms idle" + (f" + {warm} ms of memsets" if warm else "")] = sorted(ts)[1]
     crit = sum(v for k, v in rows.items() if not k.endswith("*") and not k.startswith("step"))
     print(f"groups={G} active={act} batch={a.batch}   (us per launch, all active slots together; * = side branch)")
     for k, v in rows.items():
