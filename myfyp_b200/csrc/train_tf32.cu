@@ -67,6 +67,19 @@ __device__ __forceinline__ void store_row32(float* o, const float (&v)[32]) {
     for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(o + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
   }
 }
+__device__ __forceinline__ void store_row8(float* o, const uint32_t (&b)[8]) {
+  if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+    stg256(o, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7]);
+  } else {
+    reinterpret_cast<uint4*>(o)[0] = make_uint4(b[0], b[1], b[2], b[3]);
+    reinterpret_cast<uint4*>(o)[1] = make_uint4(b[4], b[5], b[6], b[7]);
+  }
+}
+// column block `pos` (8 of the 32 columns) of a register array, without dynamic indexing
+__device__ __forceinline__ uint32_t pick8(const uint32_t (&a)[32], int pos, int j) {
+  const uint32_t lo = pos & 1 ? a[8 + j] : a[j], hi = pos & 1 ? a[24 + j] : a[16 + j];
+  return pos & 2 ? hi : lo;
+}
 __device__ __forceinline__ void store_codes32(uint8_t* ip, const uint32_t (&b)[8]) {
   if ((reinterpret_cast<uintptr_t>(ip) & 31) == 0) {
     stg256(ip, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7]);
@@ -95,6 +108,9 @@ __device__ __forceinline__ float tf32_rna(float x) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return __uint_as_float(r);
 }
+// cvt.rna.tf32.f32 is emulated on sm_100 (NaN test + add + mask); after a ReLU the operand is finite-or-inf and non-negative
+// (fmaxf(NaN, 0) = 0), where add + mask alone is the same rounding.  Returns the bits.
+__device__ __forceinline__ uint32_t tf32_rna_bits_nonneg(float x) { return (__float_as_uint(x) + 0x1000u) & 0x7fffe000u; }
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 
 __device__ __forceinline__ bool slot_live(const b2_cnn_bind& bd, int step, int batch) { return bd.active != 0 && (long long)step * batch < (long long)bd.n_samples; }
@@ -368,17 +384,20 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
           const int W = P.img_w, HW = P.img_h * W;
           const int n_img = row / HW, rem = row - n_img * HW, h = rem / W, wq = rem - h * W;
           const int pos = ((h & 1) << 1) | (wq & 1);
-          uint32_t pk[2] = {0u, 0u};
-          if (P.relu && P.out_lo == nullptr) {
+          // Phase 1: per column the window maximum and the winner's position, known to all four lanes of the window afterwards.
+          // Phase 2: the four lanes share the work - the lane at window position p converts and stores columns 8p .. 8p+7
+          // (one 32-byte sector of the pooled row, 8 winner codes).
+          uint32_t val[32];        // bits of the winning value (rounded variant: low 2 bits = 3 - winner position)
+          uint32_t pk[2] = {0u, 0u};  // other variants: 2 bits of winner position per column
+          const bool keyed = P.relu && P.out_lo == nullptr;
+          if (keyed) {
             // non-negative, stored tf32-rounded (13 low bits zero): value and position travel as ONE unsigned key, bits | (3 - pos);
             // a 2x2 max with "lowest position wins a tie" is two shuffles and two integer maxima per column
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
-              uint32_t k = (__float_as_uint(tf32_rna(v[e])) & 0x7fffffffu) | (uint32_t)(3 - pos);
+              uint32_t k = tf32_rna_bits_nonneg(v[e]) | (uint32_t)(3 - pos);
               k = max(k, __shfl_xor_sync(0xffffffffu, k, 1));
-              k = max(k, __shfl_xor_sync(0xffffffffu, k, W));
-              v[e] = __uint_as_float(k & ~3u);
-              pk[e >> 4] |= (3u - (k & 3u)) << (2 * (e & 15));
+              val[e] = max(k, __shfl_xor_sync(0xffffffffu, k, W));
             }
           } else if (P.relu) {
             // non-negative, kept exact (the consumer splits hi / lo): unsigned order is float order; the winner is the lowest
@@ -391,58 +410,54 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
               uint32_t cand = k == mx ? (uint32_t)pos : 4u;
               cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, 1));
               cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, W));
-              v[e] = __uint_as_float(mx);
+              val[e] = mx;
               pk[e >> 4] |= cand << (2 * (e & 15));
             }
-          } else
+          } else {
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            float a = v[e];
-            int pa = pos;
-            const float o1 = __shfl_xor_sync(0xffffffffu, a, 1);
-            bool take = (o1 > a) || (o1 == a && (pos ^ 1) < pa);
-            a = take ? o1 : a;
-            pa = take ? (pos ^ 1) : pa;
-            const float o2 = __shfl_xor_sync(0xffffffffu, a, W);
-            const int p2 = __shfl_xor_sync(0xffffffffu, pa, W);
-            take = (o2 > a) || (o2 == a && p2 < pa);
-            a = take ? o2 : a;
-            pa = take ? p2 : pa;
-            v[e] = a;
-            pk[e >> 4] |= (uint32_t)pa << (2 * (e & 15));
+            for (int e = 0; e < 32; ++e) {
+              float a = v[e];
+              int pa = pos;
+              const float o1 = __shfl_xor_sync(0xffffffffu, a, 1);
+              bool take = (o1 > a) || (o1 == a && (pos ^ 1) < pa);
+              a = take ? o1 : a;
+              pa = take ? (pos ^ 1) : pa;
+              const float o2 = __shfl_xor_sync(0xffffffffu, a, W);
+              const int p2 = __shfl_xor_sync(0xffffffffu, pa, W);
+              take = (o2 > a) || (o2 == a && p2 < pa);
+              a = take ? o2 : a;
+              pa = take ? p2 : pa;
+              val[e] = __float_as_uint(a);
+              pk[e >> 4] |= (uint32_t)pa << (2 * (e & 15));
+            }
           }
-          if (pos == 0 && row_ok) {
+          if (row_ok) {
             const int64_t pp = (int64_t)n_img * (HW >> 2) + (h >> 1) * (W >> 1) + (wq >> 1);
-            float* o = P.out + pp * P.ldo + nb;
-            if (P.out_lo != nullptr) {  // consumer is a 3xTF32 GEMM: exact hi / lo split
-              float* ol = P.out_lo + pp * P.ldo + nb;
-              float hi[32], lo[32];
+            const int64_t at = pp * P.ldo + nb + 8 * pos;
+            const uint32_t mypk = (pk[pos >> 1] >> (16 * (pos & 1))) & 0xffffu;
+            uint32_t hi[8], lo[8], cw[2] = {0u, 0u};
 #pragma unroll
-              for (int e = 0; e < 32; ++e) {
-                hi[e] = tf32_hi(v[e]);
-                lo[e] = tf32_rna(v[e] - hi[e]);
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t k = pick8(val, pos, j);
+              uint32_t code;
+              if (keyed) {
+                hi[j] = k & ~3u;
+                code = (3u - (k & 3u)) | (k > 3u ? 4u : 0u);
+              } else {
+                const float a = __uint_as_float(k);
+                code = ((mypk >> (2 * j)) & 3u) | (a > 0.f ? 4u : 0u);
+                if (P.out_lo != nullptr) {  // consumer is a 3xTF32 GEMM: exact hi / lo split
+                  hi[j] = k & 0xffffe000u;
+                  lo[j] = __float_as_uint(tf32_rna(a - __uint_as_float(hi[j])));
+                } else {
+                  hi[j] = __float_as_uint(tf32_rna(a));
+                }
               }
-              store_row32(o, hi);
-              store_row32(ol, lo);
-            } else {
-              float r[32];
-#pragma unroll
-              for (int e = 0; e < 32; ++e) r[e] = tf32_rna(v[e]);
-              store_row32(o, r);
+              cw[j >> 2] |= code << (8 * (j & 3));
             }
-            uint32_t bytes[8];
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              uint32_t wv = 0;
-#pragma unroll
-              for (int b = 0; b < 4; ++b) {
-                const int e = 4 * g + b;
-                const uint32_t code = ((pk[e >> 4] >> (2 * (e & 15))) & 3u) | (v[e] > 0.f ? 4u : 0u);
-                wv |= code << (8 * b);
-              }
-              bytes[g] = wv;
-            }
-            store_codes32(P.idx + pp * P.ldo + nb, bytes);
+            store_row8(P.out + at, hi);
+            if (P.out_lo != nullptr) store_row8(P.out_lo + at, lo);
+            *reinterpret_cast<uint2*>(P.idx + at) = make_uint2(cw[0], cw[1]);
           }
         } else {
           // EPI_UNPOOL / EPI_MASK: this row's 32 values are gradients of pooled outputs (pooled pixel pr, channels cbase..+32)
@@ -706,7 +721,7 @@ __device__ __forceinline__ void c0_build_patch_row(uint8_t* tile, const float* s
   c0_row_pixel(r, hh, w);
   float pv[32];
 #pragma unroll
-  for (int k = 0; k < 32; ++k) pv[k] = 0.f;
+  for (int k = 0; k < 32; ++k) pv[k] = (k == 9 * CIN || k == 9 * CIN + 1) ? 1.f : 0.f;  // the two ones meet the bias columns of conv0_fwd
 #pragma unroll
   for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
@@ -745,10 +760,17 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
   }
   if (warp == 4) tc::tmem_alloc<128>(&tmem_base_s);
   c0_zero_borders(sin, CIN, tid, C0_THREADS);
-  // weights [cout, KD] -> K-major swizzled rows padded to 32
+  // weights [cout, KD] -> K-major swizzled rows padded to 32.  Columns KD and KD+1 carry the bias (tf32 hi / lo parts) against two
+  // columns of ones in every patch row: the tensor core adds the bias, to fp32 accuracy, and the epilogue does not load it.
   for (int i = tid; i < cout * 32; i += C0_THREADS) {
     const int rowi = i >> 5, k = i & 31;
-    const float val = k < KD ? P.wm[rowi * KD + k] : 0.f;
+    float val = 0.f;
+    if (k < KD) {
+      val = P.wm[rowi * KD + k];
+    } else if (k < KD + 2) {
+      const float bv = bd.slab[P.bias_off + rowi], bh = tf32_hi(bv);
+      val = k == KD ? bh : tf32_rna(bv - bh);
+    }
     *reinterpret_cast<float*>(b_tile + tc::sw128_offset((uint32_t)rowi, (uint32_t)(k >> 2)) + (k & 3) * 4) = val;
   }
   tc::fence_proxy_async();
@@ -800,7 +822,6 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
   } else {
     // ================================ epilogue: bias + ReLU + 2x2 max-pool + winner code
     const int q = warp & 3;
-    const float* bias = bd.slab + P.bias_off;
     const int pos = ((lane >> 4) << 1) | (lane & 1);
     uint32_t it = 0;
     for (int t = blockIdx.x; t < P.tiles; t += gridDim.x, ++it) {
@@ -811,37 +832,29 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
       for (int cb = 0; cb < cout / 32; ++cb) {
         float v[32];
         tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + s * 64 + cb * 32, v);
-        // The stored activation is tf32-rounded (13 low bits zero) and non-negative after the ReLU, so value and window position
-        // travel as ONE unsigned key: bits | (3 - pos).  A 2x2 max with "lowest position wins a tie" is then two shuffles and two
-        // integer maxima per column.
+        // The bias came in through the GEMM (two spare K columns, see the prologue).  The stored activation is tf32-rounded (13 low
+        // bits zero) and non-negative after the ReLU, so value and window position travel as ONE unsigned key: bits | (3 - pos).
+        // A 2x2 max with "lowest position wins a tie" is then two shuffles and two integer maxima per column.
         uint32_t key[32];
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          const float a = tf32_rna(fmaxf(v[e] + __ldg(bias + cb * 32 + e), 0.f));
-          uint32_t k = (__float_as_uint(a) & 0x7fffffffu) | (uint32_t)(3 - pos);
+          uint32_t k = tf32_rna_bits_nonneg(fmaxf(v[e], 0.f)) | (uint32_t)(3 - pos);
           k = max(k, __shfl_xor_sync(0xffffffffu, k, 1));
-          k = max(k, __shfl_xor_sync(0xffffffffu, k, 16));
-          key[e] = k;
+          key[e] = max(k, __shfl_xor_sync(0xffffffffu, k, 16));
         }
-        if (pos == 0) {
+        // the four lanes of a window share the rest: the lane at position p stores columns 8p .. 8p+7 of the pooled row
+        {
           const int ph = (h0 >> 1) + (q >> 1), pw = ((q & 1) << 3) + ((lane & 15) >> 1);
-          const int64_t pp = ((int64_t)b * (H >> 1) + ph) * (C0_W >> 1) + pw;
-          float r[32];
+          const int64_t at = (((int64_t)b * (H >> 1) + ph) * (C0_W >> 1) + pw) * cout + cb * 32 + 8 * pos;
+          uint32_t r[8], cw[2] = {0u, 0u};
 #pragma unroll
-          for (int e = 0; e < 32; ++e) r[e] = __uint_as_float(key[e] & ~3u);
-          store_row32(P.out + pp * cout + cb * 32, r);
-          uint32_t bytes[8];
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            uint32_t wv = 0;
-#pragma unroll
-            for (int bb = 0; bb < 4; ++bb) {
-              const uint32_t k = key[4 * g + bb];
-              wv |= ((3u - (k & 3u)) | (k > 3u ? 4u : 0u)) << (8 * bb);
-            }
-            bytes[g] = wv;
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t k = pick8(key, pos, j);
+            r[j] = k & ~3u;
+            cw[j >> 2] |= ((3u - (k & 3u)) | (k > 3u ? 4u : 0u)) << (8 * (j & 3));
           }
-          store_codes32(P.idx + pp * cout + cb * 32, bytes);
+          store_row8(P.out + at, r);
+          *reinterpret_cast<uint2*>(P.idx + at) = make_uint2(cw[0], cw[1]);
         }
       }
       tc::fence_before_sync();
