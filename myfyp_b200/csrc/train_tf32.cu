@@ -162,10 +162,11 @@ struct Cfg {
   static constexpr int STAGE_BYTES = OPS * (A_BYTES + B_BYTES);
   // LEAN (kernels with a light epilogue): 3 stages, 3 CTAs per SM - these kernels are bound by the latency of their small TMA
   // boxes, not by bandwidth, so more resident CTAs is what buys throughput
-  static constexpr int STAGES = LEAN ? 3 : 4;
+  static constexpr int STAGES = LEAN ? (X3 ? 3 : 2) : 4;
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
-  static constexpr int CTAS_PER_SM = X3 ? 1 : (LEAN ? 3 : 2);
-  static constexpr uint32_t TMEM_COLS = (uint32_t)(ACC_STAGES * BN) < 32u ? 32u : (uint32_t)(ACC_STAGES * BN);
+  static constexpr int CTAS_PER_SM = X3 ? 1 : (LEAN ? 4 : 2);
+  static constexpr uint32_t ACC_COLS = (uint32_t)(ACC_STAGES * BN);
+  static constexpr uint32_t TMEM_COLS = ACC_COLS <= 32u ? 32u : ACC_COLS <= 64u ? 64u : ACC_COLS <= 128u ? 128u : ACC_COLS <= 256u ? 256u : 512u;
 };
 
 // ------------------------------------------------------------------------------------------------ grouped tf32 GEMM / implicit conv
@@ -250,9 +251,15 @@ __global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CT
             int nblk = 0;
 #pragma unroll
             for (int j = 0; j < BN / 32; ++j) nblk += (n0 + 32 * j < N) ? 1 : 0;
-            tc::mbar_arrive_expect_tx(&full_bar[s], A_BYTES + nblk * (BK * 128));
+            // likewise the 32-row blocks of A beyond M (cout = 64: half of the 128-row tile): whatever the shared memory holds there
+            // only reaches accumulator rows that are never stored
+            int ablk = 0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) tc::tma_load_2d(a_dst + j * (BK * 128), &P.ta, &full_bar[s], m0 + 32 * j, k0);
+            for (int j = 0; j < 4; ++j) ablk += (m0 + 32 * j < M) ? 1 : 0;
+            tc::mbar_arrive_expect_tx(&full_bar[s], (ablk + nblk) * (BK * 128));
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (m0 + 32 * j < M) tc::tma_load_2d(a_dst + j * (BK * 128), &P.ta, &full_bar[s], m0 + 32 * j, k0);
             int n_img, h0;
             pixel_tile(P, kb0 + kb, n_img, h0);
 #pragma unroll
@@ -637,9 +644,15 @@ __global__ void __launch_bounds__(GG_THREADS, 1) wgrad_wide_kernel(const Problem
           tc::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cb * 32), v);
           if (row < M) {
             float* o = P.out + (int64_t)row * P.ldo + nb;
+            if (nb + 32 <= N && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
 #pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+              for (int e = 0; e < 32; e += 4)
+                if (v[e] != 0.f || v[e + 1] != 0.f || v[e + 2] != 0.f || v[e + 3] != 0.f) red_add_v4(o + e, v[e], v[e + 1], v[e + 2], v[e + 3]);
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (nb + e < N && v[e] != 0.f) atomicAdd(o + e, v[e]);
+            }
           }
         }
       }
@@ -1759,9 +1772,11 @@ void* b2_cnn_plan_create(const b2_cnn_desc* d, void* workspace, int64_t bytes, v
         P.M = cout; P.N = kdim; P.K = pixels; P.batch = B;
         P.tiles_m = (cout + BM - 1) / BM; P.tiles_n = (kdim + 63) / 64;
         const int total_k = pixels / BK;
-        // K splits: as many as fill this slot's share of the chip in ONE wave (3 resident CTAs per SM), at least 4 k-blocks each
+        // K splits: as many as fill this slot's share of the chip in ONE wave (3 resident CTAs per SM), at least 4 k-blocks each.
+        // (96-column tiles - 9 * cin is a whole number of them, dz is re-read 3x instead of 4.5x - fit only 2 CTAs per SM and
+        // measured 1.9x SLOWER: these kernels live on the number of resident CTAs, not on bytes.)
         const int out_tiles = ((cout + BM - 1) / BM) * ((kdim + 63) / 64);
-        int splits = (p->sms * 3 / G) / out_tiles;
+        int splits = (p->sms * 4 / G) / out_tiles;
         if (getenv("B2_T32_WIDE_WGRAD") != nullptr) {  // one CTA per (cout tile, 288-column group, K split)
           const int wgroups = (kdim + 32 * WW_NB - 1) / (32 * WW_NB) * ((cout + BM - 1) / BM);
           int want = (p->sms + G - 1) / G;
