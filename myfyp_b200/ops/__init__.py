@@ -118,8 +118,48 @@ def accumulate(acc: torch.Tensor, src: torch.Tensor, w: float, beta: float = 1.0
 
 
 # ====================================================================== A5: median / trimmed mean
-def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Optional[torch.device] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Coordinate-wise median (``trim=None``; even K -> mean of the two middle values, like NumPy) or trimmed mean."""
+SHARD_MIN_ELEMS = 1 << 18  # below this a second GPU's launch + event costs more than its share of the reads saves
+
+
+def shard_devices(slabs: Sequence[torch.Tensor], device: torch.device, force: bool = False) -> List[torch.device]:
+    """GPUs of this process that take a coordinate shard of a K-way reduction whose result goes to ``device``: the destination
+    plus every other GPU that holds one of the inputs (SURVEY 8, A5/A6 "coordinate-sharded across GPUs").
+
+    Sharding pays when the single launch would pull most of its K inputs through ONE GPU's NVLink ingress: with the inputs spread
+    over g GPUs that ingress carries (g-1)/g of K models unsharded, but only 2 (g-1)/g of ONE model sharded (the slices it reads
+    plus the slices the others store into it).  With two GPUs the two are about equal and the second launch costs more than it
+    saves (measured on 2 x B200, 4 x 64 MB: 280 us in one launch, 320 us sharded; profiles/peer_pull_timing.txt), so the
+    automatic choice shards from three GPUs on; ``force`` shards whenever a second GPU holds an input."""
+    if device.type != "cuda" or slabs[0].numel() < SHARD_MIN_ELEMS:
+        return [device]
+    others = sorted({s.device.index for s in slabs if s.is_cuda and s.device != device})
+    if not others or (len(others) < 2 and not force):
+        return [device]
+    return [torch.device("cuda", i) for i in others] + [device]  # the destination launches last: the others are already running
+
+
+def _shard_bounds(n: int, parts: int, align: int = 1024) -> List[int]:
+    per = ((n + parts - 1) // parts + align - 1) // align * align
+    return [min(i * per, n) for i in range(parts + 1)]
+
+
+def _join_shards(workers: Sequence[torch.device], device: torch.device) -> None:
+    """``device``'s stream waits for what the other shard workers just queued (one event each, no host synchronisation)."""
+    for w in workers:
+        if w != device:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(w))
+            torch.cuda.current_stream(device).wait_event(ev)
+
+
+def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Optional[torch.device] = None, out: Optional[torch.Tensor] = None,
+           shard: Optional[bool] = None) -> torch.Tensor:
+    """Coordinate-wise median (``trim=None``; even K -> mean of the two middle values, like NumPy) or trimmed mean.
+
+    When the contributors live on several GPUs of this process the coordinates are sharded over those GPUs: each one sorts ONE
+    contiguous slice - reading its K inputs in place over NVLink - and stores the result straight into ``out`` on ``device``
+    (peer stores), so the K x model bytes arrive over all the GPUs' links instead of one.  ``shard``: None = automatic (three or
+    more GPUs, see :func:`shard_devices`), True = whenever a second GPU holds an input, False = one launch on ``device``."""
     device = device or pick_device(slabs)
     slabs = _same_place(slabs, device)
     k, n = len(slabs), slabs[0].numel()
@@ -129,12 +169,23 @@ def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Op
         out = torch.empty(n, dtype=torch.float32, device=device)
     if device.type == "cuda":
         lib = native.load()
-        with native.device_guard(device):
-            native.check(
-                lib.b2_median(native.ptr(out), native.ptr_array(slabs), k, ctypes.c_int(-1 if trim is None else trim), ctypes.c_int64(n), native.stream_ptr(device)),
-                "b2_median",
-            )
-        native.count_launch()
+        workers = [device] if shard is False else shard_devices(slabs, device, force=bool(shard))
+        bounds = _shard_bounds(n, len(workers))
+        for w, lo, hi in zip(workers, bounds[:-1], bounds[1:]):
+            if hi <= lo:
+                continue
+            if w != device:
+                order_after_producers(list(slabs) + [out], w)
+            ptrs = native.ptr_array(slabs)
+            for i, t in enumerate(slabs):
+                ptrs[i] = t.data_ptr() + 4 * lo
+            with native.device_guard(w):
+                native.check(
+                    lib.b2_median(ctypes.c_void_p(out.data_ptr() + 4 * lo), ptrs, k, ctypes.c_int(-1 if trim is None else trim), ctypes.c_int64(hi - lo), native.stream_ptr(w)),
+                    "b2_median",
+                )
+            native.count_launch()
+        _join_shards(workers, device)
     else:
         st = torch.sort(torch.stack([s.to(torch.float32) for s in slabs]), dim=0).values
         if trim is None:
@@ -145,7 +196,7 @@ def median(slabs: Sequence[torch.Tensor], trim: Optional[int] = None, device: Op
 
 
 # ====================================================================== A6/A7: Krum
-def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None, passes: int = 3) -> torch.Tensor:
+def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device] = None, passes: int = 3, shard: Optional[bool] = None) -> torch.Tensor:
     """K x K matrix of squared L2 distances.  CUDA: centred Gram matrix on tcgen05 (A6) + d = Gii+Gjj-2Gij.
 
     A Byzantine update may contain NaN / Inf / values whose square overflows.  Such a model is put at distance +inf from every
@@ -157,7 +208,7 @@ def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device
     bad: List[int] = []
     for ref in range(k):
         order = [ref] + [i for i in range(k) if i != ref]
-        g = _centred_gram([slabs[i] for i in order], device, passes)
+        g = _centred_gram([slabs[i] for i in order], device, passes, shard)
         # a broken centre (NaN / Inf, or so large that every difference overflows) shows as a non-finite own entry or as a
         # majority of the other models looking broken
         if bool(torch.isfinite(g[0, 0])) and (k <= 2 or int((~torch.isfinite(torch.diagonal(g)[1:])).sum()) * 2 <= k - 1):
@@ -180,19 +231,37 @@ def pairwise_sqdist(slabs: Sequence[torch.Tensor], device: Optional[torch.device
     return dist.fill_diagonal_(0.0).float()
 
 
-def _centred_gram(slabs: Sequence[torch.Tensor], device: torch.device, passes: int) -> torch.Tensor:
+def _centred_gram(slabs: Sequence[torch.Tensor], device: torch.device, passes: int, shard: Optional[bool] = None) -> torch.Tensor:
     """fp64 view of G[i][j] = <slab_i - slab_0, slab_j - slab_0>."""
     k, n = len(slabs), slabs[0].numel()
     if device.type == "cuda":
         if k > MAX_K:
             raise ValueError(f"krum over {k} models: at most {MAX_K}")
         lib = native.load()
-        gram = torch.empty(MAX_K * MAX_K, dtype=torch.float32, device=device)
-        ws = _krum_workspace(device)
-        with native.device_guard(device):
-            native.check(lib.b2_krum_gram(native.ptr(gram), native.ptr_array(slabs), k, ctypes.c_int64(n), native.ptr(ws), ctypes.c_int(passes), native.stream_ptr(device)), "b2_krum_gram")
-        native.count_launch()
-        return gram.view(MAX_K, MAX_K)[:k, :k].double()
+        # coordinate-sharded over the GPUs that hold the models: a Gram matrix is a sum over coordinates, so every GPU forms the
+        # partial K x K matrix of ONE slice (centred on the same model) and the destination adds the K x K partials
+        workers = [device] if shard is False else shard_devices(slabs, device, force=bool(shard))
+        bounds = _shard_bounds(n, len(workers))
+        parts = []
+        for w, lo, hi in zip(workers, bounds[:-1], bounds[1:]):
+            if hi <= lo:
+                continue
+            if w != device:
+                order_after_producers(slabs, w)
+            gram = torch.empty(MAX_K * MAX_K, dtype=torch.float32, device=w)
+            ws = _krum_workspace(w)
+            ptrs = native.ptr_array(slabs)
+            for i, t in enumerate(slabs):
+                ptrs[i] = t.data_ptr() + 4 * lo
+            with native.device_guard(w):
+                native.check(lib.b2_krum_gram(native.ptr(gram), ptrs, k, ctypes.c_int64(hi - lo), native.ptr(ws), ctypes.c_int(passes), native.stream_ptr(w)), "b2_krum_gram")
+            native.count_launch()
+            parts.append(gram)
+        _join_shards(workers, device)
+        total = parts[0].view(MAX_K, MAX_K)[:k, :k].double()
+        for g in parts[1:]:
+            total = total + g.to(device).view(MAX_K, MAX_K)[:k, :k].double()
+        return total
     m = torch.stack([s.double() for s in slabs])
     m = m - m[0:1]
     return (m @ m.T).float().double()  # through fp32 like the kernel's result: values whose square overflows fp32 count as broken

@@ -422,6 +422,37 @@ def test_fedavg_pulls_from_peer_gpus():
     torch.testing.assert_close(med, (st[1] + st[2]) / 2, rtol=1e-6, atol=1e-6)
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_median_and_krum_gram_are_sharded_by_coordinate_over_the_gpus_that_hold_the_models():
+    """with contributors on two GPUs each GPU reduces one slice of the coordinates (peer reads, peer stores into
+    the destination); the result equals the single-launch one bit for bit (median) / to fp32 summation order (Gram)."""
+    from myfyp_b200 import ops
+
+    n = (1 << 20) + 1536 + 3  # not a multiple of the shard alignment
+    g = torch.Generator().manual_seed(3)
+    slabs = [torch.randn(n, generator=g).to(f"cuda:{i % 2}") for i in range(7)]
+    dev0 = torch.device("cuda", 0)
+    assert [d.index for d in ops.shard_devices(slabs, dev0, force=True)] == [1, 0]
+    assert [d.index for d in ops.shard_devices(slabs, dev0)] == [0]  # automatic: from three GPUs on
+    before = ops.native.launches()
+    sharded = ops.median(slabs, device=dev0, shard=True)
+    assert ops.native.launches() - before == 2  # one launch per GPU
+    single = ops.median(slabs, device=dev0, shard=False)
+    torch.cuda.synchronize()
+    assert torch.equal(sharded, single)
+    ref = torch.stack([s.to(dev0) for s in slabs]).median(dim=0).values
+    torch.testing.assert_close(sharded, ref, rtol=0, atol=0)
+    tm = ops.median(slabs, trim=2, device=torch.device("cuda", 1), shard=True)
+    st = torch.stack([s.to("cuda:1") for s in slabs]).sort(dim=0).values
+    torch.testing.assert_close(tm, st[2:5].mean(dim=0), rtol=1e-5, atol=1e-6)
+    slabs = [s[: n - 3] for s in slabs]  # the Gram kernel takes whole 16-byte groups (slab layouts guarantee them)
+    dist = ops.pairwise_sqdist(slabs, device=dev0, shard=True)
+    big = torch.stack([s.to(dev0).double() for s in slabs])
+    want = torch.cdist(big, big) ** 2
+    torch.testing.assert_close(dist.double(), want, rtol=1e-4, atol=1e-2)
+    assert [int(i) for i in dist.sum(1).argsort()] == [int(i) for i in want.sum(1).argsort()]
+
+
 @pytest.mark.parametrize("world,n", [(2, 4096), (4, 235264), (8, 1 << 20), (3, 1000 * 4)])
 def test_twoshot_fedavg_emulated_ranks(dev, world, n):
     """The fused reduce-scatter + all-gather kernel with all ranks in one launch (the single-GPU way to run ranks that wait on each other)."""

@@ -1,4 +1,6 @@
 #!/usr/bin/env bash
+# NOTE: compute-sanitizer is CLOSED on the B200 pool of this project (profiles/sanitizer/README.md); tools/bounds_check.py is the
+# guard-band stand-in that runs there.  On a box where the tool is open:
 # compute-sanitizer targets for the kernels.  ONE tool per invocation (and per gpurun call): running several
 # tools back to back in one call has left B200 boxes unusable (B200_PROFILING.md), so pick one:
 #
