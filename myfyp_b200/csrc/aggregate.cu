@@ -111,29 +111,6 @@ __device__ __forceinline__ void bitonic_sort(float (&v)[KPAD]) {
   }
 }
 
-// Batcher's odd-even merge sort: the same depth as the bitonic network with ~20 % fewer compare-exchanges at 32 / 64 inputs
-// (191 / 543 against 240 / 672); all indices are compile-time constants after unrolling.
-template <int KPAD>
-__device__ __forceinline__ void oddeven_merge_sort(float (&v)[KPAD]) {
-#pragma unroll
-  for (int p = 1; p < KPAD; p <<= 1) {
-#pragma unroll
-    for (int k = p; k >= 1; k >>= 1) {
-#pragma unroll
-      for (int j = k % p; j + k < KPAD; j += 2 * k) {
-#pragma unroll
-        for (int i = 0; i < k; ++i) {
-          if (i + j + k < KPAD && (i + j) / (2 * p) == (i + j + k) / (2 * p)) {
-            const float lo = fminf(v[i + j], v[i + j + k]), hi = fmaxf(v[i + j], v[i + j + k]);
-            v[i + j] = lo;
-            v[i + j + k] = hi;
-          }
-        }
-      }
-    }
-  }
-}
-
 template <int KPAD>
 __device__ __forceinline__ float pick_median(const float (&v)[KPAD], int K, int trim) {
   float r = 0.f;
@@ -174,6 +151,28 @@ __global__ void __launch_bounds__(256) median4_kernel(float4* __restrict__ out, 
   }
 }
 
+// Two coordinates per thread (KPAD = 32): 8-byte loads, 64 values in registers.
+template <int KPAD>
+__global__ void __launch_bounds__(256) median2_kernel(float2* __restrict__ out, const __grid_constant__ PtrTable srcs, int K, int trim, int64_t n2) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+    float a[KPAD], b[KPAD];
+#pragma unroll
+    for (int k = 0; k < KPAD; ++k) {
+      if (k < K) {
+        float2 t;
+        asm volatile("ld.global.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(t.x), "=f"(t.y) : "l"(reinterpret_cast<const float2*>(srcs.p[k]) + i));
+        a[k] = t.x; b[k] = t.y;
+      } else {
+        a[k] = b[k] = __int_as_float(0x7f800000);
+      }
+    }
+    bitonic_sort<KPAD>(a);
+    bitonic_sort<KPAD>(b);
+    out[i] = make_float2(pick_median<KPAD>(a, K, trim), pick_median<KPAD>(b, K, trim));
+  }
+}
+
 template <int KPAD>
 __global__ void __launch_bounds__(KPAD >= 64 ? 128 : 256) median_kernel(float* __restrict__ out, const __grid_constant__ PtrTable srcs, int K, int trim, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -181,8 +180,9 @@ __global__ void __launch_bounds__(KPAD >= 64 ? 128 : 256) median_kernel(float* _
     float v[KPAD];
 #pragma unroll
     for (int k = 0; k < KPAD; ++k) v[k] = (k < K) ? ld_stream1(srcs.p[k] + i) : __int_as_float(0x7f800000);
-    if constexpr (KPAD >= 32) oddeven_merge_sort<KPAD>(v);
-    else bitonic_sort<KPAD>(v);
+    // (Batcher's odd-even merge network has 20 % fewer compare-exchanges at 32 / 64 inputs, but nvcc does not resolve its index
+    // arithmetic at compile time: v[] went to local memory and K = 64 ran 4.6x slower than this bitonic network.)
+    bitonic_sort<KPAD>(v);
     out[i] = pick_median<KPAD>(v, K, trim);
   }
 }
@@ -320,6 +320,11 @@ int b2_median(float* out, const void* const* srcs, int K, int trim, int64_t n, v
   B2_MEDIAN4_CASE(8)
   B2_MEDIAN4_CASE(16)
 #undef B2_MEDIAN4_CASE
+  if (vec4 && K <= 32) {
+    median2_kernel<32><<<stream_grid(n / 2, 256, 8), 256, 0, s>>>(reinterpret_cast<float2*>(out), pt, K, trim, n / 2);
+    B2_LAUNCH_CHECK("median2_kernel");
+    return 0;
+  }
 #define B2_MEDIAN_CASE(KP, TH)                                                             \
   if (K <= KP) {                                                                           \
     median_kernel<KP><<<stream_grid(n, TH, 8), TH, 0, s>>>(out, pt, K, trim, n);           \

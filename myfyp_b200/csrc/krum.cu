@@ -39,6 +39,9 @@ constexpr int GR_ACCS = 8;                          // TMEM accumulators used ro
 constexpr int GR_MAX_CTAS = 296;
 constexpr int GR_HEADER = 256;
 
+// UPT = float4 items per producer thread and stage = ceil(K / 8): a thread's items are the SAME 4 coordinates of UPT different
+// models (item q = u * 256 + tid -> row q / 32, coordinate group q % 32 = tid % 32), so the reference chunk is loaded once.
+template <int UPT>
 __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restrict__ gram, const __grid_constant__ PtrTable srcs, int K, int64_t n, int passes,
                                                                    unsigned int* __restrict__ counter, float* __restrict__ partials) {
   extern __shared__ uint8_t smem_raw[];
@@ -52,7 +55,7 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
 
   if (tid == 0) {
     for (int s = 0; s < GR_STAGES; ++s) {
-      tc::mbar_init(&full_bar[s], GR_PRODUCERS);
+      tc::mbar_init(&full_bar[s], GR_PRODUCERS / 32);  // one arrival per producer warp
       tc::mbar_init(&empty_bar[s], 1);
     }
     tc::mbar_init(&done_bar, 1);
@@ -72,50 +75,61 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
 
   if (warp < 8) {
     // ================================ producers: pull, centre, split, swizzle-store
-    const int items = K * (GR_CC / 4);  // float4 items per stage
+    // The loads of stage it+1 are issued BEFORE stage it is converted and stored (two register buffers): with one stage of loads
+    // in flight per CTA the kernel ran at the latency of a DRAM round trip per 128 coordinates (1.4 TB/s at K = 32).
     const float* ref = srcs.p[0];
-    for (int64_t it = 0; it < my_chunks; ++it) {
-      const int s = (int)(it % GR_STAGES);
-      const uint32_t ph = (uint32_t)((it / GR_STAGES) & 1);
-      tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-      const int64_t c0 = (blockIdx.x + it * gridDim.x) * (int64_t)GR_CC;
+    const int j = tid & 31, row0 = tid >> 5;
+    auto issue = [&](int64_t it, float4 (&v)[UPT], float4& r) {
+      const int64_t c = (blockIdx.x + it * gridDim.x) * (int64_t)GR_CC + 4 * j;
+      const bool in = c < n;  // n % 4 == 0 is enforced by the host wrapper
+      r = in ? __ldg(reinterpret_cast<const float4*>(ref + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < UPT; ++u) {
+        const int row = row0 + 8 * u;
+        v[u] = (in && row < K) ? ld_stream(reinterpret_cast<const float4*>(srcs.p[row] + c)) : r;  // r - r = 0 for rows that do not exist
+      }
+    };
+    auto convert = [&](int s, const float4 (&v)[UPT], const float4& r) {
       uint8_t* hi_tile = tiles + s * GR_STAGE_BYTES;
       uint8_t* lo_tile = hi_tile + GR_TILE_BYTES;
-      for (int q0 = 0; q0 < items; q0 += 4 * GR_PRODUCERS) {
-        float4 v[4], r[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int q = q0 + u * GR_PRODUCERS + tid;
-          const int row = q >> 5, j = q & 31;
-          const int64_t c = c0 + 4 * j;
-          v[u] = r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (q < items && c < n) {  // n % 4 == 0 is enforced by the host wrapper
-            v[u] = ld_stream(reinterpret_cast<const float4*>(srcs.p[row] + c));
-            r[u] = __ldg(reinterpret_cast<const float4*>(ref + c));
+      for (int u = 0; u < UPT; ++u) {
+        const int row = row0 + 8 * u;
+        if (row < K) {
+          const float d[4] = {v[u].x - r.x, v[u].y - r.y, v[u].z - r.z, v[u].w - r.w};
+          float4 h, l;
+          float* hp = &h.x;
+          float* lp = &l.x;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            hp[e] = __uint_as_float(__float_as_uint(d[e]) & 0xffffe000u);  // tf32 keeps 10 mantissa bits
+            lp[e] = d[e] - hp[e];
           }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int q = q0 + u * GR_PRODUCERS + tid;
-          if (q < items) {
-            const int row = q >> 5, j = q & 31;
-            const float d[4] = {v[u].x - r[u].x, v[u].y - r[u].y, v[u].z - r[u].z, v[u].w - r[u].w};
-            float4 h, l;
-            float* hp = &h.x;
-            float* lp = &l.x;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              hp[e] = __uint_as_float(__float_as_uint(d[e]) & 0xffffe000u);  // tf32 keeps 10 mantissa bits
-              lp[e] = d[e] - hp[e];
-            }
-            const uint32_t off = (uint32_t)(j >> 3) * GR_ATOM_BYTES + tc::sw128_offset((uint32_t)row, (uint32_t)(j & 7));
-            *reinterpret_cast<float4*>(hi_tile + off) = h;
-            *reinterpret_cast<float4*>(lo_tile + off) = l;
-          }
+          const uint32_t off = (uint32_t)(j >> 3) * GR_ATOM_BYTES + tc::sw128_offset((uint32_t)row, (uint32_t)(j & 7));
+          *reinterpret_cast<float4*>(hi_tile + off) = h;
+          *reinterpret_cast<float4*>(lo_tile + off) = l;
         }
       }
+    };
+    auto publish = [&](int64_t it, const float4 (&v)[UPT], const float4& r) {
+      const int s = (int)(it % GR_STAGES);
+      tc::mbar_wait(&empty_bar[s], (uint32_t)((it / GR_STAGES) & 1) ^ 1u);
+      convert(s, v, r);
+      // every lane publishes its stores to the async proxy, the warp meets, ONE lane arrives: 8 arrivals per stage instead of
+      // 256 serialised updates of the same barrier word
       tc::fence_proxy_async();
-      tc::mbar_arrive(&full_bar[s]);
+      __syncwarp();
+      if ((tid & 31) == 0) tc::mbar_arrive(&full_bar[s]);
+    };
+    float4 va[UPT], vb[UPT], ra, rb;
+    if (my_chunks > 0) issue(0, va, ra);
+    for (int64_t it = 0; it < my_chunks; it += 2) {
+      if (it + 1 < my_chunks) issue(it + 1, vb, rb);
+      publish(it, va, ra);
+      if (it + 1 < my_chunks) {
+        if (it + 2 < my_chunks) issue(it + 2, va, ra);
+        publish(it + 1, vb, rb);
+      }
     }
   } else if (tc::elect_one()) {
     // ================================ MMA issuer (one thread)
@@ -183,12 +197,39 @@ __global__ void __launch_bounds__(GR_THREADS, 1) krum_gram_kernel(float* __restr
   }
   __syncthreads();
   if (is_last_s) {
+    // fixed summation order (deterministic), 16 bytes per load, four partials in flight per thread, and only the K x K corner is
+    // read at all: the plain "one float, one partial at a time" loop cost 0.35 ms on its own (148 dependent L2 round trips x 14)
     __threadfence();
-    for (int o = tid; o < GR_ROWS * GR_ROWS; o += GR_THREADS) {
-      float acc = 0.f;
-      for (unsigned int b = 0; b < gridDim.x; ++b) acc += __ldcg(partials + (size_t)b * (GR_ROWS * GR_ROWS) + o);
-      const int i = o / GR_ROWS, j = o % GR_ROWS;
-      gram[o] = (i < K && j < K) ? acc : 0.f;
+    for (int o4 = tid; o4 < GR_ROWS * GR_ROWS / 4; o4 += GR_THREADS) {
+      const int i = (4 * o4) / GR_ROWS, j = (4 * o4) % GR_ROWS;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < K && j < K) {
+        const float4* p = reinterpret_cast<const float4*>(partials) + o4;
+        const size_t stride4 = GR_ROWS * GR_ROWS / 4;
+        float4 a[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned int b = 0;
+        for (; b + 4 <= gridDim.x; b += 4) {
+          float4 t[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) t[u] = __ldcg(p + (size_t)(b + u) * stride4);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) a[u].x += t[u].x, a[u].y += t[u].y, a[u].z += t[u].z, a[u].w += t[u].w;
+        }
+        for (; b < gridDim.x; ++b) {
+          const float4 t = __ldcg(p + (size_t)b * stride4);
+          a[0].x += t.x, a[0].y += t.y, a[0].z += t.z, a[0].w += t.w;
+        }
+        acc.x = (a[0].x + a[1].x) + (a[2].x + a[3].x);
+        acc.y = (a[0].y + a[1].y) + (a[2].y + a[3].y);
+        acc.z = (a[0].z + a[1].z) + (a[2].z + a[3].z);
+        acc.w = (a[0].w + a[1].w) + (a[2].w + a[3].w);
+        if (j + 1 >= K) acc.y = 0.f;
+        if (j + 2 >= K) acc.z = 0.f;
+        if (j + 3 >= K) acc.w = 0.f;
+      }
+      reinterpret_cast<float4*>(gram)[o4] = acc;
     }
     if (tid == 0) *counter = 0u;  // ready for the next call
   }
@@ -232,6 +273,14 @@ __global__ void __launch_bounds__(64) krum_select_kernel(const float* __restrict
   }
 }
 
+
+static void launch_gram(int grid, cudaStream_t st, float* gram, const PtrTable& pt, int K, int64_t n, int passes, unsigned int* counter, float* partials) {
+  if (K <= 8) krum_gram_kernel<1><<<grid, GR_THREADS, GR_SMEM, st>>>(gram, pt, K, n, passes, counter, partials);
+  else if (K <= 16) krum_gram_kernel<2><<<grid, GR_THREADS, GR_SMEM, st>>>(gram, pt, K, n, passes, counter, partials);
+  else if (K <= 32) krum_gram_kernel<4><<<grid, GR_THREADS, GR_SMEM, st>>>(gram, pt, K, n, passes, counter, partials);
+  else krum_gram_kernel<8><<<grid, GR_THREADS, GR_SMEM, st>>>(gram, pt, K, n, passes, counter, partials);
+}
+
 }  // namespace b2
 
 using namespace b2;
@@ -264,7 +313,10 @@ int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* w
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+    B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
     attr_set[dev] = true;
   }
   const int64_t chunks = (n + GR_CC - 1) / GR_CC;
@@ -273,7 +325,7 @@ int b2_krum_gram(float* gram, const void* const* srcs, int K, int64_t n, void* w
   if (chunks < grid) grid = (int)chunks;
   unsigned int* counter = static_cast<unsigned int*>(workspace);
   float* partials = reinterpret_cast<float*>(static_cast<char*>(workspace) + GR_HEADER);
-  krum_gram_kernel<<<grid, GR_THREADS, GR_SMEM, static_cast<cudaStream_t>(stream)>>>(gram, pt, K, n, passes, counter, partials);
+  launch_gram(grid, static_cast<cudaStream_t>(stream), gram, pt, K, n, passes, counter, partials);
   B2_LAUNCH_CHECK("krum_gram_kernel");
   return 0;
 }
@@ -345,7 +397,10 @@ int b2_krum_gram_static(float* gram, const void* const* srcs, int K, int64_t n, 
     if (scratch_ptr[dev] == nullptr) {
       void* p = nullptr;
       B2_CUDA(cudaGetSymbolAddress(&p, g_static_gram_scratch));
-      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
+      B2_CUDA(cudaFuncSetAttribute(krum_gram_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, GR_SMEM));
       scratch_ptr[dev] = p;
     }
   }
@@ -356,7 +411,7 @@ int b2_krum_gram_static(float* gram, const void* const* srcs, int K, int64_t n, 
   if (grid > B2_STATIC_GRAM_CTAS) grid = B2_STATIC_GRAM_CTAS;
   if (chunks < grid) grid = (int)chunks;
   B2_CUDA(cudaMemsetAsync(base, 0, GR_HEADER, s));  // the completion counter must start at zero
-  krum_gram_kernel<<<grid, GR_THREADS, GR_SMEM, s>>>(gram, pt, K, n, passes, reinterpret_cast<unsigned int*>(base), reinterpret_cast<float*>(base + GR_HEADER));
+  launch_gram(grid, s, gram, pt, K, n, passes, reinterpret_cast<unsigned int*>(base), reinterpret_cast<float*>(base + GR_HEADER));
   B2_LAUNCH_CHECK("krum_gram_kernel(static scratch)");
   return 0;
 }

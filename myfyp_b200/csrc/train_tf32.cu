@@ -764,7 +764,7 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
 
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) {
-      tc::mbar_init(&full_bar[s], 128);
+      tc::mbar_init(&full_bar[s], 4);  // one arrival per producer warp
       tc::mbar_init(&empty_bar[s], 1);
       tc::mbar_init(&acc_full[s], 1);
       tc::mbar_init(&acc_empty[s], 4);
@@ -812,8 +812,10 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_fwd_kernel(const Conv0Pro
       if (tnn < P.tiles) smp_next = c0_sample(bd, step, P.batch, tnn / tiles_per_img);
       tc::mbar_wait(&empty_bar[s], ((it >> 1) & 1u) ^ 1u);
       c0_build_patch_row<CIN, false>(a_tiles + s * A_BYTES, sn, tid);
+      // every lane publishes its stores to the async proxy, the warp meets, one lane arrives (4 barrier updates per tile, not 128)
       tc::fence_proxy_async();
-      tc::mbar_arrive(&full_bar[s]);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&full_bar[s]);
     }
   } else if (warp == 4) {
     if (tc::elect_one()) {
@@ -906,7 +908,7 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_wgrad_kernel(const Conv0P
 
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) {
-      tc::mbar_init(&full_bar[s], 128);
+      tc::mbar_init(&full_bar[s], 4);  // one arrival per producer warp
       tc::mbar_init(&empty_bar[s], 1);
     }
     tc::mbar_init(&done_bar, 1);
@@ -975,7 +977,8 @@ __global__ void __launch_bounds__(C0_THREADS, 2) conv0_wgrad_kernel(const Conv0P
       if (tn < P.tiles) fetch(tn, cur);  // in flight while the patch row is built and the next input rows arrive
       c0_build_patch_row<CIN, true>(b_tiles + s * A_BYTES, sn, tid);
       tc::fence_proxy_async();
-      tc::mbar_arrive(&full_bar[s]);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&full_bar[s]);
     }
   } else if (warp == 4) {
     if (tc::elect_one()) {
