@@ -26,6 +26,9 @@ import sys
 import threading
 import time
 
+if os.environ.get("B2_SWITCH_INTERVAL"):  # experiment: interpreter-lock hand-off latency between node threads (default 5 ms)
+    sys.setswitchinterval(float(os.environ["B2_SWITCH_INTERVAL"]))
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 

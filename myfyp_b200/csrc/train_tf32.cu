@@ -155,16 +155,20 @@ __device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane) {
   return w[0];
 }
 
-template <bool X3, int BN, bool LEAN = false>
+__host__ __device__ constexpr int cfg_mode(int epi) { return epi == EPI_ATOMIC ? 1 : ((epi == EPI_UNPOOL || epi == EPI_MASK) ? 2 : 0); }
+// MODE 0: 4 stages, 2 CTAs per SM.  1 (split-K kernels with the atomic epilogue): 2 stages, 4 CTAs.  2 (convolutions with the
+// un-pool / mask epilogues): 3 stages, 3 CTAs.  The TMA-fed kernels here live on the number of resident CTAs per SM.
+template <bool X3, int BN, int MODE = 0>
 struct Cfg {
+  static constexpr bool LEAN = MODE == 1;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int OPS = X3 ? 2 : 1;
   static constexpr int STAGE_BYTES = OPS * (A_BYTES + B_BYTES);
   // LEAN (kernels with a light epilogue): 3 stages, 3 CTAs per SM - these kernels are bound by the latency of their small TMA
   // boxes, not by bandwidth, so more resident CTAs is what buys throughput
-  static constexpr int STAGES = LEAN ? (X3 ? 3 : 2) : 4;
+  static constexpr int STAGES = LEAN ? (X3 ? 3 : 2) : ((MODE == 2 && !X3) ? 3 : 4);
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
-  static constexpr int CTAS_PER_SM = X3 ? 1 : (LEAN ? 4 : 2);
+  static constexpr int CTAS_PER_SM = X3 ? 1 : (LEAN ? 4 : (MODE == 2 ? 3 : 2));
   static constexpr uint32_t ACC_COLS = (uint32_t)(ACC_STAGES * BN);
   static constexpr uint32_t TMEM_COLS = ACC_COLS <= 32u ? 32u : ACC_COLS <= 64u ? 64u : ACC_COLS <= 128u ? 128u : ACC_COLS <= 256u ? 256u : 512u;
 };
@@ -172,8 +176,8 @@ struct Cfg {
 // ------------------------------------------------------------------------------------------------ grouped tf32 GEMM / implicit conv
 // CONV 0: plain GEMM   1: A = 4-D activation boxes (fwd, or dgrad with B_MN)   2: wgrad (A = dz MN-major, B = activation boxes MN-major)
 template <int CONV, bool A_MN, bool B_MN, bool X3, int EPI, int BN>
-__global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, EPI == EPI_ATOMIC>::CTAS_PER_SM) ggemm_kernel(const Problem* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
-  using C = Cfg<X3, BN, EPI == EPI_ATOMIC>;
+__global__ void __launch_bounds__(GG_THREADS, Cfg<X3, BN, cfg_mode(EPI)>::CTAS_PER_SM) ggemm_kernel(const Problem* __restrict__ probs, const b2_cnn_bind* __restrict__ binds, int step) {
+  using C = Cfg<X3, BN, cfg_mode(EPI)>;
   const Problem& P = probs[blockIdx.y];
   const b2_cnn_bind& bd = binds[blockIdx.y];
   if (!slot_live(bd, step, P.batch)) return;  // whole CTA leaves before any barrier / TMEM allocation
@@ -1551,7 +1555,7 @@ static int64_t tables_bytes(const Plan& p) {
 
 template <int CONV, bool A_MN, bool B_MN, bool X3, int EPI, int BN>
 static int launch_gg(const Plan& p, int pi, int step, cudaStream_t st) {
-  using C = Cfg<X3, BN, EPI == EPI_ATOMIC>;
+  using C = Cfg<X3, BN, cfg_mode(EPI)>;
   auto kern = ggemm_kernel<CONV, A_MN, B_MN, X3, EPI, BN>;
   static bool attr_set[64] = {false};
   static std::mutex mu;
