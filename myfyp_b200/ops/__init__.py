@@ -258,9 +258,10 @@ def _centred_gram(slabs: Sequence[torch.Tensor], device: torch.device, passes: i
             native.count_launch()
             parts.append(gram)
         _join_shards(workers, device)
-        total = parts[0].view(MAX_K, MAX_K)[:k, :k].double()
-        for g in parts[1:]:
-            total = total + g.to(device).view(MAX_K, MAX_K)[:k, :k].double()
+        total = None
+        for g in parts:  # K x K partials: the ones born on other GPUs come over as 16 KB copies
+            part = g.to(device).view(MAX_K, MAX_K)[:k, :k].double()
+            total = part if total is None else total + part
         return total
     m = torch.stack([s.double() for s in slabs])
     m = m - m[0:1]
