@@ -126,6 +126,12 @@ def run(name, n_nodes, model_name, aggregator_factory, topology, rounds, samples
         "kernel_launches": native.launches(), "fault_events": [(e[0], e[1], e[2]) for e in fi.events],
         "rejoined_rounds": {n.addr: n.learning_workflow.history.count("RoundFinishedStage") for n in late},
     }
+    # wall time per stage, mean over the nodes that finished, per round (ms): where a round goes at this scale
+    acc_t: dict = {}
+    for n in alive:
+        for st_name, dt in n.learning_workflow.timings:
+            acc_t[st_name] = acc_t.get(st_name, 0.0) + dt
+    out["stage_ms_per_round"] = {k: round(1e3 * v / max(len(alive), 1) / rounds, 1) for k, v in acc_t.items()}
     print(json.dumps(out), flush=True)
     for n in nodes + late:
         try:

@@ -42,6 +42,9 @@ def _send_pool() -> ThreadPoolExecutor:
     return _POOL
 
 
+_inline = threading.local()  # forwarding depth of the current thread (add_message, inline_ok)
+
+
 class Gossiper(threading.Thread):
     def __init__(self, self_addr: str, client: Client, period: Optional[float] = None, messages_per_period: Optional[int] = None) -> None:
         super().__init__(daemon=True, name=f"gossiper-thread-{self_addr}")
@@ -70,7 +73,7 @@ class Gossiper(threading.Thread):
             self.__pool.shutdown(wait=False)
 
     # ------------------------------------------------------------------ flood
-    def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None, linger: float = 0.0) -> None:
+    def add_message(self, msg: Any, pending_neis: List[str], coalesce_key: Any = None, linger: float = 0.0, inline_ok: bool = False) -> None:
         """Queue ``msg`` for ``pending_neis``.  With a ``coalesce_key`` a still-unsent message queued under the same key is
         *replaced* (its remaining recipients get the newer message instead): a burst of state announcements costs one
         message per neighbour, not one per state change.  ``linger`` holds a coalescable message back for that many
@@ -78,6 +81,22 @@ class Gossiper(threading.Thread):
         ``linger = 0`` with an entry already queued under the key sends the replacement at once."""
         if not pending_neis:
             return
+        if inline_ok and coalesce_key is None and linger <= 0 and Settings.GOSSIP_INLINE_FORWARD and getattr(self.__client, "in_process", False):
+            # Forwarding a flooded message between nodes of ONE process: the next hop's handler is a function call, so the hop is
+            # made on the thread that is delivering the message instead of waking this node's gossiper thread for it (at 64 nodes
+            # a broadcast cost ~60 thread wake-ups under one interpreter lock).  Depth-limited: a long chain of hops falls back
+            # to the queue, and so does every message a HANDLER emits (those go through broadcast_async, never through here).
+            depth = getattr(_inline, "depth", 0)
+            if depth < Settings.GOSSIP_INLINE_DEPTH:
+                _inline.depth = depth + 1
+                try:
+                    for nei in pending_neis:
+                        if self.__terminate.is_set():
+                            return
+                        self.__client.send(nei, msg)
+                finally:
+                    _inline.depth = depth
+                return
         now = time.monotonic()
         with self.__cv:
             if coalesce_key is not None:

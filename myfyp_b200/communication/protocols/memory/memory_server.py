@@ -76,9 +76,11 @@ class InMemoryServer:
             fwd = dict(request)
             fwd["ttl"] = request["ttl"] - 1
             seen = request.get("seen") or []
-            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n != request["source"] and n not in seen]
+            known = set(seen)
+            known.add(request["source"])
+            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n not in known]
             fwd["seen"] = [*seen, *pending]
-            self.__gossiper.add_message(fwd, pending)
+            self.__gossiper.add_message(fwd, pending, inline_ok=True)
         handler = self.__commands.get(cmd)
         if handler is None:
             logger.error(self.addr, f"Unknown command: {cmd} from {request['source']}")

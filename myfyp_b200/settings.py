@@ -66,6 +66,8 @@ class Settings(metaclass=_SettingsMeta):
     FORWARD_GRACE: float = 0.02
     GOSSIP_MODELS_PER_ROUND: int = 2
     GOSSIP_EXIT_ON_X_EQUAL_ROUNDS: int = 10
+    GOSSIP_INLINE_FORWARD: bool = True   # in-process protocols: forward a flooded message on the delivering thread (no gossiper wake-up per hop)
+    GOSSIP_INLINE_DEPTH: int = 12        # ... for at most this many nested hops; deeper ones are queued
 
     # --- TLS -------------------------------------------------------------------
     USE_SSL: bool = True
