@@ -101,7 +101,7 @@ class ComposedProtocol(CommunicationProtocol):
         """Queue ``msg`` for every direct neighbour on the gossiper thread and return at once (used inside handlers).
         ``coalesce``: a queued, not yet sent message of the same command and round is superseded by this one;
         ``linger``: hold a coalescable message back this long so that a burst of them collapses into one."""
-        nodes = list(self._neighbors.get_all(only_direct=True))
+        nodes = list(self._neighbors.direct_addrs())
         if _is_flood(msg):
             self._gossiper.check_and_set_processed(msg["hash"])
             msg["seen"] = [self.addr, *nodes]

@@ -81,7 +81,8 @@ class Gossiper(threading.Thread):
         ``linger = 0`` with an entry already queued under the key sends the replacement at once."""
         if not pending_neis:
             return
-        if inline_ok and coalesce_key is None and linger <= 0 and Settings.GOSSIP_INLINE_FORWARD and getattr(self.__client, "in_process", False):
+        if inline_ok and coalesce_key is None and linger <= 0 and Settings.GOSSIP_INLINE_FORWARD:
+            # (the caller vouches that ``pending_neis`` live in this process)
             # Forwarding a flooded message between nodes of ONE process: the next hop's handler is a function call, so the hop is
             # made on the thread that is delivering the message instead of waking this node's gossiper thread for it (at 64 nodes
             # a broadcast cost ~60 thread wake-ups under one interpreter lock).  Depth-limited: a long chain of hops falls back

@@ -122,7 +122,7 @@ class GrpcServer:
         if not is_weights and cmd != "beat" and msg["source"] != self.addr:
             # any message proves its origin is alive: learn about it now rather than at its next heartbeat
             self._neighbors.refresh_or_add(msg["source"], time.time())
-        if cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS:
+        if logger.is_debug() and (cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS):
             logger.debug(self.addr, f"📫 {cmd.upper()} received from {msg['source']}")
         handler = self._commands.get(cmd)
         if handler is None:
@@ -140,10 +140,23 @@ class GrpcServer:
         if not is_weights and msg["ttl"] > 0:
             fwd = dict(msg)
             fwd["ttl"] = msg["ttl"] - 1
-            seen = msg.get("seen") or []
-            pending = [n for n in self._neighbors.get_all(only_direct=True) if n != msg["source"] and n not in seen]
-            fwd["seen"] = [*seen, *pending]
-            self._gossiper.add_message(fwd, pending)
+            # who has the message or is about to get it: a list on the wire ("seen", an extension field), ONE shared set object
+            # between the nodes of a process, so that co-resident hops see what their siblings already targeted
+            known = msg.get("_seen_set")
+            if known is None:
+                known = set(msg.get("seen") or ())
+                known.add(msg["source"])
+            known.add(self.addr)
+            pending = [n for n in self._neighbors.direct_addrs() if n not in known]
+            known.update(pending)
+            fwd["_seen_set"] = known
+            local = [n for n in pending if self._neighbors.is_local(n)] if Settings.GOSSIP_INLINE_FORWARD else []
+            if local:  # next hop lives in this process: its handler is a function call, made on this thread
+                self._gossiper.add_message(fwd, local, inline_ok=True)
+            if len(local) < len(pending):
+                lset = set(local)
+                fwd["seen"] = list(known)
+                self._gossiper.add_message(fwd, [n for n in pending if n not in lset])
         return None
 
     # ------------------------------------------------------------------ RPC adapters

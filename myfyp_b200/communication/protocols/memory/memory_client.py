@@ -72,7 +72,7 @@ class InMemoryClient(Client):
                 raise
 
     def broadcast(self, msg: Dict[str, Any], node_list: Optional[List[str]] = None) -> None:
-        nodes = node_list if node_list is not None else list(self.__neighbors.get_all(only_direct=True))
+        nodes = node_list if node_list is not None else list(self.__neighbors.direct_addrs())
         if "hash" in msg and node_list is None:
             # flood bookkeeping: who has (or is about to get) this message - receivers do not forward to them
             msg["seen"] = [self.__self_addr, *nodes]

@@ -69,17 +69,23 @@ class InMemoryServer:
             # any message proves its origin is alive: learn about it now rather than at its next heartbeat (a node that
             # just (re)joined would otherwise be missing from some nodes' vote bookkeeping -> diverging train sets)
             self.__neighbors.refresh_or_add(request["source"], time.time())
-        if cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS:
+        if logger.is_debug() and (cmd != "beat" or not Settings.EXCLUDE_BEAT_LOGS):
             logger.debug(self.addr, f"📫 {cmd.upper()} received from {request['source']} (ttl={request['ttl']})")
         # re-gossip first (same order as the reference, memory_server.py:155-165)
         if request["ttl"] > 0:
             fwd = dict(request)
             fwd["ttl"] = request["ttl"] - 1
-            seen = request.get("seen") or []
-            known = set(seen)
-            known.add(request["source"])
-            pending = [n for n in self.__neighbors.get_all(only_direct=True) if n not in known]
-            fwd["seen"] = [*seen, *pending]
+            # Flood bookkeeping inside one process: ONE set object travels with the message through every hop ("who has it or is
+            # about to get it"), so a hop sees what its siblings have already targeted - the per-path lists of the wire protocols
+            # (gRPC / UDS: "seen") let ~10 redundant probes through per delivery at 64 nodes with degree 20.
+            known = request.get("_seen_set")
+            if known is None:
+                known = set(request.get("seen") or ())
+                known.add(request["source"])
+            known.add(self.addr)
+            pending = [n for n in self.__neighbors.direct_addrs() if n not in known]
+            known.update(pending)
+            fwd["_seen_set"] = known
             self.__gossiper.add_message(fwd, pending, inline_ok=True)
         handler = self.__commands.get(cmd)
         if handler is None:

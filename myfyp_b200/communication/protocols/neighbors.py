@@ -19,6 +19,7 @@ class Neighbors:
         self.neis: Dict[str, Any] = {}
         self.neis_lock = threading.RLock()
         self._listeners: List[Callable[[], None]] = []
+        self._direct: Any = None  # cached tuple of the direct neighbours' addresses (membership changes only in add / remove)
 
     # -- to be provided by the transport ------------------------------------------
     def connect(self, addr: str, *args, **kwargs) -> Any:
@@ -35,6 +36,7 @@ class Neighbors:
         self._listeners.append(fn)
 
     def _changed(self) -> None:
+        self._direct = None
         for fn in self._listeners:
             try:
                 fn()
@@ -63,6 +65,7 @@ class Neighbors:
             cur = self.neis.get(addr)
             if cur is None or (not cur[1] and entry[1]):
                 self.neis[addr] = entry
+                self._direct = None
         self._changed()
         return True
 
@@ -70,6 +73,7 @@ class Neighbors:
         with self.neis_lock:
             present = addr in self.neis
             entry = self.neis.pop(addr, None)
+            self._direct = None
         if present:
             try:
                 self.disconnect(addr, *args, entry=entry, **kwargs)
@@ -79,6 +83,20 @@ class Neighbors:
 
     def get(self, addr: str) -> Any:
         return self.neis[addr]
+
+    def is_local(self, addr: str) -> bool:
+        """True when ``addr`` is a direct neighbour living in this process (its server is called, not messaged)."""
+        e = self.neis.get(addr)
+        return bool(e is not None and e[1] is not None and getattr(e[1], "local", False))
+
+    def direct_addrs(self) -> tuple:
+        """Addresses of the direct neighbours - the flood's fan-out, asked for once per forwarded message."""
+        d = self._direct
+        if d is None:
+            with self.neis_lock:
+                d = tuple(k for k, v in self.neis.items() if v[1])
+                self._direct = d
+        return d
 
     def get_all(self, only_direct: bool = False) -> Dict[str, Any]:
         with self.neis_lock:

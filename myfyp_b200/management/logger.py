@@ -145,6 +145,10 @@ class P2PFLogger:
     def info(self, node: str, message: str) -> None:
         self.log(logging.INFO, node, message)
 
+    def is_debug(self) -> bool:
+        """Hot paths ask before formatting a debug line."""
+        return self._logger.isEnabledFor(logging.DEBUG)
+
     def debug(self, node: str, message: str) -> None:
         self.log(logging.DEBUG, node, message)
 

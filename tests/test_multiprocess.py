@@ -80,7 +80,7 @@ def test_two_processes_over_sockets(proto_name):
     assert h0.count("RoundFinishedStage") == 2 and h1.count("RoundFinishedStage") == 2
 
 
-def _rank_worker(rank, addrs, q, rounds, per_rank):
+def _rank_worker(rank, addrs, q, rounds, per_rank, topology="full"):
     """`per_rank` nodes in this process (local shortcut between them), unix-socket frames to the other rank - the shape of
     `bench.py` with several nodes per GPU process."""
     import torch
@@ -104,8 +104,8 @@ def _rank_worker(rank, addrs, q, rounds, per_rank):
         n.start()
     q.put(("up", rank))
     t_conn = time.time() + 90
-    for i, n in nodes.items():  # full mesh: every node connects to every node with a larger index
-        for j in range(i + 1, len(addrs)):
+    for i, n in nodes.items():  # full mesh: every node connects to every node with a larger index; line: to the next one only
+        for j in range(i + 1, len(addrs) if topology == "full" else min(i + 2, len(addrs))):
             while not n.connect(addrs[j]):
                 assert time.time() < t_conn, "could not reach a peer"
                 time.sleep(0.3)
@@ -128,13 +128,16 @@ def _rank_worker(rank, addrs, q, rounds, per_rank):
         n.stop()
 
 
-def test_two_ranks_with_two_nodes_each_over_unix_sockets():
+@pytest.mark.parametrize("topology,per_rank", [("full", 2), ("line", 3)])
+def test_two_ranks_with_several_nodes_each_over_unix_sockets(topology, per_rank):
+    """``line``: every flooded message crosses in-process hops (forwarded on the delivering thread, one shared "seen" set) AND a
+    socket hop (the set leaves the process as the wire's "seen" list) on its way from one end to the other."""
     ctx = mp.get_context("spawn")
     d = tempfile.mkdtemp()
-    per_rank, rounds = 2, 3
+    rounds = 3
     addrs = [f"uds://{d}/n{i}.sock" for i in range(2 * per_rank)]
     q = ctx.Queue()
-    procs = [ctx.Process(target=_rank_worker, args=(r, addrs, q, rounds, per_rank)) for r in range(2)]
+    procs = [ctx.Process(target=_rank_worker, args=(r, addrs, q, rounds, per_rank, topology)) for r in range(2)]
     for p in procs:
         p.start()
     results = {}
