@@ -1982,23 +1982,29 @@ int b2_cnn_plan_train_step(void* plan, int step, void* stream) {
   if (n < 0) return -1;
   if (launch_head(p, step, 1, st)) return -1;
   ++n;
-  // weight-gradient GEMMs on the side stream: a parallel branch next to the input-gradient chain
+  // weight-gradient GEMMs on the side stream: a parallel branch next to the input-gradient chain.  B2_T32_WGRAD_BRANCH=0 makes it one
+  // chain: on random data at G = 8 the chain looked better (336 vs 351 us per step, tools/t32_step_profile.py), inside the federation
+  // the branch wins (epoch graph 34.9 vs 36.2 ms) - the branch stays.
+  static const char* branch_env = getenv("B2_T32_WGRAD_BRANCH");
+  const bool branch = branch_env != nullptr ? branch_env[0] != '0' : true;
+  cudaStream_t ws = branch ? p.side : st;
   auto fork = [&](int i) -> int {
+    if (!branch) return 0;
     if (cudaEventRecord(p.ev_fork[i], st) != cudaSuccess || cudaStreamWaitEvent(p.side, p.ev_fork[i], 0) != cudaSuccess) return cuda_fail(cudaGetLastError(), "fork to the wgrad stream");
     return 0;
   };
   if (fork(0)) return -1;
-  if (launch_gg<0, true, true, true, EPI_STORE, 64>(p, p.p_fc1_wgrad(), step, p.side)) return -1;
+  if (launch_gg<0, true, true, true, EPI_STORE, 64>(p, p.p_fc1_wgrad(), step, ws)) return -1;
   if (launch_gg<0, false, true, true, EPI_UNPOOL, 64>(p, p.p_fc1_dgrad(), step, st)) return -1;
   n += 2;
   for (int l = p.nl - 1; l >= 1; --l) {
     if (fork(l)) return -1;
-    if (run_conv_wgrad(p, l, step, p.side)) return -1;
+    if (run_conv_wgrad(p, l, step, ws)) return -1;
     if (run_conv_dgrad(p, l, step, st)) return -1;
     n += 2;
   }
   if (launch_conv0(p, true, step, st)) return -1;
-  if (cudaEventRecord(p.ev_join[0], p.side) != cudaSuccess || cudaStreamWaitEvent(st, p.ev_join[0], 0) != cudaSuccess) {
+  if (branch && (cudaEventRecord(p.ev_join[0], p.side) != cudaSuccess || cudaStreamWaitEvent(st, p.ev_join[0], 0) != cudaSuccess)) {
     cuda_fail(cudaGetLastError(), "join of the wgrad stream");
     return -1;
   }
