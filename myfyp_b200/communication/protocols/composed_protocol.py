@@ -13,6 +13,7 @@ from typing import Any, Callable, Dict, List, Optional, Union
 
 from myfyp_b200.communication.commands.command import Command
 from myfyp_b200.communication.commands.message.heartbeat_command import HeartbeatCommand
+from myfyp_b200.communication.commands.message.node_down_command import NodeDownCommand
 from myfyp_b200.communication.protocols.communication_protocol import CommunicationProtocol, running
 from myfyp_b200.communication.protocols.gossiper import Gossiper
 from myfyp_b200.communication.protocols.heartbeater import Heartbeater
@@ -37,6 +38,9 @@ class ComposedProtocol(CommunicationProtocol):
         self._server = server_cls(addr, self._gossiper, neighbors, commands)
         self._heartbeater = Heartbeater(addr, neighbors, self._client)
         self._server.add_command(HeartbeatCommand(self._heartbeater))
+        self._server.add_command(NodeDownCommand(addr, neighbors))
+        self._announced_lost: Dict[str, float] = {}
+        neighbors.on_lost(self._announce_lost)
         if commands:
             self._server.add_command(commands)
 
@@ -51,6 +55,11 @@ class ComposedProtocol(CommunicationProtocol):
 
     @running
     def stop(self) -> None:
+        if Settings.FAILURE_DISSEMINATION:  # goodbye: nodes that know us only through the flood need not wait for our beats to time out
+            try:
+                self._client.broadcast(self.build_msg(NodeDownCommand.get_name(), [self.addr]))
+            except Exception:  # noqa: BLE001
+                pass
         self._heartbeater.stop()
         self._gossiper.stop()
         self._neighbors.clear_neighbors()
@@ -78,6 +87,21 @@ class ComposedProtocol(CommunicationProtocol):
 
     def on_neighbors_changed(self, fn: Callable[[], None]) -> None:
         self._neighbors.on_change(fn)
+
+    def _announce_lost(self, dead: str) -> None:
+        """A direct neighbour of ours is gone: tell everybody (``node_down``), once per few seconds and address."""
+        import time as _t
+
+        if not Settings.FAILURE_DISSEMINATION:
+            return
+        now = _t.monotonic()
+        if now - self._announced_lost.get(dead, -1e9) < 2.0:
+            return
+        self._announced_lost[dead] = now
+        try:
+            self.broadcast_async(self.build_msg(NodeDownCommand.get_name(), [dead]))
+        except Exception:  # noqa: BLE001 - protocol stopping
+            pass
 
     # ------------------------------------------------------------------ messages
     def build_msg(self, cmd: str, args: Optional[List[str]] = None, round: Optional[int] = None) -> Any:

@@ -65,7 +65,10 @@ class GrpcClient(Client):
         except Exception as e:  # noqa: BLE001
             logger.debug(self.__self_addr, f"Cannot send message {msg['cmd']!r} to {nei}. Error: {e}")
             if remove_on_error:
+                direct = self.__neighbors.is_direct(nei)
                 self.__neighbors.remove(nei, disconnect_msg=True)
+                if direct:
+                    self.__neighbors.report_lost(nei)
             if raise_error:
                 raise
         finally:

@@ -46,7 +46,10 @@ class Heartbeater(threading.Thread):
                 for nei, entry in self.__neighbors.get_all().items():
                     if now - entry[2] > timeout:
                         logger.info(self.__self_addr, f"Heartbeat timeout for {nei} ({now - entry[2]:.2f}). Removing...")
+                        direct = bool(entry[1])
                         self.__neighbors.remove(nei)
+                        if direct:
+                            self.__neighbors.report_lost(nei)
             toggle = True  # first tick only sends; every later tick also evicts
             try:
                 self.__client.broadcast(self.__client.build_message(heartbeater_cmd_name, args=[str(time.time())]))

@@ -20,6 +20,8 @@ class Neighbors:
         self.neis_lock = threading.RLock()
         self._listeners: List[Callable[[], None]] = []
         self._direct: Any = None  # cached tuple of the direct neighbours' addresses (membership changes only in add / remove)
+        self._lost_listeners: List[Callable[[str], None]] = []
+        self._tombstones: Dict[str, float] = {}  # addr -> monotonic time until which stray messages do not re-add it
 
     # -- to be provided by the transport ------------------------------------------
     def connect(self, addr: str, *args, **kwargs) -> Any:
@@ -43,9 +45,48 @@ class Neighbors:
             except Exception:
                 pass
 
+    # -- failure dissemination --------------------------------------------------
+    def on_lost(self, fn: Callable[[str], None]) -> None:
+        """``fn(addr)`` is called when THIS node found a direct neighbour dead (a send to it failed, or its beats stopped)."""
+        self._lost_listeners.append(fn)
+
+    def report_lost(self, addr: str) -> None:
+        for fn in self._lost_listeners:
+            try:
+                fn(addr)
+            except Exception:  # noqa: BLE001
+                pass
+
+    def bury(self, addr: str, seconds: float) -> bool:
+        """Somebody else found ``addr`` dead (``node_down``): forget it if we only know it through the flood, and do not let its
+        messages that are still travelling re-add it for ``seconds``.  A direct neighbour is left to our own link (the next beat we
+        send it fails or does not); a node declared dead by mistake comes back with its first beat after the grace period."""
+        import time as _t
+
+        with self.neis_lock:
+            cur = self.neis.get(addr)
+            if cur is None or cur[1]:
+                return False
+            self._tombstones[addr] = _t.monotonic() + seconds
+        self.remove(addr, disconnect_msg=False)
+        return True
+
+    def buried(self, addr: str) -> bool:
+        t = self._tombstones.get(addr)
+        if t is None:
+            return False
+        import time as _t
+
+        if _t.monotonic() >= t:
+            self._tombstones.pop(addr, None)
+            return False
+        return True
+
     def add(self, addr: str, *args, **kwargs) -> bool:
         if addr == self.self_addr:
             logger.info(self.self_addr, "❌ Cannot add itself")
+            return False
+        if kwargs.get("non_direct") and self.buried(addr):
             return False
         with self.neis_lock:
             cur = self.neis.get(addr)
@@ -83,6 +124,10 @@ class Neighbors:
 
     def get(self, addr: str) -> Any:
         return self.neis[addr]
+
+    def is_direct(self, addr: str) -> bool:
+        e = self.neis.get(addr)
+        return bool(e is not None and e[1])
 
     def is_local(self, addr: str) -> bool:
         """True when ``addr`` is a direct neighbour living in this process (its server is called, not messaged)."""

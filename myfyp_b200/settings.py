@@ -66,6 +66,7 @@ class Settings(metaclass=_SettingsMeta):
     FORWARD_GRACE: float = 0.02
     GOSSIP_MODELS_PER_ROUND: int = 2
     GOSSIP_EXIT_ON_X_EQUAL_ROUNDS: int = 10
+    FAILURE_DISSEMINATION: bool = True   # flood ``node_down`` when a direct neighbour is found dead (nodes further away need not wait for HEARTBEAT_TIMEOUT)
     GOSSIP_INLINE_FORWARD: bool = True   # in-process protocols: forward a flooded message on the delivering thread (no gossiper wake-up per hop)
     GOSSIP_INLINE_DEPTH: int = 12        # ... for at most this many nested hops; deeper ones are queued
 

@@ -146,6 +146,47 @@ def test_abrupt_stop_is_detected(proto):
         p1.stop()
 
 
+@pytest.mark.parametrize("proto", PROTOCOLS)
+@pytest.mark.parametrize("goodbye", [True, False])
+def test_a_death_reaches_nodes_that_know_the_dead_one_only_through_the_flood(proto, goodbye):
+    """Line a - b - c: ``a`` knows ``c`` only from c's flooded beats.  When c goes (an orderly stop floods its own ``node_down``;
+    after a crash its direct neighbour b notices the failed beat and floods one), ``a`` drops it within a couple of beat periods
+    instead of waiting out HEARTBEAT_TIMEOUT (set to 30 s here) - a vote needs every known node's ballot."""
+    from myfyp_b200.settings import Settings
+
+    old = Settings.HEARTBEAT_PERIOD, Settings.HEARTBEAT_TIMEOUT
+    Settings.HEARTBEAT_PERIOD, Settings.HEARTBEAT_TIMEOUT = 0.2, 30.0
+    a, b, c = proto(), proto(), proto()
+    try:
+        for p in (a, b, c):
+            p.start()
+        assert a.connect(b.get_address()) and b.connect(c.get_address())
+        t0 = time.time()
+        while time.time() - t0 < 5 and c.get_address() not in a.get_neighbors(only_direct=False):
+            time.sleep(0.02)
+        assert c.get_address() in a.get_neighbors(only_direct=False) and c.get_address() not in a.get_neighbors(only_direct=True)
+        if goodbye:
+            c.stop()
+        else:  # crash: no disconnect, no goodbye
+            c._heartbeater.stop()
+            c._gossiper.stop()
+            c._server.stop()
+        t0 = time.time()
+        while time.time() - t0 < 4 and c.get_address() in a.get_neighbors(only_direct=False):
+            time.sleep(0.02)
+        assert c.get_address() not in a.get_neighbors(only_direct=False), "a still waits for c's beats to time out"
+        assert b.get_address() in a.get_neighbors(only_direct=True)
+    finally:
+        Settings.HEARTBEAT_PERIOD, Settings.HEARTBEAT_TIMEOUT = old
+        for p in (a, b):
+            p.stop()
+        if not goodbye:
+            try:
+                c._neighbors.clear_neighbors()
+            except Exception:  # noqa: BLE001
+                pass
+
+
 def test_stopping_one_memory_node_leaves_the_others_registered():
     a, b, c = (InMemoryCommunicationProtocol() for _ in range(3))
     for p in (a, b, c):
