@@ -280,3 +280,19 @@ def test_empty_aggregation_raises():
     for agg in (FedAvg(), FedMedian(), Krum()):
         with pytest.raises(NoModelsToAggregateError):
             agg.aggregate([])
+
+
+def test_coordinate_shards_cover_the_model_once_and_keep_16_byte_alignment():
+    """ops._shard_bounds: contiguous, aligned, complete - for any model size and worker count (the GPU side is tested on 2 GPUs)."""
+    from myfyp_b200 import ops
+
+    for n in (1, 1023, 1024, 262144, 262145, 11_173_962, (1 << 20) + 1539):
+        for parts in (1, 2, 3, 7, 8):
+            b = ops._shard_bounds(n, parts)
+            assert len(b) == parts + 1 and b[0] == 0 and b[-1] == n
+            assert all(x <= y for x, y in zip(b, b[1:]))
+            assert all(lo % 1024 == 0 for lo, hi in zip(b, b[1:]) if hi > lo)  # every non-empty slice starts 4 KB-aligned
+    # on the CPU (or for a small model) a reduction is never sharded
+    slabs = [torch.zeros(1 << 19) for _ in range(3)]
+    assert ops.shard_devices(slabs, torch.device("cpu")) == [torch.device("cpu")]
+    assert ops.shard_devices(slabs, torch.device("cpu"), force=True) == [torch.device("cpu")]
