@@ -22,7 +22,10 @@ class ModelsAggregatedCommand(Command):
             # forever -> the round ends by timeout.  (The reference overwrites, models_agregated_command.py:49-51.)
             cur = self.state.models_aggregated.get(source, [])
             self.state.models_aggregated[source] = cur + [a for a in args if a not in cur]
-            self.state.notify()
+            # read by the partial-model gossip of train-set members only (TrainStage): nobody else is woken
+            ts = self.state.train_set
+            if not ts or self.state.addr in ts:
+                self.state.notify()
         elif self.state.round is not None and round == self.state.round + 1:
             # the sender is already one round ahead of us: keep its announcement for when we get there
             nxt = self.state.models_aggregated_next.setdefault(source, [])

@@ -28,4 +28,7 @@ class ModelsReadyCommand(Command):
             return
         if round > st.nei_status.get(source, -2):
             st.nei_status[source] = round
-            st.notify()
+            # only the status of DIRECT neighbours is waited for (GossipModelStage pushes the aggregate to those that are behind)
+            probe = st.is_direct
+            if probe is None or probe(source):
+                st.notify()

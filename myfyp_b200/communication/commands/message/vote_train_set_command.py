@@ -34,8 +34,13 @@ class VoteTrainSetCommand(Command):
                     st.train_set_votes[source] = tmp
                 else:
                     st.train_set_votes_next[source] = tmp
+                have = len(st.train_set_votes)
             with contextlib.suppress(Exception):
                 st.wait_votes_ready_lock.release()
-            st.notify()
+            # the vote stage says how many ballots it is waiting for: waking it for each of the 63 that do not complete the box is
+            # 63 thread hand-offs under the interpreter lock per node and round (a neighbour change or a stop wakes it anyway)
+            need = st.votes_needed
+            if need is None or round != st.round or have >= need:
+                st.notify()
         else:
             logger.debug(st.addr, f"Vote from {source} in a late round. Ignored. {round} != {st.round} / {st.round + 1}")

@@ -86,6 +86,7 @@ class Node:
 
         self.__running = False
         self.state = NodeState(self.addr, simulation=simulation)
+        self.state.is_direct = getattr(getattr(self._communication_protocol, "_neighbors", None), "is_direct", None)  # commands wake waiting stages selectively
         self.simulation = simulation
         self.learning_workflow = LearningWorkflow()
         self._learning_thread: Optional[threading.Thread] = None
@@ -283,6 +284,12 @@ class Node:
         except Exception as e:  # noqa: BLE001
             if not self.__running:  # the node was stopped (or crashed on purpose) under its own learning thread
                 logger.debug(self.addr, f"learning thread ended after stop: {type(e).__name__}: {e}")
+                self.learning_workflow.finished = True
+                return
+            if self.state.round is None and getattr(threading.current_thread(), "b2_experiment_set", False):
+                # the experiment was stopped under this thread (set_stop_learning clears the state at once; the thread was between
+                # an early-stop check and its next use of the round counter): that is an early stop, not a reason to stop the NODE
+                logger.debug(self.addr, f"learning thread ended by a stop: {type(e).__name__}: {e}")
                 self.learning_workflow.finished = True
                 return
             logger.error(self.addr, f"Error {type(e).__name__}: {e}\n{traceback.format_exc()}")

@@ -30,6 +30,9 @@ class NodeState:
         self.models_aggregated: Dict[str, List[str]] = {}
         self.models_aggregated_next: Dict[str, List[str]] = {}  # announcements of peers that are one round ahead
         self.nei_status: Dict[str, int] = {}
+        self.votes_needed: Optional[int] = None   # set by the vote stage while it waits: ballots that complete the box
+        if not hasattr(self, "is_direct"):
+            self.is_direct = None                 # callable(addr) -> bool, installed by the Node (direct neighbour of ours?); survives clear()
         self.train_set: List[str] = []
         self.train_set_votes: Dict[str, Dict[str, int]] = {}
         self.train_set_votes_next: Dict[str, Dict[str, int]] = {}  # ballots of peers that are already one round ahead
@@ -67,6 +70,15 @@ class NodeState:
         with self.cv:
             v = self._version
             return self.cv.wait_for(lambda: self._version != v, timeout=timeout)
+
+    def version(self) -> int:
+        """Change counter: read it BEFORE looking at the state, then :meth:`wait_since` cannot miss a change made in between."""
+        return self._version
+
+    def wait_since(self, version: int, timeout: Optional[float]) -> bool:
+        """Block until the state has changed since ``version`` was read (or ``timeout``)."""
+        with self.cv:
+            return self.cv.wait_for(lambda: self._version != version, timeout=timeout)
 
     def wait_for(self, predicate, timeout: Optional[float]) -> bool:
         """Block until ``predicate()`` is true or ``timeout`` seconds pass."""

@@ -44,6 +44,7 @@ def collect(state, communication_protocol) -> Dict[str, Ballot]:
     deadline = time.monotonic() + Settings.VOTE_TIMEOUT
     while True:
         check_early_stop(state)
+        v0 = state.version()
         electorate = set(communication_protocol.get_neighbors(only_direct=False)) | {state.addr}
         with state.train_set_votes_lock:
             box = dict(state.train_set_votes)
@@ -55,9 +56,15 @@ def collect(state, communication_protocol) -> Dict[str, Ballot]:
             with state.train_set_votes_lock:
                 state.train_set_votes = {}
             return box
-        seen = len(box)
-        # woken by a ballot, a neighbour change or a stop; the short time-out only bounds a lost wake-up
-        state.wait_for(lambda: state.round is None or len(state.train_set_votes) != seen, timeout=min(0.5, max(deadline - time.monotonic(), 0.01)))
+        # woken by the ballot that completes the box (VoteTrainSetCommand reads votes_needed), a neighbour change or a stop; the
+        # short time-out only bounds a lost wake-up
+        # (a ballot that arrives before votes_needed is set notifies unconditionally and bumps the version read above, so it is not
+        # missed; afterwards only ballots that can complete the box wake this thread)
+        state.votes_needed = len(electorate)
+        try:
+            state.wait_since(v0, timeout=min(0.5, max(deadline - time.monotonic(), 0.01)))
+        finally:
+            state.votes_needed = None
 
 
 def elect(box: Dict[str, Ballot], alive: set, size: int) -> List[str]:
