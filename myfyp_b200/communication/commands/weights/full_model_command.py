@@ -37,6 +37,8 @@ class FullModelCommand(Command):
             # the sender has already finished the round we are still voting in: keep its aggregate for when we wait for it
             st.early_full_model = (round, source, weights)
             return
+        if round <= st.aggregate_round:
+            return  # we hold this round's aggregate already: one of the several neighbours that push it at the same instant was first
         if round != st.round:
             if st.rejoining and round > st.round and st.experiment is not None:
                 # we joined a running experiment believing it was in round st.round, but the network has moved on:
@@ -62,5 +64,6 @@ class FullModelCommand(Command):
                 except Exception as e:  # noqa: BLE001
                     logger.debug(st.addr, f"observe_global failed: {e}")
                 st.rejoining = False
+                st.aggregate_round = round
                 st.aggregated_model_event.set()
             st.notify()

@@ -38,6 +38,7 @@ class NodeState:
         self.train_set_votes_next: Dict[str, Dict[str, int]] = {}  # ballots of peers that are already one round ahead
         self.early_models: List[tuple] = []  # model offers that arrived before this node started collecting for that round
         self.early_full_model: Optional[tuple] = None  # (round, source, weights): an aggregated model pushed before we waited for it
+        self.aggregate_round = -1  # newest round whose aggregated model this node holds (its own aggregation or an adopted add_model)
         if not hasattr(self, "adopt_early_full_model"):
             self.adopt_early_full_model = None  # set by Node (FullModelCommand.adopt_early)
         if not hasattr(self, "absorb_early_models"):
@@ -101,6 +102,7 @@ class NodeState:
     def set_experiment(self, exp_name: str, total_rounds: int, round: int = 0) -> None:
         self.status = "Learning"
         self.experiment = Experiment(exp_name, total_rounds, round)
+        self.aggregate_round = round - 1
         self.notify()
 
     def increase_round(self) -> None:

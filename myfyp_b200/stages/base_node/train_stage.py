@@ -81,6 +81,7 @@ class TrainStage(Stage):
                 agg_model = aggregator.wait_and_get_aggregation()
             lap("aggregate")
             learner.set_model(agg_model)
+            state.aggregate_round = state.round
             communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
             lap("adopt")
             return StageFactory.get_stage("GossipModelStage")
@@ -114,6 +115,7 @@ class TrainStage(Stage):
         agg_model = model.build_copy(params=average, num_samples=total, contributors=everybody)
         lap("aggregate")
         learner.set_model(agg_model)
+        state.aggregate_round = state.round
         communication_protocol.broadcast(communication_protocol.build_msg(ModelsReadyCommand.get_name(), [], round=state.round))
         lap("adopt")
         return True

@@ -409,4 +409,6 @@ def test_cooperative_round_equals_gossip_round():
     got, msgs_coop, stats = run(True)
     assert stats == (2, 0), stats
     assert msgs_gossip.get("msgs/partial_model", 0) > 0 and msgs_coop.get("msgs/partial_model", 0) == 0, (msgs_gossip, msgs_coop)
-    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+    # two rounds of Adam from the same seeds; the gossip path sums partial aggregates in arrival order, so single elements differ by
+    # fp32 rounding that Adam's normalised step amplifies (seen: 1.3e-5 on one of 235 200 elements, one run in ~10)
+    torch.testing.assert_close(got, want, rtol=1e-3, atol=1e-4)
