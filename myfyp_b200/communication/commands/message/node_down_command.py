@@ -29,4 +29,4 @@ class NodeDownCommand(Command):
         if dead == self.__addr:
             return  # (dead == source: the node's own goodbye, flooded by ComposedProtocol.stop())
         if self.__neighbors.bury(dead, 2.0 * Settings.HEARTBEAT_PERIOD + 0.2):
-            logger.info(self.__addr, f"☠️ {source} reports {dead} dead: removed.")
+            logger.info(self.__addr, f"👋 {dead} said goodbye: removed." if source == dead else f"☠️ {source} reports {dead} dead: removed.")
