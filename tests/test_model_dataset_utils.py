@@ -206,3 +206,59 @@ def test_checkpoint_roundtrip(tmp_path):
         np.testing.assert_array_equal(a, b)
     with pytest.raises(ModelNotMatchingError):
         load_checkpoint(path, cnn_model(seed=0))
+
+
+def _write_idx(path, arr):
+    import struct
+
+    arr = np.ascontiguousarray(arr, dtype=np.uint8)
+    with open(path, "wb") as f:
+        f.write(struct.pack(">HBB", 0, 8, arr.ndim))
+        for d in arr.shape:
+            f.write(struct.pack(">I", d))
+        f.write(arr.tobytes())
+
+
+def test_torchvision_importer_writes_parquet_and_a_card_that_load_back(tmp_path, monkeypatch):
+    """Reference role: torchvision_to_datasets.py:31-190 (dataset -> Hugging Face layout -> Hub).  A tiny fabricated MNIST on disk goes
+    through the CLI (no download, no network): parquet shards with the Hub's Image struct + a dataset card; both our loader and the
+    in-memory path read the same pixels back.  Pushing needs a network: the CLI reports that instead of raising."""
+    pytest.importorskip("torchvision")
+    pytest.importorskip("pyarrow")
+    from myfyp_b200.learning.dataset import torchvision_import as tvi
+
+    rng = np.random.default_rng(0)
+    raw = tmp_path / "MNIST" / "raw"
+    raw.mkdir(parents=True)
+    xs = {"train": rng.integers(0, 256, (20, 28, 28), dtype=np.uint8), "t10k": rng.integers(0, 256, (8, 28, 28), dtype=np.uint8)}
+    ys = {"train": rng.integers(0, 10, 20, dtype=np.uint8), "t10k": rng.integers(0, 10, 8, dtype=np.uint8)}
+    for k in xs:
+        _write_idx(raw / f"{k}-images-idx3-ubyte", xs[k])
+        _write_idx(raw / f"{k}-labels-idx1-ubyte", ys[k])
+    out = tmp_path / "hf"
+    rc = tvi.main(["--dataset_name", "MNIST", "--cache_dir", str(tmp_path), "--out_dir", str(out), "--no_download", "--dataset_summary", "tiny", "--official_link", "http://example.org"])
+    assert rc == 0 and (out / "train.parquet").exists() and (out / "test.parquet").exists()
+    card = (out / "README.md").read_text()
+    assert "train: 20 examples" in card and "test: 8 examples" in card and "http://example.org" in card and "0 - zero" in card
+    import pyarrow.parquet as pq
+
+    t = pq.read_table(out / "train.parquet")
+    assert t.num_rows == 20 and t.column_names == ["image", "label"] and b"huggingface" in t.schema.metadata
+    from PIL import Image
+    import io
+
+    first = np.asarray(Image.open(io.BytesIO(t.column("image")[0].as_py()["bytes"])))
+    np.testing.assert_array_equal(first, xs["train"][0])
+    assert t.column("label").to_pylist() == [int(v) for v in ys["train"]]
+    mem = tvi.from_torchvision("MNIST", str(tmp_path), download=False)
+    assert mem.get_num_samples(train=True) == 20 and mem.get_num_samples(train=False) == 8
+    np.testing.assert_allclose(np.asarray(mem.get(0, train=True)["image"]), xs["train"][0].astype(np.float32) / 255.0)
+    # a push that cannot reach the Hub fails with a plain message and exit code 2, after the files were written
+    def unreachable(self, *a, **k):
+        raise ConnectionError("no route to huggingface.co")
+
+    import huggingface_hub
+
+    monkeypatch.setattr(huggingface_hub.HfApi, "create_repo", unreachable)
+    rc = tvi.main(["--dataset_name", "MNIST", "--cache_dir", str(tmp_path), "--out_dir", str(out), "--no_download", "--token", "hf_x", "--repo_id", "nobody/tiny-mnist"])
+    assert rc == 2
