@@ -203,3 +203,73 @@ def test_cli_launch_two_nodes_over_grpc(tmp_path):
             server.wait(timeout=20)
         except subprocess.TimeoutExpired:
             server.kill()
+
+
+def test_cohort_trainer_batches_concurrent_requests_and_releases_everybody_on_errors():
+    """Host side of the node-batched trainer (models/grouped_cnn.py) without a GPU: requests that arrive within the window run as one
+    cohort, `fit` and `evaluate` never share one, a late request becomes the next cohort, and an exception in the launch is raised
+    in EVERY waiting learner instead of leaving some of them blocked."""
+    import threading
+    import time
+
+    from myfyp_b200.models.grouped_cnn import CohortTrainer
+
+    class Fake(CohortTrainer):
+        def __init__(self):
+            super().__init__(None, None, torch.device("cpu"), 64)
+            self.window, self.max_group = 0.25, 4
+            self.cohorts = []
+
+        def _execute(self, kind, batch):
+            self.cohorts.append((kind, sorted(j.args["who"] for j in batch)))
+            if any(j.args.get("boom") for j in batch):
+                raise RuntimeError("launch failed")
+            time.sleep(0.02)
+            for j in batch:
+                j.result = (kind, j.args["who"])
+
+    tr = Fake()
+    class L:  # stands for a learner (the trainer keeps weak references)
+        pass
+
+    members = [L() for _ in range(4)]
+    for m in members:
+        tr.register(m)
+    out, errs = {}, {}
+
+    def call(i, kind, **kw):
+        try:
+            out[i] = tr.submit(kind, members[i % 4], dict(who=i, **kw))
+        except Exception as e:  # noqa: BLE001
+            errs[i] = e
+
+    ts = [threading.Thread(target=call, args=(i, "fit")) for i in range(4)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(5)
+    assert tr.cohorts == [("fit", [0, 1, 2, 3])] and out == {i: ("fit", i) for i in range(4)}  # all four registered learners asked: one cohort, no waiting out the window
+
+    tr.cohorts.clear()
+    out.clear()
+    ts = [threading.Thread(target=call, args=(0, "fit")), threading.Thread(target=call, args=(1, "eval")), threading.Thread(target=call, args=(2, "fit"))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(5)
+    kinds = sorted(tr.cohorts)
+    assert all(len({k}) == 1 for k, _ in kinds) and sorted(w for _, ws in kinds for w in ws) == [0, 1, 2]
+    assert not any(k == "fit" and 1 in ws for k, ws in kinds) and not any(k == "eval" and (0 in ws or 2 in ws) for k, ws in kinds)  # kinds never mix
+
+    tr.cohorts.clear()
+    out.clear()
+    ts = [threading.Thread(target=call, args=(i, "fit"), kwargs=dict(boom=(i == 1))) for i in range(4)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(5)
+    assert not any(t.is_alive() for t in ts) and sorted(errs) == [0, 1, 2, 3] and all("launch failed" in str(e) for e in errs.values())
+    # the trainer is usable afterwards
+    errs.clear()
+    call(0, "fit")
+    assert out[0] == ("fit", 0) and not errs
