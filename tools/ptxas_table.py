@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Regenerate profiles/ptxas_v.md: registers / stack / spills / static shared memory of every kernel (nvcc -Xptxas -v, no GPU needed)."""
 import subprocess, re, glob, os
-ROOT='/root/repo'
+ROOT=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rows=[]
 for cu in sorted(glob.glob(ROOT+'/myfyp_b200/csrc/*.cu')):
     out=subprocess.run(['nvcc','-gencode','arch=compute_100a,code=sm_100a','-O3','-std=c++17','-lineinfo','-Xptxas','-v','--use_fast_math','-I'+ROOT+'/include','-I'+ROOT+'/myfyp_b200/csrc','-c',cu,'-o','/tmp/_x.o'],capture_output=True,text=True).stderr
