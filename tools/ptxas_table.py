@@ -23,7 +23,7 @@ with open(ROOT+'/profiles/ptxas_v.md','w') as f:
     f.write("Registers per thread, local-memory stack frame, spill stores / loads (bytes), static shared memory (dynamic shared memory is set at launch).\n")
     sp=[r for r in rows if r.get('st',0) or r.get('ld',0)]
     f.write(f"{len(rows)} kernels; {len(sp)} with spills: " + ("; ".join(f"`{r['name']}` {r['st']}/{r['ld']} B" for r in sp) if sp else "none") + ".\n")
-    f.write("(The `t32::conv0_wgrad_kernel` variants trade 16-370 B of spills for a 40-register prefetch of the next tile's gradients at 96 registers / 2 CTAs per SM; the benchmark uses `<3, 1>`: 16 / 36 B.)\n\n")
+    f.write("(The `t32::conv0_wgrad_kernel` variants trade some spills for a 40-register prefetch of the next tile's gradients at 96 registers / 2 CTAs per SM; the benchmark uses `<3, 1>`.)\n\n")
     f.write("| file | kernel | regs | stack | spill st | spill ld | static smem |\n|---|---|---|---|---|---|---|\n")
     for r in rows:
         f.write(f"| {r['file']} | `{r['name']}` | {r['regs']} | {r.get('stack',0)} | {r.get('st',0)} | {r.get('ld',0)} | {r['smem']} |\n")
