@@ -11,7 +11,7 @@ import time
 from typing import Any, Dict, List, Optional
 
 from myfyp_b200.communication.protocols.client import Client
-from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError
+from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError, peer_looks_dead
 from myfyp_b200.communication.protocols.memory.registry import ServerRegistry
 from myfyp_b200.management.logger import logger
 from myfyp_b200.settings import Settings
@@ -69,7 +69,7 @@ class InMemoryClient(Client):
             if remove_on_error:
                 direct = self.__neighbors.is_direct(nei)
                 self.__neighbors.remove(nei, disconnect_msg=True)
-                if direct:
+                if direct and peer_looks_dead(e):
                     self.__neighbors.report_lost(nei)
             if raise_error:
                 raise

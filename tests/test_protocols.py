@@ -187,6 +187,37 @@ def test_a_death_reaches_nodes_that_know_the_dead_one_only_through_the_flood(pro
                 pass
 
 
+def test_a_peer_that_answers_with_an_error_is_not_declared_dead():
+    """``node_down`` is for peers that are GONE (no server, refused / broken / silent connection).  A peer whose handler raised has
+    answered: its direct neighbour may drop the link (the reference's behaviour), but nobody else is told to forget the node."""
+    from myfyp_b200.communication.protocols.exceptions import CommunicationError, NeighborNotConnectedError, peer_looks_dead
+
+    assert peer_looks_dead(ConnectionRefusedError()) and peer_looks_dead(TimeoutError()) and peer_looks_dead(CommunicationError("Error while sending a message: 'x': 'server not running'"))
+    assert not peer_looks_dead(CommunicationError("Error while sending a message: 'mock': 'Error while processing command: mock []: boom'"))
+    assert not peer_looks_dead(NeighborNotConnectedError("no stub")) and not peer_looks_dead(ValueError("x"))
+
+    class Boom(MockCommand):
+        def execute(self, source, round, *args, **kwargs):
+            raise RuntimeError("boom")
+
+    a, b, c = (InMemoryCommunicationProtocol() for _ in range(3))
+    try:
+        for p in (a, b, c):
+            p.start()
+        assert a.connect(b.get_address()) and b.connect(c.get_address())
+        t0 = time.time()
+        while time.time() - t0 < 5 and c.get_address() not in a.get_neighbors(only_direct=False):
+            time.sleep(0.02)
+        c.add_command(Boom())
+        b.send(c.get_address(), b.build_msg("mock"))  # c answers with an error: b drops its link to c ...
+        assert c.get_address() not in b.get_neighbors(only_direct=True)
+        time.sleep(0.3)
+        assert c.get_address() in a.get_neighbors(only_direct=False)  # ... but a was not told that c is dead
+    finally:
+        for p in (a, b, c):
+            p.stop()
+
+
 def test_stopping_one_memory_node_leaves_the_others_registered():
     a, b, c = (InMemoryCommunicationProtocol() for _ in range(3))
     for p in (a, b, c):
