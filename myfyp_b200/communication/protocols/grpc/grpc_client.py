@@ -56,6 +56,10 @@ class GrpcClient(Client):
 
                 payload = dict(msg)
                 payload["weights"] = encode_descriptor(msg["weights"])
+            if stub.local and "weight" not in msg and Settings.DEDUP_BEFORE_SEND:
+                srv = self.__neighbors.local_server(nei)  # in-process short-circuit of the flood: the receiver has seen this hash already
+                if srv is not None and srv.gossiper.was_processed(msg["hash"]):
+                    return
             if not raise_error and "weight" not in msg and hasattr(stub, "send_oneway"):
                 err = stub.send_oneway(payload)  # the caller does not want the peer's verdict: do not wait for it
             else:
@@ -76,9 +80,11 @@ class GrpcClient(Client):
                 channel.close()
 
     def broadcast(self, msg: Dict[str, Any], node_list: Optional[List[str]] = None) -> None:
-        nodes = node_list if node_list is not None else list(self.__neighbors.get_all(only_direct=True))
+        nodes = node_list if node_list is not None else list(self.__neighbors.direct_addrs())
         if "hash" in msg and node_list is None:
-            # flood bookkeeping: who has (or is about to get) this message - receivers do not forward to them
+            # flood bookkeeping: who has (or is about to get) this message - receivers do not forward to them.  (Every first-hop
+            # receiver starts its own shared set from this list: handing them ONE set from here removes the flood's last
+            # redundancy - each node is then targeted exactly once - and made federations stall now and then.)
             msg["seen"] = [self.__self_addr, *nodes]
         for n in nodes:
             self.send(n, msg)

@@ -77,6 +77,10 @@ def make_stub(addr: str) -> Tuple[Optional[grpc.Channel], Any]:
 
 
 class GrpcNeighbors(Neighbors):
+    def local_server(self, addr: str):
+        """The peer's server object when it lives in this process (``LocalStub``), else None."""
+        return local_server(addr)
+
     def make_stub(self, addr: str) -> Tuple[Any, Any]:
         """``(closable channel or None, stub)`` for ``addr`` - the transport hook subclasses override."""
         return make_stub(addr)
